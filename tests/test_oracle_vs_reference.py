@@ -1,0 +1,85 @@
+"""Live cross-check of the oracle against the reference's own functions, executed from
+/root/reference (build container only; skipped on the GPU box where it does not exist)."""
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import dinov2, ref_loader, servo
+
+pytestmark = pytest.mark.skipif(not ref_loader.available(), reason="/root/reference not present")
+
+
+@pytest.fixture(scope="module")
+def vits():
+    return dinov2.build("dinov2_vits14", seed=0)
+
+
+def test_extractor_descriptors_bit_equal(vits):
+    ex = ref_loader.make_extractor(vits, "dinov2_vits14")
+    g = torch.Generator().manual_seed(0)
+    batch = torch.randn(1, 3, 98, 98, generator=g)                  # 7x7 patches: fast
+    with torch.no_grad(), warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        for bin_ in (False, True):
+            ref = ex.extract_descriptors(batch, layer=11, facet="token", bin=bin_)
+            mine = servo.extract_descriptors(vits, batch, 11, bin_)
+            assert torch.equal(ref, mine)
+        ref = ex.extract_descriptors(batch, layer=5, facet="token", bin=False)
+        assert torch.equal(ref, servo.extract_descriptors(vits, batch, 5, False))
+
+
+def test_attention_matches_reference_module(vits):
+    """oracle Attention == dino_patch/attention.py MemEffAttention (xFormers absent => SDPA)."""
+    A = ref_loader.attention()
+    blk = vits.blocks[3].attn
+    ref = A.MemEffAttention(384, num_heads=6, qkv_bias=True, proj_bias=True).eval()
+    ref.qkv.load_state_dict(blk.qkv.state_dict())
+    ref.proj.load_state_dict(blk.proj.state_dict())
+    x = torch.randn(2, 50, 384, generator=torch.Generator().manual_seed(1))
+    with torch.no_grad():
+        assert torch.equal(ref(x), blk(x))
+
+
+def test_preprocess_matches_reference(vits):
+    from PIL import Image
+    from vitvs_b200 import synth
+    ex = ref_loader.make_extractor(vits, "dinov2_vits14")
+    g, _, _ = synth.frame_pair(1, 308)
+    assert torch.equal(ex.preprocess_pil(Image.fromarray(g)), servo.preprocess_u8(g))
+
+
+def test_pos_embed_interpolation_matches_reference_patch(vits):
+    """dinov2_extractor.py:94-120 (_fix_pos_enc) evaluated at stride 14 == oracle's method."""
+    ex_mod = ref_loader.extractor()
+    fn = ex_mod.ViTExtractor._fix_pos_enc(14, (14, 14))
+    x = torch.zeros(1, 1 + 22 * 22, 384)
+    with torch.no_grad():
+        ref = fn(vits, x, 308, 308)
+        mine = vits.interpolate_pos_encoding(x, 308, 308)
+    assert torch.allclose(ref, mine, atol=1e-6)
+
+
+def test_full_candidate_set_is_mutual_nn_set():
+    v = ref_loader.vitvs()
+    g = torch.Generator().manual_seed(2)
+    for T, d in ((64, 32), (121, 16)):
+        a = torch.randn(1, 1, T, d, generator=g)
+        b = a[:, :, torch.randperm(T, generator=g)] + 2.5 * torch.randn(1, 1, T, d, generator=g)
+        p1, p2, sim = v.find_correspondences_batch(a, b, num_pairs=T)
+        w = int(np.sqrt(T))
+        tok1 = np.sort((p1[:, 0] * w + p1[:, 1]).numpy())
+        m = servo.match(servo.cosine_similarity_matrix_literal(a, b)[0, 0])
+        assert np.array_equal(tok1, m.candidates)
+        assert np.array_equal(m.candidates, np.nonzero(m.mutual)[0])
+
+
+def test_cyclic_distance_bit_equal_to_pairwise_distance():
+    """Exhaustive over every (drow, dcol) offset of a 46x46 grid (covers 22x22 and 34x45)."""
+    r = torch.arange(-45, 46)
+    dr, dc = torch.meshgrid(r, r, indexing="ij")
+    a = torch.stack([dr.reshape(-1), dc.reshape(-1)], -1)
+    ref = torch.nn.PairwiseDistance(p=2)(a, torch.zeros_like(a)).numpy()
+    mine = servo.cyclic_distance_f32(dr.reshape(-1).numpy(), dc.reshape(-1).numpy())
+    assert np.array_equal(ref, mine)
