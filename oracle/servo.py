@@ -113,10 +113,14 @@ class MatchResult:
 
 def cyclic_distance_f32(dr: np.ndarray, dc: np.ndarray) -> np.ndarray:
     """vitvs_v2.py:117-120: PairwiseDistance(p=2) on int64 (row,col) pairs = ||a - b + 1e-6||_2
-    evaluated in fp32 (int64 promoted by the float eps)."""
-    a = np.float32(dr) + np.float32(1e-6)
-    b = np.float32(dc) + np.float32(1e-6)
-    return np.sqrt((a * a + b * b).astype(np.float32)).astype(np.float32)
+    evaluated in fp32 (int64 promoted by the float eps).  torch's CPU 2-norm accumulates with
+    fused multiply-adds: acc = fl(a*a); acc = fma(b, b, acc); sqrt - bit-exact over every offset of
+    a 46x46 grid (tests/test_oracle_vs_reference.py)."""
+    a = np.asarray(dr).astype(np.float32) + np.float32(1e-6)
+    b = np.asarray(dc).astype(np.float32) + np.float32(1e-6)
+    aa = (a * a).astype(np.float32).astype(np.float64)
+    acc = (b.astype(np.float64) * b.astype(np.float64) + aa).astype(np.float32)   # exact product, one rounding
+    return np.sqrt(acc).astype(np.float32)
 
 
 def match(S: torch.Tensor, cfg=DEFAULT_CFG) -> MatchResult:
