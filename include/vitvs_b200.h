@@ -1,0 +1,172 @@
+/* vitvs_b200 - C ABI of the B200-native ViT-VS `dino` servoing hot path.
+ *
+ * What this replaces.  The reference (begbaj/ViT-VS) has no FFI on this path: `--method dino` selects
+ * catkin_ws/ibvs/src/vitvs_v2.py (run_ibvs.sh:57-62) whose servo loop reaches the feature method only
+ * through Controller.detect_features() (vitvs_v2.py:464-523) and the control law through
+ * Controller.ibvs() (:588-632).  The entry points below are what a ctypes binding inside those two
+ * methods would call; each cites the reference code it stands in for.  INTEGRATION.md shows the stub.
+ *
+ * Conventions: plain C types; the CALLER owns every buffer passed in (device pointers unless the name
+ * says _host); the library owns only its workspace and its bf16 copies of the weights inside the
+ * handle.  Every call returns 0 or a negative vvs_status (no exceptions cross the ABI) and
+ * vvs_last_error() gives the message.  Calls are stream-ordered and asynchronous unless documented
+ * otherwise.  One handle per device, re-entrant across handles, not thread-safe per handle.
+ * There is no CPU fallback: on a machine without an sm_100 GPU vvs_create() fails.
+ */
+#ifndef VITVS_B200_H_
+#define VITVS_B200_H_
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define VVS_API __attribute__((visibility("default")))
+#else
+#define VVS_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct vvs_ctx* vvs_handle;
+typedef void* vvs_stream; /* cudaStream_t */
+
+enum vvs_status {
+  VVS_SUCCESS = 0,
+  VVS_INVALID_ARGUMENT = -1,
+  VVS_CUDA_ERROR = -2,
+  VVS_BAD_STATE = -3,
+  VVS_UNSUPPORTED_DEVICE = -4
+};
+
+enum vvs_dtype { VVS_F32 = 0, VVS_BF16 = 1 };
+enum vvs_image_kind {
+  VVS_IMAGE_U8_HWC = 0,  /* [n, S, S, 3] uint8 RGB, already resized (vitvs_v2.py:474-475 stays on the host) */
+  VVS_IMAGE_F32_NCHW = 1 /* [n, 3, S, S] fp32, output of ViTExtractor.preprocess_pil (dinov2_extractor.py:177-191) */
+};
+
+/* Mirrors the keys Controller.load_parameters reads (vitvs_v2.py:272-323, config/config.yaml) plus the
+ * constants the reference hard-codes (vitvs_v2.py:72,84,250,484-485). */
+typedef struct vvs_config {
+  /* architecture: dinov2_vit{s,b,l,g}14 */
+  int32_t dim;          /* 384 / 768 / 1024 / 1536 */
+  int32_t heads;        /* dim / 64 */
+  int32_t depth;        /* 12 / 12 / 24 / 40 */
+  int32_t ffn_hidden;   /* 4*dim, or 4096 for the SwiGLU giant */
+  int32_t swiglu;       /* 0 = Mlp(GELU), 1 = SwiGLUFFNFused */
+  /* geometry */
+  int32_t image_size;   /* dino_input_size (308) - square ViT input, multiple of 14 */
+  int32_t max_images;   /* workspace sizing: images in flight (= 2 x frame pairs per call) */
+  /* camera / control (config.yaml) */
+  int32_t frame_width;  /* u_max 640 */
+  int32_t frame_height; /* v_max 480 */
+  double f_x, f_y;      /* 502.3016357421875 */
+  double c_x, c_y;      /* u_max/2, v_max/2 (vitvs_v2.py:282-283) */
+  double lambda_;       /* 0.03 */
+  double ema_alpha;     /* 0.8 */
+  int32_t num_pairs;    /* 24 (48 in the best-pose search, vitvs_v2.py:1158) */
+  int32_t layer;        /* 11 (vitvs_v2.py:484) - the forward stops after this block */
+  int32_t use_feature_binning; /* 1 */
+  float same_image_threshold;  /* 0.99 (vitvs_v2.py:84) */
+  int32_t max_match_tokens;    /* workspace for vvs_match on caller descriptors (0 => tokens of image_size) */
+  int32_t max_match_dim;       /* (0 => 9*dim) */
+} vvs_config;
+
+/* replaces: Controller.__init__ -> ViTExtractor(...) model construction (vitvs_v2.py:249-250,
+ * dinov2_extractor.py:25-55).  Allocates the workspace; weights arrive through vvs_set_weight. */
+VVS_API int vvs_create(const vvs_config* cfg, vvs_handle* out);
+VVS_API int vvs_destroy(vvs_handle h);
+/* message of the last failing call on this handle (h may be NULL: last vvs_create failure). */
+VVS_API const char* vvs_last_error(vvs_handle h);
+VVS_API int vvs_num_sms(vvs_handle h);
+
+/* replaces: the state_dict torch.hub.load() fills (dinov2_extractor.py:65-67).  `name` uses the upstream
+ * DINOv2 parameter names: patch_embed.proj.{weight,bias}, cls_token, blocks.<i>.norm{1,2}.{weight,bias},
+ * blocks.<i>.attn.{qkv,proj}.{weight,bias}, blocks.<i>.ls{1,2}.gamma, blocks.<i>.mlp.{fc1,fc2}.{weight,bias}
+ * or blocks.<i>.mlp.{w12,w3}.{weight,bias}; plus `pos_embed_interp` [1+T, dim]: pos_embed already
+ * interpolated to the patch grid (done once per geometry by the host mirror with the maths of
+ * dinov2_extractor.py:94-120).  dev_ptr is a device pointer, copied/converted (bf16 for GEMM operands). */
+VVS_API int vvs_set_weight(vvs_handle h, const char* name, const void* dev_ptr, int32_t dtype, const int64_t* shape,
+                   int32_t rank, vvs_stream stream);
+/* 0 when every parameter of blocks[0..layer] and the embeddings has been set. */
+VVS_API int vvs_weights_ready(vvs_handle h);
+
+/* replaces: ViTExtractor._extract_features with facet 'token' (dinov2_extractor.py:245-263): runs
+ * patch-embed .. blocks[layer] and leaves the residual stream [n_img, 1+T, dim] fp32 in the workspace. */
+VVS_API int vvs_forward_tokens(vvs_handle h, const void* images, int32_t image_kind, int32_t n_img, int32_t layer,
+                       vvs_stream stream);
+/* copy of that residual stream (hook output, dinov2_extractor.py:198-201) to tokens_out [n_img, 1+T, dim] */
+VVS_API int vvs_get_tokens(vvs_handle h, float* tokens_out, int32_t n_img, vvs_stream stream);
+/* replaces: ViTExtractor.extract_descriptors(..., facet='token', bin, include_cls=False)
+ * (dinov2_extractor.py:313-337, _log_bin :265-311) on the tokens of the last vvs_forward_tokens call:
+ * desc_out [n_img, T, (bin ? 9 : 1) * dim] fp32. */
+VVS_API int vvs_descriptors(vvs_handle h, int32_t n_img, int32_t bin, float* desc_out, vvs_stream stream);
+
+typedef struct vvs_match_out { /* every pointer optional (NULL = not wanted), device memory */
+  int32_t* nn1;          /* [n_pairs, T]   argmax_j S[i,j]         (vitvs_v2.py:80) */
+  int32_t* nn2;          /* [n_pairs, T]   argmax_i S[i,j]         (vitvs_v2.py:81) */
+  float* sim1;           /* [n_pairs, T]   max_j S[i,j] */
+  uint8_t* candidate;    /* [n_pairs, T]   passes the cyclic-distance rule (:105-131) == mutual NN */
+  float* mean_sim1;      /* [n_pairs] */
+  int32_t* n_candidates; /* [n_pairs] */
+  int32_t* n_selected;   /* [n_pairs]   min(num_pairs, n_candidates) */
+  int32_t* flags;        /* [n_pairs]   bit 0: same-image branch taken (:84-101) */
+  int32_t* sel_tok;      /* [n_pairs, num_pairs] chosen goal tokens, best similarity first, -1 padded */
+  float* sel_sim;        /* [n_pairs, num_pairs] */
+  int32_t* uv_star;      /* [n_pairs, num_pairs, 2] goal keypoints (u,v) in camera pixels (:511-553) */
+  int32_t* uv;           /* [n_pairs, num_pairs, 2] current keypoints */
+} vvs_match_out;
+
+/* replaces: chunk_cosine_sim + find_correspondences_batch + calculate_uv (vitvs_v2.py:49-155, 511-553) on
+ * caller-supplied descriptors desc1/desc2 [n_pairs, T, d] fp32 (rows = goal / current tokens), patch grid
+ * grid_w x grid_w.  The T x T similarity matrix is never written.  Selection is deterministic (num_pairs
+ * best by similarity); the full candidate set comes back in `candidate` for callers that want to draw
+ * their own random subset like the reference does (:139-141). */
+VVS_API int vvs_match(vvs_handle h, const float* desc1, const float* desc2, int32_t n_pairs, int32_t T, int32_t d,
+              int32_t grid_w, int32_t num_pairs, const vvs_match_out* out, vvs_stream stream);
+/* debugging / tests: dense S [n_pairs, T, T] fp32 of the same descriptors (vitvs_v2.py:49-56). */
+VVS_API int vvs_similarity(vvs_handle h, const float* desc1, const float* desc2, int32_t n_pairs, int32_t T, int32_t d,
+                   float* S_out, vvs_stream stream);
+
+/* replaces: get_depth + transform_to_real_world + calculate_interaction_matrix + pinv + EMA
+ * (vitvs_v2.py:566-586, 610-623, 634-659).  uv / uv_star [n_pairs, K, 2] int32 (u,v), depth
+ * [n_pairs, frame_height, frame_width] uint16 mm.  twist [n_pairs, 6] fp64 (EMA-smoothed when ema_state
+ * != NULL: ema_state [n_pairs, 6] fp64 and ema_init [n_pairs] int32 are caller-owned episode state);
+ * twist_raw (optional) is the value before smoothing. */
+VVS_API int vvs_ibvs(vvs_handle h, const int32_t* uv, const int32_t* uv_star, const uint16_t* depth, int32_t n_pairs,
+             int32_t K, double* twist, double* twist_raw, double* ema_state, int32_t* ema_init, vvs_stream stream);
+
+typedef struct vvs_pair_out { /* device memory; twist required, the rest optional */
+  double* twist;          /* [n_pairs, 6]  v_c = -lambda * pinv(L) e   (vitvs_v2.py:622) */
+  int32_t* n_selected;    /* [n_pairs] */
+  float* mean_sim_sel;    /* [n_pairs]  mean similarity of the selected pairs (best-pose search, :1170) */
+  vvs_match_out match;    /* per-stage outputs for parity checks */
+} vvs_pair_out;
+
+/* replaces: one Controller.ibvs() iteration per frame pair (vitvs_v2.py:588-623), batched:
+ * goal / current [n_pairs, S, S, 3] uint8 (device), depth [n_pairs, H, W] uint16 (device). */
+VVS_API int vvs_frame_pairs_to_twist(vvs_handle h, const uint8_t* goal, const uint8_t* current, const uint16_t* depth,
+                             int32_t n_pairs, const vvs_pair_out* out, vvs_stream stream);
+/* same with HOST buffers: H2D of the frames, the whole path, D2H of twist [n_pairs,6] / n_selected
+ * [n_pairs] / mean_sim_sel [n_pairs] (last two optional), then a stream synchronise.  Pinned host memory
+ * makes the copies asynchronous. */
+VVS_API int vvs_frame_pairs_to_twist_host(vvs_handle h, const uint8_t* goal_host, const uint8_t* current_host,
+                                  const uint16_t* depth_host, int32_t n_pairs, double* twist_host,
+                                  int32_t* n_selected_host, float* mean_sim_sel_host, vvs_stream stream);
+/* number of kernels the last vvs_frame_pairs_to_twist* call launched (bench.py gpu_launches). */
+VVS_API int vvs_last_launch_count(vvs_handle h);
+
+/* ---- kernel-level entry points (unit tests, per-kernel benchmarks; device pointers) ---------------- */
+/* C = A[M,K] * B[N,K]^T with one of the fused epilogues (see csrc/vvs_internal.h Epilogue). */
+VVS_API int vvs_dbg_gemm(vvs_handle h, const void* A_bf16, const void* B_bf16, int32_t M, int32_t N, int32_t K,
+                 int32_t epilogue, const float* bias, const float* gamma, float* x_f32, void* out_bf16, int32_t ldo,
+                 int32_t q_cols, float q_scale, const float* pos, int32_t T, vvs_stream stream);
+VVS_API int vvs_dbg_attention(vvs_handle h, const void* qkv_bf16, void* out_bf16, int32_t n_img, int32_t n_tok,
+                      int32_t heads, vvs_stream stream);
+VVS_API int vvs_dbg_layernorm(vvs_handle h, const float* x, const float* w, const float* b, void* out_bf16, int32_t rows,
+                      int32_t dim, vvs_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VITVS_B200_H_ */

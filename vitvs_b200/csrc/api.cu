@@ -1,0 +1,655 @@
+// C ABI (include/vitvs_b200.h): handle, weight registry, workspace and the stream-ordered
+// orchestration of the dino hot path.  No torch types, no CPU fallback.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/vitvs_b200.h"
+#include "vvs_internal.h"
+
+namespace vvs {
+
+static std::string g_create_error;
+
+void set_error(std::string* slot, const std::string& msg) {
+  if (slot) *slot = msg;
+}
+
+namespace {
+
+constexpr int kPatch = 14;
+constexpr int kPatchKPad = 640;   // 588 -> multiple of the 64-element K tile
+
+// fp32 / bf16 [rows, cols] -> bf16 [rows, cpad] (zero padded), optional source-row permutation for the
+// SwiGLU tile interleave: dst row r (tile n = r / bn) takes w12 row n*bn/2 + j (x1) or hidden + ... (x2).
+template <typename SrcT>
+__global__ void convert_matrix_kernel(const SrcT* __restrict__ src, bf16* __restrict__ dst, int rows, int cols, int cpad,
+                                      int interleave_bn, int hidden) {
+  const long long total = static_cast<long long>(rows) * cpad;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / cpad), c = static_cast<int>(i % cpad);
+    int sr = r;
+    if (interleave_bn) {
+      const int half = interleave_bn / 2, n = r / interleave_bn, wi = r % interleave_bn;
+      sr = wi < half ? n * half + wi : hidden + n * half + (wi - half);
+    }
+    float v = 0.f;
+    if (c < cols) v = static_cast<float>(src[static_cast<size_t>(sr) * cols + c]);
+    dst[i] = __float2bfloat16_rn(v);
+  }
+}
+
+template <typename SrcT>
+__global__ void convert_vector_kernel(const SrcT* __restrict__ src, float* __restrict__ dst, int n, int interleave_bn,
+                                      int hidden) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int s = i;
+  if (interleave_bn) {
+    const int half = interleave_bn / 2, t = i / interleave_bn, wi = i % interleave_bn;
+    s = wi < half ? t * half + wi : hidden + t * half + (wi - half);
+  }
+  dst[i] = static_cast<float>(src[s]);
+}
+
+__global__ void mean_selected_kernel(const float* __restrict__ sel_sim, const int32_t* __restrict__ n_sel, int K,
+                                     float* __restrict__ out, int n_pairs) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pairs) return;
+  const int n = n_sel[p];
+  float s = 0.f;
+  for (int k = 0; k < n; ++k) s += sel_sim[static_cast<size_t>(p) * K + k];
+  out[p] = n > 0 ? s / n : 0.f;
+}
+
+struct BlockW {
+  bf16* qkv_w = nullptr; bf16* proj_w = nullptr; bf16* ffn1_w = nullptr; bf16* ffn2_w = nullptr;
+  float* qkv_b = nullptr; float* proj_b = nullptr; float* ffn1_b = nullptr; float* ffn2_b = nullptr;
+  float* n1w = nullptr; float* n1b = nullptr; float* n2w = nullptr; float* n2b = nullptr;
+  float* ls1 = nullptr; float* ls2 = nullptr;
+  unsigned set_mask = 0;   // 14 bits
+};
+
+}  // namespace
+}  // namespace vvs
+
+using namespace vvs;
+
+struct vvs_ctx {
+  vvs_config cfg;
+  int device = 0;
+  int num_sms = 148;
+  std::string err;
+  int grid = 0, T = 0, N = 0;
+  // embeddings
+  bf16* pe_w = nullptr; float* pe_b = nullptr; float* cls = nullptr; float* pos = nullptr;
+  unsigned emb_mask = 0;   // 4 bits
+  std::vector<BlockW> blocks;
+  // workspace
+  float* x = nullptr;        // residual stream [max_images * N, D] fp32
+  bf16* h = nullptr;         // LN out / attention out [max_images * N, D]
+  bf16* big = nullptr;       // im2col / qkv / ffn hidden
+  size_t big_elems = 0;
+  bf16* desc = nullptr;      // unit-norm descriptors
+  size_t desc_elems = 0;
+  float* sqn = nullptr;      // [max_images * T]
+  unsigned long long* row_best = nullptr;
+  unsigned long long* col_best = nullptr;
+  size_t match_cap = 0;      // tokens (summed over pairs) the match outputs hold
+  int32_t* nn1 = nullptr; int32_t* nn2 = nullptr; float* sim1 = nullptr; uint8_t* cand = nullptr;
+  int max_pairs = 0;
+  int k_cap = 0;
+  float* mean_sim1 = nullptr; int32_t* n_cand = nullptr; int32_t* n_sel = nullptr; int32_t* flags = nullptr;
+  int32_t* sel_tok = nullptr; float* sel_sim = nullptr; int32_t* uv_star = nullptr; int32_t* uv = nullptr;
+  float* mean_sel = nullptr;
+  double* twist = nullptr;
+  uint8_t* stage_img = nullptr;    // [max_images, S, S, 3]
+  uint16_t* stage_depth = nullptr; // [max_pairs, H, W]
+  int last_n_img = 0;
+  int launch_count = 0;
+};
+
+namespace {
+
+template <typename T>
+int dev_alloc(vvs_ctx* c, T** p, size_t count) {
+  VVS_CUDA_OK(cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T) + 256), &c->err);
+  return VVS_OK;
+}
+
+int fail(vvs_ctx* c, int code, const std::string& msg) {
+  if (c) c->err = msg; else g_create_error = msg;
+  return code;
+}
+
+int upload_matrix(vvs_ctx* c, bf16** dst, const void* src, int dtype, int rows, int cols, int cpad, int interleave_bn,
+                  int hidden, cudaStream_t s) {
+  if (!*dst) {
+    int rc = dev_alloc(c, dst, static_cast<size_t>(rows) * cpad);
+    if (rc) return rc;
+  }
+  const long long total = static_cast<long long>(rows) * cpad;
+  const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
+  if (dtype == VVS_F32)
+    convert_matrix_kernel<float><<<grid, 256, 0, s>>>(static_cast<const float*>(src), *dst, rows, cols, cpad,
+                                                       interleave_bn, hidden);
+  else
+    convert_matrix_kernel<bf16><<<grid, 256, 0, s>>>(static_cast<const bf16*>(src), *dst, rows, cols, cpad,
+                                                      interleave_bn, hidden);
+  VVS_CUDA_OK(cudaGetLastError(), &c->err);
+  return VVS_OK;
+}
+
+int upload_vector(vvs_ctx* c, float** dst, const void* src, int dtype, int n, int interleave_bn, int hidden,
+                  cudaStream_t s) {
+  if (!*dst) {
+    int rc = dev_alloc(c, dst, static_cast<size_t>(n));
+    if (rc) return rc;
+  }
+  if (dtype == VVS_F32)
+    convert_vector_kernel<float><<<(n + 255) / 256, 256, 0, s>>>(static_cast<const float*>(src), *dst, n,
+                                                                  interleave_bn, hidden);
+  else
+    convert_vector_kernel<bf16><<<(n + 255) / 256, 256, 0, s>>>(static_cast<const bf16*>(src), *dst, n, interleave_bn,
+                                                                 hidden);
+  VVS_CUDA_OK(cudaGetLastError(), &c->err);
+  return VVS_OK;
+}
+
+long long numel(const int64_t* shape, int rank) {
+  long long n = 1;
+  for (int i = 0; i < rank; ++i) n *= shape[i];
+  return n;
+}
+
+int gemm(vvs_ctx* c, const GemmArgs& a, cudaStream_t s) {
+  ++c->launch_count;
+  return launch_gemm(a, c->num_sms, s, &c->err);
+}
+
+GemmArgs plain_gemm(const bf16* A, const bf16* B, int M, int N, int K, int epi) {
+  GemmArgs g;
+  memset(&g, 0, sizeof(g));
+  g.A = A; g.B = B; g.M = M; g.N = N; g.K = K; g.lda = K; g.ldb = K; g.batch = 1;
+  g.epilogue = epi;
+  return g;
+}
+
+int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int layer, cudaStream_t s) {
+  const vvs_config& f = c->cfg;
+  if (n_img < 1 || n_img > f.max_images) return fail(c, VVS_ERR_INVALID, "n_img outside [1, max_images]");
+  if (layer < 0 || layer >= f.depth) return fail(c, VVS_ERR_INVALID, "layer outside [0, depth)");
+  if (c->emb_mask != 0xF) return fail(c, VVS_ERR_STATE, "embedding weights not set (patch_embed.*, cls_token, pos_embed_interp)");
+  for (int i = 0; i <= layer; ++i)
+    if (c->blocks[i].set_mask != 0x3FFF)
+      return fail(c, VVS_ERR_STATE, "weights of blocks." + std::to_string(i) + " incomplete");
+  const int D = f.dim, H = f.ffn_hidden, T = c->T, N = c->N;
+  const int M = n_img * N, Mp = n_img * T;
+  int rc;
+  if (kind == VVS_IMAGE_U8_HWC)
+    rc = launch_im2col_u8(static_cast<const uint8_t*>(images), c->big, n_img, f.image_size, kPatchKPad, s, &c->err);
+  else if (kind == VVS_IMAGE_F32_NCHW)
+    rc = launch_im2col_f32(static_cast<const float*>(images), c->big, n_img, f.image_size, kPatchKPad, s, &c->err);
+  else
+    return fail(c, VVS_ERR_INVALID, "unknown image_kind");
+  if (rc) return rc;
+  rc = launch_cls_rows(c->x, c->cls, c->pos, n_img, N, D, s, &c->err);
+  if (rc) return rc;
+  c->launch_count += 2;
+  {
+    GemmArgs g = plain_gemm(c->big, c->pe_w, Mp, D, kPatchKPad, EPI_PATCH_F32);
+    g.bias = c->pe_b; g.x_f32 = c->x; g.ldo = D; g.pos = c->pos; g.T = T;
+    if ((rc = gemm(c, g, s))) return rc;
+  }
+  for (int i = 0; i <= layer; ++i) {
+    const BlockW& w = c->blocks[i];
+    if ((rc = launch_layernorm(c->x, w.n1w, w.n1b, c->h, M, D, 1e-6f, s, &c->err))) return rc;
+    {
+      GemmArgs g = plain_gemm(c->h, w.qkv_w, M, 3 * D, D, EPI_BIAS_BF16);
+      g.bias = w.qkv_b; g.out_bf16 = c->big; g.ldo = 3 * D; g.q_cols = D; g.q_scale = 0.125f;   // hd^-0.5, hd = 64
+      if ((rc = gemm(c, g, s))) return rc;
+    }
+    if ((rc = launch_attention(c->big, c->h, n_img, N, f.heads, s, &c->err))) return rc;
+    {
+      GemmArgs g = plain_gemm(c->h, w.proj_w, M, D, D, EPI_RESID_F32);
+      g.bias = w.proj_b; g.gamma = w.ls1; g.x_f32 = c->x; g.ldo = D;
+      if ((rc = gemm(c, g, s))) return rc;
+    }
+    if ((rc = launch_layernorm(c->x, w.n2w, w.n2b, c->h, M, D, 1e-6f, s, &c->err))) return rc;
+    {
+      GemmArgs g = plain_gemm(c->h, w.ffn1_w, M, f.swiglu ? 2 * H : H, D, f.swiglu ? EPI_SWIGLU_BF16 : EPI_GELU_BF16);
+      g.bias = w.ffn1_b; g.out_bf16 = c->big; g.ldo = H;
+      if ((rc = gemm(c, g, s))) return rc;
+    }
+    {
+      GemmArgs g = plain_gemm(c->big, w.ffn2_w, M, D, H, EPI_RESID_F32);
+      g.bias = w.ffn2_b; g.gamma = w.ls2; g.x_f32 = c->x; g.ldo = D;
+      if ((rc = gemm(c, g, s))) return rc;
+    }
+    c->launch_count += 3;   // 2 LayerNorms + attention
+  }
+  c->last_n_img = n_img;
+  return VVS_OK;
+}
+
+// similarity arg-max + selection on unit-norm bf16 descriptors already in c->desc:
+// goal sets at desc[0 .. n_pairs), current sets at desc[n_pairs .. 2 n_pairs), each [T, dpad].
+int match_on_desc(vvs_ctx* c, int n_pairs, int T, int dpad, int grid_w, int K, const vvs_match_out* out,
+                  cudaStream_t s) {
+  if (static_cast<size_t>(n_pairs) * T > c->match_cap)
+    return fail(c, VVS_ERR_STATE, "match workspace too small (raise max_images / max_match_tokens)");
+  if (K > c->k_cap || n_pairs > c->max_pairs)
+    return fail(c, VVS_ERR_STATE, "num_pairs / n_pairs beyond the workspace of this handle");
+  const size_t keys = static_cast<size_t>(n_pairs) * T;
+  VVS_CUDA_OK(cudaMemsetAsync(c->row_best, 0, keys * sizeof(unsigned long long), s), &c->err);
+  VVS_CUDA_OK(cudaMemsetAsync(c->col_best, 0, keys * sizeof(unsigned long long), s), &c->err);
+  GemmArgs g;
+  memset(&g, 0, sizeof(g));
+  g.A = c->desc;
+  g.B = c->desc + static_cast<size_t>(n_pairs) * T * dpad;
+  g.M = T; g.N = T; g.K = dpad; g.lda = dpad; g.ldb = dpad; g.batch = n_pairs;
+  g.a_batch_pitch = static_cast<long long>(T) * dpad;
+  g.b_batch_pitch = static_cast<long long>(T) * dpad;
+  g.epilogue = EPI_SIM;
+  g.row_best = c->row_best; g.col_best = c->col_best; g.best_pitch = T;
+  int rc = gemm(c, g, s);
+  if (rc) return rc;
+  SelectArgs a;
+  memset(&a, 0, sizeof(a));
+  a.row_best = c->row_best; a.col_best = c->col_best; a.best_pitch = T;
+  a.n_pairs = n_pairs; a.T = T; a.grid_w = grid_w; a.K = K;
+  a.same_thresh = c->cfg.same_image_threshold;
+  a.image_size = c->cfg.image_size;
+  a.cam.width = c->cfg.frame_width; a.cam.height = c->cfg.frame_height;
+  a.cam.fx = c->cfg.f_x; a.cam.fy = c->cfg.f_y; a.cam.cx = c->cfg.c_x; a.cam.cy = c->cfg.c_y;
+  a.nn1 = c->nn1; a.nn2 = c->nn2; a.sim1 = c->sim1; a.candidate = c->cand;
+  a.mean_sim1 = c->mean_sim1; a.n_candidates = c->n_cand; a.n_selected = c->n_sel; a.flags = c->flags;
+  a.sel_tok = c->sel_tok; a.sel_sim = c->sel_sim; a.uv_star = c->uv_star; a.uv = c->uv;
+  if ((rc = launch_select(a, s, &c->err))) return rc;
+  ++c->launch_count;
+  if (out) {
+#define VVS_COPY_OUT(field, src, count, type)                                                                  \
+  if (out->field)                                                                                              \
+    VVS_CUDA_OK(cudaMemcpyAsync(out->field, src, static_cast<size_t>(count) * sizeof(type), cudaMemcpyDeviceToDevice, s), \
+                &c->err)
+    VVS_COPY_OUT(nn1, c->nn1, keys, int32_t);
+    VVS_COPY_OUT(nn2, c->nn2, keys, int32_t);
+    VVS_COPY_OUT(sim1, c->sim1, keys, float);
+    VVS_COPY_OUT(candidate, c->cand, keys, uint8_t);
+    VVS_COPY_OUT(mean_sim1, c->mean_sim1, n_pairs, float);
+    VVS_COPY_OUT(n_candidates, c->n_cand, n_pairs, int32_t);
+    VVS_COPY_OUT(n_selected, c->n_sel, n_pairs, int32_t);
+    VVS_COPY_OUT(flags, c->flags, n_pairs, int32_t);
+    VVS_COPY_OUT(sel_tok, c->sel_tok, static_cast<size_t>(n_pairs) * K, int32_t);
+    VVS_COPY_OUT(sel_sim, c->sel_sim, static_cast<size_t>(n_pairs) * K, float);
+    VVS_COPY_OUT(uv_star, c->uv_star, static_cast<size_t>(n_pairs) * K * 2, int32_t);
+    VVS_COPY_OUT(uv, c->uv, static_cast<size_t>(n_pairs) * K * 2, int32_t);
+#undef VVS_COPY_OUT
+  }
+  return VVS_OK;
+}
+
+int normalise_caller_descriptors(vvs_ctx* c, const float* d1, const float* d2, int n_pairs, int T, int d, int* dpad_out,
+                                 cudaStream_t s) {
+  const int dpad = (d + 7) / 8 * 8;
+  if (2ull * n_pairs * T * dpad > c->desc_elems)
+    return fail(c, VVS_ERR_STATE, "descriptor workspace too small (raise max_match_tokens / max_match_dim)");
+  int rc = launch_normalize_rows_bf16(d1, c->desc, n_pairs * T, d, dpad, s, &c->err);
+  if (rc) return rc;
+  rc = launch_normalize_rows_bf16(d2, c->desc + static_cast<size_t>(n_pairs) * T * dpad, n_pairs * T, d, dpad, s,
+                                  &c->err);
+  c->launch_count += 2;
+  *dpad_out = dpad;
+  return rc;
+}
+
+int run_ibvs(vvs_ctx* c, const int32_t* uv, const int32_t* uv_star, const uint16_t* depth, int n_pairs, int K,
+             double* twist, double* twist_raw, double* ema_state, int32_t* ema_init, cudaStream_t s) {
+  IbvsArgs a;
+  memset(&a, 0, sizeof(a));
+  a.uv = uv; a.uv_star = uv_star; a.depth = depth; a.n_pairs = n_pairs; a.K = K;
+  a.cam.width = c->cfg.frame_width; a.cam.height = c->cfg.frame_height;
+  a.cam.fx = c->cfg.f_x; a.cam.fy = c->cfg.f_y; a.cam.cx = c->cfg.c_x; a.cam.cy = c->cfg.c_y;
+  a.lambda = c->cfg.lambda_; a.ema_alpha = c->cfg.ema_alpha;
+  a.ema_state = ema_state; a.ema_init = ema_init; a.twist = twist; a.twist_raw = twist_raw;
+  ++c->launch_count;
+  return launch_ibvs(a, s, &c->err);
+}
+
+int pairs_to_twist(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth, int n_pairs,
+                   const vvs_pair_out* out, cudaStream_t s) {
+  const vvs_config& f = c->cfg;
+  if (n_pairs < 1 || 2 * n_pairs > f.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
+  if (!out || !out->twist) return fail(c, VVS_ERR_INVALID, "out->twist is required");
+  c->launch_count = 0;
+  const size_t img_bytes = static_cast<size_t>(f.image_size) * f.image_size * 3;
+  const uint8_t* images = goal;
+  if (cur != goal + n_pairs * img_bytes) {   // make [goal.. | current..] contiguous
+    if (goal != c->stage_img)
+      VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img, goal, n_pairs * img_bytes, cudaMemcpyDeviceToDevice, s), &c->err);
+    VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img + n_pairs * img_bytes, cur, n_pairs * img_bytes, cudaMemcpyDeviceToDevice, s),
+                &c->err);
+    images = c->stage_img;
+  }
+  int rc = forward_tokens(c, images, VVS_IMAGE_U8_HWC, 2 * n_pairs, f.layer, s);
+  if (rc) return rc;
+  const int parts = f.use_feature_binning ? 9 : 1;
+  rc = launch_descriptors_unit_bf16(c->x, c->desc, c->sqn, 2 * n_pairs, c->grid, c->grid, f.dim,
+                                    f.use_feature_binning, s, &c->err);
+  if (rc) return rc;
+  c->launch_count += 2;
+  rc = match_on_desc(c, n_pairs, c->T, parts * f.dim, c->grid, f.num_pairs, &out->match, s);
+  if (rc) return rc;
+  rc = run_ibvs(c, c->uv, c->uv_star, depth, n_pairs, f.num_pairs, out->twist, nullptr, nullptr, nullptr, s);
+  if (rc) return rc;
+  if (out->n_selected)
+    VVS_CUDA_OK(cudaMemcpyAsync(out->n_selected, c->n_sel, n_pairs * sizeof(int32_t), cudaMemcpyDeviceToDevice, s),
+                &c->err);
+  if (out->mean_sim_sel) {
+    mean_selected_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(c->sel_sim, c->n_sel, f.num_pairs, out->mean_sim_sel,
+                                                               n_pairs);
+    VVS_CUDA_OK(cudaGetLastError(), &c->err);
+    ++c->launch_count;
+  }
+  return VVS_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------- C ABI
+extern "C" {
+
+int vvs_create(const vvs_config* cfg, vvs_handle* out) {
+  if (!cfg || !out) return fail(nullptr, VVS_ERR_INVALID, "vvs_create: null argument");
+  *out = nullptr;
+  int dev = 0;
+  cudaDeviceProp prop;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess)
+    return fail(nullptr, VVS_ERR_CUDA, "vvs_create: no usable CUDA device (this library has no CPU fallback)");
+  if (prop.major != 10)
+    return fail(nullptr, VVS_ERR_UNSUPPORTED,
+                std::string("vvs_create: device '") + prop.name + "' is sm_" + std::to_string(prop.major) +
+                    std::to_string(prop.minor) + "; the kernels are built for sm_100a only");
+  if (cfg->dim % 128 || cfg->heads * 64 != cfg->dim || cfg->depth < 1 || cfg->ffn_hidden % 64 ||
+      cfg->image_size % kPatch || cfg->image_size < kPatch || cfg->max_images < 1 || cfg->num_pairs < 1 ||
+      cfg->num_pairs > 256 || cfg->layer < 0 || cfg->layer >= cfg->depth)
+    return fail(nullptr, VVS_ERR_INVALID, "vvs_create: inconsistent vvs_config");
+  if (cfg->dim != 384 && cfg->dim != 768 && cfg->dim != 1024 && cfg->dim != 1536)
+    return fail(nullptr, VVS_ERR_INVALID, "vvs_create: dim must be 384/768/1024/1536 (dinov2_vit{s,b,l,g}14)");
+  vvs_ctx* c = new vvs_ctx();
+  c->cfg = *cfg;
+  c->device = dev;
+  c->num_sms = prop.multiProcessorCount;
+  c->grid = cfg->image_size / kPatch;
+  c->T = c->grid * c->grid;
+  c->N = c->T + 1;
+  c->blocks.resize(cfg->depth);
+  const size_t rows = static_cast<size_t>(cfg->max_images) * c->N;
+  const int D = cfg->dim, H = cfg->ffn_hidden;
+  const size_t widest = std::max<size_t>(std::max<size_t>(3 * D, H), kPatchKPad);
+  c->big_elems = rows * widest;
+  const int mt = cfg->max_match_tokens > 0 ? cfg->max_match_tokens : c->T;
+  const int md = cfg->max_match_dim > 0 ? cfg->max_match_dim : 9 * D;
+  c->desc_elems = std::max<size_t>(static_cast<size_t>(cfg->max_images) * c->T * 9 * D,
+                                   2ull * mt * ((md + 7) / 8 * 8));
+  c->max_pairs = std::max(1, cfg->max_images / 2);
+  c->match_cap = std::max<size_t>(static_cast<size_t>(c->max_pairs) * c->T, mt);
+  c->k_cap = std::max(cfg->num_pairs, 64);
+  const size_t img_bytes = static_cast<size_t>(cfg->image_size) * cfg->image_size * 3;
+  int rc = 0;
+  rc |= dev_alloc(c, &c->x, rows * D);
+  rc |= dev_alloc(c, &c->h, rows * D);
+  rc |= dev_alloc(c, &c->big, c->big_elems);
+  rc |= dev_alloc(c, &c->desc, c->desc_elems);
+  rc |= dev_alloc(c, &c->sqn, static_cast<size_t>(cfg->max_images) * c->T);
+  rc |= dev_alloc(c, &c->row_best, c->match_cap);
+  rc |= dev_alloc(c, &c->col_best, c->match_cap);
+  rc |= dev_alloc(c, &c->nn1, c->match_cap);
+  rc |= dev_alloc(c, &c->nn2, c->match_cap);
+  rc |= dev_alloc(c, &c->sim1, c->match_cap);
+  rc |= dev_alloc(c, &c->cand, c->match_cap);
+  rc |= dev_alloc(c, &c->mean_sim1, c->max_pairs);
+  rc |= dev_alloc(c, &c->n_cand, c->max_pairs);
+  rc |= dev_alloc(c, &c->n_sel, c->max_pairs);
+  rc |= dev_alloc(c, &c->flags, c->max_pairs);
+  rc |= dev_alloc(c, &c->mean_sel, c->max_pairs);
+  rc |= dev_alloc(c, &c->sel_tok, static_cast<size_t>(c->max_pairs) * c->k_cap);
+  rc |= dev_alloc(c, &c->sel_sim, static_cast<size_t>(c->max_pairs) * c->k_cap);
+  rc |= dev_alloc(c, &c->uv_star, static_cast<size_t>(c->max_pairs) * c->k_cap * 2);
+  rc |= dev_alloc(c, &c->uv, static_cast<size_t>(c->max_pairs) * c->k_cap * 2);
+  rc |= dev_alloc(c, &c->twist, static_cast<size_t>(c->max_pairs) * 6);
+  rc |= dev_alloc(c, &c->stage_img, static_cast<size_t>(cfg->max_images) * img_bytes);
+  rc |= dev_alloc(c, &c->stage_depth, static_cast<size_t>(c->max_pairs) * cfg->frame_width * cfg->frame_height);
+  if (rc) {
+    g_create_error = "vvs_create: workspace allocation failed: " + c->err;
+    vvs_destroy(c);
+    return VVS_ERR_CUDA;
+  }
+  *out = c;
+  return VVS_OK;
+}
+
+int vvs_destroy(vvs_handle c) {
+  if (!c) return VVS_OK;
+  void* ptrs[] = {c->pe_w, c->pe_b, c->cls, c->pos, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
+                  c->nn1, c->nn2, c->sim1, c->cand, c->mean_sim1, c->n_cand, c->n_sel, c->flags, c->mean_sel,
+                  c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  for (BlockW& w : c->blocks) {
+    void* bp[] = {w.qkv_w, w.proj_w, w.ffn1_w, w.ffn2_w, w.qkv_b, w.proj_b, w.ffn1_b, w.ffn2_b,
+                  w.n1w, w.n1b, w.n2w, w.n2b, w.ls1, w.ls2};
+    for (void* p : bp)
+      if (p) cudaFree(p);
+  }
+  delete c;
+  return VVS_OK;
+}
+
+const char* vvs_last_error(vvs_handle c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+int vvs_num_sms(vvs_handle c) { return c ? c->num_sms : 0; }
+int vvs_last_launch_count(vvs_handle c) { return c ? c->launch_count : 0; }
+
+int vvs_set_weight(vvs_handle c, const char* name_c, const void* p, int32_t dtype, const int64_t* shape, int32_t rank,
+                   vvs_stream stream) {
+  if (!c || !name_c || !p || !shape) return fail(c, VVS_ERR_INVALID, "vvs_set_weight: null argument");
+  if (dtype != VVS_F32 && dtype != VVS_BF16) return fail(c, VVS_ERR_INVALID, "vvs_set_weight: dtype must be f32 or bf16");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const std::string name(name_c);
+  const int D = c->cfg.dim, H = c->cfg.ffn_hidden;
+  const long long n = numel(shape, rank);
+  auto bad_shape = [&]() { return fail(c, VVS_ERR_INVALID, "vvs_set_weight: wrong element count for " + name); };
+  if (name == "patch_embed.proj.weight") {
+    if (n != static_cast<long long>(D) * 588) return bad_shape();
+    c->emb_mask |= 1;
+    return upload_matrix(c, &c->pe_w, p, dtype, D, 588, kPatchKPad, 0, 0, s);
+  }
+  if (name == "patch_embed.proj.bias") {
+    if (n != D) return bad_shape();
+    c->emb_mask |= 2;
+    return upload_vector(c, &c->pe_b, p, dtype, D, 0, 0, s);
+  }
+  if (name == "cls_token") {
+    if (n != D) return bad_shape();
+    c->emb_mask |= 4;
+    return upload_vector(c, &c->cls, p, dtype, D, 0, 0, s);
+  }
+  if (name == "pos_embed_interp") {
+    if (n != static_cast<long long>(c->N) * D) return bad_shape();
+    c->emb_mask |= 8;
+    return upload_vector(c, &c->pos, p, dtype, c->N * D, 0, 0, s);
+  }
+  if (name.rfind("blocks.", 0) == 0) {
+    const size_t dot = name.find('.', 7);
+    if (dot == std::string::npos) return fail(c, VVS_ERR_INVALID, "vvs_set_weight: malformed name " + name);
+    const int idx = atoi(name.substr(7, dot - 7).c_str());
+    if (idx < 0 || idx >= c->cfg.depth) return fail(c, VVS_ERR_INVALID, "vvs_set_weight: block index out of range in " + name);
+    BlockW& w = c->blocks[idx];
+    const std::string leaf = name.substr(dot + 1);
+    const bool sg = c->cfg.swiglu != 0;
+    const int bn12 = sg ? gemm_block_n(2 * H) : 0;
+    struct Vec { const char* leaf; float** dst; int n; int bit; int il; };
+    const Vec vecs[] = {
+        {"norm1.weight", &w.n1w, D, 0, 0}, {"norm1.bias", &w.n1b, D, 1, 0},
+        {"norm2.weight", &w.n2w, D, 2, 0}, {"norm2.bias", &w.n2b, D, 3, 0},
+        {"ls1.gamma", &w.ls1, D, 4, 0}, {"ls2.gamma", &w.ls2, D, 5, 0},
+        {"attn.qkv.bias", &w.qkv_b, 3 * D, 6, 0}, {"attn.proj.bias", &w.proj_b, D, 7, 0},
+        {sg ? "mlp.w12.bias" : "mlp.fc1.bias", &w.ffn1_b, sg ? 2 * H : H, 8, bn12},
+        {sg ? "mlp.w3.bias" : "mlp.fc2.bias", &w.ffn2_b, D, 9, 0}};
+    for (const Vec& v : vecs)
+      if (leaf == v.leaf) {
+        if (n != v.n) return bad_shape();
+        w.set_mask |= 1u << v.bit;
+        return upload_vector(c, v.dst, p, dtype, v.n, v.il, H, s);
+      }
+    struct Mat { const char* leaf; bf16** dst; int rows, cols; int bit; int il; };
+    const Mat mats[] = {
+        {"attn.qkv.weight", &w.qkv_w, 3 * D, D, 10, 0}, {"attn.proj.weight", &w.proj_w, D, D, 11, 0},
+        {sg ? "mlp.w12.weight" : "mlp.fc1.weight", &w.ffn1_w, sg ? 2 * H : H, D, 12, bn12},
+        {sg ? "mlp.w3.weight" : "mlp.fc2.weight", &w.ffn2_w, D, H, 13, 0}};
+    for (const Mat& m : mats)
+      if (leaf == m.leaf) {
+        if (n != static_cast<long long>(m.rows) * m.cols) return bad_shape();
+        w.set_mask |= 1u << m.bit;
+        return upload_matrix(c, m.dst, p, dtype, m.rows, m.cols, m.cols, m.il, H, s);
+      }
+  }
+  return fail(c, VVS_ERR_INVALID, "vvs_set_weight: unknown parameter name " + name);
+}
+
+int vvs_weights_ready(vvs_handle c) {
+  if (!c) return VVS_ERR_INVALID;
+  if (c->emb_mask != 0xF) return fail(c, VVS_ERR_STATE, "embedding weights not set");
+  for (int i = 0; i <= c->cfg.layer; ++i)
+    if (c->blocks[i].set_mask != 0x3FFF) return fail(c, VVS_ERR_STATE, "weights of blocks." + std::to_string(i) + " incomplete");
+  return VVS_OK;
+}
+
+int vvs_forward_tokens(vvs_handle c, const void* images, int32_t kind, int32_t n_img, int32_t layer, vvs_stream stream) {
+  if (!c || !images) return fail(c, VVS_ERR_INVALID, "vvs_forward_tokens: null argument");
+  c->launch_count = 0;
+  return forward_tokens(c, images, kind, n_img, layer, static_cast<cudaStream_t>(stream));
+}
+
+int vvs_get_tokens(vvs_handle c, float* out, int32_t n_img, vvs_stream stream) {
+  if (!c || !out) return fail(c, VVS_ERR_INVALID, "vvs_get_tokens: null argument");
+  if (n_img < 1 || n_img > c->last_n_img) return fail(c, VVS_ERR_STATE, "vvs_get_tokens: no forward pass holds that many images");
+  VVS_CUDA_OK(cudaMemcpyAsync(out, c->x, static_cast<size_t>(n_img) * c->N * c->cfg.dim * sizeof(float),
+                              cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)),
+              &c->err);
+  return VVS_OK;
+}
+
+int vvs_descriptors(vvs_handle c, int32_t n_img, int32_t bin, float* out, vvs_stream stream) {
+  if (!c || !out) return fail(c, VVS_ERR_INVALID, "vvs_descriptors: null argument");
+  if (n_img < 1 || n_img > c->last_n_img) return fail(c, VVS_ERR_STATE, "vvs_descriptors: no forward pass holds that many images");
+  ++c->launch_count;
+  return launch_descriptors_f32(c->x, out, n_img, c->grid, c->grid, c->cfg.dim, bin, static_cast<cudaStream_t>(stream),
+                                &c->err);
+}
+
+int vvs_match(vvs_handle c, const float* d1, const float* d2, int32_t n_pairs, int32_t T, int32_t d, int32_t grid_w,
+              int32_t num_pairs, const vvs_match_out* out, vvs_stream stream) {
+  if (!c || !d1 || !d2) return fail(c, VVS_ERR_INVALID, "vvs_match: null argument");
+  if (n_pairs < 1 || T < 1 || d < 1 || grid_w < 1 || num_pairs < 1)
+    return fail(c, VVS_ERR_INVALID, "vvs_match: empty problem");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  c->launch_count = 0;
+  int dpad = 0;
+  int rc = normalise_caller_descriptors(c, d1, d2, n_pairs, T, d, &dpad, s);
+  if (rc) return rc;
+  return match_on_desc(c, n_pairs, T, dpad, grid_w, num_pairs, out, s);
+}
+
+int vvs_similarity(vvs_handle c, const float* d1, const float* d2, int32_t n_pairs, int32_t T, int32_t d, float* S,
+                   vvs_stream stream) {
+  if (!c || !d1 || !d2 || !S) return fail(c, VVS_ERR_INVALID, "vvs_similarity: null argument");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int dpad = 0;
+  int rc = normalise_caller_descriptors(c, d1, d2, n_pairs, T, d, &dpad, s);
+  if (rc) return rc;
+  GemmArgs g;
+  memset(&g, 0, sizeof(g));
+  g.A = c->desc;
+  g.B = c->desc + static_cast<size_t>(n_pairs) * T * dpad;
+  g.M = T; g.N = T; g.K = dpad; g.lda = dpad; g.ldb = dpad; g.batch = n_pairs;
+  g.a_batch_pitch = static_cast<long long>(T) * dpad;
+  g.b_batch_pitch = static_cast<long long>(T) * dpad;
+  g.epilogue = EPI_STORE_F32;
+  g.x_f32 = S; g.ldo = T;
+  return gemm(c, g, s);
+}
+
+int vvs_ibvs(vvs_handle c, const int32_t* uv, const int32_t* uv_star, const uint16_t* depth, int32_t n_pairs, int32_t K,
+             double* twist, double* twist_raw, double* ema_state, int32_t* ema_init, vvs_stream stream) {
+  if (!c || !uv || !uv_star || !depth || !twist) return fail(c, VVS_ERR_INVALID, "vvs_ibvs: null argument");
+  if (n_pairs < 1 || K < 1) return fail(c, VVS_ERR_INVALID, "vvs_ibvs: empty problem");
+  if ((ema_state == nullptr) != (ema_init == nullptr))
+    return fail(c, VVS_ERR_INVALID, "vvs_ibvs: ema_state and ema_init go together");
+  return run_ibvs(c, uv, uv_star, depth, n_pairs, K, twist, twist_raw, ema_state, ema_init,
+                  static_cast<cudaStream_t>(stream));
+}
+
+int vvs_frame_pairs_to_twist(vvs_handle c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth,
+                             int32_t n_pairs, const vvs_pair_out* out, vvs_stream stream) {
+  if (!c || !goal || !cur || !depth) return fail(c, VVS_ERR_INVALID, "vvs_frame_pairs_to_twist: null argument");
+  return pairs_to_twist(c, goal, cur, depth, n_pairs, out, static_cast<cudaStream_t>(stream));
+}
+
+int vvs_frame_pairs_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth,
+                                  int32_t n_pairs, double* twist, int32_t* n_selected, float* mean_sim_sel,
+                                  vvs_stream stream) {
+  if (!c || !goal || !cur || !depth || !twist)
+    return fail(c, VVS_ERR_INVALID, "vvs_frame_pairs_to_twist_host: null argument");
+  if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const size_t img_bytes = static_cast<size_t>(c->cfg.image_size) * c->cfg.image_size * 3;
+  const size_t depth_elems = static_cast<size_t>(c->cfg.frame_width) * c->cfg.frame_height;
+  VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img, goal, n_pairs * img_bytes, cudaMemcpyHostToDevice, s), &c->err);
+  VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img + n_pairs * img_bytes, cur, n_pairs * img_bytes, cudaMemcpyHostToDevice, s),
+              &c->err);
+  VVS_CUDA_OK(cudaMemcpyAsync(c->stage_depth, depth, n_pairs * depth_elems * sizeof(uint16_t), cudaMemcpyHostToDevice, s),
+              &c->err);
+  vvs_pair_out o;
+  memset(&o, 0, sizeof(o));
+  o.twist = c->twist;
+  o.mean_sim_sel = mean_sim_sel ? c->mean_sel : nullptr;
+  int rc = pairs_to_twist(c, c->stage_img, c->stage_img + n_pairs * img_bytes, c->stage_depth, n_pairs, &o, s);
+  if (rc) return rc;
+  VVS_CUDA_OK(cudaMemcpyAsync(twist, c->twist, n_pairs * 6 * sizeof(double), cudaMemcpyDeviceToHost, s), &c->err);
+  if (n_selected)
+    VVS_CUDA_OK(cudaMemcpyAsync(n_selected, c->n_sel, n_pairs * sizeof(int32_t), cudaMemcpyDeviceToHost, s), &c->err);
+  if (mean_sim_sel)
+    VVS_CUDA_OK(cudaMemcpyAsync(mean_sim_sel, c->mean_sel, n_pairs * sizeof(float), cudaMemcpyDeviceToHost, s), &c->err);
+  VVS_CUDA_OK(cudaStreamSynchronize(s), &c->err);
+  return VVS_OK;
+}
+
+int vvs_dbg_gemm(vvs_handle c, const void* A, const void* B, int32_t M, int32_t N, int32_t K, int32_t epilogue,
+                 const float* bias, const float* gamma, float* x_f32, void* out_bf16, int32_t ldo, int32_t q_cols,
+                 float q_scale, const float* pos, int32_t T, vvs_stream stream) {
+  if (!c || !A || !B) return fail(c, VVS_ERR_INVALID, "vvs_dbg_gemm: null argument");
+  GemmArgs g = plain_gemm(static_cast<const bf16*>(A), static_cast<const bf16*>(B), M, N, K, epilogue);
+  g.bias = bias; g.gamma = gamma; g.x_f32 = x_f32; g.out_bf16 = static_cast<bf16*>(out_bf16); g.ldo = ldo;
+  g.q_cols = q_cols; g.q_scale = q_scale; g.pos = pos; g.T = T;
+  return gemm(c, g, static_cast<cudaStream_t>(stream));
+}
+
+int vvs_dbg_attention(vvs_handle c, const void* qkv, void* out, int32_t n_img, int32_t n_tok, int32_t heads,
+                      vvs_stream stream) {
+  if (!c || !qkv || !out) return fail(c, VVS_ERR_INVALID, "vvs_dbg_attention: null argument");
+  return launch_attention(static_cast<const bf16*>(qkv), static_cast<bf16*>(out), n_img, n_tok, heads,
+                          static_cast<cudaStream_t>(stream), &c->err);
+}
+
+int vvs_dbg_layernorm(vvs_handle c, const float* x, const float* w, const float* b, void* out, int32_t rows, int32_t dim,
+                      vvs_stream stream) {
+  if (!c || !x || !w || !b || !out) return fail(c, VVS_ERR_INVALID, "vvs_dbg_layernorm: null argument");
+  return launch_layernorm(x, w, b, static_cast<bf16*>(out), rows, dim, 1e-6f, static_cast<cudaStream_t>(stream), &c->err);
+}
+
+}  // extern "C"

@@ -1,0 +1,288 @@
+// HBM-bound kernels of the dino path (SURVEY §2b k0,k2,k8): pre-processing + im2col for the
+// patch-embed GEMM, LayerNorm, descriptor gather (CLS drop, 3x3 log-binning) and L2 normalisation.
+// Vectorised (128-bit) coalesced access, one warp per row with shuffle reductions; no tensor work.
+#include <string>
+
+#include "vvs_internal.h"
+
+namespace vvs {
+namespace {
+
+constexpr int kPatch = 14;
+constexpr int kPatchK = 3 * kPatch * kPatch;   // 588
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// ToTensor + Normalize (dinov2_extractor.py:186-190, constants :49-50), evaluated in fp32 as torch does:
+// (u8 / 255 - mean) / std with IEEE division.
+__device__ __forceinline__ float normalize_px(uint8_t v, int c) {
+  const float mean[3] = {0.485f, 0.456f, 0.406f};
+  const float stdv[3] = {0.229f, 0.224f, 0.225f};
+  return __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(v), 255.0f), mean[c]), stdv[c]);
+}
+
+// A_pe[img*T + t][k], k = c*196 + ky*14 + kx (Conv2d weight [D,3,14,14] flattened), zero padded to kpad.
+// One thread = 8 consecutive k of one patch row -> one 16-byte store.
+template <bool kU8>
+__global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ out, int n_img, int S, int kpad) {
+  const int gp = S / kPatch;
+  const int T = gp * gp;
+  const int k8_per_row = kpad / 8;
+  const long long total = static_cast<long long>(n_img) * T * k8_per_row;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int k8 = static_cast<int>(idx % k8_per_row);
+    const long long row = idx / k8_per_row;
+    const int t = static_cast<int>(row % T);
+    const int img = static_cast<int>(row / T);
+    const int py = t / gp, px = t - py * gp;
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int k = k8 * 8 + e;
+      if (k < kPatchK) {
+        const int c = k / (kPatch * kPatch);
+        const int rem = k - c * kPatch * kPatch;
+        const int ky = rem / kPatch, kx = rem - ky * kPatch;
+        const int y = py * kPatch + ky, x = px * kPatch + kx;
+        if (kU8) {
+          const uint8_t* img8 = static_cast<const uint8_t*>(img_);
+          v[e] = normalize_px(img8[((static_cast<size_t>(img) * S + y) * S + x) * 3 + c], c);
+        } else {
+          const float* imgf = static_cast<const float*>(img_);
+          v[e] = imgf[((static_cast<size_t>(img) * 3 + c) * S + y) * S + x];
+        }
+      } else {
+        v[e] = 0.f;
+      }
+    }
+    uint4 w = make_uint4(pack2(v[0], v[1]), pack2(v[2], v[3]), pack2(v[4], v[5]), pack2(v[6], v[7]));
+    *reinterpret_cast<uint4*>(out + row * kpad + k8 * 8) = w;
+  }
+}
+
+__global__ void cls_rows_kernel(float* __restrict__ x, const float* __restrict__ cls, const float* __restrict__ pos,
+                                int n_img, int n_tok, int D) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_img * D) return;
+  const int img = idx / D, d = idx - img * D;
+  x[static_cast<size_t>(img) * n_tok * D + d] = cls[d] + pos[d];
+}
+
+// LayerNorm over D (eps 1e-6, affine), fp32 in -> bf16 out. One warp per row, NV float4 per lane.
+template <int NV>
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                 bf16* __restrict__ out, int rows, float eps) {
+  constexpr int D = NV * 128;
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const float4* xr = reinterpret_cast<const float4*>(x + static_cast<size_t>(row) * D);
+  float4 v[NV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    v[i] = xr[i * 32 + lane];
+    s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+  }
+  const float mean = warp_sum(s) * (1.0f / D);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const float a = v[i].x - mean, c = v[i].y - mean, e = v[i].z - mean, f = v[i].w - mean;
+    q += (a * a + c * c) + (e * e + f * f);
+  }
+  const float rstd = rsqrtf(warp_sum(q) * (1.0f / D) + eps);
+  uint2* orow = reinterpret_cast<uint2*>(out + static_cast<size_t>(row) * D);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const float4 g = __ldg(reinterpret_cast<const float4*>(w) + i * 32 + lane);
+    const float4 h = __ldg(reinterpret_cast<const float4*>(b) + i * 32 + lane);
+    const float y0 = (v[i].x - mean) * rstd * g.x + h.x;
+    const float y1 = (v[i].y - mean) * rstd * g.y + h.y;
+    const float y2 = (v[i].z - mean) * rstd * g.z + h.z;
+    const float y3 = (v[i].w - mean) * rstd * g.w + h.w;
+    orow[i * 32 + lane] = make_uint2(pack2(y0, y1), pack2(y2, y3));
+  }
+}
+
+__device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+// x: [n_img, 1+T, D] residual stream.  out: [n_img, T, P*D] fp32, P = 9 (bin) or 1.
+// dinov2_extractor.py:326-336 + :265-311 (hierarchy 1): parts in (dy,dx) row-major order, replicate clamp.
+__global__ void descriptors_f32_kernel(const float* __restrict__ x, float* __restrict__ out, int n_img, int hp, int wp,
+                                       int D, int parts) {
+  const int T = hp * wp;
+  const int d4 = D / 4;
+  const long long total = static_cast<long long>(n_img) * T * parts * d4;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c4 = static_cast<int>(idx % d4);
+    long long r = idx / d4;
+    const int part = static_cast<int>(r % parts);
+    r /= parts;
+    const int t = static_cast<int>(r % T);
+    const int img = static_cast<int>(r / T);
+    int sy = t / wp, sx = t - sy * wp;
+    if (parts == 9) {
+      sy = clampi(sy + part / 3 - 1, 0, hp - 1);
+      sx = clampi(sx + part % 3 - 1, 0, wp - 1);
+    }
+    const float4 v = *reinterpret_cast<const float4*>(x + (static_cast<size_t>(img) * (T + 1) + 1 + sy * wp + sx) * D +
+                                                      c4 * 4);
+    *reinterpret_cast<float4*>(out + ((static_cast<size_t>(img) * T + t) * parts + part) * D + c4 * 4) = v;
+  }
+}
+
+// squared L2 norm of every patch token (CLS skipped): one warp per token.
+__global__ void token_sqnorm_kernel(const float* __restrict__ x, float* __restrict__ n2, int n_img, int T, int D) {
+  const int lane = threadIdx.x & 31;
+  const long long tok = blockIdx.x * static_cast<long long>(blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (tok >= static_cast<long long>(n_img) * T) return;
+  const int img = static_cast<int>(tok / T), t = static_cast<int>(tok % T);
+  const float4* r = reinterpret_cast<const float4*>(x + (static_cast<size_t>(img) * (T + 1) + 1 + t) * D);
+  float s = 0.f;
+  for (int i = lane; i < D / 4; i += 32) {
+    const float4 v = r[i];
+    s += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+  }
+  s = warp_sum(s);
+  if (lane == 0) n2[tok] = s;
+}
+
+// unit-norm bf16 descriptors for the similarity GEMM: ||F_p||^2 = sum over the 9 clamped neighbours of
+// ||f||^2 (log-binning is a gather), so the binned row is written already scaled by 1/||F_p||.
+// One block (128 threads) per (image, token).
+__global__ void __launch_bounds__(128)
+descriptors_unit_bf16_kernel(const float* __restrict__ x, const float* __restrict__ n2, bf16* __restrict__ out, int hp,
+                             int wp, int D, int parts) {
+  const int T = hp * wp;
+  const int t = blockIdx.x % T;
+  const int img = blockIdx.x / T;
+  const int y0 = t / wp, x0 = t - y0 * wp;
+  int src[9];
+  float tot = 0.f;
+#pragma unroll
+  for (int p = 0; p < 9; ++p) {
+    if (p < parts) {
+      int sy = y0, sx = x0;
+      if (parts == 9) {
+        sy = clampi(y0 + p / 3 - 1, 0, hp - 1);
+        sx = clampi(x0 + p % 3 - 1, 0, wp - 1);
+      }
+      src[p] = sy * wp + sx;
+      tot += n2[static_cast<size_t>(img) * T + src[p]];
+    }
+  }
+  const float inv = 1.0f / fmaxf(sqrtf(tot), 1e-8f);   // CosineSimilarity eps (vitvs_v2.py:55)
+  const int d8 = D / 8;
+  bf16* orow = out + (static_cast<size_t>(img) * T + t) * parts * D;
+  for (int i = threadIdx.x; i < parts * d8; i += blockDim.x) {
+    const int p = i / d8, c8 = i - p * d8;
+    const float4* s4 =
+        reinterpret_cast<const float4*>(x + (static_cast<size_t>(img) * (T + 1) + 1 + src[p]) * D + c8 * 8);
+    const float4 a = s4[0], b = s4[1];
+    const uint4 w = make_uint4(pack2(a.x * inv, a.y * inv), pack2(a.z * inv, a.w * inv), pack2(b.x * inv, b.y * inv),
+                               pack2(b.z * inv, b.w * inv));
+    *reinterpret_cast<uint4*>(orow + p * D + c8 * 8) = w;
+  }
+}
+
+// arbitrary fp32 rows -> unit-norm bf16 rows (zero padded to dpad): one block per row.
+__global__ void __launch_bounds__(256)
+normalize_rows_kernel(const float* __restrict__ in, bf16* __restrict__ out, int d, int dpad) {
+  __shared__ float red[8];
+  const float* r = in + static_cast<size_t>(blockIdx.x) * d;
+  float s = 0.f;
+  for (int i = threadIdx.x; i < d; i += blockDim.x) s += r[i] * r[i];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) tot += red[i];
+  const float inv = 1.0f / fmaxf(sqrtf(tot), 1e-8f);
+  bf16* o = out + static_cast<size_t>(blockIdx.x) * dpad;
+  for (int i = threadIdx.x; i < dpad; i += blockDim.x) o[i] = __float2bfloat16_rn(i < d ? r[i] * inv : 0.f);
+}
+
+int grid_for(long long work_items, int block) {
+  long long g = (work_items + block - 1) / block;
+  return static_cast<int>(g < 1 ? 1 : (g > 148 * 32 ? 148 * 32 : g));
+}
+
+}  // namespace
+
+int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err) {
+  const long long items = static_cast<long long>(n_img) * (size / kPatch) * (size / kPatch) * (kpad / 8);
+  im2col_kernel<true><<<grid_for(items, 256), 256, 0, s>>>(img, out, n_img, size, kpad);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_im2col_f32(const float* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err) {
+  const long long items = static_cast<long long>(n_img) * (size / kPatch) * (size / kPatch) * (kpad / 8);
+  im2col_kernel<false><<<grid_for(items, 256), 256, 0, s>>>(img, out, n_img, size, kpad);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int n_tok, int D, cudaStream_t s,
+                    std::string* err) {
+  cls_rows_kernel<<<(n_img * D + 255) / 256, 256, 0, s>>>(x, cls, pos, n_img, n_tok, D);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, int rows, int D, float eps,
+                     cudaStream_t s, std::string* err) {
+  const int grid = (rows + 7) / 8;
+  switch (D) {
+    case 384: layernorm_kernel<3><<<grid, 256, 0, s>>>(x, w, b, out, rows, eps); break;
+    case 768: layernorm_kernel<6><<<grid, 256, 0, s>>>(x, w, b, out, rows, eps); break;
+    case 1024: layernorm_kernel<8><<<grid, 256, 0, s>>>(x, w, b, out, rows, eps); break;
+    case 1536: layernorm_kernel<12><<<grid, 256, 0, s>>>(x, w, b, out, rows, eps); break;
+    default: set_error(err, "layernorm: unsupported width (384/768/1024/1536)"); return VVS_ERR_INVALID;
+  }
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_descriptors_f32(const float* x, float* out, int n_img, int hp, int wp, int D, int bin, cudaStream_t s,
+                           std::string* err) {
+  const int parts = bin ? 9 : 1;
+  const long long items = static_cast<long long>(n_img) * hp * wp * parts * (D / 4);
+  descriptors_f32_kernel<<<grid_for(items, 256), 256, 0, s>>>(x, out, n_img, hp, wp, D, parts);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_descriptors_unit_bf16(const float* x, bf16* out, float* sqnorm_scratch, int n_img, int hp, int wp, int D,
+                                 int bin, cudaStream_t s, std::string* err) {
+  const int T = hp * wp;
+  const long long toks = static_cast<long long>(n_img) * T;
+  token_sqnorm_kernel<<<static_cast<int>((toks + 7) / 8), 256, 0, s>>>(x, sqnorm_scratch, n_img, T, D);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  descriptors_unit_bf16_kernel<<<static_cast<int>(toks), 128, 0, s>>>(x, sqnorm_scratch, out, hp, wp, D, bin ? 9 : 1);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_normalize_rows_bf16(const float* in, bf16* out, int rows, int d, int dpad, cudaStream_t s,
+                               std::string* err) {
+  normalize_rows_kernel<<<rows, 256, 0, s>>>(in, out, d, dpad);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+}  // namespace vvs

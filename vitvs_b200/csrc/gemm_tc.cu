@@ -1,0 +1,455 @@
+// tcgen05 / TMEM / TMA GEMM family for sm_100a (SURVEY §2b k1,k3,k5,k6,k7,k9).
+//
+//   C[b] = A[b] (M x K, K-major bf16) * B[b|0] (N x K, K-major bf16)^T, fp32 accumulation in TMEM,
+//   with the consumer of C fused into the epilogue (bias / GELU / SwiGLU / LayerScale+residual /
+//   patch-embed row remap + pos-embed / similarity arg-max).
+//
+// Structure (one persistent CTA per SM, 192 threads):
+//   warp 0  lane 0 : TMA producer   - 128x64 A box + BNx64 B box per stage, SWIZZLE_128B, mbarrier tx
+//   warp 1  lane 0 : MMA issuer     - 4 x tcgen05.mma (M128, N=BN, K16) per stage, commit -> empty[stage]
+//   warps 2..5     : epilogue       - tcgen05.ld (32 lanes x 32 columns), fused op, global store
+//   TMEM: two accumulators of BN columns (double buffered: epilogue of tile i overlaps MMA of tile i+1)
+// Tiles are ordered N-fastest so the CTAs running at one time share A row-panels and the whole weight
+// matrix through the 126 MB L2.
+#include <cuda.h>
+
+#include <algorithm>
+#include <string>
+
+#include "ptx.cuh"
+#include "vvs_internal.h"
+
+namespace vvs {
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int kGemmThreads = 192;
+
+struct GemmDev {
+  int M, N, K, batch, b_batched;
+  int m_tiles, n_tiles, num_kb;
+  const float* bias;
+  const float* gamma;
+  float* x_f32;
+  bf16* out_bf16;
+  int ldo;
+  int q_cols;
+  float q_scale;
+  const float* pos;
+  int T;
+  unsigned long long* row_best;
+  unsigned long long* col_best;
+  int best_pitch;
+};
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr uint32_t kABytes = BM * BK * 2;
+  static constexpr uint32_t kBBytes = BN * BK * 2;
+  static constexpr uint32_t kStageBytes = kABytes + kBBytes;
+  static constexpr uint32_t kTmemCols = 2 * BN;
+  static constexpr uint32_t kSmemBytes = kStages * kStageBytes + 256 /*barriers*/ + 1024 /*align slack*/;
+};
+
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
+__device__ __forceinline__ float silu(float x) { return x / (1.0f + __expf(-x)); }
+
+// monotone float -> uint32 map (larger float => larger key)
+__device__ __forceinline__ uint32_t ord_f32(float f) {
+  uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+__device__ __forceinline__ void store_bf16x32(bf16* dst, const float (&v)[32]) {
+  uint4* d4 = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    uint4 w;
+    w.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]);
+    w.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
+    w.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]);
+    w.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
+    d4[q] = w;
+  }
+}
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmDev p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* empty = full + C::kStages;
+  uint64_t* tfull = empty + C::kStages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<C::kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int tiles_per_batch = p.m_tiles * p.n_tiles;
+  const int total_tiles = p.batch * tiles_per_batch;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int b = tile / tiles_per_batch;
+        const int r = tile - b * tiles_per_batch;
+        const int m_blk = r / p.n_tiles;
+        const int n_blk = r - m_blk * p.n_tiles;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * C::kStageBytes;
+          mbar_expect_tx(&full[stage], C::kStageBytes);
+          tma_load_3d(sa, &tmA, &full[stage], kb * BK, m_blk * BM, b, kEvictNormal);
+          tma_load_3d(sa + C::kABytes, &tmB, &full[stage], kb * BK, n_blk * BN, p.b_batched ? b : 0, kEvictLast);
+          if (++stage == C::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, false);
+      uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * C::kStageBytes);
+          const uint32_t b_addr = a_addr + C::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            umma_bf16(d_tmem, umma_smem_desc(a_addr + k * 32, 16, 1024), umma_smem_desc(b_addr + k * 32, 16, 1024),
+                      idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty[stage]);
+          if (++stage == C::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tfull[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+    __syncwarp();
+  } else {
+    // ------------------------------------------------------------------ epilogue (4 warps)
+    const int quarter = warp & 3;             // TMEM lane quarter this warp may read
+    const uint32_t lane_field = static_cast<uint32_t>(quarter * 32) << 16;
+    uint32_t acc = 0, acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int b = tile / tiles_per_batch;
+      const int r = tile - b * tiles_per_batch;
+      const int m_blk = r / p.n_tiles;
+      const int n_blk = r - m_blk * p.n_tiles;
+      const int row = m_blk * BM + quarter * 32 + lane;     // row inside batch b
+      const bool row_ok = row < p.M;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_acc = tmem_base + acc * BN + lane_field;
+
+      if constexpr (EPI == EPI_SIM) {
+        // running row best over this tile's columns; ties -> lowest column (strict >, ascending scan)
+        float best_v = -INFINITY;
+        int best_j = 0x7fffffff;
+        const uint32_t row_tag = 0xFFFFFFFFu - static_cast<uint32_t>(row);
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          const int col0 = n_blk * BN + c * 32;
+          if (col0 >= p.N) break;            // warp-uniform
+          uint32_t raw[32];
+          tmem_ld32(t_acc + c * 32, raw);
+          tmem_ld_wait();
+          unsigned long long key[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float v = __uint_as_float(raw[j]);
+            const bool col_ok = (col0 + j) < p.N;
+            if (col_ok && v > best_v) {
+              best_v = v;
+              best_j = col0 + j;
+            }
+            key[j] = (row_ok && col_ok) ? ((static_cast<unsigned long long>(ord_f32(v)) << 32) | row_tag) : 0ull;
+          }
+          // transposed butterfly: afterwards lane L holds max over the warp's 32 rows of column col0+L
+#pragma unroll
+          for (int w = 16; w >= 1; w >>= 1) {
+            const bool upper = (lane & w) != 0;
+#pragma unroll
+            for (int i = 0; i < w; ++i) {
+              const unsigned long long send = upper ? key[i] : key[i + w];
+              const unsigned long long keep = upper ? key[i + w] : key[i];
+              const unsigned long long recv = __shfl_xor_sync(0xffffffffu, send, w);
+              key[i] = keep > recv ? keep : recv;
+            }
+          }
+          if (col0 + lane < p.N && key[0] != 0ull)
+            atomicMax(&p.col_best[static_cast<size_t>(b) * p.best_pitch + col0 + lane], key[0]);
+        }
+        if (row_ok && best_j != 0x7fffffff) {
+          const unsigned long long k =
+              (static_cast<unsigned long long>(ord_f32(best_v)) << 32) | (0xFFFFFFFFu - static_cast<uint32_t>(best_j));
+          atomicMax(&p.row_best[static_cast<size_t>(b) * p.best_pitch + row], k);
+        }
+      } else if constexpr (EPI == EPI_SWIGLU_BF16) {
+        // tile columns [0,BN/2) = x1 slice, [BN/2,BN) = matching x2 slice (rows of w12 interleaved on load)
+        const size_t grow = static_cast<size_t>(b) * p.M + row;
+#pragma unroll 1
+        for (int c = 0; c < BN / 64; ++c) {
+          const int tcol = n_blk * BN + c * 32;                 // column in the interleaved N space
+          if (tcol >= p.N) break;
+          uint32_t r1[32], r2[32];
+          tmem_ld32(t_acc + c * 32, r1);
+          tmem_ld32(t_acc + BN / 2 + c * 32, r2);
+          tmem_ld_wait();
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float x1 = __uint_as_float(r1[j]) + __ldg(p.bias + tcol + j);
+            const float x2 = __uint_as_float(r2[j]) + __ldg(p.bias + tcol + BN / 2 + j);
+            v[j] = silu(x1) * x2;
+          }
+          const int hcol = n_blk * (BN / 2) + c * 32;            // hidden column
+          if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + hcol, v);
+        }
+      } else {
+        const size_t grow = static_cast<size_t>(b) * p.M + row;
+        size_t orow = grow;
+        const float* pos_row = nullptr;
+        if constexpr (EPI == EPI_PATCH_F32) {
+          const int img = row / p.T;
+          const int t = row - img * p.T;
+          orow = static_cast<size_t>(img) * (p.T + 1) + 1 + t;
+          pos_row = p.pos + static_cast<size_t>(1 + t) * p.ldo;
+        }
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          const int col0 = n_blk * BN + c * 32;
+          if (col0 >= p.N) break;            // warp-uniform (N % 32 == 0 enforced by the launcher)
+          uint32_t raw[32];
+          tmem_ld32(t_acc + c * 32, raw);
+          tmem_ld_wait();
+          float v[32];
+          if constexpr (EPI == EPI_STORE_F32) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]) + __ldg(p.bias + col0 + j);
+          }
+          if constexpr (EPI == EPI_BIAS_BF16) {
+            if (col0 < p.q_cols) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] *= p.q_scale;
+            }
+            if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + col0, v);
+          } else if constexpr (EPI == EPI_GELU_BF16) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+            if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + col0, v);
+          } else if constexpr (EPI == EPI_RESID_F32) {
+            if (row_ok) {
+              float4* x4 = reinterpret_cast<float4*>(p.x_f32 + grow * p.ldo + col0);
+              float4 old[8];
+#pragma unroll
+              for (int q = 0; q < 8; ++q) old[q] = x4[q];
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                const float4 g = __ldg(reinterpret_cast<const float4*>(p.gamma + col0) + q);
+                old[q].x = fmaf(g.x, v[q * 4 + 0], old[q].x);
+                old[q].y = fmaf(g.y, v[q * 4 + 1], old[q].y);
+                old[q].z = fmaf(g.z, v[q * 4 + 2], old[q].z);
+                old[q].w = fmaf(g.w, v[q * 4 + 3], old[q].w);
+                x4[q] = old[q];
+              }
+            }
+          } else if constexpr (EPI == EPI_PATCH_F32) {
+            if (row_ok) {
+              float4* x4 = reinterpret_cast<float4*>(p.x_f32 + orow * p.ldo + col0);
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                const float4 ps = __ldg(reinterpret_cast<const float4*>(pos_row + col0) + q);
+                x4[q] = make_float4(v[q * 4 + 0] + ps.x, v[q * 4 + 1] + ps.y, v[q * 4 + 2] + ps.z,
+                                    v[q * 4 + 3] + ps.w);
+              }
+            }
+          } else if constexpr (EPI == EPI_STORE_F32) {
+            if (row_ok) {
+              float* dst = p.x_f32 + grow * p.ldo + col0;
+              if (col0 + 32 <= p.N && (p.ldo & 3) == 0) {
+                float4* x4 = reinterpret_cast<float4*>(dst);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) x4[q] = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (col0 + j < p.N) dst[j] = v[j];
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<C::kTmemCols>(tmem_base);
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn(std::string* err) {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || sym == nullptr) {
+    set_error(err, std::string("cudaGetDriverEntryPoint(cuTensorMapEncodeTiled) failed: ") + cudaGetErrorString(e));
+    return nullptr;
+  }
+  fn = reinterpret_cast<EncodeTiledFn>(sym);
+  return fn;
+}
+
+template <int BN, int EPI>
+int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmDev& d, int grid, cudaStream_t stream,
+               std::string* err) {
+  using C = Cfg<BN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    VVS_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     static_cast<int>(C::kSmemBytes)),
+                err);
+    attr_set = true;
+  }
+  gemm_tc_kernel<BN, EPI><<<grid, kGemmThreads, C::kSmemBytes, stream>>>(tmA, tmB, d);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+template <int BN>
+int dispatch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmDev& d, int grid,
+                 cudaStream_t stream, std::string* err) {
+  switch (epi) {
+    case EPI_BIAS_BF16: return launch_one<BN, EPI_BIAS_BF16>(tmA, tmB, d, grid, stream, err);
+    case EPI_GELU_BF16: return launch_one<BN, EPI_GELU_BF16>(tmA, tmB, d, grid, stream, err);
+    case EPI_RESID_F32: return launch_one<BN, EPI_RESID_F32>(tmA, tmB, d, grid, stream, err);
+    case EPI_PATCH_F32: return launch_one<BN, EPI_PATCH_F32>(tmA, tmB, d, grid, stream, err);
+    case EPI_SWIGLU_BF16: return launch_one<BN, EPI_SWIGLU_BF16>(tmA, tmB, d, grid, stream, err);
+    case EPI_SIM: return launch_one<BN, EPI_SIM>(tmA, tmB, d, grid, stream, err);
+    case EPI_STORE_F32: return launch_one<BN, EPI_STORE_F32>(tmA, tmB, d, grid, stream, err);
+    default: set_error(err, "launch_gemm: unknown epilogue"); return VVS_ERR_INVALID;
+  }
+}
+
+}  // namespace
+
+int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t cols, uint64_t rows, uint64_t batch, uint64_t ld,
+                   uint64_t batch_pitch, uint32_t box_rows, std::string* err) {
+  EncodeTiledFn fn = get_encode_fn(err);
+  if (!fn) return VVS_ERR_CUDA;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld * 2) % 16 || (batch_pitch * 2) % 16) {
+    set_error(err, "make_tmap_bf16: base / pitches must be 16-byte aligned");
+    return VVS_ERR_INVALID;
+  }
+  if (batch <= 1) batch_pitch = rows * ld;   // unused by the hardware, must still be a legal stride
+  cuuint64_t dims[3] = {cols, rows, batch < 1 ? 1 : batch};
+  cuuint64_t strides[2] = {ld * 2, batch_pitch * 2};
+  cuuint32_t box[3] = {64, box_rows, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error(err, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string(static_cast<int>(r)));
+    return VVS_ERR_CUDA;
+  }
+  return VVS_OK;
+}
+
+int gemm_block_n(int N) { return (N % 256 == 0 || N > 1024) ? 256 : 128; }
+
+int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string* err) {
+  if (a.M <= 0 || a.N <= 0 || a.K <= 0 || a.batch <= 0) {
+    set_error(err, "launch_gemm: empty problem");
+    return VVS_ERR_INVALID;
+  }
+  if (a.K % 8 || a.lda % 8 || a.ldb % 8) {
+    set_error(err, "launch_gemm: K, lda, ldb must be multiples of 8 (16-byte TMA rows)");
+    return VVS_ERR_INVALID;
+  }
+  const bool masked_n = (a.epilogue == EPI_SIM || a.epilogue == EPI_STORE_F32);
+  if (!masked_n && (a.N % 32 || a.ldo % 8)) {
+    set_error(err, "launch_gemm: N must be a multiple of 32 and ldo of 8 for this epilogue");
+    return VVS_ERR_INVALID;
+  }
+  const int bn = gemm_block_n(a.N);
+  if (a.epilogue == EPI_SWIGLU_BF16 && a.N % bn) {
+    set_error(err, "launch_gemm: SwiGLU needs N to be a multiple of the N tile");
+    return VVS_ERR_INVALID;
+  }
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap_bf16(&tmA, a.A, a.K, a.M, a.batch, a.lda, a.a_batch_pitch, BM, err);
+  if (rc) return rc;
+  const bool b_batched = a.b_batch_pitch != 0;
+  rc = make_tmap_bf16(&tmB, a.B, a.K, a.N, b_batched ? a.batch : 1, a.ldb, a.b_batch_pitch, bn, err);
+  if (rc) return rc;
+  GemmDev d;
+  d.M = a.M; d.N = a.N; d.K = a.K; d.batch = a.batch; d.b_batched = b_batched ? 1 : 0;
+  d.m_tiles = (a.M + BM - 1) / BM;
+  d.n_tiles = (a.N + bn - 1) / bn;
+  d.num_kb = (a.K + BK - 1) / BK;
+  d.bias = a.bias; d.gamma = a.gamma; d.x_f32 = a.x_f32; d.out_bf16 = a.out_bf16; d.ldo = a.ldo;
+  d.q_cols = a.q_cols; d.q_scale = a.q_scale; d.pos = a.pos; d.T = a.T;
+  d.row_best = a.row_best; d.col_best = a.col_best; d.best_pitch = a.best_pitch;
+  const long long tiles = static_cast<long long>(d.batch) * d.m_tiles * d.n_tiles;
+  const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
+  if (bn == 256) return dispatch_epi<256>(a.epilogue, tmA, tmB, d, grid, stream, err);
+  return dispatch_epi<128>(a.epilogue, tmA, tmB, d, grid, stream, err);
+}
+
+}  // namespace vvs

@@ -1,0 +1,331 @@
+// Latency-bound tail of the dino path:
+//   select_kernel : packed arg-max keys -> nn1 / nn2 / sim1, same-image test, cyclic-distance candidate
+//                   rule (== mutual-NN set), deterministic top-K selection, patch-centre keypoints in
+//                   camera pixels (vitvs_v2.py:80-151, :511-513, :525-553)
+//   ibvs_kernel   : depth lookup, normalised coordinates, interaction rows, 6x6 normal equations in
+//                   fp64, v = -lambda * L^+ e, optional EMA (vitvs_v2.py:566-586, :610-623, :634-659)
+#include <string>
+
+#include "vvs_internal.h"
+
+namespace vvs {
+namespace {
+
+__device__ __forceinline__ float unord_f32(uint32_t k) {
+  const uint32_t u = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+  return __uint_as_float(u);
+}
+__device__ __forceinline__ uint32_t ord_f32(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+template <typename T, typename Op>
+__device__ __forceinline__ T block_reduce(T v, Op op, T* scratch /* >= 32 */) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = op(v, __shfl_xor_sync(0xffffffffu, v, o));
+  __syncthreads();   // scratch reuse across calls
+  if ((threadIdx.x & 31) == 0) scratch[threadIdx.x >> 5] = v;
+  __syncthreads();
+  T r = scratch[0];
+  for (int i = 1; i < (blockDim.x >> 5); ++i) r = op(r, scratch[i]);
+  return r;
+}
+
+// vitvs_v2.py:117-120 as evaluated by torch on CPU: fp32, acc = a*a; acc = fma(b,b,acc); sqrt
+// (bit-exactness against PairwiseDistance is pinned by tests/test_oracle_vs_reference.py).
+__device__ __forceinline__ float cyclic_distance(int dr, int dc) {
+  const float a = __fadd_rn(static_cast<float>(dr), 1e-6f);
+  const float b = __fadd_rn(static_cast<float>(dc), 1e-6f);
+  return __fsqrt_rn(__fmaf_rn(b, b, __fmul_rn(a, a)));
+}
+
+__global__ void __launch_bounds__(256) select_kernel(const SelectArgs a) {
+  __shared__ unsigned long long s_u64[32];
+  __shared__ float s_f32[32];
+  __shared__ double s_f64[32];
+  __shared__ int s_i32[32];
+  const int pair = blockIdx.x;
+  const int T = a.T, w = a.grid_w;
+  const unsigned long long* rb = a.row_best + static_cast<size_t>(pair) * a.best_pitch;
+  const unsigned long long* cb = a.col_best + static_cast<size_t>(pair) * a.best_pitch;
+  int32_t* nn1 = a.nn1 + static_cast<size_t>(pair) * T;
+  int32_t* nn2 = a.nn2 + static_cast<size_t>(pair) * T;
+  float* sim1 = a.sim1 + static_cast<size_t>(pair) * T;
+  uint8_t* cand = a.candidate + static_cast<size_t>(pair) * T;
+
+  // 1. decode packed keys (value in the high word, ~index in the low word)
+  double ssum = 0.0;
+  for (int i = threadIdx.x; i < T; i += blockDim.x) {
+    const unsigned long long kr = rb[i], kc = cb[i];
+    nn1[i] = static_cast<int32_t>(0xFFFFFFFFu - static_cast<uint32_t>(kr));
+    const float s = unord_f32(static_cast<uint32_t>(kr >> 32));
+    sim1[i] = s;
+    ssum += s;
+    nn2[i] = static_cast<int32_t>(0xFFFFFFFFu - static_cast<uint32_t>(kc));
+  }
+  ssum = block_reduce(ssum, [](double x, double y) { return x + y; }, s_f64);
+  const float mean_sim = static_cast<float>(ssum / T);
+  const bool same = mean_sim > a.same_thresh;          // vitvs_v2.py:84
+  __syncthreads();   // nn1/nn2 of every token visible
+
+  // 2. cyclic distances (vitvs_v2.py:105-124): d = -||ij(nn2[nn1[i]]) - ij(i) + 1e-6||
+  float dmin = INFINITY, dmax = -INFINITY;
+  for (int i = threadIdx.x; i < T; i += blockDim.x) {
+    const int c = nn2[nn1[i]];
+    const float d = -cyclic_distance(c / w - i / w, c % w - i % w);
+    dmin = fminf(dmin, d);
+    dmax = fmaxf(dmax, d);
+  }
+  dmin = block_reduce(dmin, [](float x, float y) { return fminf(x, y); }, s_f32);
+  dmax = block_reduce(dmax, [](float x, float y) { return fmaxf(x, y); }, s_f32);
+  const float denom = __fadd_rn(__fsub_rn(dmax, dmin), 1e-8f);   // max(d - min) + 1e-8
+  int ncand = 0;
+  for (int i = threadIdx.x; i < T; i += blockDim.x) {
+    const int c = nn2[nn1[i]];
+    const float d = -cyclic_distance(c / w - i / w, c % w - i % w);
+    const bool ok = __fdiv_rn(__fsub_rn(d, dmin), denom) >= 1.0f;   // distance_threshold = 1 (:72,:130)
+    cand[i] = ok ? 1 : 0;
+    ncand += ok ? 1 : 0;
+  }
+  ncand = block_reduce(ncand, [](int x, int y) { return x + y; }, s_i32);
+  __syncthreads();
+
+  // 3. deterministic selection: K best by sim1 (ties -> lower token) among the candidates
+  //    (same-image branch: among all tokens, identical points, sim = 1; vitvs_v2.py:86-101)
+  const int K = a.K;
+  int32_t* sel_tok = a.sel_tok + static_cast<size_t>(pair) * K;
+  float* sel_sim = a.sel_sim + static_cast<size_t>(pair) * K;
+  int32_t* uvs = a.uv_star + static_cast<size_t>(pair) * K * 2;
+  int32_t* uvc = a.uv + static_cast<size_t>(pair) * K * 2;
+  const int avail = same ? T : ncand;
+  const int nsel = avail < K ? avail : K;
+  unsigned long long prev = ~0ull;
+  for (int k = 0; k < K; ++k) {
+    unsigned long long best = 0ull;
+    if (k < nsel) {
+      for (int i = threadIdx.x; i < T; i += blockDim.x) {
+        if (same || cand[i]) {
+          const unsigned long long key =
+              (static_cast<unsigned long long>(ord_f32(sim1[i])) << 32) | (0xFFFFFFFFu - static_cast<uint32_t>(i));
+          if (key < prev && key > best) best = key;
+        }
+      }
+      best = block_reduce(best, [](unsigned long long x, unsigned long long y) { return x > y ? x : y; }, s_u64);
+      prev = best;
+    }
+    if (threadIdx.x == 0) {
+      if (k < nsel) {
+        const int tok = static_cast<int>(0xFFFFFFFFu - static_cast<uint32_t>(best));
+        sel_tok[k] = tok;
+        sel_sim[k] = same ? 1.0f : sim1[tok];
+      } else {
+        sel_tok[k] = -1;
+        sel_sim[k] = 0.f;
+      }
+    }
+  }
+  __syncthreads();
+
+  // 4. keypoints (vitvs_v2.py:511-513 in fp32 as torch evaluates `long * float + float`, then
+  //    calculate_uv :525-553 in fp64 with round-half-even); < 4 pairs => all-zero arrays (:539-541)
+  if (threadIdx.x < K) {
+    const int k = threadIdx.x;
+    int u_s = 0, v_s = 0, u_c = 0, v_c = 0;
+    if (k < nsel && (nsel == K || nsel >= 4)) {
+      const int t1 = sel_tok[k];
+      const int t2 = same ? t1 : nn1[t1];
+      const double scale_d = static_cast<double>(a.image_size) / static_cast<double>(w);
+      const float scale = static_cast<float>(scale_d), half = static_cast<float>(scale_d / 2);
+      const double sx = static_cast<double>(a.cam.width) / a.image_size;
+      const double sy = static_cast<double>(a.cam.height) / a.image_size;
+      const float r1 = __fadd_rn(__fmul_rn(static_cast<float>(t1 / w), scale), half);
+      const float c1 = __fadd_rn(__fmul_rn(static_cast<float>(t1 % w), scale), half);
+      const float r2 = __fadd_rn(__fmul_rn(static_cast<float>(t2 / w), scale), half);
+      const float c2 = __fadd_rn(__fmul_rn(static_cast<float>(t2 % w), scale), half);
+      u_s = static_cast<int>(rint(static_cast<double>(c1) * sx));   // flip (row,col) -> (u,v)
+      v_s = static_cast<int>(rint(static_cast<double>(r1) * sy));
+      u_c = static_cast<int>(rint(static_cast<double>(c2) * sx));
+      v_c = static_cast<int>(rint(static_cast<double>(r2) * sy));
+    }
+    uvs[2 * k] = u_s;
+    uvs[2 * k + 1] = v_s;
+    uvc[2 * k] = u_c;
+    uvc[2 * k + 1] = v_c;
+  }
+  if (threadIdx.x == 0) {
+    a.mean_sim1[pair] = mean_sim;
+    a.n_candidates[pair] = ncand;
+    a.n_selected[pair] = nsel;
+    a.flags[pair] = same ? 1 : 0;
+  }
+}
+
+__device__ __forceinline__ double warp_sum_f64(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// symmetric 6x6 pseudo-inverse solve by cyclic Jacobi (rank-deficient fall-back for np.linalg.pinv)
+__device__ void pinv_solve6(double A[6][6], const double g[6], double x[6]) {
+  double V[6][6];
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j < 6; ++j) V[i][j] = (i == j) ? 1.0 : 0.0;
+  for (int sweep = 0; sweep < 30; ++sweep) {
+    double off = 0.0;
+    for (int p = 0; p < 6; ++p)
+      for (int q = p + 1; q < 6; ++q) off += A[p][q] * A[p][q];
+    if (off < 1e-300) break;
+    for (int p = 0; p < 6; ++p) {
+      for (int q = p + 1; q < 6; ++q) {
+        if (fabs(A[p][q]) < 1e-300) continue;
+        const double theta = (A[q][q] - A[p][p]) / (2.0 * A[p][q]);
+        const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+        const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
+        for (int k = 0; k < 6; ++k) {
+          const double akp = A[k][p], akq = A[k][q];
+          A[k][p] = c * akp - s * akq;
+          A[k][q] = s * akp + c * akq;
+        }
+        for (int k = 0; k < 6; ++k) {
+          const double apk = A[p][k], aqk = A[q][k];
+          A[p][k] = c * apk - s * aqk;
+          A[q][k] = s * apk + c * aqk;
+        }
+        for (int k = 0; k < 6; ++k) {
+          const double vkp = V[k][p], vkq = V[k][q];
+          V[k][p] = c * vkp - s * vkq;
+          V[k][q] = s * vkp + c * vkq;
+        }
+      }
+    }
+  }
+  double lmax = 0.0;
+  for (int i = 0; i < 6; ++i) lmax = fmax(lmax, A[i][i]);
+  for (int i = 0; i < 6; ++i) x[i] = 0.0;
+  for (int e = 0; e < 6; ++e) {
+    if (A[e][e] <= lmax * 1e-13 || A[e][e] <= 0.0) continue;   // null-space direction (pinv drops it)
+    double proj = 0.0;
+    for (int i = 0; i < 6; ++i) proj += V[i][e] * g[i];
+    proj /= A[e][e];
+    for (int i = 0; i < 6; ++i) x[i] += V[i][e] * proj;
+  }
+}
+
+// one warp per frame pair
+__global__ void __launch_bounds__(128) ibvs_kernel(const IbvsArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int pair = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (pair >= a.n_pairs) return;
+  const int K = a.K;
+  const int32_t* uv = a.uv + static_cast<size_t>(pair) * K * 2;
+  const int32_t* uvs = a.uv_star + static_cast<size_t>(pair) * K * 2;
+  const uint16_t* depth = a.depth + static_cast<size_t>(pair) * a.cam.width * a.cam.height;
+
+  double acc[27];   // 21 upper-triangular entries of L^T L, then 6 of L^T e
+#pragma unroll
+  for (int i = 0; i < 27; ++i) acc[i] = 0.0;
+  for (int k = lane; k < K; k += 32) {
+    const int u = uv[2 * k], v = uv[2 * k + 1];
+    double z = 100.0;                                         // vitvs_v2.py:582-584
+    if (u >= 0 && u < a.cam.width && v >= 0 && v < a.cam.height) {
+      const uint16_t dmm = depth[static_cast<size_t>(v) * a.cam.width + u];
+      if (dmm != 0) z = static_cast<double>(dmm) / 1000.0;
+    }
+    const double x = (u - a.cam.cx) / a.cam.fx, y = (v - a.cam.cy) / a.cam.fy;   // :634-648
+    const double xs = (uvs[2 * k] - a.cam.cx) / a.cam.fx, ys = (uvs[2 * k + 1] - a.cam.cy) / a.cam.fy;
+    const double e1 = x - xs, e2 = y - ys;
+    const double r1[6] = {-1.0 / z, 0.0, x / z, x * y, -(1.0 + x * x), y};        // :650-659
+    const double r2[6] = {0.0, -1.0 / z, y / z, 1.0 + y * y, -x * y, -x};
+    int n = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+      for (int j = i; j < 6; ++j) acc[n++] += r1[i] * r1[j] + r2[i] * r2[j];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) acc[21 + i] += r1[i] * e1 + r2[i] * e2;
+  }
+#pragma unroll
+  for (int i = 0; i < 27; ++i) acc[i] = warp_sum_f64(acc[i]);
+  if (lane != 0) return;
+
+  double A[6][6], g[6], sol[6];
+  {
+    int n = 0;
+    for (int i = 0; i < 6; ++i)
+      for (int j = i; j < 6; ++j) {
+        A[i][j] = acc[n];
+        A[j][i] = acc[n];
+        ++n;
+      }
+    for (int i = 0; i < 6; ++i) g[i] = acc[21 + i];
+  }
+  // Cholesky A = C C^T when safely positive definite (rank 6), else Jacobi pseudo-inverse
+  double C[6][6];
+  bool ok = true;
+  double dmax = 0.0;
+  for (int i = 0; i < 6; ++i) dmax = fmax(dmax, A[i][i]);
+  for (int i = 0; i < 6 && ok; ++i) {
+    for (int j = 0; j <= i; ++j) {
+      double s = A[i][j];
+      for (int k = 0; k < j; ++k) s -= C[i][k] * C[j][k];
+      if (i == j) {
+        if (!(s > dmax * 1e-10)) {
+          ok = false;
+          break;
+        }
+        C[i][i] = sqrt(s);
+      } else {
+        C[i][j] = s / C[j][j];
+      }
+    }
+  }
+  if (ok) {
+    double y[6];
+    for (int i = 0; i < 6; ++i) {
+      double s = g[i];
+      for (int k = 0; k < i; ++k) s -= C[i][k] * y[k];
+      y[i] = s / C[i][i];
+    }
+    for (int i = 5; i >= 0; --i) {
+      double s = y[i];
+      for (int k = i + 1; k < 6; ++k) s -= C[k][i] * sol[k];
+      sol[i] = s / C[i][i];
+    }
+  } else {
+    pinv_solve6(A, g, sol);
+  }
+  double* tw = a.twist + static_cast<size_t>(pair) * 6;
+  for (int i = 0; i < 6; ++i) {
+    double v = -a.lambda * sol[i];                                               // :622
+    if (a.twist_raw) a.twist_raw[static_cast<size_t>(pair) * 6 + i] = v;
+    if (a.ema_state) {                                                           // :329-343
+      double* st = a.ema_state + static_cast<size_t>(pair) * 6 + i;
+      v = a.ema_init[pair] ? a.ema_alpha * v + (1.0 - a.ema_alpha) * (*st) : v;
+      *st = v;
+    }
+    tw[i] = v;
+  }
+  if (a.ema_state) a.ema_init[pair] = 1;
+}
+
+}  // namespace
+
+int launch_select(const SelectArgs& a, cudaStream_t s, std::string* err) {
+  if (a.K > 256 || a.K < 1) {
+    set_error(err, "select: num_pairs must be in [1, 256]");
+    return VVS_ERR_INVALID;
+  }
+  select_kernel<<<a.n_pairs, 256, 0, s>>>(a);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_ibvs(const IbvsArgs& a, cudaStream_t s, std::string* err) {
+  ibvs_kernel<<<(a.n_pairs + 3) / 4, 128, 0, s>>>(a);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+}  // namespace vvs

@@ -1,0 +1,142 @@
+// Internal C++ declarations shared by the vitvs_b200 translation units (not part of the C ABI).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+
+namespace vvs {
+
+typedef __nv_bfloat16 bf16;
+
+// ---- error plumbing: no exceptions cross the C ABI -------------------------------------------
+enum Status : int {
+  VVS_OK = 0,
+  VVS_ERR_INVALID = -1,    // bad argument / unsupported shape
+  VVS_ERR_CUDA = -2,       // a CUDA runtime / driver call failed
+  VVS_ERR_STATE = -3,      // weights missing, workspace too small, ...
+  VVS_ERR_UNSUPPORTED = -4 // device is not sm_100
+};
+void set_error(std::string* slot, const std::string& msg);
+
+#define VVS_CUDA_OK(expr, errslot)                                                                      \
+  do {                                                                                                  \
+    cudaError_t _e = (expr);                                                                            \
+    if (_e != cudaSuccess) {                                                                            \
+      vvs::set_error(errslot, std::string(#expr) + ": " + cudaGetErrorString(_e));                      \
+      return vvs::VVS_ERR_CUDA;                                                                         \
+    }                                                                                                   \
+  } while (0)
+
+// ---- TMA tensor maps ---------------------------------------------------------------------------
+// bf16 tensor [batch, rows, cols] (cols contiguous, row pitch ld elements, batch pitch in elements),
+// box = {64 cols, box_rows, 1}, SWIZZLE_128B, zero fill out of bounds.
+int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t cols, uint64_t rows, uint64_t batch, uint64_t ld,
+                   uint64_t batch_pitch, uint32_t box_rows, std::string* err);
+
+// ---- tcgen05 GEMM family -----------------------------------------------------------------------
+enum Epilogue : int {
+  EPI_BIAS_BF16 = 0,   // out_bf16 = (acc + bias) * (col < q_cols ? q_scale : 1)              (qkv)
+  EPI_GELU_BF16 = 1,   // out_bf16 = gelu_erf(acc + bias)                                      (mlp.fc1)
+  EPI_RESID_F32 = 2,   // x_f32   += gamma * (acc + bias)                                      (attn.proj, mlp.fc2 / w3)
+  EPI_PATCH_F32 = 3,   // x_f32[img*(T+1)+1+t] = acc + bias + pos[1+t]                         (patch embed)
+  EPI_SWIGLU_BF16 = 4, // out_bf16 = silu(acc1 + b1) * (acc2 + b2), weight rows tile-interleaved (mlp.w12)
+  EPI_SIM = 5,         // packed row / column arg-max of the similarity tile, S never stored    (matching)
+  EPI_STORE_F32 = 6    // out_f32 = acc  (plain fp32 store; unit tests / similarity dump)
+};
+
+struct GemmArgs {
+  // C[b] = A[b] (M x K, K-major) * B[b or 0] (N x K, K-major)^T
+  const bf16* A;
+  const bf16* B;
+  int M, N, K;
+  int lda, ldb;
+  int batch;             // independent problems
+  long long a_batch_pitch, b_batch_pitch;   // elements; b_batch_pitch == 0 => B shared by all batches
+  int epilogue;
+  // epilogue operands (unused ones may be null)
+  const float* bias;     // [N]
+  const float* gamma;    // [N]
+  float* x_f32;          // EPI_RESID/PATCH/STORE_F32 destination, pitch ldo
+  bf16* out_bf16;        // bf16 destination, pitch ldo
+  int ldo;
+  int q_cols;
+  float q_scale;
+  const float* pos;      // [T+1, ldo] (EPI_PATCH_F32)
+  int T;                 // patches per image (EPI_PATCH_F32)
+  unsigned long long* row_best;   // [batch, best_pitch] (EPI_SIM)
+  unsigned long long* col_best;   // [batch, best_pitch]
+  int best_pitch;
+};
+int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string* err);
+int gemm_block_n(int N);   // the N tile the launcher picks for this N (128 or 256)
+
+// ---- attention ---------------------------------------------------------------------------------
+// qkv: [n_img * n_tok, 3*D] bf16 (q pre-scaled by hd^-0.5), out: [n_img * n_tok, D] bf16
+int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
+                     std::string* err);
+
+// ---- bandwidth-bound kernels -------------------------------------------------------------------
+int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err);
+int launch_im2col_f32(const float* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err);
+int launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int n_tok, int D, cudaStream_t s,
+                    std::string* err);
+int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, int rows, int D, float eps,
+                     cudaStream_t s, std::string* err);
+// residual stream [n_img, 1+T, D] -> descriptors (CLS dropped, optional 3x3 log-binning)
+int launch_descriptors_f32(const float* x, float* out, int n_img, int hp, int wp, int D, int bin, cudaStream_t s,
+                           std::string* err);
+int launch_descriptors_unit_bf16(const float* x, bf16* out, float* sqnorm_scratch, int n_img, int hp, int wp, int D,
+                                 int bin, cudaStream_t s, std::string* err);
+// arbitrary fp32 rows [rows, d] -> unit-norm bf16 rows [rows, dpad] (zero padded)
+int launch_normalize_rows_bf16(const float* in, bf16* out, int rows, int d, int dpad, cudaStream_t s,
+                               std::string* err);
+
+// ---- matching tail + control law ----------------------------------------------------------------
+struct Camera {
+  int width, height;      // u_max, v_max
+  double fx, fy, cx, cy;
+};
+struct SelectArgs {
+  const unsigned long long* row_best;
+  const unsigned long long* col_best;
+  int best_pitch;
+  int n_pairs, T, grid_w;
+  int K;                  // num_pairs
+  float same_thresh;      // 0.99
+  int image_size;         // S
+  Camera cam;
+  // outputs
+  int32_t* nn1;           // [n_pairs, T]
+  int32_t* nn2;           // [n_pairs, T]
+  float* sim1;            // [n_pairs, T]
+  uint8_t* candidate;     // [n_pairs, T]
+  float* mean_sim1;       // [n_pairs]
+  int32_t* n_candidates;  // [n_pairs]
+  int32_t* n_selected;    // [n_pairs]
+  int32_t* flags;         // [n_pairs] bit0 = same-image branch
+  int32_t* sel_tok;       // [n_pairs, K] chosen goal tokens (-1 padded)
+  float* sel_sim;         // [n_pairs, K]
+  int32_t* uv_star;       // [n_pairs, K, 2]
+  int32_t* uv;            // [n_pairs, K, 2]
+};
+int launch_select(const SelectArgs& a, cudaStream_t s, std::string* err);
+
+struct IbvsArgs {
+  const int32_t* uv;        // [n_pairs, K, 2] current (u,v)
+  const int32_t* uv_star;   // [n_pairs, K, 2] goal
+  const uint16_t* depth;    // [n_pairs, height, width] millimetres
+  int n_pairs, K;
+  Camera cam;
+  double lambda;
+  double ema_alpha;         // used when ema_state != null
+  double* ema_state;        // [n_pairs, 6] or null
+  int32_t* ema_init;        // [n_pairs] 0 = first call copies
+  double* twist;            // [n_pairs, 6] (after EMA when enabled)
+  double* twist_raw;        // [n_pairs, 6] or null (before EMA)
+};
+int launch_ibvs(const IbvsArgs& a, cudaStream_t s, std::string* err);
+
+}  // namespace vvs
