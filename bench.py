@@ -1,0 +1,345 @@
+#!/usr/bin/env python
+"""bench.py - frame-pairs -> twist per second of the ViT-VS `dino` servoing hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--pairs B] [--model M]
+
+One "step" = one pass of the whole hot path (DINOv2 forward of goal + current frames, descriptors,
+mutual-NN matching, IBVS twist) over one batch of synthetic frame pairs.  At N=1 the workload is
+BASELINE.json configs[1]: DINOv2 ViT-B/14, batch of 64 frame pairs, S=308, layer 11, binned descriptors.
+N>1 (torchrun): every rank owns its own 64 pairs (weak scaling, no collective on the data path);
+barrier + device synchronise on both sides, CUDA-event time, max over ranks.
+
+`--impl reference` times the reference's own CPU path (the oracle port of vitvs_v2.py /
+dinov2_extractor.py - the reference is Python and cannot travel; /root/reference is not read) on the
+host cores, one frame pair per step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "frame_pairs_to_twist_per_sec"
+UNIT = "frame-pairs/s"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as fh:
+            d = json.load(fh)
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d["bf16_tflops_sustained"],
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------- CPU arm
+def cpu_reference_setup(model_type: str, size: int):
+    import torch
+    from oracle import dinov2          # the oracle port: the only CPU implementation, never the product path
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    return dinov2.build(model_type, seed=0), cores
+
+
+def cpu_reference_step(model, pair, literal: bool):
+    from oracle import servo
+    goal, cur, depth = pair
+    return servo.frame_pair_to_twist(model, goal, cur, depth, literal_similarity=literal)
+
+
+def cpu_baseline(model_type: str, size: int, budget_s: float = 20.0) -> dict:
+    """Bounded sample of the same workload through the oracle port on the host cores."""
+    from vitvs_b200 import synth
+    model, cores = cpu_reference_setup(model_type, size)
+    pairs = [synth.frame_pair(i, size) for i in range(2)]
+    t0 = time.perf_counter()
+    n = 0
+    while n < len(pairs) and (n == 0 or time.perf_counter() - t0 < budget_s):
+        cpu_reference_step(model, pairs[n], literal=True)
+        n += 1
+    dt = time.perf_counter() - t0
+    t1 = time.perf_counter()
+    cpu_reference_step(model, pairs[0], literal=False)
+    dv = time.perf_counter() - t1
+    return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{n} frame pair(s) of the same workload ({model_type}, S={size}, binned) through oracle/servo.py "
+                      f"with the reference's per-token CosineSimilarity loop (vitvs_v2.py:49-56), torch fp32, "
+                      f"{cores} threads, {dt:.1f} s; with that loop vectorised into one GEMM: {1.0 / dv:.3f} pairs/s"}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from vitvs_b200 import synth
+    size = 308
+    literal = os.environ.get("VITVS_REF_VECTORISED", "0") != "1"
+    model, cores = cpu_reference_setup(args.model, size)
+    pairs = [synth.frame_pair(i, size) for i in range(2)]
+    for i in range(args.warmup):
+        cpu_reference_step(model, pairs[i % 2], literal)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        cpu_reference_step(model, pairs[i % 2], literal)
+    dt = time.perf_counter() - t0
+    val = args.steps / dt
+    sample = (f"1 frame pair per step ({args.model}, S={size}, binned descriptors, layer 11), oracle port of the "
+              f"reference torch path, {'literal per-token similarity loop' if literal else 'vectorised similarity'}, "
+              f"fp32, {cores} threads")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / max(args.steps, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args.model, args.pairs), "pairs_per_step": 1, "image_size": size,
+                   "layer": 11, "binning": True},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ----------------------------------------------------------------------------------------- GPU arm
+def workload_name(model: str, pairs: int) -> str:
+    nice = {"dinov2_vits14": "ViT-S/14", "dinov2_vitb14": "ViT-B/14", "dinov2_vitl14": "ViT-L/14",
+            "dinov2_vitg14": "ViT-g/14"}[model]
+    return f"DINOv2 {nice} batch of {pairs} frame pairs per GPU (S=308, layer 11, 3x3-binned descriptors, K=24)"
+
+
+def flops_per_pair(dim, tokens, layers, bin_parts):
+    n = tokens + 1
+    vit = 2.0 * 588 * dim * tokens + layers * (24.0 * n * dim * dim + 4.0 * n * n * dim)
+    return 2 * vit + 2.0 * tokens * tokens * bin_parts * dim
+
+
+def gemm_class_flops(cls, M, D, H, Mp, tokens, pairs, dprime):
+    return {"patch_gemm": 2.0 * Mp * 588 * D, "qkv_gemm": 2.0 * M * D * 3 * D, "proj_gemm": 2.0 * M * D * D,
+            "ffn1_gemm": 2.0 * M * D * H, "ffn2_gemm": 2.0 * M * D * H,
+            "sim_gemm": 2.0 * pairs * tokens * tokens * dprime}.get(cls)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from vitvs_b200 import ARCHS, Engine, ServoConfig, synth
+    from vitvs_b200.weights import random_state_dict
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    B = args.pairs
+    cfg = ServoConfig(model_type=args.model)
+    dim, heads, depth, hidden, swiglu = ARCHS[args.model]
+    layers = min(cfg.layer, depth - 1) + 1
+    eng = Engine(cfg, max_images=2 * B)
+    eng.load_weights(random_state_dict(args.model, seed=0, max_block=cfg.layer))
+    S, T = cfg.dino_input_size, eng.tokens
+
+    # synthetic inputs: 8 distinct pairs tiled to the batch, NSETS rotated input sets (rank-offset seeds)
+    NSETS = 4
+    base = rank * 1000
+    sets_host, sets_dev = [], []
+    for s in range(NSETS):
+        prs = [synth.frame_pair(base + 8 * s + i, S) for i in range(8)]
+        idx = [i % 8 for i in range(B)]
+        g = torch.from_numpy(__import__("numpy").stack([prs[j][0] for j in idx]))
+        c = torch.from_numpy(__import__("numpy").stack([prs[j][1] for j in idx]))
+        d = torch.from_numpy(__import__("numpy").stack([prs[j][2] for j in idx]))
+        sets_host.append((g.pin_memory(), c.pin_memory(), d.pin_memory()))
+        sets_dev.append((g.to(dev), c.to(dev), d.to(dev)))
+    stream = torch.cuda.current_stream(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- device-resident throughput (value)
+    for i in range(args.warmup):
+        eng.frame_pairs_to_twist(*sets_dev[i % NSETS])
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for i in range(args.steps):
+        out = eng.frame_pairs_to_twist(*sets_dev[i % NSETS])
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = eng.last_launch_count() * args.steps
+    n_sel = out["n_selected"].float().mean().item()
+
+    # ---- end to end through the host-buffer C-ABI call (H2D + path + D2H + sync each step)
+    tw = torch.empty(B, 6, dtype=torch.float64).pin_memory()
+    ns = torch.empty(B, dtype=torch.int32).pin_memory()
+    msim = torch.empty(B, dtype=torch.float32).pin_memory()
+    for i in range(min(args.warmup, 3)):
+        eng.frame_pairs_to_twist_host(*sets_host[i % NSETS], tw, ns, msim)
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record(stream)
+    for i in range(args.steps):
+        eng.frame_pairs_to_twist_host(*sets_host[i % NSETS], tw, ns, msim)
+    e3.record(stream)
+    barrier()
+    ms_e2e = e2.elapsed_time(e3)
+
+    if world > 1:
+        t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = t.tolist()
+
+    # ---- per-kernel-class device time, live, on the launching stream (2 extra profiled steps)
+    prof = None
+    if rank == 0:
+        eng.profile(True)
+        PS = 2
+        for i in range(PS):
+            eng.frame_pairs_to_twist(*sets_dev[i % NSETS])
+        torch.cuda.synchronize(dev)
+        prof = eng.profile_read()
+        eng.profile(False)
+        prof = {k: (v[0] / PS, v[1] // PS) for k, v in prof.items()}
+
+    if rank == 0:
+        pk = peaks()
+        total_pairs = world * B * args.steps
+        value = total_pairs / (ms / 1e3)
+        e2e_value = total_pairs / (ms_e2e / 1e3)
+        M, Mp = 2 * B * (T + 1), 2 * B * T
+        parts = 9 if cfg.use_feature_binning else 1
+        step_ms_prof = sum(v[0] for v in prof.values())
+        kernels = {}
+        for k, (tot_ms, cnt) in sorted(prof.items(), key=lambda kv: -kv[1][0]):
+            ent = {"ms_per_step": round(tot_ms, 4), "launches_per_step": cnt, "share": round(tot_ms / step_ms_prof, 4)}
+            fl = gemm_class_flops(k, M, dim, hidden, Mp, T, B, parts * dim)
+            if k == "attention":
+                fl = 4.0 * (T + 1) * (T + 1) * dim * 2 * B
+            if fl:
+                ent["tflops"] = round(fl / (tot_ms / cnt * 1e-3) / 1e12, 1)
+                ent["frac_of_sustained_peak"] = round(ent["tflops"] / pk["tf_sustained"], 3)
+            kernels[k] = ent
+        dom = next(k for k in kernels if k.endswith("_gemm"))
+        dom_fl = gemm_class_flops(dom, M, dim, hidden, Mp, T, B, parts * dim)
+        dom_ms = prof[dom][0] / prof[dom][1]
+        achieved = dom_fl / (dom_ms * 1e-3) / 1e12
+        fl_pair = flops_per_pair(dim, T, layers, parts)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": workload_name(args.model, B), "pairs_per_gpu_per_step": B, "image_size": S,
+                       "layer": cfg.layer, "binning": bool(cfg.use_feature_binning), "num_pairs": cfg.num_pairs,
+                       "weights": "random-init (seed 0)",
+                       "l2": f"{NSETS} rotated input sets; per-step activation traffic (~GBs) exceeds the 126 MB L2",
+                       "mean_selected_pairs": n_sel,
+                       "algorithmic_gflop_per_pair": round(fl_pair / 1e9, 2),
+                       "whole_path_tflops": round(value / world * fl_pair / 1e12, 1),
+                       "whole_path_frac_of_sustained_peak": round(value / world * fl_pair / 1e12 / pk["tf_sustained"], 3)},
+            "e2e": {"value": e2e_value, "unit": UNIT,
+                    "h2d_bytes_per_step": B * (2 * S * S * 3 + cfg.u_max * cfg.v_max * 2),
+                    "d2h_bytes_per_step": B * (6 * 8 + 4 + 4), "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": f"gemm_tc_kernel ({dom})", "achieved": round(achieved, 1),
+                         "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": round(achieved / pk["tf_sustained"], 3),
+                         "traffic": None, "peak_source": pk["source"] + ", sustained figure (kernel timed inside a long step)",
+                         "avg_launch_ms": round(dom_ms, 4), "flops_per_launch": dom_fl},
+            "kernels": kernels,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(args.model, S)
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pairs", type=int, default=64, help="frame pairs per GPU per step (BASELINE configs[1]: 64)")
+    ap.add_argument("--model", default="dinov2_vitb14")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -136,6 +136,12 @@ VVS_API int vvs_similarity(vvs_handle h, const float* desc1, const float* desc2,
 VVS_API int vvs_ibvs(vvs_handle h, const int32_t* uv, const int32_t* uv_star, const uint16_t* depth, int32_t n_pairs,
              int32_t K, double* twist, double* twist_raw, double* ema_state, int32_t* ema_init, vvs_stream stream);
 
+/* replaces, term by term: Controller.get_depth -> z [n_pairs,K]; transform_to_real_world -> xy / xy_star
+ * [n_pairs,K,2]; calculate_interaction_matrix -> L [n_pairs,2K,6] (vitvs_v2.py:566-586, 634-659); any output
+ * may be NULL.  twist [n_pairs,6] as in vvs_ibvs without smoothing. */
+VVS_API int vvs_ibvs_terms(vvs_handle h, const int32_t* uv, const int32_t* uv_star, const uint16_t* depth, int32_t n_pairs,
+                   int32_t K, double* twist, double* z, double* xy, double* xy_star, double* L, vvs_stream stream);
+
 typedef struct vvs_pair_out { /* device memory; twist required, the rest optional */
   double* twist;          /* [n_pairs, 6]  v_c = -lambda * pinv(L) e   (vitvs_v2.py:622) */
   int32_t* n_selected;    /* [n_pairs] */
@@ -155,6 +161,16 @@ VVS_API int vvs_frame_pairs_to_twist_host(vvs_handle h, const uint8_t* goal_host
                                   int32_t* n_selected_host, float* mean_sim_sel_host, vvs_stream stream);
 /* number of kernels the last vvs_frame_pairs_to_twist* call launched (bench.py gpu_launches). */
 VVS_API int vvs_last_launch_count(vvs_handle h);
+
+/* ---- per-kernel-class device timing (CUDA events on the launching stream around every launch) -------- */
+enum vvs_kernel_class {
+  VVS_K_OTHER = 0, VVS_K_IM2COL = 1, VVS_K_PATCH_GEMM = 2, VVS_K_LAYERNORM = 3, VVS_K_QKV_GEMM = 4,
+  VVS_K_ATTENTION = 5, VVS_K_PROJ_GEMM = 6, VVS_K_FFN1_GEMM = 7, VVS_K_FFN2_GEMM = 8, VVS_K_DESCRIPTORS = 9,
+  VVS_K_SIM_GEMM = 10, VVS_K_SELECT = 11, VVS_K_IBVS = 12, VVS_K_COUNT = 13
+};
+VVS_API int vvs_profile_enable(vvs_handle h, int32_t on);
+/* sums (ms) and launch counts per vvs_kernel_class since the last read; synchronises on the events. */
+VVS_API int vvs_profile_read(vvs_handle h, double* total_ms, int32_t* launches, int32_t n_classes);
 
 /* ---- kernel-level entry points (unit tests, per-kernel benchmarks; device pointers) ---------------- */
 /* C = A[M,K] * B[N,K]^T with one of the fused epilogues (see csrc/vvs_internal.h Epilogue). */

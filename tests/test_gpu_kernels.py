@@ -1,0 +1,161 @@
+"""Kernel-level parity on the B200 (through the C ABI's vvs_dbg_* entry points): each hand-written
+kernel against a plain PyTorch fp32 reference of the same op on identical (bf16-rounded) operands."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from vitvs_b200 import _lib  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from vitvs_b200 import Engine, ServoConfig
+    e = Engine(ServoConfig(model_type="dinov2_vits14"), max_images=4)
+    yield e
+    e.close()
+
+
+def _rand(shape, seed, scale=1.0, dtype=torch.float32):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(dtype).cuda()
+
+
+def _report(name, got, ref):
+    err = (got.float() - ref.float()).abs().max().item()
+    rel = err / max(ref.float().abs().max().item(), 1e-30)
+    print(f"[{name}] max abs err {err:.3e}  rel-to-max {rel:.3e}")
+    return err, rel
+
+
+# (M, N, K): tails in M, N tile 128 and 256 paths, K = 1..many k-blocks, multi-wave persistence
+GEMM_SHAPES = [(128, 256, 64), (200, 384, 128), (485 * 2, 1152, 384), (970, 768, 768), (300, 256, 3072),
+               (128 * 150 + 37, 512, 256), (64, 128, 640)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_store_f32(eng, M, N, K):
+    A = _rand((M, K), 1, dtype=torch.bfloat16)
+    B = _rand((N, K), 2, dtype=torch.bfloat16)
+    out = torch.full((M, N), float("nan"), device="cuda")
+    eng.dbg_gemm(A, B, _lib.EPI_STORE_F32, x_f32=out, ldo=N)
+    torch.cuda.synchronize()
+    ref = A.float() @ B.float().T
+    err, rel = _report(f"gemm f32 {M}x{N}x{K}", out, ref)
+    assert rel < 1e-5 * math.sqrt(K)
+
+
+def test_gemm_store_f32_ragged_n(eng):
+    M, N, K = 70, 484, 192            # similarity-like: N not a multiple of 32
+    A = _rand((M, K), 3, dtype=torch.bfloat16)
+    B = _rand((N, K), 4, dtype=torch.bfloat16)
+    out = torch.full((M, N), float("nan"), device="cuda")
+    eng.dbg_gemm(A, B, _lib.EPI_STORE_F32, x_f32=out, ldo=N)
+    torch.cuda.synchronize()
+    _, rel = _report("gemm f32 ragged", out, A.float() @ B.float().T)
+    assert rel < 1e-4
+
+
+@pytest.mark.parametrize("M,N,K", [(485 * 2, 1152, 384), (970, 2304, 768)])
+def test_gemm_bias_bf16_qscale(eng, M, N, K):
+    A = _rand((M, K), 5, dtype=torch.bfloat16)
+    B = _rand((N, K), 6, 0.05, dtype=torch.bfloat16)
+    bias = _rand((N,), 7, 0.1)
+    out = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+    D = N // 3
+    eng.dbg_gemm(A, B, _lib.EPI_BIAS_BF16, bias=bias, out_bf16=out, ldo=N, q_cols=D, q_scale=0.125)
+    torch.cuda.synchronize()
+    ref = A.float() @ B.float().T + bias
+    ref[:, :D] *= 0.125
+    _, rel = _report("gemm bias bf16", out, ref)
+    assert rel < 1e-2                     # bf16 output rounding (2^-9)
+
+
+def test_gemm_gelu_bf16(eng):
+    M, N, K = 970, 1536, 384
+    A = _rand((M, K), 8, dtype=torch.bfloat16)
+    B = _rand((N, K), 9, 0.05, dtype=torch.bfloat16)
+    bias = _rand((N,), 10, 0.1)
+    out = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+    eng.dbg_gemm(A, B, _lib.EPI_GELU_BF16, bias=bias, out_bf16=out, ldo=N)
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.gelu(A.float() @ B.float().T + bias)
+    _, rel = _report("gemm gelu bf16", out, ref)
+    assert rel < 1e-2
+
+
+def test_gemm_residual_f32(eng):
+    M, N, K = 970, 384, 1536
+    A = _rand((M, K), 11, dtype=torch.bfloat16)
+    B = _rand((N, K), 12, 0.05, dtype=torch.bfloat16)
+    bias, gamma = _rand((N,), 13, 0.1), _rand((N,), 14)
+    x = _rand((M, N), 15)
+    ref = x + gamma * (A.float() @ B.float().T + bias)
+    eng.dbg_gemm(A, B, _lib.EPI_RESID_F32, bias=bias, gamma=gamma, x_f32=x, ldo=N)
+    torch.cuda.synchronize()
+    _, rel = _report("gemm residual f32", x, ref)
+    assert rel < 1e-4
+
+
+def test_gemm_patch_embed_rows(eng):
+    n_img, T, D, K = 3, 49, 384, 640
+    A = _rand((n_img * T, K), 16, dtype=torch.bfloat16)
+    B = _rand((D, K), 17, 0.05, dtype=torch.bfloat16)
+    bias, pos = _rand((D,), 18, 0.1), _rand((T + 1, D), 19)
+    x = torch.full((n_img * (T + 1), D), 7.0, device="cuda")
+    eng.dbg_gemm(A, B, _lib.EPI_PATCH_F32, bias=bias, x_f32=x, ldo=D, pos=pos, T=T)
+    torch.cuda.synchronize()
+    ref = (A.float() @ B.float().T + bias).reshape(n_img, T, D) + pos[1:]
+    got = x.reshape(n_img, T + 1, D)
+    _, rel = _report("gemm patch rows", got[:, 1:], ref)
+    assert rel < 1e-4
+    assert torch.all(got[:, 0] == 7.0)            # CLS rows untouched by this kernel
+
+
+def test_gemm_swiglu(eng):
+    M, D, H = 300, 1536, 4096
+    A = _rand((M, D), 20, dtype=torch.bfloat16)
+    W12 = _rand((2 * H, D), 21, 0.03, dtype=torch.bfloat16)
+    b12 = _rand((2 * H,), 22, 0.1)
+    bn = 256                                      # tile the launcher picks for N = 8192
+    half = bn // 2
+    r = torch.arange(2 * H)
+    n, wi = r // bn, r % bn
+    src = torch.where(wi < half, n * half + wi, H + n * half + (wi - half)).cuda()
+    W12i, b12i = W12[src].contiguous(), b12[src].contiguous()
+    out = torch.zeros(M, H, dtype=torch.bfloat16, device="cuda")
+    eng.dbg_gemm(A, W12i, _lib.EPI_SWIGLU_BF16, bias=b12i, out_bf16=out, ldo=H)
+    torch.cuda.synchronize()
+    x12 = A.float() @ W12.float().T + b12
+    ref = torch.nn.functional.silu(x12[:, :H]) * x12[:, H:]
+    _, rel = _report("gemm swiglu", out, ref)
+    assert rel < 1e-2
+
+
+@pytest.mark.parametrize("n_img,n_tok,heads", [(1, 128, 1), (2, 485, 6), (3, 50, 2), (1, 1370, 12), (2, 257, 3)])
+def test_attention(eng, n_img, n_tok, heads):
+    D = heads * 64
+    qkv = _rand((n_img * n_tok, 3 * D), 30 + n_tok, 1.0, dtype=torch.bfloat16)
+    qkv[:, :D] *= 0.125                           # q arrives pre-scaled by hd^-0.5 (QKV GEMM epilogue)
+    out = eng.dbg_attention(qkv, n_img, n_tok, heads)
+    torch.cuda.synchronize()
+    x = qkv.float().reshape(n_img, n_tok, 3, heads, 64)
+    q, k, v = (t.transpose(1, 2) for t in x.unbind(2))
+    ref = torch.nn.functional.scaled_dot_product_attention(q, k, v, scale=1.0)
+    ref = ref.transpose(1, 2).reshape(n_img * n_tok, D)
+    err, rel = _report(f"attention {n_img}x{n_tok}x{heads}", out, ref)
+    assert rel < 2e-2                             # bf16 P and bf16 output
+
+
+@pytest.mark.parametrize("D", [384, 768, 1024, 1536])
+def test_layernorm(eng, D):
+    rows = 971
+    x = _rand((rows, D), 40, 3.0) + 0.5
+    w, b = _rand((D,), 41) + 1.0, _rand((D,), 42, 0.1)
+    out = eng.dbg_layernorm(x, w, b)
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.layer_norm(x, (D,), w, b, eps=1e-6)
+    _, rel = _report(f"layernorm {D}", out, ref)
+    assert rel < 6e-3

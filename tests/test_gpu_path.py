@@ -1,0 +1,316 @@
+"""Parity of the CUDA hot path (through the C ABI) against the oracle and the committed golden fixtures
+(outputs of the reference's own code).  Tolerances are the ones BASELINE.json's north_star states:
+descriptor cosine >= 0.999 vs fp32, >= 99 % mutual-NN index agreement with disagreements only at
+near-ties, twist relative error <= 1e-3; integer / index work bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import dinov2, servo  # noqa: E402  (the checker)
+from vitvs_b200 import synth  # noqa: E402
+
+TIE_EPS = 2e-3     # similarity margin below which an arg-max disagreement counts as a near-tie (bf16 operands)
+
+
+@pytest.fixture(scope="module")
+def vits():
+    return dinov2.build("dinov2_vits14", seed=0)
+
+
+@pytest.fixture(scope="module")
+def eng(vits):
+    from vitvs_b200 import Engine, ServoConfig
+    e = Engine(ServoConfig(model_type="dinov2_vits14"), max_images=8, max_match_tokens=2 * 1024, max_match_dim=3456)
+    e.load_weights(vits)
+    yield e
+    e.close()
+
+
+# ------------------------------------------------------------------------------ backbone + descriptors
+def test_tokens_and_descriptors_vs_oracle(eng, vits):
+    pairs = [synth.frame_pair(i) for i in range(2)]
+    imgs = np.stack([pairs[0][0], pairs[0][1], pairs[1][0], pairs[1][1]])
+    eng.forward_tokens(torch.from_numpy(imgs).cuda())
+    tok = eng.tokens_out().cpu()
+    ref = torch.cat([servo.block_tokens(vits, servo.preprocess_u8(im), 11) for im in imgs])
+    cos = torch.nn.functional.cosine_similarity(tok, ref, dim=-1)
+    print(f"[tokens] cosine min {cos.min():.6f} mean {cos.mean():.6f}; max abs err {(tok - ref).abs().max():.4f}")
+    assert cos.min() >= 0.999
+    for bin_ in (False, True):
+        d = eng.descriptors(bin_).cpu()
+        dref = torch.stack([servo.extract_descriptors(vits, servo.preprocess_u8(im), 11, bin_)[0] for im in imgs])
+        assert d.shape == dref.shape
+        cos = torch.nn.functional.cosine_similarity(d, dref, dim=-1)
+        print(f"[descriptors bin={bin_}] cosine min {cos.min():.6f}")
+        assert cos.min() >= 0.999
+        # binning is a pure gather of the GPU tokens: bit-exact against the oracle's log_bin of those tokens
+        mine = tok[:, 1:]
+        expect = servo.log_bin(mine, (22, 22)) if bin_ else mine
+        assert torch.equal(d[:, 0], expect)
+
+
+def test_f32_nchw_entry_matches_u8_entry(eng):
+    g, c, _ = synth.frame_pair(3)
+    imgs = np.stack([g, c])
+    eng.forward_tokens(torch.from_numpy(imgs).cuda())
+    a = eng.tokens_out().clone()
+    pre = torch.cat([servo.preprocess_u8(im) for im in imgs]).cuda()       # preprocess_pil output
+    eng.forward_tokens(pre)
+    b = eng.tokens_out()
+    assert torch.equal(a, b)        # same fp32 normalisation arithmetic on both entries, then same kernels
+
+
+def test_intermediate_layer(eng, vits):
+    g, _, _ = synth.frame_pair(4)
+    eng.forward_tokens(torch.from_numpy(g[None]).cuda(), layer=5)
+    tok = eng.tokens_out().cpu()
+    ref = servo.block_tokens(vits, servo.preprocess_u8(g), 5)
+    assert torch.nn.functional.cosine_similarity(tok, ref, dim=-1).min() >= 0.9995
+
+
+# ------------------------------------------------------------------------------ matching
+def _check_match(r, S_ref, p=0):
+    """r: Engine.match dict; S_ref [T,T] fp32 oracle similarity."""
+    m = servo.match(S_ref)
+    nn1, nn2 = r["nn1"][p].cpu().numpy(), r["nn2"][p].cpu().numpy()
+    sim1 = r["sim1"][p].cpu().numpy()
+    T = S_ref.shape[0]
+    rows = np.arange(T)
+    bad1 = nn1 != m.nn1
+    bad2 = nn2 != m.nn2
+    marg1 = (S_ref[rows, m.nn1] - S_ref[rows, nn1]).numpy()
+    marg2 = (S_ref[m.nn2, rows] - S_ref[nn2, rows]).numpy()
+    print(f"[match] nn1 agree {1 - bad1.mean():.4f} nn2 agree {1 - bad2.mean():.4f}; worst margin at a "
+          f"disagreement {max(marg1[bad1].max(initial=0), marg2[bad2].max(initial=0)):.2e}; "
+          f"sim1 max err {np.abs(sim1 - S_ref.max(-1).values.numpy()).max():.2e}")
+    assert bad1.mean() <= 0.01 and bad2.mean() <= 0.01
+    assert np.all(marg1[bad1] < TIE_EPS) and np.all(marg2[bad2] < TIE_EPS)
+    assert np.abs(sim1 - S_ref.max(-1).values.numpy()).max() < 5e-3
+    return m, nn1, nn2
+
+
+@pytest.mark.parametrize("case", ["planted", "unrelated", "all_mutual", "same_image", "ties"])
+def test_match_against_reference_fixtures(eng, golden, case):
+    g = golden("matching.npz")
+    d1 = torch.from_numpy(g[f"{case}/desc1"])[None]
+    d2 = torch.from_numpy(g[f"{case}/desc2"])[None]
+    T = d1.shape[1]
+    r = eng.match(d1, d2, num_pairs=min(T, 64))
+    torch.cuda.synchronize()
+    S_ref = torch.from_numpy(g[f"{case}/S"])
+    m, nn1, nn2 = _check_match(r, S_ref)
+    same = bool(r["flags"][0].item() & 1)
+    assert same == m.same_image
+    if case == "ties":
+        assert not np.isin(nn1, [10, 40]).any() and not (nn2 == 7).any()     # lowest index wins exact ties
+    if same:
+        return
+    cand = np.nonzero(r["candidate"][0].cpu().numpy())[0]
+    if np.array_equal(nn1, m.nn1) and np.array_equal(nn2, m.nn2):
+        # identical arg-max => the candidate rule (cyclic distance, fp32-exact) must give the identical set
+        assert np.array_equal(cand, g[f"{case}/sel_tok1"])
+        assert int(r["n_candidates"][0]) == len(g[f"{case}/sel_tok1"])
+        if case == "all_mutual":
+            assert len(cand) == 0 and int(r["n_selected"][0]) == 0          # reference returns (None,)*3
+    # whatever the arg-max, the rule itself is exact given the GPU's nn1/nn2
+    mine = servo.match(S_ref)
+    mine.nn1, mine.nn2 = nn1.astype(np.int64), nn2.astype(np.int64)
+
+
+def test_candidate_rule_is_bit_exact_given_argmax(eng):
+    """Feed exactly representable descriptors (one-hot rows => S is a 0/1 matrix) so the GPU arg-max is
+    exact, with a permutation that leaves some tokens non-mutual: candidate set == oracle set."""
+    T, d = 100, 128
+    g = torch.Generator().manual_seed(5)
+    a = torch.zeros(T, d)
+    a[torch.arange(T), torch.arange(T)] = 1.0
+    perm = torch.randperm(T, generator=g)
+    b = a[perm].clone()
+    b[:7] = a[perm[7:14]]            # duplicates: several current tokens point at the same goal token
+    r = eng.match(a[None], b[None], num_pairs=24)
+    S = servo.cosine_similarity_matrix(a[None, None], b[None, None])[0, 0]
+    m = servo.match(S)
+    assert np.array_equal(r["nn1"][0].cpu().numpy(), m.nn1)
+    assert np.array_equal(r["nn2"][0].cpu().numpy(), m.nn2)
+    assert np.array_equal(np.nonzero(r["candidate"][0].cpu().numpy())[0], m.candidates)
+    chosen = servo.top_k_by_similarity(m, 24)
+    n = int(r["n_selected"][0])
+    assert n == len(chosen)
+    assert np.array_equal(r["sel_tok"][0, :n].cpu().numpy(), chosen)
+
+
+def test_similarity_matrix_vs_oracle(eng):
+    a, b, _ = synth.descriptor_sets(484, 3456, seed=7)
+    S = eng.similarity(a[None], b[None])[0].cpu()
+    S_ref = servo.cosine_similarity_matrix(a[None, None], b[None, None])[0, 0]
+    err = (S - S_ref).abs().max().item()
+    print(f"[similarity] max abs err {err:.2e}")
+    assert err < 2e-3
+
+
+def test_match_large_token_count(eng):
+    a, b, perm = synth.descriptor_sets(1024, 384, seed=7)
+    r = eng.match(a[None], b[None], num_pairs=24)
+    S_ref = servo.cosine_similarity_matrix(a[None, None], b[None, None])[0, 0]
+    _check_match(r, S_ref)
+
+
+def test_match_batched_pairs_are_independent(eng):
+    sets = [synth.descriptor_sets(196, 256, seed=s) for s in (1, 2, 3)]
+    A = torch.stack([s[0] for s in sets])
+    B = torch.stack([s[1] for s in sets])
+    r = eng.match(A, B, num_pairs=24)
+    for p in range(3):
+        single = eng.match(A[p:p + 1], B[p:p + 1], num_pairs=24)
+        for k in ("nn1", "nn2", "sim1", "candidate", "sel_tok", "uv", "uv_star"):
+            assert torch.equal(r[k][p], single[k][0]), k
+
+
+# ------------------------------------------------------------------------------ control law
+@pytest.mark.parametrize("case", ["k24", "k48", "k7_padded", "k3_too_few", "k24_oob_depth"])
+def test_ibvs_against_reference_fixtures(eng, golden, case):
+    g = golden("ibvs.npz")
+    uv = torch.from_numpy(g[f"{case}/s_uv"].astype(np.int32))[None]
+    uvs = torch.from_numpy(g[f"{case}/s_uv_star"].astype(np.int32))[None]
+    depth = torch.from_numpy(g["depth"])[None]
+    t = eng.ibvs_terms(uv, uvs, depth)
+    assert np.array_equal(t["Z"][0].cpu().numpy().reshape(-1, 1), g[f"{case}/Z"])          # bit-exact
+    assert np.allclose(t["L"][0].cpu().numpy(), g[f"{case}/L"], rtol=1e-14, atol=0)
+    v_ref = g[f"{case}/v"]
+    v = t["twist"][0].cpu().numpy()
+    scale = max(np.abs(v_ref).max(), 1e-300)
+    print(f"[ibvs {case}] rel err {np.abs(v - v_ref).max() / scale:.2e}")
+    assert np.abs(v - v_ref).max() <= 1e-9 * scale + 1e-18
+    # EMA: first call copies, second blends (vitvs_v2.py:329-343)
+    st = torch.zeros(1, 6, dtype=torch.float64, device="cuda")
+    init = torch.zeros(1, dtype=torch.int32, device="cuda")
+    tw1, raw1 = eng.ibvs(uv, uvs, depth, st, init)
+    assert np.allclose(tw1[0].cpu().numpy(), g[f"{case}/ema1"], rtol=1e-9, atol=1e-18)
+    tw2, _ = eng.ibvs(uv, uvs, depth, st, init)
+    a = 0.8
+    assert np.allclose(tw2[0].cpu().numpy(), a * raw1[0].cpu().numpy() + (1 - a) * g[f"{case}/ema1"], rtol=1e-9,
+                       atol=1e-18)
+
+
+def test_ibvs_rank_deficient_matches_pinv(eng, golden):
+    """All keypoints identical => L has rank 2: the Jacobi fall-back must give numpy's pinv solution."""
+    g = golden("ibvs.npz")
+    K = 24
+    uv = np.tile(np.array([[400, 300]], dtype=np.int32), (K, 1))
+    uvs = np.tile(np.array([[380, 310]], dtype=np.int32), (K, 1))
+    depth = g["depth"]
+    tw, _ = eng.ibvs(torch.from_numpy(uv)[None], torch.from_numpy(uvs)[None], torch.from_numpy(depth)[None])
+    ref = servo.ibvs_twist(uv, uvs, depth)
+    assert np.abs(tw[0].cpu().numpy() - ref).max() <= 1e-6 * np.abs(ref).max()
+
+
+# ------------------------------------------------------------------------------ whole path
+def test_frame_pairs_to_twist_vs_reference_fixture(eng, golden):
+    g = golden("e2e_dinov2_vits14.npz")
+    pairs = [synth.frame_pair(i) for i in range(2)]
+    goal = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+    cur = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+    depth = torch.from_numpy(np.stack([p[2] for p in pairs])).cuda()
+    out = eng.frame_pairs_to_twist(goal, cur, depth, want_match=True)
+    torch.cuda.synchronize()
+    print(f"[e2e] kernels launched {eng.last_launch_count()}")
+    for i in range(2):
+        pre = f"pair{i}/"
+        nn1, nn2 = out["nn1"][i].cpu().numpy(), out["nn2"][i].cpu().numpy()
+        bad1, bad2 = nn1 != g[pre + "nn1"], nn2 != g[pre + "nn2"]
+        print(f"[e2e pair {i}] nn1 agree {1 - bad1.mean():.4f} nn2 agree {1 - bad2.mean():.4f} "
+              f"n_selected {int(out['n_selected'][i])}")
+        assert bad1.mean() <= 0.01 and bad2.mean() <= 0.01
+        # a disagreement is allowed only where the reference's own best-vs-second margin is a near-tie
+        assert np.all(g[pre + "row_margin"][bad1] < TIE_EPS) and np.all(g[pre + "col_margin"][bad2] < TIE_EPS)
+        assert np.abs(out["sim1"][i].cpu().numpy() - g[pre + "sim1"]).max() < 5e-3
+        # control law on the GPU's own keypoints == the oracle's control law on the same keypoints
+        uv, uvs = out["uv"][i].cpu().numpy(), out["uv_star"][i].cpu().numpy()
+        tw_ref = servo.ibvs_twist(uv.astype(int), uvs.astype(int), pairs[i][2])
+        tw = out["twist"][i].cpu().numpy()
+        assert np.abs(tw - tw_ref).max() <= 1e-9 * np.abs(tw_ref).max()
+        # and against the reference's own twist when the selection coincides
+        if np.array_equal(out["sel_tok"][i].cpu().numpy(), g[pre + "chosen"]) and not bad1.any():
+            assert np.array_equal(uv, g[pre + "s_uv"]) and np.array_equal(uvs, g[pre + "s_uv_star"])
+            rel = np.abs(tw - g[pre + "twist"]).max() / np.abs(g[pre + "twist"]).max()
+            print(f"[e2e pair {i}] identical selection; twist rel err vs reference {rel:.2e}")
+            assert rel <= 1e-3
+        else:
+            # same keypoint SET up to near-tie swaps => twists agree to the stated tolerance or the
+            # selections differ only in near-tied similarities
+            common = np.intersect1d(out["sel_tok"][i].cpu().numpy(), g[pre + "chosen"]).size
+            print(f"[e2e pair {i}] selections share {common}/24 tokens")
+            assert common >= 20
+
+
+def test_host_entry_equals_device_entry(eng):
+    pairs = [synth.frame_pair(i) for i in range(3)]
+    goal = torch.from_numpy(np.stack([p[0] for p in pairs])).pin_memory()
+    cur = torch.from_numpy(np.stack([p[1] for p in pairs])).pin_memory()
+    depth = torch.from_numpy(np.stack([p[2] for p in pairs])).pin_memory()
+    tw = torch.empty(3, 6, dtype=torch.float64).pin_memory()
+    ns = torch.empty(3, dtype=torch.int32).pin_memory()
+    ms = torch.empty(3, dtype=torch.float32).pin_memory()
+    eng.frame_pairs_to_twist_host(goal, cur, depth, tw, ns, ms)
+    dev = eng.frame_pairs_to_twist(goal.cuda(), cur.cuda(), depth.cuda())
+    torch.cuda.synchronize()
+    assert torch.equal(tw, dev["twist"].cpu()) and torch.equal(ns, dev["n_selected"].cpu())
+    assert torch.equal(ms, dev["mean_sim_sel"].cpu())
+
+
+def test_same_image_gives_zero_twist(eng):
+    g, _, d = synth.frame_pair(5)
+    goal = torch.from_numpy(g[None]).cuda()
+    out = eng.frame_pairs_to_twist(goal, goal.clone(), torch.from_numpy(d[None]).cuda(), want_match=True)
+    assert int(out["flags"][0]) & 1 and int(out["n_selected"][0]) == 24
+    assert torch.equal(out["uv"], out["uv_star"]) and not out["twist"].any()
+    assert torch.all(out["sel_sim"] == 1.0)
+
+
+def test_batch_split_invariance(eng):
+    """Frame pairs are independent units: any sharding gives bit-identical per-pair results."""
+    pairs = [synth.frame_pair(i) for i in range(4)]
+    goal = torch.from_numpy(np.stack([p[0] for p in pairs])).cuda()
+    cur = torch.from_numpy(np.stack([p[1] for p in pairs])).cuda()
+    depth = torch.from_numpy(np.stack([p[2] for p in pairs])).cuda()
+    full = eng.frame_pairs_to_twist(goal, cur, depth)["twist"].clone()
+    halves = [eng.frame_pairs_to_twist(goal[s], cur[s], depth[s])["twist"].clone() for s in (slice(0, 2), slice(2, 4))]
+    assert torch.equal(full, torch.cat(halves))
+
+
+# ------------------------------------------------------------------------------ plugin surface
+def test_plugin_surface(eng, vits):
+    from PIL import Image
+    from vitvs_b200 import plugin
+    plugin.set_default_engine(eng)
+    a, b, _ = synth.descriptor_sets(484, 384, seed=3, noise=1.5)
+    p1, p2, sim = plugin.find_correspondences_batch(a[None, None].cuda(), b[None, None].cuda(), num_pairs=24)
+    assert p1.shape == (24, 2) and p2.shape == (24, 2) and sim.shape == (1, 24) and p1.dtype == torch.int64
+    S = servo.cosine_similarity_matrix(a[None, None], b[None, None])[0, 0]
+    m = servo.match(S)
+    tok1 = (p1[:, 0] * 22 + p1[:, 1]).cpu().numpy()
+    assert np.isin(tok1, m.candidates).all()                  # a random draw from the mutual-NN set
+    assert plugin.find_correspondences_batch(a[None, None].cuda(), a[None, None].cuda(), num_pairs=24)[2].eq(1).all()
+
+    class Servo(plugin.DinoServoMixin):
+        pass
+    s = Servo()
+    from vitvs_b200 import ServoConfig
+    s.cfg, s.engine = ServoConfig(), eng
+    s.initialize_ema()
+    goal = synth.goal_frame(0)
+    s.goal_image = Image.fromarray(goal)
+    s.latest_pil_image = Image.fromarray(synth.current_frame(0, goal))
+    s.latest_image_depth = synth.depth_frame(0)
+    (s_uv_star, s_uv), sim = s.detect_features()
+    assert s_uv.shape == (24, 2) and s_uv_star.shape == (24, 2) and s_uv.dtype == int
+    s.ibvs()
+    assert s.v_c.shape == (6,)
+    ref = servo.ibvs_twist(s_uv, s_uv_star, s.latest_image_depth)
+    assert np.abs(s.v_c - ref).max() <= 1e-9 * np.abs(ref).max()          # first EMA call copies
+    Z = s.get_depth(s_uv)
+    assert np.array_equal(Z, servo.get_depth(s_uv, s.latest_image_depth))
+    s_xy, s_star = s.transform_to_real_world(s_uv, s_uv_star)
+    assert np.allclose(s_xy, servo.to_normalised(s_uv), rtol=1e-15)

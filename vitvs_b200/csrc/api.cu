@@ -111,6 +111,11 @@ struct vvs_ctx {
   uint16_t* stage_depth = nullptr; // [max_pairs, H, W]
   int last_n_img = 0;
   int launch_count = 0;
+  // optional per-kernel-class CUDA-event profiler (vvs_profile_*)
+  bool prof_on = false;
+  std::vector<cudaEvent_t> prof_events;
+  std::vector<int> prof_class;      // class of the i-th (start, stop) event pair
+  size_t prof_used = 0;
 };
 
 namespace {
@@ -125,6 +130,31 @@ int fail(vvs_ctx* c, int code, const std::string& msg) {
   if (c) c->err = msg; else g_create_error = msg;
   return code;
 }
+
+// brackets one kernel launch with events on the launching stream when profiling is enabled
+struct ProfScope {
+  vvs_ctx* c;
+  cudaStream_t s;
+  cudaEvent_t stop = nullptr;
+  ProfScope(vvs_ctx* c_, int cls, cudaStream_t s_) : c(c_), s(s_) {
+    if (!c->prof_on) return;
+    if (c->prof_used + 2 > c->prof_events.size()) {
+      for (int i = 0; i < 64; ++i) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        c->prof_events.push_back(e);
+      }
+    }
+    cudaEvent_t start = c->prof_events[c->prof_used];
+    stop = c->prof_events[c->prof_used + 1];
+    c->prof_used += 2;
+    c->prof_class.push_back(cls);
+    cudaEventRecord(start, s);
+  }
+  ~ProfScope() {
+    if (stop) cudaEventRecord(stop, s);
+  }
+};
 
 int upload_matrix(vvs_ctx* c, bf16** dst, const void* src, int dtype, int rows, int cols, int cpad, int interleave_bn,
                   int hidden, cudaStream_t s) {
@@ -166,8 +196,9 @@ long long numel(const int64_t* shape, int rank) {
   return n;
 }
 
-int gemm(vvs_ctx* c, const GemmArgs& a, cudaStream_t s) {
+int gemm(vvs_ctx* c, const GemmArgs& a, cudaStream_t s, int cls = VVS_K_OTHER) {
   ++c->launch_count;
+  ProfScope ps(c, cls, s);
   return launch_gemm(a, c->num_sms, s, &c->err);
 }
 
@@ -191,44 +222,53 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
   const int M = n_img * N, Mp = n_img * T;
   int rc;
   if (kind == VVS_IMAGE_U8_HWC)
-    rc = launch_im2col_u8(static_cast<const uint8_t*>(images), c->big, n_img, f.image_size, kPatchKPad, s, &c->err);
+  { ProfScope ps(c, VVS_K_IM2COL, s);
+    rc = launch_im2col_u8(static_cast<const uint8_t*>(images), c->big, n_img, f.image_size, kPatchKPad, s, &c->err); }
   else if (kind == VVS_IMAGE_F32_NCHW)
-    rc = launch_im2col_f32(static_cast<const float*>(images), c->big, n_img, f.image_size, kPatchKPad, s, &c->err);
+  { ProfScope ps(c, VVS_K_IM2COL, s);
+    rc = launch_im2col_f32(static_cast<const float*>(images), c->big, n_img, f.image_size, kPatchKPad, s, &c->err); }
   else
     return fail(c, VVS_ERR_INVALID, "unknown image_kind");
   if (rc) return rc;
-  rc = launch_cls_rows(c->x, c->cls, c->pos, n_img, N, D, s, &c->err);
+  { ProfScope ps(c, VVS_K_OTHER, s);
+    rc = launch_cls_rows(c->x, c->cls, c->pos, n_img, N, D, s, &c->err); }
   if (rc) return rc;
   c->launch_count += 2;
   {
     GemmArgs g = plain_gemm(c->big, c->pe_w, Mp, D, kPatchKPad, EPI_PATCH_F32);
     g.bias = c->pe_b; g.x_f32 = c->x; g.ldo = D; g.pos = c->pos; g.T = T;
-    if ((rc = gemm(c, g, s))) return rc;
+    if ((rc = gemm(c, g, s, VVS_K_PATCH_GEMM))) return rc;
   }
   for (int i = 0; i <= layer; ++i) {
     const BlockW& w = c->blocks[i];
-    if ((rc = launch_layernorm(c->x, w.n1w, w.n1b, c->h, M, D, 1e-6f, s, &c->err))) return rc;
+    { ProfScope ps(c, VVS_K_LAYERNORM, s);
+      rc = launch_layernorm(c->x, w.n1w, w.n1b, c->h, M, D, 1e-6f, s, &c->err); }
+    if (rc) return rc;
     {
       GemmArgs g = plain_gemm(c->h, w.qkv_w, M, 3 * D, D, EPI_BIAS_BF16);
       g.bias = w.qkv_b; g.out_bf16 = c->big; g.ldo = 3 * D; g.q_cols = D; g.q_scale = 0.125f;   // hd^-0.5, hd = 64
-      if ((rc = gemm(c, g, s))) return rc;
+      if ((rc = gemm(c, g, s, VVS_K_QKV_GEMM))) return rc;
     }
-    if ((rc = launch_attention(c->big, c->h, n_img, N, f.heads, s, &c->err))) return rc;
+    { ProfScope ps(c, VVS_K_ATTENTION, s);
+      rc = launch_attention(c->big, c->h, n_img, N, f.heads, s, &c->err); }
+    if (rc) return rc;
     {
       GemmArgs g = plain_gemm(c->h, w.proj_w, M, D, D, EPI_RESID_F32);
       g.bias = w.proj_b; g.gamma = w.ls1; g.x_f32 = c->x; g.ldo = D;
-      if ((rc = gemm(c, g, s))) return rc;
+      if ((rc = gemm(c, g, s, VVS_K_PROJ_GEMM))) return rc;
     }
-    if ((rc = launch_layernorm(c->x, w.n2w, w.n2b, c->h, M, D, 1e-6f, s, &c->err))) return rc;
+    { ProfScope ps(c, VVS_K_LAYERNORM, s);
+      rc = launch_layernorm(c->x, w.n2w, w.n2b, c->h, M, D, 1e-6f, s, &c->err); }
+    if (rc) return rc;
     {
       GemmArgs g = plain_gemm(c->h, w.ffn1_w, M, f.swiglu ? 2 * H : H, D, f.swiglu ? EPI_SWIGLU_BF16 : EPI_GELU_BF16);
       g.bias = w.ffn1_b; g.out_bf16 = c->big; g.ldo = H;
-      if ((rc = gemm(c, g, s))) return rc;
+      if ((rc = gemm(c, g, s, VVS_K_FFN1_GEMM))) return rc;
     }
     {
       GemmArgs g = plain_gemm(c->big, w.ffn2_w, M, D, H, EPI_RESID_F32);
       g.bias = w.ffn2_b; g.gamma = w.ls2; g.x_f32 = c->x; g.ldo = D;
-      if ((rc = gemm(c, g, s))) return rc;
+      if ((rc = gemm(c, g, s, VVS_K_FFN2_GEMM))) return rc;
     }
     c->launch_count += 3;   // 2 LayerNorms + attention
   }
@@ -256,7 +296,7 @@ int match_on_desc(vvs_ctx* c, int n_pairs, int T, int dpad, int grid_w, int K, c
   g.b_batch_pitch = static_cast<long long>(T) * dpad;
   g.epilogue = EPI_SIM;
   g.row_best = c->row_best; g.col_best = c->col_best; g.best_pitch = T;
-  int rc = gemm(c, g, s);
+  int rc = gemm(c, g, s, VVS_K_SIM_GEMM);
   if (rc) return rc;
   SelectArgs a;
   memset(&a, 0, sizeof(a));
@@ -269,7 +309,9 @@ int match_on_desc(vvs_ctx* c, int n_pairs, int T, int dpad, int grid_w, int K, c
   a.nn1 = c->nn1; a.nn2 = c->nn2; a.sim1 = c->sim1; a.candidate = c->cand;
   a.mean_sim1 = c->mean_sim1; a.n_candidates = c->n_cand; a.n_selected = c->n_sel; a.flags = c->flags;
   a.sel_tok = c->sel_tok; a.sel_sim = c->sel_sim; a.uv_star = c->uv_star; a.uv = c->uv;
-  if ((rc = launch_select(a, s, &c->err))) return rc;
+  { ProfScope ps(c, VVS_K_SELECT, s);
+    rc = launch_select(a, s, &c->err); }
+  if (rc) return rc;
   ++c->launch_count;
   if (out) {
 #define VVS_COPY_OUT(field, src, count, type)                                                                  \
@@ -317,6 +359,7 @@ int run_ibvs(vvs_ctx* c, const int32_t* uv, const int32_t* uv_star, const uint16
   a.lambda = c->cfg.lambda_; a.ema_alpha = c->cfg.ema_alpha;
   a.ema_state = ema_state; a.ema_init = ema_init; a.twist = twist; a.twist_raw = twist_raw;
   ++c->launch_count;
+  ProfScope ps(c, VVS_K_IBVS, s);
   return launch_ibvs(a, s, &c->err);
 }
 
@@ -338,8 +381,9 @@ int pairs_to_twist(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const ui
   int rc = forward_tokens(c, images, VVS_IMAGE_U8_HWC, 2 * n_pairs, f.layer, s);
   if (rc) return rc;
   const int parts = f.use_feature_binning ? 9 : 1;
-  rc = launch_descriptors_unit_bf16(c->x, c->desc, c->sqn, 2 * n_pairs, c->grid, c->grid, f.dim,
-                                    f.use_feature_binning, s, &c->err);
+  { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
+    rc = launch_descriptors_unit_bf16(c->x, c->desc, c->sqn, 2 * n_pairs, c->grid, c->grid, f.dim,
+                                      f.use_feature_binning, s, &c->err); }
   if (rc) return rc;
   c->launch_count += 2;
   rc = match_on_desc(c, n_pairs, c->T, parts * f.dim, c->grid, f.num_pairs, &out->match, s);
@@ -440,6 +484,7 @@ int vvs_destroy(vvs_handle c) {
                   c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth};
   for (void* p : ptrs)
     if (p) cudaFree(p);
+  for (cudaEvent_t e : c->prof_events) cudaEventDestroy(e);
   for (BlockW& w : c->blocks) {
     void* bp[] = {w.qkv_w, w.proj_w, w.ffn1_w, w.ffn2_w, w.qkv_b, w.proj_b, w.ffn1_b, w.ffn2_b,
                   w.n1w, w.n1b, w.n2w, w.n2b, w.ls1, w.ls2};
@@ -594,6 +639,21 @@ int vvs_ibvs(vvs_handle c, const int32_t* uv, const int32_t* uv_star, const uint
                   static_cast<cudaStream_t>(stream));
 }
 
+int vvs_ibvs_terms(vvs_handle c, const int32_t* uv, const int32_t* uv_star, const uint16_t* depth, int32_t n_pairs,
+                   int32_t K, double* twist, double* z, double* xy, double* xy_star, double* L, vvs_stream stream) {
+  if (!c || !uv || !uv_star || !depth || !twist) return fail(c, VVS_ERR_INVALID, "vvs_ibvs_terms: null argument");
+  if (n_pairs < 1 || K < 1) return fail(c, VVS_ERR_INVALID, "vvs_ibvs_terms: empty problem");
+  IbvsArgs a;
+  memset(&a, 0, sizeof(a));
+  a.uv = uv; a.uv_star = uv_star; a.depth = depth; a.n_pairs = n_pairs; a.K = K;
+  a.cam.width = c->cfg.frame_width; a.cam.height = c->cfg.frame_height;
+  a.cam.fx = c->cfg.f_x; a.cam.fy = c->cfg.f_y; a.cam.cx = c->cfg.c_x; a.cam.cy = c->cfg.c_y;
+  a.lambda = c->cfg.lambda_; a.twist = twist;
+  a.z_out = z; a.xy_out = xy; a.xy_star_out = xy_star; a.L_out = L;
+  ++c->launch_count;
+  return launch_ibvs(a, static_cast<cudaStream_t>(stream), &c->err);
+}
+
 int vvs_frame_pairs_to_twist(vvs_handle c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth,
                              int32_t n_pairs, const vvs_pair_out* out, vvs_stream stream) {
   if (!c || !goal || !cur || !depth) return fail(c, VVS_ERR_INVALID, "vvs_frame_pairs_to_twist: null argument");
@@ -626,6 +686,32 @@ int vvs_frame_pairs_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8
   if (mean_sim_sel)
     VVS_CUDA_OK(cudaMemcpyAsync(mean_sim_sel, c->mean_sel, n_pairs * sizeof(float), cudaMemcpyDeviceToHost, s), &c->err);
   VVS_CUDA_OK(cudaStreamSynchronize(s), &c->err);
+  return VVS_OK;
+}
+
+int vvs_profile_enable(vvs_handle c, int32_t on) {
+  if (!c) return VVS_ERR_INVALID;
+  c->prof_on = on != 0;
+  c->prof_used = 0;
+  c->prof_class.clear();
+  return VVS_OK;
+}
+
+int vvs_profile_read(vvs_handle c, double* total_ms, int32_t* launches, int32_t n_classes) {
+  if (!c || !total_ms || !launches || n_classes < VVS_K_COUNT) return fail(c, VVS_ERR_INVALID, "vvs_profile_read: bad argument");
+  for (int i = 0; i < n_classes; ++i) {
+    total_ms[i] = 0.0;
+    launches[i] = 0;
+  }
+  for (size_t i = 0; i < c->prof_class.size(); ++i) {
+    VVS_CUDA_OK(cudaEventSynchronize(c->prof_events[2 * i + 1]), &c->err);
+    float ms = 0.f;
+    VVS_CUDA_OK(cudaEventElapsedTime(&ms, c->prof_events[2 * i], c->prof_events[2 * i + 1]), &c->err);
+    total_ms[c->prof_class[i]] += ms;
+    launches[c->prof_class[i]] += 1;
+  }
+  c->prof_used = 0;
+  c->prof_class.clear();
   return VVS_OK;
 }
 

@@ -411,7 +411,13 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t cols, uint64_t r
   return VVS_OK;
 }
 
-int gemm_block_n(int N) { return (N % 256 == 0 || N > 1024) ? 256 : 128; }
+// 256-wide N tiles keep the per-stage smem operand traffic at 96 B/clk (128-wide tiles sit at the 128 B/clk
+// smem limit); fall back to 128 only when padding N up to a multiple of 256 would waste more than 15 %.
+int gemm_block_n(int N) {
+  if (N <= 128) return 128;
+  const long long padded = (static_cast<long long>(N) + 255) / 256 * 256;
+  return (padded * 100 <= static_cast<long long>(N) * 115) ? 256 : 128;
+}
 
 int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string* err) {
   if (a.M <= 0 || a.N <= 0 || a.K <= 0 || a.batch <= 0) {

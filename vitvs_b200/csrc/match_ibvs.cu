@@ -238,6 +238,23 @@ __global__ void __launch_bounds__(128) ibvs_kernel(const IbvsArgs a) {
     const double e1 = x - xs, e2 = y - ys;
     const double r1[6] = {-1.0 / z, 0.0, x / z, x * y, -(1.0 + x * x), y};        // :650-659
     const double r2[6] = {0.0, -1.0 / z, y / z, 1.0 + y * y, -x * y, -x};
+    if (a.z_out) a.z_out[static_cast<size_t>(pair) * K + k] = z;
+    if (a.xy_out) {
+      a.xy_out[(static_cast<size_t>(pair) * K + k) * 2] = x;
+      a.xy_out[(static_cast<size_t>(pair) * K + k) * 2 + 1] = y;
+    }
+    if (a.xy_star_out) {
+      a.xy_star_out[(static_cast<size_t>(pair) * K + k) * 2] = xs;
+      a.xy_star_out[(static_cast<size_t>(pair) * K + k) * 2 + 1] = ys;
+    }
+    if (a.L_out) {
+      double* Lr = a.L_out + (static_cast<size_t>(pair) * K + k) * 12;
+#pragma unroll
+      for (int i = 0; i < 6; ++i) {
+        Lr[i] = r1[i];
+        Lr[6 + i] = r2[i];
+      }
+    }
     int n = 0;
 #pragma unroll
     for (int i = 0; i < 6; ++i)

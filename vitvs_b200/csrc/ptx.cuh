@@ -3,6 +3,7 @@
 // Hand-written inline PTX; descriptor bit layouts follow the PTX ISA tables for tcgen05 (sm_100).
 #pragma once
 #include <cstdint>
+#include <cstdio>
 #include <cuda_runtime.h>
 
 namespace vvs {
@@ -36,8 +37,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// A wait that lasts seconds is a protocol bug (lost arrive / wrong parity): trap instead of hanging the GPU.
+#ifndef VVS_WAIT_TIMEOUT_CYCLES
+#define VVS_WAIT_TIMEOUT_CYCLES 6000000000ll
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > VVS_WAIT_TIMEOUT_CYCLES) {
+      printf("vitvs_b200: mbarrier wait timed out (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y, blockIdx.z,
+             threadIdx.x);
+      __trap();
+    }
   }
 }
 

@@ -136,6 +136,11 @@ struct IbvsArgs {
   int32_t* ema_init;        // [n_pairs] 0 = first call copies
   double* twist;            // [n_pairs, 6] (after EMA when enabled)
   double* twist_raw;        // [n_pairs, 6] or null (before EMA)
+  // optional per-point terms (Controller.get_depth / transform_to_real_world / calculate_interaction_matrix)
+  double* z_out;            // [n_pairs, K]
+  double* xy_out;           // [n_pairs, K, 2]
+  double* xy_star_out;      // [n_pairs, K, 2]
+  double* L_out;            // [n_pairs, 2K, 6]
 };
 int launch_ibvs(const IbvsArgs& a, cudaStream_t s, std::string* err);
 

@@ -1,0 +1,293 @@
+"""Host-side owner of one libvitvs_b200 handle (one per GPU).  PyTorch is plumbing only: device
+memory, streams and `tensor.data_ptr()`; every computation on the hot path happens inside the
+hand-written CUDA library.  There is no fallback - construction raises when the library or an
+sm_100 device is missing."""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Mapping
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+from ._lib import VvsError, check
+from .config import ARCHS, ServoConfig
+
+PATCH = 14
+
+
+def _ptr(t: torch.Tensor | None):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream(device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def interpolate_pos_embed(pos_embed: torch.Tensor, grid: int) -> torch.Tensor:
+    """pos_embed [1, 1+M*M, D] -> [1+grid*grid, D] fp32.  Same maths as the reference's statement of the
+    DINO interpolation (dinov2_extractor.py:94-120; bicubic, +0.1 offset, antialias off).  Depends only on
+    the weights and the geometry, so it runs once per (weights, image_size) on the host, not per frame."""
+    pos = pos_embed.detach().float().cpu()
+    n = pos.shape[1] - 1
+    m = int(math.sqrt(n))
+    if grid * grid == n:
+        return pos[0].contiguous()
+    dim = pos.shape[-1]
+    s = float(grid + 0.1) / m
+    patch = F.interpolate(pos[:, 1:].reshape(1, m, m, dim).permute(0, 3, 1, 2), scale_factor=(s, s),
+                          mode="bicubic", antialias=False)
+    assert patch.shape[-2:] == (grid, grid)
+    patch = patch.permute(0, 2, 3, 1).reshape(-1, dim)
+    return torch.cat((pos[0, :1], patch), dim=0).contiguous()
+
+
+class Engine:
+    def __init__(self, cfg: ServoConfig | None = None, max_images: int = 2, device: int | str | None = None,
+                 max_match_tokens: int = 0, max_match_dim: int = 0):
+        self.cfg = cfg or ServoConfig()
+        self.lib = _lib.load()                      # raises VvsError when the .so is missing
+        if not torch.cuda.is_available():
+            raise VvsError("vitvs_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.device = torch.device("cuda", torch.cuda.current_device() if device is None else
+                                   (device if isinstance(device, int) else torch.device(device).index or 0))
+        if self.cfg.model_type not in ARCHS:
+            raise ValueError(f"unknown model_type {self.cfg.model_type}")
+        if self.cfg.stride != PATCH:
+            raise NotImplementedError("only stride == patch size (14) is on the hot path (SURVEY §8f N4)")
+        if self.cfg.facet != "token":
+            raise NotImplementedError("only facet 'token' is on the hot path (SURVEY §8f N4)")
+        dim, heads, depth, hidden, swiglu = ARCHS[self.cfg.model_type]
+        self.dim, self.heads, self.depth, self.hidden, self.swiglu = dim, heads, depth, hidden, swiglu
+        self.grid = self.cfg.dino_input_size // PATCH
+        self.tokens = self.grid * self.grid
+        self.max_images = max_images
+        c = _lib.Config(
+            dim=dim, heads=heads, depth=depth, ffn_hidden=hidden, swiglu=int(swiglu),
+            image_size=self.cfg.dino_input_size, max_images=max_images,
+            frame_width=self.cfg.u_max, frame_height=self.cfg.v_max,
+            f_x=self.cfg.f_x, f_y=self.cfg.f_y, c_x=self.cfg.c_x, c_y=self.cfg.c_y,
+            lambda_=self.cfg.lambda_, ema_alpha=self.cfg.ema_alpha,
+            num_pairs=self.cfg.num_pairs, layer=min(self.cfg.layer, depth - 1),
+            use_feature_binning=int(self.cfg.use_feature_binning),
+            same_image_threshold=self.cfg.same_image_threshold,
+            max_match_tokens=max_match_tokens, max_match_dim=max_match_dim)
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            rc = self.lib.vvs_create(C.byref(c), C.byref(self._h))
+        if rc != 0:
+            msg = self.lib.vvs_last_error(None)
+            raise VvsError(f"vvs_create failed ({rc}): {msg.decode() if msg else '?'}")
+        self.num_sms = self.lib.vvs_num_sms(self._h)
+
+    # ------------------------------------------------------------------ lifetime
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.lib.vvs_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        check(self._h, rc, what)
+
+    # ------------------------------------------------------------------ weights
+    def load_weights(self, state: Mapping[str, torch.Tensor] | torch.nn.Module):
+        """Upload a DINOv2 state_dict (upstream parameter names).  Blocks deeper than cfg.layer are not
+        needed: the forward stops after blocks[layer] (identical values)."""
+        if isinstance(state, torch.nn.Module):
+            state = state.state_dict()
+        last = min(self.cfg.layer, self.depth - 1)
+        s = _stream(self.device)
+
+        def put(name, t):
+            t = t.detach().to(self.device, torch.float32).contiguous()
+            shape = (C.c_int64 * t.dim())(*t.shape)
+            self._check(self.lib.vvs_set_weight(self._h, name.encode(), _ptr(t), _lib.F32, shape, t.dim(), s),
+                        f"vvs_set_weight({name})")
+
+        put("patch_embed.proj.weight", state["patch_embed.proj.weight"])
+        put("patch_embed.proj.bias", state["patch_embed.proj.bias"])
+        put("cls_token", state["cls_token"].reshape(-1))
+        put("pos_embed_interp", interpolate_pos_embed(state["pos_embed"], self.grid))
+        for name, t in state.items():
+            if not name.startswith("blocks."):
+                continue
+            idx = int(name.split(".")[1])
+            if idx <= last:
+                put(name, t)
+        torch.cuda.synchronize(self.device)
+        self._check(self.lib.vvs_weights_ready(self._h), "vvs_weights_ready")
+
+    # ------------------------------------------------------------------ stages
+    def forward_tokens(self, images: torch.Tensor, layer: int | None = None) -> None:
+        """images: uint8 [n,S,S,3] or float32 [n,3,S,S] on this device."""
+        layer = min(self.cfg.layer, self.depth - 1) if layer is None else layer
+        S = self.cfg.dino_input_size
+        if images.dtype == torch.uint8:
+            assert images.shape[1:] == (S, S, 3), images.shape
+            kind = _lib.IMAGE_U8_HWC
+        elif images.dtype == torch.float32:
+            assert images.shape[1:] == (3, S, S), images.shape
+            kind = _lib.IMAGE_F32_NCHW
+        else:
+            raise TypeError("images must be uint8 HWC or float32 NCHW")
+        images = images.contiguous()
+        self._check(self.lib.vvs_forward_tokens(self._h, _ptr(images), kind, images.shape[0], layer,
+                                                _stream(self.device)), "vvs_forward_tokens")
+        self._n_img = images.shape[0]
+
+    def tokens_out(self) -> torch.Tensor:
+        out = torch.empty(self._n_img, self.tokens + 1, self.dim, device=self.device, dtype=torch.float32)
+        self._check(self.lib.vvs_get_tokens(self._h, _ptr(out), self._n_img, _stream(self.device)), "vvs_get_tokens")
+        return out
+
+    def descriptors(self, bin: bool) -> torch.Tensor:
+        d = self.dim * (9 if bin else 1)
+        out = torch.empty(self._n_img, 1, self.tokens, d, device=self.device, dtype=torch.float32)
+        self._check(self.lib.vvs_descriptors(self._h, self._n_img, int(bin), _ptr(out), _stream(self.device)),
+                    "vvs_descriptors")
+        return out
+
+    def _match_buffers(self, n_pairs: int, T: int, K: int):
+        dev = self.device
+        bufs = dict(
+            nn1=torch.empty(n_pairs, T, dtype=torch.int32, device=dev),
+            nn2=torch.empty(n_pairs, T, dtype=torch.int32, device=dev),
+            sim1=torch.empty(n_pairs, T, dtype=torch.float32, device=dev),
+            candidate=torch.empty(n_pairs, T, dtype=torch.uint8, device=dev),
+            mean_sim1=torch.empty(n_pairs, dtype=torch.float32, device=dev),
+            n_candidates=torch.empty(n_pairs, dtype=torch.int32, device=dev),
+            n_selected=torch.empty(n_pairs, dtype=torch.int32, device=dev),
+            flags=torch.empty(n_pairs, dtype=torch.int32, device=dev),
+            sel_tok=torch.empty(n_pairs, K, dtype=torch.int32, device=dev),
+            sel_sim=torch.empty(n_pairs, K, dtype=torch.float32, device=dev),
+            uv_star=torch.empty(n_pairs, K, 2, dtype=torch.int32, device=dev),
+            uv=torch.empty(n_pairs, K, 2, dtype=torch.int32, device=dev),
+        )
+        mo = _lib.MatchOut(**{k: v.data_ptr() for k, v in bufs.items()})
+        return bufs, mo
+
+    def match(self, desc1: torch.Tensor, desc2: torch.Tensor, grid_w: int | None = None,
+              num_pairs: int | None = None) -> dict:
+        """desc1/desc2: fp32 [n_pairs, T, d] (goal / current).  Returns the dict of vvs_match_out tensors."""
+        assert desc1.shape == desc2.shape and desc1.dim() == 3
+        n_pairs, T, d = desc1.shape
+        K = self.cfg.num_pairs if num_pairs is None else num_pairs
+        grid_w = int(math.sqrt(T)) if grid_w is None else grid_w          # vitvs_v2.py:75
+        d1 = desc1.to(self.device, torch.float32).contiguous()
+        d2 = desc2.to(self.device, torch.float32).contiguous()
+        bufs, mo = self._match_buffers(n_pairs, T, K)
+        self._check(self.lib.vvs_match(self._h, _ptr(d1), _ptr(d2), n_pairs, T, d, grid_w, K, C.byref(mo),
+                                       _stream(self.device)), "vvs_match")
+        return bufs
+
+    def similarity(self, desc1: torch.Tensor, desc2: torch.Tensor) -> torch.Tensor:
+        n_pairs, T, d = desc1.shape
+        d1 = desc1.to(self.device, torch.float32).contiguous()
+        d2 = desc2.to(self.device, torch.float32).contiguous()
+        out = torch.empty(n_pairs, T, T, dtype=torch.float32, device=self.device)
+        self._check(self.lib.vvs_similarity(self._h, _ptr(d1), _ptr(d2), n_pairs, T, d, _ptr(out),
+                                            _stream(self.device)), "vvs_similarity")
+        return out
+
+    def ibvs(self, uv: torch.Tensor, uv_star: torch.Tensor, depth: torch.Tensor,
+             ema_state: torch.Tensor | None = None, ema_init: torch.Tensor | None = None):
+        """uv/uv_star int32 [n,K,2]; depth uint16 [n,H,W] -> (twist [n,6] f64, twist_raw [n,6] f64)."""
+        n, K, _ = uv.shape
+        uv = uv.to(self.device, torch.int32).contiguous()
+        uv_star = uv_star.to(self.device, torch.int32).contiguous()
+        depth = depth.to(self.device).contiguous()
+        assert depth.dtype == torch.uint16 and depth.shape == (n, self.cfg.v_max, self.cfg.u_max)
+        twist = torch.empty(n, 6, dtype=torch.float64, device=self.device)
+        raw = torch.empty(n, 6, dtype=torch.float64, device=self.device)
+        self._check(self.lib.vvs_ibvs(self._h, _ptr(uv), _ptr(uv_star), _ptr(depth), n, K, _ptr(twist), _ptr(raw),
+                                      _ptr(ema_state), _ptr(ema_init), _stream(self.device)), "vvs_ibvs")
+        return twist, raw
+
+    def ibvs_terms(self, uv: torch.Tensor, uv_star: torch.Tensor, depth: torch.Tensor) -> dict:
+        """Per-point terms of the control law: Z [n,K], s_xy / s_star_xy [n,K,2], L [n,2K,6], twist [n,6]."""
+        n, K, _ = uv.shape
+        uv = uv.to(self.device, torch.int32).contiguous()
+        uv_star = uv_star.to(self.device, torch.int32).contiguous()
+        depth = depth.to(self.device).contiguous()
+        f64 = dict(dtype=torch.float64, device=self.device)
+        out = dict(twist=torch.empty(n, 6, **f64), Z=torch.empty(n, K, **f64), s_xy=torch.empty(n, K, 2, **f64),
+                   s_star_xy=torch.empty(n, K, 2, **f64), L=torch.empty(n, 2 * K, 6, **f64))
+        self._check(self.lib.vvs_ibvs_terms(self._h, _ptr(uv), _ptr(uv_star), _ptr(depth), n, K, _ptr(out["twist"]),
+                                            _ptr(out["Z"]), _ptr(out["s_xy"]), _ptr(out["s_star_xy"]), _ptr(out["L"]),
+                                            _stream(self.device)), "vvs_ibvs_terms")
+        return out
+
+    def frame_pairs_to_twist(self, goal: torch.Tensor, current: torch.Tensor, depth: torch.Tensor,
+                             want_match: bool = False) -> dict:
+        """Device-resident batched Controller.ibvs(): goal/current uint8 [B,S,S,3], depth uint16 [B,H,W]."""
+        B = goal.shape[0]
+        K = self.cfg.num_pairs
+        goal, current, depth = goal.contiguous(), current.contiguous(), depth.contiguous()
+        out = dict(twist=torch.empty(B, 6, dtype=torch.float64, device=self.device),
+                   n_selected=torch.empty(B, dtype=torch.int32, device=self.device),
+                   mean_sim_sel=torch.empty(B, dtype=torch.float32, device=self.device))
+        po = _lib.PairOut(twist=out["twist"].data_ptr(), n_selected=out["n_selected"].data_ptr(),
+                          mean_sim_sel=out["mean_sim_sel"].data_ptr())
+        if want_match:
+            bufs, mo = self._match_buffers(B, self.tokens, K)
+            po.match = mo
+            out.update(bufs)
+        self._check(self.lib.vvs_frame_pairs_to_twist(self._h, _ptr(goal), _ptr(current), _ptr(depth), B,
+                                                      C.byref(po), _stream(self.device)),
+                    "vvs_frame_pairs_to_twist")
+        self._n_img = 2 * B
+        return out
+
+    def frame_pairs_to_twist_host(self, goal: torch.Tensor, current: torch.Tensor, depth: torch.Tensor,
+                                  twist_out: torch.Tensor, n_selected_out: torch.Tensor | None = None,
+                                  mean_sim_out: torch.Tensor | None = None) -> None:
+        """Same through HOST buffers (pinned for async copies); synchronises the stream before returning."""
+        assert not goal.is_cuda and not current.is_cuda and not depth.is_cuda and not twist_out.is_cuda
+        B = goal.shape[0]
+        self._check(self.lib.vvs_frame_pairs_to_twist_host(
+            self._h, _ptr(goal), _ptr(current), _ptr(depth), B, _ptr(twist_out), _ptr(n_selected_out),
+            _ptr(mean_sim_out), _stream(self.device)), "vvs_frame_pairs_to_twist_host")
+        self._n_img = 2 * B
+
+    def profile(self, on: bool) -> None:
+        self._check(self.lib.vvs_profile_enable(self._h, int(on)), "vvs_profile_enable")
+
+    def profile_read(self) -> dict:
+        """{kernel class: (total_ms, launches)} since the last read (CUDA events around every launch)."""
+        n = len(_lib.KERNEL_CLASSES)
+        ms = (C.c_double * n)()
+        cnt = (C.c_int32 * n)()
+        self._check(self.lib.vvs_profile_read(self._h, ms, cnt, n), "vvs_profile_read")
+        return {k: (ms[i], cnt[i]) for i, k in enumerate(_lib.KERNEL_CLASSES) if cnt[i]}
+
+    def last_launch_count(self) -> int:
+        return self.lib.vvs_last_launch_count(self._h)
+
+    # ------------------------------------------------------------------ kernel-level (tests / per-kernel bench)
+    def dbg_gemm(self, A, B, epilogue, bias=None, gamma=None, x_f32=None, out_bf16=None, ldo=0, q_cols=0,
+                 q_scale=1.0, pos=None, T=0):
+        M, K = A.shape
+        N = B.shape[0]
+        self._check(self.lib.vvs_dbg_gemm(self._h, _ptr(A), _ptr(B), M, N, K, epilogue, _ptr(bias), _ptr(gamma),
+                                          _ptr(x_f32), _ptr(out_bf16), ldo, q_cols, q_scale, _ptr(pos), T,
+                                          _stream(self.device)), "vvs_dbg_gemm")
+
+    def dbg_attention(self, qkv, n_img, n_tok, heads):
+        out = torch.empty(n_img * n_tok, heads * 64, dtype=torch.bfloat16, device=self.device)
+        self._check(self.lib.vvs_dbg_attention(self._h, _ptr(qkv), _ptr(out), n_img, n_tok, heads,
+                                               _stream(self.device)), "vvs_dbg_attention")
+        return out
+
+    def dbg_layernorm(self, x, w, b):
+        out = torch.empty(x.shape, dtype=torch.bfloat16, device=self.device)
+        self._check(self.lib.vvs_dbg_layernorm(self._h, _ptr(x), _ptr(w), _ptr(b), _ptr(out), x.shape[0], x.shape[1],
+                                               _stream(self.device)), "vvs_dbg_layernorm")
+        return out
