@@ -85,8 +85,9 @@ def _check_match(r, S_ref, p=0):
     print(f"[match] nn1 agree {1 - bad1.mean():.4f} nn2 agree {1 - bad2.mean():.4f}; worst margin at a "
           f"disagreement {max(marg1[bad1].max(initial=0), marg2[bad2].max(initial=0)):.2e}; "
           f"sim1 max err {np.abs(sim1 - S_ref.max(-1).values.numpy()).max():.2e}")
-    assert bad1.mean() <= 0.01 and bad2.mean() <= 0.01
-    assert np.all(marg1[bad1] < TIE_EPS) and np.all(marg2[bad2] < TIE_EPS)
+    allowed = max(1, int(np.ceil(0.01 * T)))        # >= 99 % agreement (at least one token on tiny grids) ...
+    assert bad1.sum() <= allowed and bad2.sum() <= allowed
+    assert np.all(marg1[bad1] < TIE_EPS) and np.all(marg2[bad2] < TIE_EPS)     # ... and only at near-ties
     assert np.abs(sim1 - S_ref.max(-1).values.numpy()).max() < 5e-3
     return m, nn1, nn2
 
@@ -285,13 +286,16 @@ def test_plugin_surface(eng, vits):
     from PIL import Image
     from vitvs_b200 import plugin
     plugin.set_default_engine(eng)
-    a, b, _ = synth.descriptor_sets(484, 384, seed=3, noise=1.5)
+    a, b, _ = synth.descriptor_sets(484, 384, seed=3, noise=8.0)     # ~half the tokens mutual
     p1, p2, sim = plugin.find_correspondences_batch(a[None, None].cuda(), b[None, None].cuda(), num_pairs=24)
     assert p1.shape == (24, 2) and p2.shape == (24, 2) and sim.shape == (1, 24) and p1.dtype == torch.int64
     S = servo.cosine_similarity_matrix(a[None, None], b[None, None])[0, 0]
     m = servo.match(S)
     tok1 = (p1[:, 0] * 22 + p1[:, 1]).cpu().numpy()
     assert np.isin(tok1, m.candidates).all()                  # a random draw from the mutual-NN set
+    # every token mutual => the reference's own quirk: (None, None, None) (SURVEY §4 v)
+    e, f, _ = synth.descriptor_sets(484, 384, seed=3, noise=1.5)
+    assert plugin.find_correspondences_batch(e[None, None].cuda(), f[None, None].cuda(), num_pairs=24) == (None,) * 3
     assert plugin.find_correspondences_batch(a[None, None].cuda(), a[None, None].cuda(), num_pairs=24)[2].eq(1).all()
 
     class Servo(plugin.DinoServoMixin):
