@@ -16,6 +16,7 @@
 #include <cuda.h>
 
 #include <string>
+#include <type_traits>
 
 #include "ptx.cuh"
 #include "vvs_internal.h"
@@ -31,6 +32,12 @@ constexpr uint32_t kPBytes = kBQ * kBKV * 2;          // 32 KB: P as two 64-key 
 constexpr uint32_t kAttnSmem = 3 * kTileBytes + kPBytes + 128 + 1024;
 constexpr uint32_t kAttnTmemCols = 256;
 constexpr float kLog2e = 1.4426950408889634f;
+
+__device__ __forceinline__ float ex2_approx(float x) {   // single MUFU.EX2; ex2(-inf) = 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 __global__ void __launch_bounds__(128, 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ out, int n_tok, int D) {
@@ -113,51 +120,82 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ o
     }
     __syncwarp();
     const int valid = n_tok - j * kBKV;   // keys [0, valid) of this block exist
-
-    // pass 1: row max
-    float mx = -INFINITY;
-#pragma unroll 1
-    for (int c = 0; c < kBKV / 32; ++c) {
-      uint32_t raw[32];
-      tmem_ld32(tS + c * 32, raw);
-      tmem_ld_wait();
+    float alpha, psum;
+    // Softmax of one 128-key block.  kTail = the last, partially filled block: keys >= valid are masked
+    // (max ignores them, p = 0).  Full blocks carry no per-element masking at all.  TMEM loads are double
+    // buffered; max / sum use 4 independent accumulators to keep the FMNMX / FADD chains short.
+    auto softmax_block = [&](auto tail_tag) {
+      constexpr bool kTail = decltype(tail_tag)::value;
+      uint32_t raw[2][32];
+      // ---- pass 1: row max
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+      tmem_ld32(tS, raw[0]);
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const float s = __uint_as_float(raw[i]);
-        if (c * 32 + i < valid) mx = fmaxf(mx, s);
-      }
-    }
-    const float m_new = fmaxf(m_run, mx * kLog2e);
-    const float alpha = exp2f(m_run - m_new);
-    m_run = m_new;
-
-    // pass 2: p = exp2(s*log2e - m), row sum, bf16 P -> smem (K-major, SWIZZLE_128B, two 64-key atoms)
-    float psum = 0.f;
-#pragma unroll 1
-    for (int c = 0; c < kBKV / 32; ++c) {
-      uint32_t raw[32];
-      tmem_ld32(tS + c * 32, raw);
-      tmem_ld_wait();
-      float pv[32];
+      for (int c = 0; c < kBKV / 32; ++c) {
+        tmem_ld_wait();
+        if (c + 1 < kBKV / 32) tmem_ld32(tS + (c + 1) * 32, raw[(c + 1) & 1]);
+        else tmem_ld32(tS, raw[(c + 1) & 1]);                 // first chunk again for pass 2
+        if (kTail && c * 32 >= valid) continue;
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const float s = __uint_as_float(raw[i]);
-        const float e = exp2f(fmaf(s, kLog2e, -m_new));
-        pv[i] = (c * 32 + i < valid) ? e : 0.f;
-        psum += pv[i];
+        for (int i = 0; i < 32; i += 4) {
+          float s0 = __uint_as_float(raw[c & 1][i]), s1 = __uint_as_float(raw[c & 1][i + 1]);
+          float s2 = __uint_as_float(raw[c & 1][i + 2]), s3 = __uint_as_float(raw[c & 1][i + 3]);
+          if (kTail) {
+            if (c * 32 + i + 0 >= valid) s0 = -INFINITY;
+            if (c * 32 + i + 1 >= valid) s1 = -INFINITY;
+            if (c * 32 + i + 2 >= valid) s2 = -INFINITY;
+            if (c * 32 + i + 3 >= valid) s3 = -INFINITY;
+          }
+          mx0 = fmaxf(mx0, s0);
+          mx1 = fmaxf(mx1, s1);
+          mx2 = fmaxf(mx2, s2);
+          mx3 = fmaxf(mx3, s3);
+        }
       }
-      uint8_t* atom = sP + (c >> 1) * (kBQ * 128) + p_row_off;
+      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+      const float m_new = fmaxf(m_run, mx * kLog2e);
+      alpha = ex2_approx(m_run - m_new);
+      m_run = m_new;
+      const float neg_m = -m_new;
+      // ---- pass 2: p = exp2(s*log2e - m), row sum, bf16 P -> smem (K-major, SWIZZLE_128B, two 64-key atoms)
+      float ps0 = 0.f, ps1 = 0.f, ps2 = 0.f, ps3 = 0.f;
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        uint4 w;
-        w.x = pack_bf16x2(pv[q * 8 + 0], pv[q * 8 + 1]);
-        w.y = pack_bf16x2(pv[q * 8 + 2], pv[q * 8 + 3]);
-        w.z = pack_bf16x2(pv[q * 8 + 4], pv[q * 8 + 5]);
-        w.w = pack_bf16x2(pv[q * 8 + 6], pv[q * 8 + 7]);
-        const uint32_t chunk = static_cast<uint32_t>((c & 1) * 4 + q);
-        *reinterpret_cast<uint4*>(atom + ((chunk ^ sw) << 4)) = w;
+      for (int c = 0; c < kBKV / 32; ++c) {
+        tmem_ld_wait();
+        if (c + 1 < kBKV / 32) tmem_ld32(tS + (c + 1) * 32, raw[(c + 1) & 1]);   // chunk c sits in raw[c & 1]
+        const uint32_t(&rw)[32] = raw[c & 1];
+        float pv[32];
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          float e0 = ex2_approx(fmaf(__uint_as_float(rw[i + 0]), kLog2e, neg_m));
+          float e1 = ex2_approx(fmaf(__uint_as_float(rw[i + 1]), kLog2e, neg_m));
+          float e2 = ex2_approx(fmaf(__uint_as_float(rw[i + 2]), kLog2e, neg_m));
+          float e3 = ex2_approx(fmaf(__uint_as_float(rw[i + 3]), kLog2e, neg_m));
+          if (kTail) {
+            if (c * 32 + i + 0 >= valid) e0 = 0.f;
+            if (c * 32 + i + 1 >= valid) e1 = 0.f;
+            if (c * 32 + i + 2 >= valid) e2 = 0.f;
+            if (c * 32 + i + 3 >= valid) e3 = 0.f;
+          }
+          pv[i + 0] = e0; pv[i + 1] = e1; pv[i + 2] = e2; pv[i + 3] = e3;
+          ps0 += e0; ps1 += e1; ps2 += e2; ps3 += e3;
+        }
+        uint8_t* atom = sP + (c >> 1) * (kBQ * 128) + p_row_off;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 w;
+          w.x = pack_bf16x2(pv[q * 8 + 0], pv[q * 8 + 1]);
+          w.y = pack_bf16x2(pv[q * 8 + 2], pv[q * 8 + 3]);
+          w.z = pack_bf16x2(pv[q * 8 + 4], pv[q * 8 + 5]);
+          w.w = pack_bf16x2(pv[q * 8 + 6], pv[q * 8 + 7]);
+          const uint32_t chunk = static_cast<uint32_t>((c & 1) * 4 + q);
+          *reinterpret_cast<uint4*>(atom + ((chunk ^ sw) << 4)) = w;
+        }
       }
-    }
+      psum = (ps0 + ps1) + (ps2 + ps3);
+    };
+    if (valid >= kBKV) softmax_block(std::false_type{});
+    else softmax_block(std::true_type{});
     l_run = l_run * alpha + psum;
 
     fence_proxy_async_smem();   // P (generic proxy) -> visible to the tensor core (async proxy)

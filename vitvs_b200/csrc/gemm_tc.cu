@@ -4,10 +4,10 @@
 //   with the consumer of C fused into the epilogue (bias / GELU / SwiGLU / LayerScale+residual /
 //   patch-embed row remap + pos-embed / similarity arg-max).
 //
-// Structure (one persistent CTA per SM, 192 threads):
+// Structure (one persistent CTA per SM, 320 threads):
 //   warp 0  lane 0 : TMA producer   - 128x64 A box + BNx64 B box per stage, SWIZZLE_128B, mbarrier tx
 //   warp 1  lane 0 : MMA issuer     - 4 x tcgen05.mma (M128, N=BN, K16) per stage, commit -> empty[stage]
-//   warps 2..5     : epilogue       - tcgen05.ld (32 lanes x 32 columns), fused op, global store
+//   warps 2..9     : epilogue       - tcgen05.ld (32 lanes x 32 columns, double buffered), fused op, global store
 //   TMEM: two accumulators of BN columns (double buffered: epilogue of tile i overlaps MMA of tile i+1)
 // Tiles are ordered N-fastest so the CTAs running at one time share A row-panels and the whole weight
 // matrix through the 126 MB L2.
@@ -25,7 +25,7 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;   // TMA warp + MMA warp + 8 epilogue warps
 
 struct GemmDev {
   int M, N, K, batch, b_batched;
@@ -54,8 +54,22 @@ struct Cfg {
   static constexpr uint32_t kSmemBytes = kStages * kStageBytes + 256 /*barriers*/ + 1024 /*align slack*/;
 };
 
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
-__device__ __forceinline__ float silu(float x) { return x / (1.0f + __expf(-x)); }
+// exact (erf) GELU = x * Phi(x), Phi(x) = 1 - q (x >= 0) or q (x < 0) with q = 0.5 erfc(|x|/sqrt2) from
+// Abramowitz-Stegun 7.1.26 (|error| <= 7.5e-8 on Phi, far below the bf16 rounding of the output):
+// 2 MUFU (rcp, ex2) + ~11 FMA-pipe instructions instead of erff()'s ~30.
+__device__ __forceinline__ float gelu_erf(float x) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  float t, e;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * -0.72134752044448170368f));   // exp(-x^2/2)
+  float pl = fmaf(t, 0.5f * 1.061405429f, 0.5f * -1.453152027f);
+  pl = fmaf(pl, t, 0.5f * 1.421413741f);
+  pl = fmaf(pl, t, 0.5f * -0.284496736f);
+  pl = fmaf(pl, t, 0.5f * 0.254829592f);
+  const float q = pl * t * e;
+  return x * (x >= 0.f ? 1.0f - q : q);
+}
+__device__ __forceinline__ float silu(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
 
 // monotone float -> uint32 map (larger float => larger key)
 __device__ __forceinline__ uint32_t ord_f32(float f) {
@@ -100,7 +114,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 4);
+      mbar_init(&tempty[a], 8);
     }
     fence_mbar_init();
   }
@@ -168,9 +182,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     __syncwarp();
   } else {
-    // ------------------------------------------------------------------ epilogue (4 warps)
+    // ------------------------------------------------------------------ epilogue (8 warps)
+    // Two warps per TMEM lane quarter; each owns half of the tile's 32-column chunks.  TMEM loads are
+    // double buffered (the load of chunk i+1 is in flight while chunk i is processed) and the residual
+    // epilogue prefetches its fp32 rows one chunk ahead, so neither latency sits on the critical path.
     const int quarter = warp & 3;             // TMEM lane quarter this warp may read
+    const int half = (warp - 2) >> 2;         // which half of the chunks
     const uint32_t lane_field = static_cast<uint32_t>(quarter * 32) << 16;
+    constexpr int NC = BN / 32;               // chunks per tile
     uint32_t acc = 0, acc_phase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int b = tile / tiles_per_batch;
@@ -179,76 +198,45 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int n_blk = r - m_blk * p.n_tiles;
       const int row = m_blk * BM + quarter * 32 + lane;     // row inside batch b
       const bool row_ok = row < p.M;
+      const size_t grow = static_cast<size_t>(b) * p.M + row;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_acc = tmem_base + acc * BN + lane_field;
 
-      if constexpr (EPI == EPI_SIM) {
-        // running row best over this tile's columns; ties -> lowest column (strict >, ascending scan)
-        float best_v = -INFINITY;
-        int best_j = 0x7fffffff;
-        const uint32_t row_tag = 0xFFFFFFFFu - static_cast<uint32_t>(row);
-#pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-          const int col0 = n_blk * BN + c * 32;
-          if (col0 >= p.N) break;            // warp-uniform
-          uint32_t raw[32];
-          tmem_ld32(t_acc + c * 32, raw);
-          tmem_ld_wait();
-          unsigned long long key[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float v = __uint_as_float(raw[j]);
-            const bool col_ok = (col0 + j) < p.N;
-            if (col_ok && v > best_v) {
-              best_v = v;
-              best_j = col0 + j;
-            }
-            key[j] = (row_ok && col_ok) ? ((static_cast<unsigned long long>(ord_f32(v)) << 32) | row_tag) : 0ull;
-          }
-          // transposed butterfly: afterwards lane L holds max over the warp's 32 rows of column col0+L
-#pragma unroll
-          for (int w = 16; w >= 1; w >>= 1) {
-            const bool upper = (lane & w) != 0;
-#pragma unroll
-            for (int i = 0; i < w; ++i) {
-              const unsigned long long send = upper ? key[i] : key[i + w];
-              const unsigned long long keep = upper ? key[i + w] : key[i];
-              const unsigned long long recv = __shfl_xor_sync(0xffffffffu, send, w);
-              key[i] = keep > recv ? keep : recv;
-            }
-          }
-          if (col0 + lane < p.N && key[0] != 0ull)
-            atomicMax(&p.col_best[static_cast<size_t>(b) * p.best_pitch + col0 + lane], key[0]);
-        }
-        if (row_ok && best_j != 0x7fffffff) {
-          const unsigned long long k =
-              (static_cast<unsigned long long>(ord_f32(best_v)) << 32) | (0xFFFFFFFFu - static_cast<uint32_t>(best_j));
-          atomicMax(&p.row_best[static_cast<size_t>(b) * p.best_pitch + row], k);
-        }
-      } else if constexpr (EPI == EPI_SWIGLU_BF16) {
+      if constexpr (EPI == EPI_SWIGLU_BF16) {
         // tile columns [0,BN/2) = x1 slice, [BN/2,BN) = matching x2 slice (rows of w12 interleaved on load)
-        const size_t grow = static_cast<size_t>(b) * p.M + row;
-#pragma unroll 1
-        for (int c = 0; c < BN / 64; ++c) {
+        constexpr int NP = NC / 4;              // (x1, x2) chunk pairs per warp
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+          const int c = half * NP + i;
           const int tcol = n_blk * BN + c * 32;                 // column in the interleaved N space
-          if (tcol >= p.N) break;
           uint32_t r1[32], r2[32];
           tmem_ld32(t_acc + c * 32, r1);
           tmem_ld32(t_acc + BN / 2 + c * 32, r2);
           tmem_ld_wait();
-          float v[32];
+          if (tcol < p.N) {
+            float v[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float x1 = __uint_as_float(r1[j]) + __ldg(p.bias + tcol + j);
-            const float x2 = __uint_as_float(r2[j]) + __ldg(p.bias + tcol + BN / 2 + j);
-            v[j] = silu(x1) * x2;
+            for (int q = 0; q < 8; ++q) {
+              const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + tcol) + q);
+              const float4 b2 = __ldg(reinterpret_cast<const float4*>(p.bias + tcol + BN / 2) + q);
+              v[q * 4 + 0] = silu(__uint_as_float(r1[q * 4 + 0]) + b1.x) * (__uint_as_float(r2[q * 4 + 0]) + b2.x);
+              v[q * 4 + 1] = silu(__uint_as_float(r1[q * 4 + 1]) + b1.y) * (__uint_as_float(r2[q * 4 + 1]) + b2.y);
+              v[q * 4 + 2] = silu(__uint_as_float(r1[q * 4 + 2]) + b1.z) * (__uint_as_float(r2[q * 4 + 2]) + b2.z);
+              v[q * 4 + 3] = silu(__uint_as_float(r1[q * 4 + 3]) + b1.w) * (__uint_as_float(r2[q * 4 + 3]) + b2.w);
+            }
+            const int hcol = n_blk * (BN / 2) + c * 32;          // hidden column
+            if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + hcol, v);
           }
-          const int hcol = n_blk * (BN / 2) + c * 32;            // hidden column
-          if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + hcol, v);
         }
       } else {
-        const size_t grow = static_cast<size_t>(b) * p.M + row;
+        constexpr int NCH = NC / 2;             // chunks per warp
+        const int c_begin = half * NCH;
+        // EPI_SIM state: running row best over this warp's columns; ties -> lowest column
+        float best_v = -INFINITY;
+        int best_j = 0x7fffffff;
+        const uint32_t row_tag = 0xFFFFFFFFu - static_cast<uint32_t>(row);
+        // EPI_PATCH_F32 row remap
         size_t orow = grow;
         const float* pos_row = nullptr;
         if constexpr (EPI == EPI_PATCH_F32) {
@@ -257,70 +245,125 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           orow = static_cast<size_t>(img) * (p.T + 1) + 1 + t;
           pos_row = p.pos + static_cast<size_t>(1 + t) * p.ldo;
         }
-#pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-          const int col0 = n_blk * BN + c * 32;
-          if (col0 >= p.N) break;            // warp-uniform (N % 32 == 0 enforced by the launcher)
-          uint32_t raw[32];
-          tmem_ld32(t_acc + c * 32, raw);
-          tmem_ld_wait();
-          float v[32];
-          if constexpr (EPI == EPI_STORE_F32) {
+        uint32_t raw[2][32];
+        float4 xin[2][8];
+        auto prefetch_x = [&](int c, float4 (&dst)[8]) {
+          if constexpr (EPI == EPI_RESID_F32) {
+            const int col0 = n_blk * BN + c * 32;
+            if (row_ok && col0 < p.N) {
+              const float4* x4 = reinterpret_cast<const float4*>(p.x_f32 + grow * p.ldo + col0);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]) + __ldg(p.bias + col0 + j);
+              for (int q = 0; q < 8; ++q) dst[q] = x4[q];
+            }
           }
-          if constexpr (EPI == EPI_BIAS_BF16) {
-            if (col0 < p.q_cols) {
+        };
+        tmem_ld32(t_acc + c_begin * 32, raw[0]);
+        prefetch_x(c_begin, xin[0]);
 #pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] *= p.q_scale;
+        for (int i = 0; i < NCH; ++i) {
+          const int c = c_begin + i;
+          const int col0 = n_blk * BN + c * 32;
+          tmem_ld_wait();
+          if (i + 1 < NCH) {
+            tmem_ld32(t_acc + (c + 1) * 32, raw[(i + 1) & 1]);
+            prefetch_x(c + 1, xin[(i + 1) & 1]);
+          }
+          const uint32_t(&rw)[32] = raw[i & 1];
+          if (col0 >= p.N) continue;            // warp-uniform (ragged last N tile)
+
+          if constexpr (EPI == EPI_SIM) {
+            unsigned long long key[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float v = __uint_as_float(rw[j]);
+              const bool col_ok = (col0 + j) < p.N;
+              if (col_ok && v > best_v) {
+                best_v = v;
+                best_j = col0 + j;
+              }
+              key[j] = (row_ok && col_ok) ? ((static_cast<unsigned long long>(ord_f32(v)) << 32) | row_tag) : 0ull;
             }
-            if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + col0, v);
-          } else if constexpr (EPI == EPI_GELU_BF16) {
+            // transposed butterfly: afterwards lane L holds max over the warp's 32 rows of column col0+L
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-            if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + col0, v);
-          } else if constexpr (EPI == EPI_RESID_F32) {
-            if (row_ok) {
-              float4* x4 = reinterpret_cast<float4*>(p.x_f32 + grow * p.ldo + col0);
-              float4 old[8];
+            for (int w = 16; w >= 1; w >>= 1) {
+              const bool upper = (lane & w) != 0;
 #pragma unroll
-              for (int q = 0; q < 8; ++q) old[q] = x4[q];
+              for (int k = 0; k < w; ++k) {
+                const unsigned long long send = upper ? key[k] : key[k + w];
+                const unsigned long long keep = upper ? key[k + w] : key[k];
+                const unsigned long long recv = __shfl_xor_sync(0xffffffffu, send, w);
+                key[k] = keep > recv ? keep : recv;
+              }
+            }
+            if (col0 + lane < p.N && key[0] != 0ull)
+              atomicMax(&p.col_best[static_cast<size_t>(b) * p.best_pitch + col0 + lane], key[0]);
+          } else {
+            float v[32];
+            if constexpr (EPI == EPI_STORE_F32) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(rw[j]);
+            } else {
 #pragma unroll
               for (int q = 0; q < 8; ++q) {
-                const float4 g = __ldg(reinterpret_cast<const float4*>(p.gamma + col0) + q);
-                old[q].x = fmaf(g.x, v[q * 4 + 0], old[q].x);
-                old[q].y = fmaf(g.y, v[q * 4 + 1], old[q].y);
-                old[q].z = fmaf(g.z, v[q * 4 + 2], old[q].z);
-                old[q].w = fmaf(g.w, v[q * 4 + 3], old[q].w);
-                x4[q] = old[q];
+                const float4 bq = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
+                v[q * 4 + 0] = __uint_as_float(rw[q * 4 + 0]) + bq.x;
+                v[q * 4 + 1] = __uint_as_float(rw[q * 4 + 1]) + bq.y;
+                v[q * 4 + 2] = __uint_as_float(rw[q * 4 + 2]) + bq.z;
+                v[q * 4 + 3] = __uint_as_float(rw[q * 4 + 3]) + bq.w;
               }
             }
-          } else if constexpr (EPI == EPI_PATCH_F32) {
-            if (row_ok) {
-              float4* x4 = reinterpret_cast<float4*>(p.x_f32 + orow * p.ldo + col0);
+            if constexpr (EPI == EPI_BIAS_BF16) {
+              if (col0 < p.q_cols) {
 #pragma unroll
-              for (int q = 0; q < 8; ++q) {
-                const float4 ps = __ldg(reinterpret_cast<const float4*>(pos_row + col0) + q);
-                x4[q] = make_float4(v[q * 4 + 0] + ps.x, v[q * 4 + 1] + ps.y, v[q * 4 + 2] + ps.z,
-                                    v[q * 4 + 3] + ps.w);
+                for (int j = 0; j < 32; ++j) v[j] *= p.q_scale;
+              }
+              if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + col0, v);
+            } else if constexpr (EPI == EPI_GELU_BF16) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+              if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + col0, v);
+            } else if constexpr (EPI == EPI_RESID_F32) {
+              if (row_ok) {
+                float4* x4 = reinterpret_cast<float4*>(p.x_f32 + grow * p.ldo + col0);
+                const float4(&old)[8] = xin[i & 1];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                  const float4 g = __ldg(reinterpret_cast<const float4*>(p.gamma + col0) + q);
+                  x4[q] = make_float4(fmaf(g.x, v[q * 4 + 0], old[q].x), fmaf(g.y, v[q * 4 + 1], old[q].y),
+                                      fmaf(g.z, v[q * 4 + 2], old[q].z), fmaf(g.w, v[q * 4 + 3], old[q].w));
+                }
+              }
+            } else if constexpr (EPI == EPI_PATCH_F32) {
+              if (row_ok) {
+                float4* x4 = reinterpret_cast<float4*>(p.x_f32 + orow * p.ldo + col0);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                  const float4 ps = __ldg(reinterpret_cast<const float4*>(pos_row + col0) + q);
+                  x4[q] = make_float4(v[q * 4 + 0] + ps.x, v[q * 4 + 1] + ps.y, v[q * 4 + 2] + ps.z,
+                                      v[q * 4 + 3] + ps.w);
+                }
+              }
+            } else if constexpr (EPI == EPI_STORE_F32) {
+              if (row_ok) {
+                float* dst = p.x_f32 + grow * p.ldo + col0;
+                if (col0 + 32 <= p.N && (p.ldo & 3) == 0) {
+                  float4* x4 = reinterpret_cast<float4*>(dst);
+#pragma unroll
+                  for (int q = 0; q < 8; ++q) x4[q] = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j)
+                    if (col0 + j < p.N) dst[j] = v[j];
+                }
               }
             }
-          } else if constexpr (EPI == EPI_STORE_F32) {
-            if (row_ok) {
-              float* dst = p.x_f32 + grow * p.ldo + col0;
-              if (col0 + 32 <= p.N && (p.ldo & 3) == 0) {
-                float4* x4 = reinterpret_cast<float4*>(dst);
-#pragma unroll
-                for (int q = 0; q < 8; ++q) x4[q] = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
-              } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                  if (col0 + j < p.N) dst[j] = v[j];
-              }
-            }
+          }
+        }
+        if constexpr (EPI == EPI_SIM) {
+          if (row_ok && best_j != 0x7fffffff) {
+            const unsigned long long k = (static_cast<unsigned long long>(ord_f32(best_v)) << 32) |
+                                         (0xFFFFFFFFu - static_cast<uint32_t>(best_j));
+            atomicMax(&p.row_best[static_cast<size_t>(b) * p.best_pitch + row], k);
           }
         }
       }
