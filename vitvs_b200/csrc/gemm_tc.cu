@@ -51,7 +51,8 @@ struct Cfg {
   static constexpr uint32_t kBBytes = BN * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr uint32_t kTmemCols = 2 * BN;
-  static constexpr uint32_t kSmemBytes = kStages * kStageBytes + 256 /*barriers*/ + 1024 /*align slack*/;
+  static constexpr uint32_t kStagingBytes = 8 * 4096;   // one 32-row x 128-byte transpose buffer per epilogue warp
+  static constexpr uint32_t kSmemBytes = kStages * kStageBytes + kStagingBytes + 256 /*barriers*/ + 1024 /*align slack*/;
 };
 
 // exact (erf) GELU = x * Phi(x), Phi(x) = 1 - q (x >= 0) or q (x < 0) with q = 0.5 erfc(|x|/sqrt2) from
@@ -96,7 +97,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint8_t* staging = smem + C::kStages * C::kStageBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(staging + C::kStagingBytes);
   uint64_t* empty = full + C::kStages;
   uint64_t* tfull = empty + C::kStages;
   uint64_t* tempty = tfull + 2;
@@ -225,9 +227,76 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               v[q * 4 + 2] = silu(__uint_as_float(r1[q * 4 + 2]) + b1.z) * (__uint_as_float(r2[q * 4 + 2]) + b2.z);
               v[q * 4 + 3] = silu(__uint_as_float(r1[q * 4 + 3]) + b1.w) * (__uint_as_float(r2[q * 4 + 3]) + b2.w);
             }
-            const int hcol = n_blk * (BN / 2) + c * 32;          // hidden column
-            if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + hcol, v);
+            // stage this 32-column chunk; the pair of chunks a warp owns forms one 128-byte-row slab
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const uint4 w = make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                         pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]));
+              *reinterpret_cast<uint4*>(staging + (warp - 2) * 4096 + lane * 128 + (((i * 4 + q) ^ (lane & 7)) << 4)) = w;
+            }
           }
+        }
+        {
+          uint8_t* stg = staging + (warp - 2) * 4096;
+          const int rr0 = lane >> 3, qq = lane & 7;
+          const int tile_row0 = m_blk * BM + quarter * 32;
+          const size_t gslab0 = static_cast<size_t>(b) * p.M + tile_row0;
+          const int hcol0 = n_blk * (BN / 2) + half * NP * 32;    // first hidden column of the slab
+          __syncwarp();
+          if (n_blk * BN + half * NP * 32 < p.N) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int rr = it * 4 + rr0;
+              const uint4 w = *reinterpret_cast<const uint4*>(stg + rr * 128 + ((qq ^ (rr & 7)) << 4));
+              if (tile_row0 + rr < p.M && qq < NP * 4)
+                *reinterpret_cast<uint4*>(p.out_bf16 + (gslab0 + rr) * p.ldo + hcol0 + qq * 8) = w;
+            }
+          }
+          __syncwarp();
+        }
+      } else if constexpr (EPI == EPI_RESID_F32) {
+        // x += gamma * (acc + bias), fp32 in place.  HBM-bound (the fp32 residual rows are read and written
+        // once per GEMM), so the loop is kept simple: per 32-column chunk the warp first issues the
+        // COALESCED loads of its 32x32 fp32 block (4 full 128-byte lines per instruction), then fetches the
+        // accumulators, transposes gamma*(acc+bias) through its swizzled smem buffer and adds.
+        constexpr int NCH = NC / 2;
+        uint8_t* stg = staging + (warp - 2) * 4096;
+        const int rr0 = lane >> 3, qq = lane & 7;
+        const int tile_row0 = m_blk * BM + quarter * 32;
+        const size_t gslab0 = static_cast<size_t>(b) * p.M + tile_row0;
+#pragma unroll 1
+        for (int i = 0; i < NCH; ++i) {
+          const int c = half * NCH + i;
+          const int col0 = n_blk * BN + c * 32;
+          if (col0 >= p.N) break;               // warp-uniform
+          float4 old[8];
+          float* xg = p.x_f32 + gslab0 * p.ldo + col0 + qq * 4;
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + rr0;
+            if (tile_row0 + rr < p.M) old[it] = *reinterpret_cast<const float4*>(xg + static_cast<size_t>(rr) * p.ldo);
+          }
+          uint32_t rw[32];
+          tmem_ld32(t_acc + c * 32, rw);
+          tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 bq = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
+            const float4 g = __ldg(reinterpret_cast<const float4*>(p.gamma + col0) + q);
+            *reinterpret_cast<float4*>(stg + lane * 128 + ((q ^ (lane & 7)) << 4)) =
+                make_float4(g.x * (__uint_as_float(rw[q * 4 + 0]) + bq.x), g.y * (__uint_as_float(rw[q * 4 + 1]) + bq.y),
+                            g.z * (__uint_as_float(rw[q * 4 + 2]) + bq.z), g.w * (__uint_as_float(rw[q * 4 + 3]) + bq.w));
+          }
+          __syncwarp();
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + rr0;
+            const float4 d = *reinterpret_cast<const float4*>(stg + rr * 128 + ((qq ^ (rr & 7)) << 4));
+            if (tile_row0 + rr < p.M)
+              *reinterpret_cast<float4*>(xg + static_cast<size_t>(rr) * p.ldo) =
+                  make_float4(old[it].x + d.x, old[it].y + d.y, old[it].z + d.z, old[it].w + d.w);
+          }
+          __syncwarp();
         }
       } else {
         constexpr int NCH = NC / 2;             // chunks per warp
@@ -245,29 +314,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           orow = static_cast<size_t>(img) * (p.T + 1) + 1 + t;
           pos_row = p.pos + static_cast<size_t>(1 + t) * p.ldo;
         }
+        // Coalescing: a thread owns one accumulator ROW, so direct global access would touch 32 different
+        // rows per warp instruction.  Instead each warp transposes its 32x(128 byte) slab through a private,
+        // XOR-swizzled smem buffer and then reads / writes global memory with 4 full 128-byte lines per
+        // instruction (lane -> row it*4 + lane/8, 16-byte chunk lane%8).
+        uint8_t* stg = staging + (warp - 2) * 4096;
+        const int rr0 = lane >> 3, qq = lane & 7;              // read-back mapping
+        const int tile_row0 = m_blk * BM + quarter * 32;       // first row of this warp's slab (inside batch b)
+        const size_t gslab0 = static_cast<size_t>(b) * p.M + tile_row0;
         uint32_t raw[2][32];
-        float4 xin[2][8];
-        auto prefetch_x = [&](int c, float4 (&dst)[8]) {
-          if constexpr (EPI == EPI_RESID_F32) {
-            const int col0 = n_blk * BN + c * 32;
-            if (row_ok && col0 < p.N) {
-              const float4* x4 = reinterpret_cast<const float4*>(p.x_f32 + grow * p.ldo + col0);
-#pragma unroll
-              for (int q = 0; q < 8; ++q) dst[q] = x4[q];
-            }
-          }
-        };
         tmem_ld32(t_acc + c_begin * 32, raw[0]);
-        prefetch_x(c_begin, xin[0]);
 #pragma unroll
         for (int i = 0; i < NCH; ++i) {
           const int c = c_begin + i;
           const int col0 = n_blk * BN + c * 32;
           tmem_ld_wait();
-          if (i + 1 < NCH) {
-            tmem_ld32(t_acc + (c + 1) * 32, raw[(i + 1) & 1]);
-            prefetch_x(c + 1, xin[(i + 1) & 1]);
-          }
+          if (i + 1 < NCH) tmem_ld32(t_acc + (c + 1) * 32, raw[(i + 1) & 1]);
           const uint32_t(&rw)[32] = raw[i & 1];
           if (col0 >= p.N) continue;            // warp-uniform (ragged last N tile)
 
@@ -312,26 +374,35 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 v[q * 4 + 3] = __uint_as_float(rw[q * 4 + 3]) + bq.w;
               }
             }
-            if constexpr (EPI == EPI_BIAS_BF16) {
-              if (col0 < p.q_cols) {
+            if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_GELU_BF16) {
+              if constexpr (EPI == EPI_BIAS_BF16) {
+                if (col0 < p.q_cols) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] *= p.q_scale;
-              }
-              if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + col0, v);
-            } else if constexpr (EPI == EPI_GELU_BF16) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-              if (row_ok) store_bf16x32(p.out_bf16 + grow * p.ldo + col0, v);
-            } else if constexpr (EPI == EPI_RESID_F32) {
-              if (row_ok) {
-                float4* x4 = reinterpret_cast<float4*>(p.x_f32 + grow * p.ldo + col0);
-                const float4(&old)[8] = xin[i & 1];
-#pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                  const float4 g = __ldg(reinterpret_cast<const float4*>(p.gamma + col0) + q);
-                  x4[q] = make_float4(fmaf(g.x, v[q * 4 + 0], old[q].x), fmaf(g.y, v[q * 4 + 1], old[q].y),
-                                      fmaf(g.z, v[q * 4 + 2], old[q].z), fmaf(g.w, v[q * 4 + 3], old[q].w));
+                  for (int j = 0; j < 32; ++j) v[j] *= p.q_scale;
                 }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+              }
+              // two 32-column chunks (64 bf16 = 128 bytes per row) form one slab
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const uint4 w = make_uint4(pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                           pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]));
+                *reinterpret_cast<uint4*>(stg + lane * 128 + ((((i & 1) * 4 + q) ^ (lane & 7)) << 4)) = w;
+              }
+              const bool slab_done = (i & 1) || (i + 1 == NCH) || (col0 + 32 >= p.N);
+              if (slab_done) {
+                const int scol0 = col0 - (i & 1) * 32;          // first column of the slab
+                __syncwarp();
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                  const int rr = it * 4 + rr0;
+                  const uint4 w = *reinterpret_cast<const uint4*>(stg + rr * 128 + ((qq ^ (rr & 7)) << 4));
+                  if (tile_row0 + rr < p.M && scol0 + qq * 8 <= col0 + 24)
+                    *reinterpret_cast<uint4*>(p.out_bf16 + (gslab0 + rr) * p.ldo + scol0 + qq * 8) = w;
+                }
+                __syncwarp();
               }
             } else if constexpr (EPI == EPI_PATCH_F32) {
               if (row_ok) {
