@@ -78,18 +78,6 @@ __device__ __forceinline__ uint32_t ord_f32(float f) {
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
-__device__ __forceinline__ void store_bf16x32(bf16* dst, const float (&v)[32]) {
-  uint4* d4 = reinterpret_cast<uint4*>(dst);
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    uint4 w;
-    w.x = pack_bf16x2(v[q * 8 + 0], v[q * 8 + 1]);
-    w.y = pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]);
-    w.z = pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]);
-    w.w = pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]);
-    d4[q] = w;
-  }
-}
 
 template <int BN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
