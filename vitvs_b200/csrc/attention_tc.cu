@@ -8,8 +8,9 @@
 //
 // One CTA = 256 query rows (two 128-row tiles) of one (image, head), warp specialised (see the kernel).
 // Per 128-key block and tile:  S = Q K^T (tcgen05, fp32 in TMEM) -> online softmax in registers (thread =
-// row = TMEM lane; two TMEM passes: max, then exp2 / sum / bf16 P to swizzled smem) -> PV = P V (tcgen05,
-// V consumed MN-major straight from its row-major tile) -> O = O * alpha + PV in registers.
+// row = TMEM lane; ONE TMEM pass: the row of S is held in registers for max, exp2, sum and the bf16 P that
+// goes to swizzled smem) -> O += P V (tcgen05, V consumed MN-major straight from its row-major tile, O
+// accumulated in TMEM across blocks with lazy rescaling) -> O / l once at the end.
 // Keys past n_tok (the next image's rows or TMA zero fill) are masked to p = 0.
 #include <cuda.h>
 
@@ -124,13 +125,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ o
           umma_bf16(tmem_base + tile * 128, umma_smem_desc(qa + k * 32, 16, 1024), umma_smem_desc(ka + k * 32, 16, 1024),
                     idescS, k != 0);
       };
-      auto issue_PV = [&](int tile, int st) {
+      auto issue_PV = [&](int tile, int st, bool first_block) {
         const uint32_t pa = sbase + kOffP + tile * kPBytes, va = sbase + kOffV + st * kTileBytes;
 #pragma unroll
         for (int kk = 0; kk < kBKV / 16; ++kk)
           umma_bf16(tmem_base + 256 + tile * 64, umma_smem_desc(pa + (kk >> 2) * (kBQ * 128) + (kk & 3) * 32, 16, 1024),
                     umma_smem_desc(va + kk * 2048, 1024, 1024),   // MN-major V: 16 keys = 2 x 1024 B groups
-                    idescPV, kk != 0);
+                    idescPV, (!first_block || kk != 0) ? 1u : 0u);   // O accumulates in TMEM across key blocks
       };
       mbar_wait(q_full, 0);
       mbar_wait(&k_full[0], 0);
@@ -147,10 +148,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ o
         const uint32_t ph = (j >> 1) & 1;
         const bool more = j + 1 < nblk;
         const int nst = (j + 1) & 1;
-        mbar_wait(&p_full[0], j & 1);              // P_A(j) written, S_A(j) and PV_A(j-1) fully read
+        mbar_wait(&p_full[0], j & 1);              // P_A(j) written, S_A(j) fully read, O_A rescaled if needed
         mbar_wait(&v_full[st], ph);
         tc_fence_after();
-        issue_PV(0, st);
+        issue_PV(0, st, j == 0);
         umma_commit(&o_full[0]);
         if (more) {
           mbar_wait(&k_full[nst], ((j + 1) >> 1) & 1);
@@ -161,7 +162,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ o
         if (has_b) {
           mbar_wait(&p_full[1], j & 1);
           tc_fence_after();
-          issue_PV(1, st);
+          issue_PV(1, st, j == 0);
           umma_commit(&o_full[1]);
           if (more) {
             issue_S(1, nst);
@@ -186,112 +187,118 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ o
       const uint32_t p_row_off = static_cast<uint32_t>(row >> 3) * 1024 + static_cast<uint32_t>(row & 7) * 128;
       const uint32_t sw = static_cast<uint32_t>(row & 7);
 
-      float o[kHD];
-#pragma unroll
-      for (int d = 0; d < kHD; ++d) o[d] = 0.f;
-      float m_run = -INFINITY;   // running max, already multiplied by log2(e)
+      float m_run = -INFINITY;   // reference max of the exponentials, already multiplied by log2(e)
       float l_run = 0.f;
 
+      // TMEM reads are the scarce resource of this kernel (~64 B/clk/SM), so every score is read exactly
+      // once: the thread pulls its whole 128-key row of S into registers, and O stays in TMEM, accumulated
+      // by the PV MMAs across key blocks.  The running max is only raised (and O / l rescaled) when a block's
+      // max exceeds it by more than 2^kRescaleLog2 - until then p = exp2(s - m_run) may exceed 1 (bounded by
+      // 256: exact in fp32 sums, representable in bf16), which leaves O / l unchanged mathematically.
+      constexpr float kRescaleLog2 = 8.0f;
       for (int j = 0; j < nblk; ++j) {
         const uint32_t par = j & 1;
         mbar_wait(&s_full[tile], par);
         tc_fence_after();
         const int valid = n_tok - j * kBKV;   // keys [0, valid) of this block exist
-        float alpha, psum;
-        // Softmax of one 128-key block.  kTail = the last, partially filled block: keys >= valid are masked
-        // (max ignores them, p = 0); full blocks carry no per-element masking.  TMEM loads are double
-        // buffered; max / sum use 4 independent accumulators to keep the FMNMX / FADD chains short.
-        auto softmax_block = [&](auto tail_tag) {
-          constexpr bool kTail = decltype(tail_tag)::value;
-          uint32_t raw[2][32];
-          float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-          tmem_ld32(tS, raw[0]);
+        uint32_t sc[4][32];                   // the row of S (fp32 bits), later reused for packed bf16 P
 #pragma unroll
-          for (int c = 0; c < kBKV / 32; ++c) {
-            tmem_ld_wait();
-            if (c + 1 < kBKV / 32) tmem_ld32(tS + (c + 1) * 32, raw[(c + 1) & 1]);
-            else tmem_ld32(tS, raw[(c + 1) & 1]);                 // first chunk again for pass 2
-            if (kTail && c * 32 >= valid) continue;
+        for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, sc[c]);
+        tmem_ld_wait();
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+        if (valid >= kBKV) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c)
 #pragma unroll
             for (int i = 0; i < 32; i += 4) {
-              float s0 = __uint_as_float(raw[c & 1][i]), s1 = __uint_as_float(raw[c & 1][i + 1]);
-              float s2 = __uint_as_float(raw[c & 1][i + 2]), s3 = __uint_as_float(raw[c & 1][i + 3]);
-              if (kTail) {
-                if (c * 32 + i + 0 >= valid) s0 = -INFINITY;
-                if (c * 32 + i + 1 >= valid) s1 = -INFINITY;
-                if (c * 32 + i + 2 >= valid) s2 = -INFINITY;
-                if (c * 32 + i + 3 >= valid) s3 = -INFINITY;
-              }
-              mx0 = fmaxf(mx0, s0);
-              mx1 = fmaxf(mx1, s1);
-              mx2 = fmaxf(mx2, s2);
-              mx3 = fmaxf(mx3, s3);
+              mx0 = fmaxf(mx0, __uint_as_float(sc[c][i]));
+              mx1 = fmaxf(mx1, __uint_as_float(sc[c][i + 1]));
+              mx2 = fmaxf(mx2, __uint_as_float(sc[c][i + 2]));
+              mx3 = fmaxf(mx3, __uint_as_float(sc[c][i + 3]));
             }
-          }
-          const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-          const float m_new = fmaxf(m_run, mx * kLog2e);
-          alpha = ex2_approx(m_run - m_new);
-          m_run = m_new;
-          const float neg_m = -m_new;
-          float ps0 = 0.f, ps1 = 0.f, ps2 = 0.f, ps3 = 0.f;
+        } else {
 #pragma unroll
-          for (int c = 0; c < kBKV / 32; ++c) {
-            tmem_ld_wait();
-            if (c + 1 < kBKV / 32) tmem_ld32(tS + (c + 1) * 32, raw[(c + 1) & 1]);   // chunk c sits in raw[c & 1]
-            const uint32_t(&rw)[32] = raw[c & 1];
-            uint8_t* atom = sP + (c >> 1) * (kBQ * 128) + p_row_off;
+          for (int c = 0; c < 4; ++c)
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              float e[8];
-#pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                e[i] = ex2_approx(fmaf(__uint_as_float(rw[q * 8 + i]), kLog2e, neg_m));
-                if (kTail && c * 32 + q * 8 + i >= valid) e[i] = 0.f;
-              }
-              ps0 += e[0] + e[4];
-              ps1 += e[1] + e[5];
-              ps2 += e[2] + e[6];
-              ps3 += e[3] + e[7];
-              const uint4 w = make_uint4(pack_bf16x2(e[0], e[1]), pack_bf16x2(e[2], e[3]), pack_bf16x2(e[4], e[5]),
-                                         pack_bf16x2(e[6], e[7]));
-              const uint32_t chunk = static_cast<uint32_t>((c & 1) * 4 + q);
-              *reinterpret_cast<uint4*>(atom + ((chunk ^ sw) << 4)) = w;
+            for (int i = 0; i < 32; ++i) {
+              if (c * 32 + i >= valid) sc[c][i] = 0xff800000u;      // -inf: ignored by the max, exp2 -> 0
+              mx0 = fmaxf(mx0, __uint_as_float(sc[c][i]));
             }
+        }
+        const float m_blk = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * kLog2e;
+        const bool raise = m_blk > m_run + kRescaleLog2;           // always true for j == 0 (m_run = -inf)
+        const float alpha = raise ? ex2_approx(m_run - m_blk) : 1.0f;
+        if (raise) m_run = m_blk;
+        const float neg_m = -m_run;
+        float ps0 = 0.f, ps1 = 0.f, ps2 = 0.f, ps3 = 0.f;
+        uint32_t pk[4][16];                   // bf16x2-packed P row
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            const float e0 = ex2_approx(fmaf(__uint_as_float(sc[c][i + 0]), kLog2e, neg_m));
+            const float e1 = ex2_approx(fmaf(__uint_as_float(sc[c][i + 1]), kLog2e, neg_m));
+            const float e2 = ex2_approx(fmaf(__uint_as_float(sc[c][i + 2]), kLog2e, neg_m));
+            const float e3 = ex2_approx(fmaf(__uint_as_float(sc[c][i + 3]), kLog2e, neg_m));
+            ps0 += e0; ps1 += e1; ps2 += e2; ps3 += e3;
+            pk[c][i / 2] = pack_bf16x2(e0, e1);
+            pk[c][i / 2 + 1] = pack_bf16x2(e2, e3);
           }
-          psum = (ps0 + ps1) + (ps2 + ps3);
-        };
-        if (valid >= kBKV) softmax_block(std::false_type{});
-        else softmax_block(std::true_type{});
-        l_run = l_run * alpha + psum;
+        l_run = l_run * alpha + ((ps0 + ps1) + (ps2 + ps3));
 
+        if (j > 0) {
+          // PV(j-1) must have finished: it reads the P buffer we are about to overwrite and writes the O
+          // accumulator a rescale would touch.
+          mbar_wait(&o_full[tile], (j - 1) & 1);
+          tc_fence_after();
+          if (__any_sync(0xffffffffu, raise)) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              uint32_t ov[32];
+              tmem_ld32(tPV + h * 32, ov);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) ov[i] = __float_as_uint(__uint_as_float(ov[i]) * alpha);
+              tmem_st32(tPV + h * 32, ov);
+            }
+            tmem_st_wait();
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint8_t* atom = sP + (c >> 1) * (kBQ * 128) + p_row_off;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t chunk = static_cast<uint32_t>((c & 1) * 4 + q);
+            *reinterpret_cast<uint4*>(atom + ((chunk ^ sw) << 4)) =
+                make_uint4(pk[c][q * 4 + 0], pk[c][q * 4 + 1], pk[c][q * 4 + 2], pk[c][q * 4 + 3]);
+          }
+        }
         fence_proxy_async_smem();   // P (generic proxy) -> visible to the tensor core (async proxy)
         tc_fence_before();
         mbar_arrive(&p_full[tile]);
-
-        mbar_wait(&o_full[tile], par);
-        tc_fence_after();
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          uint32_t pvr[32];
-          tmem_ld32(tPV + h * 32, pvr);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[h * 32 + i] = fmaf(o[h * 32 + i], alpha, __uint_as_float(pvr[i]));
-        }
       }
 
+      mbar_wait(&o_full[tile], (nblk - 1) & 1);
+      tc_fence_after();
       const int q = q0 + tile * kBQ + row;
-      if (q < n_tok) {
-        const float inv = 1.0f / l_run;
-        uint4* dst = reinterpret_cast<uint4*>(out + static_cast<size_t>(row_base + q) * D + head * kHD);
+      const float inv = 1.0f / l_run;
+      uint4* dst = reinterpret_cast<uint4*>(out + static_cast<size_t>(row_base + q) * D + head * kHD);
 #pragma unroll
-        for (int g = 0; g < 8; ++g) {
-          uint4 w;
-          w.x = pack_bf16x2(o[g * 8 + 0] * inv, o[g * 8 + 1] * inv);
-          w.y = pack_bf16x2(o[g * 8 + 2] * inv, o[g * 8 + 3] * inv);
-          w.z = pack_bf16x2(o[g * 8 + 4] * inv, o[g * 8 + 5] * inv);
-          w.w = pack_bf16x2(o[g * 8 + 6] * inv, o[g * 8 + 7] * inv);
-          dst[g] = w;
+      for (int h = 0; h < 2; ++h) {
+        uint32_t ov[32];
+        tmem_ld32(tPV + h * 32, ov);
+        tmem_ld_wait();
+        if (q < n_tok) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4 w;
+            w.x = pack_bf16x2(__uint_as_float(ov[g * 8 + 0]) * inv, __uint_as_float(ov[g * 8 + 1]) * inv);
+            w.y = pack_bf16x2(__uint_as_float(ov[g * 8 + 2]) * inv, __uint_as_float(ov[g * 8 + 3]) * inv);
+            w.z = pack_bf16x2(__uint_as_float(ov[g * 8 + 4]) * inv, __uint_as_float(ov[g * 8 + 5]) * inv);
+            w.w = pack_bf16x2(__uint_as_float(ov[g * 8 + 6]) * inv, __uint_as_float(ov[g * 8 + 7]) * inv);
+            dst[h * 4 + g] = w;
+          }
         }
       }
     }
