@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libvitvs_b200.so")
+LIB_PATH = os.environ.get("VITVS_LIB", os.path.join(HERE, "libvitvs_b200.so"))   # override: experiment builds only
 
 c_i32, c_i64, c_f32, c_f64, c_vp = C.c_int32, C.c_int64, C.c_float, C.c_double, C.c_void_p
 

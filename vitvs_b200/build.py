@@ -33,6 +33,15 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def build_variant(name: str, defines: list[str]) -> str:
+    """Experiment builds (tools/): libvitvs_b200_<name>.so with extra -D flags; load with VITVS_LIB=<path>."""
+    nvcc = _nvcc()
+    out = os.path.join(HERE, f"libvitvs_b200_{name}.so")
+    srcs = [os.path.join(CSRC, f) for f in SOURCES]
+    subprocess.check_call([nvcc, *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-shared", "-o", out, *srcs])
+    return out
+
+
 def build_library(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB

@@ -37,9 +37,13 @@ constexpr uint32_t kAttnTmemCols = 512;               // S_A 0..127 | S_B 128..2
 constexpr float kLog2e = 1.4426950408889634f;
 
 __device__ __forceinline__ float ex2_approx(float x) {   // single MUFU.EX2; ex2(-inf) = 0
+#ifdef VVS_EXPERIMENT_NO_MUFU    // timing experiment only: wrong numerics
+  return fmaf(x, 0.001f, 0.5f);
+#else
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+#endif
 }
 
 // Warp roles (384 threads = 3 warpgroups so that setmaxnreg can move registers between them):
@@ -225,6 +229,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ o
               mx0 = fmaxf(mx0, __uint_as_float(sc[c][i]));
             }
         }
+#ifdef VVS_EXPERIMENT_NO_MAX
+        mx0 = __uint_as_float(sc[0][0]); mx1 = __uint_as_float(sc[1][1]);
+#endif
         const float m_blk = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * kLog2e;
         const bool raise = m_blk > m_run + kRescaleLog2;           // always true for j == 0 (m_run = -inf)
         const float alpha = raise ? ex2_approx(m_run - m_blk) : 1.0f;
@@ -264,6 +271,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ o
             tmem_st_wait();
           }
         }
+#ifndef VVS_EXPERIMENT_NO_PSTORE
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           uint8_t* atom = sP + (c >> 1) * (kBQ * 128) + p_row_off;
@@ -274,6 +282,9 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQKV, bf16* __restrict__ o
                 make_uint4(pk[c][q * 4 + 0], pk[c][q * 4 + 1], pk[c][q * 4 + 2], pk[c][q * 4 + 3]);
           }
         }
+#else
+        if (pk[0][0] == 0x12345678u && pk[1][3] == 7u && pk[2][5] == 9u && pk[3][15] == 1u) sP[p_row_off] = 1;
+#endif
         fence_proxy_async_smem();   // P (generic proxy) -> visible to the tensor core (async proxy)
         tc_fence_before();
         mbar_arrive(&p_full[tile]);
