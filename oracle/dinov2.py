@@ -185,7 +185,7 @@ class DinoV2(nn.Module):
         return self.norm(x)[:, 0]   # head = Identity on the normed CLS token
 
 
-def build(model_type: str = "dinov2_vits14", seed: int = 0, rich: bool = True) -> DinoV2:
+def build(model_type: str = "dinov2_vits14", seed: int = 0, rich: bool = True, max_depth: int | None = None) -> DinoV2:
     """Random-init weights of the named architecture:
     Linear/Conv trunc-normal sigma 0.02, biases 0, LN (1,0), LayerScale 1.0,
     pos_embed trunc-normal 0.02, cls_token N(0, 1e-6).  fp32, CPU, eval mode.
@@ -193,6 +193,11 @@ def build(model_type: str = "dinov2_vits14", seed: int = 0, rich: bool = True) -
     affine (1+N(0,0.1), N(0,0.05)) and LayerScale gamma (U(0.5,1.5)) so that parity
     tests exercise every epilogue term instead of multiplying by 1 / adding 0."""
     arch = ARCHS[model_type]
+    if max_depth is not None and max_depth < arch.depth:
+        # the servo path hooks blocks[11] (vitvs_v2.py:484): deeper blocks never influence its output, so tests of
+        # the 24 / 40-block models may instantiate only the blocks that matter (same seed => same leading weights
+        # is NOT guaranteed vs the full model; each variant is self-consistent between oracle and GPU path)
+        arch = Arch(arch.name, arch.dim, arch.heads, max_depth, arch.swiglu)
     g = torch.Generator().manual_seed(seed)
     m = DinoV2(arch)
     with torch.no_grad():

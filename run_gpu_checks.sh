@@ -1,6 +1,6 @@
 # GPU-box check script (gpurun -- 'bash run_gpu_checks.sh [profile]'): parity tests, smoke, bench, optional ncu.
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q -p no:cacheprovider > gpurun_out/tests.log 2>&1
+timeout 1500 python -m pytest tests -m gpu -q -s -p no:cacheprovider > gpurun_out/tests.log 2>&1
 echo "exit $?" >> gpurun_out/tests.log
 timeout 300 python __graft_entry__.py --smoke > gpurun_out/smoke.log 2>&1
 echo "exit $?" >> gpurun_out/smoke.log

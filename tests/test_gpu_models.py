@@ -1,0 +1,73 @@
+"""Whole-path parity for the other DINOv2 sizes of BASELINE.json's configs (ViT-B/14, ViT-L/14, ViT-g/14 with
+the SwiGLU FFN), one synthetic frame pair each, against the fp32 oracle on the host; plus the matching +
+IBVS-only sweep of config 5 at a large token count."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import dinov2, servo  # noqa: E402
+from vitvs_b200 import synth  # noqa: E402
+
+TIE_EPS = 2e-3
+
+
+@pytest.mark.parametrize("model_type", ["dinov2_vitb14", "dinov2_vitl14", "dinov2_vitg14"])
+def test_model_family_parity(model_type):
+    from vitvs_b200 import Engine, ServoConfig
+    torch.set_num_threads(max(1, torch.get_num_threads()))
+    model = dinov2.build(model_type, seed=1, max_depth=12)        # blocks[0..11] are all the path evaluates
+    eng = Engine(ServoConfig(model_type=model_type), max_images=2)
+    eng.load_weights(model)
+    goal, cur, depth = synth.frame_pair(7)
+    out = eng.frame_pairs_to_twist(torch.from_numpy(goal[None].copy()).cuda(), torch.from_numpy(cur[None].copy()).cuda(),
+                                   torch.from_numpy(depth[None].copy()).cuda(), want_match=True)
+    torch.cuda.synchronize()
+    tok = eng.tokens_out().cpu()
+    ref_tok = torch.cat([servo.block_tokens(model, servo.preprocess_u8(im), 11) for im in (goal, cur)])
+    cos = torch.nn.functional.cosine_similarity(tok, ref_tok, dim=-1)
+    print(f"[{model_type}] token cosine min {cos.min():.6f}")
+    assert cos.min() >= 0.999                                                # north_star: descriptor cosine >= 0.999
+    ref = servo.frame_pair_to_twist(model, goal, cur, depth)
+    S, m = ref["S"], ref["match"]
+    nn1, nn2 = out["nn1"][0].cpu().numpy(), out["nn2"][0].cpu().numpy()
+    rows = np.arange(S.shape[0])
+    bad1, bad2 = nn1 != m.nn1, nn2 != m.nn2
+    marg1 = (S[rows, m.nn1] - S[rows, nn1]).numpy()
+    marg2 = (S[m.nn2, rows] - S[nn2, rows]).numpy()
+    print(f"[{model_type}] nn1 agree {1 - bad1.mean():.4f} nn2 agree {1 - bad2.mean():.4f} "
+          f"worst margin {max(marg1.max(), marg2.max()):.2e}")
+    assert bad1.mean() <= 0.01 and bad2.mean() <= 0.01                       # >= 99 % index agreement ...
+    assert np.all(marg1[bad1] < TIE_EPS) and np.all(marg2[bad2] < TIE_EPS)   # ... disagreements only at near-ties
+    uv, uvs = out["uv"][0].cpu().numpy().astype(int), out["uv_star"][0].cpu().numpy().astype(int)
+    tw_ref = servo.ibvs_twist(uv, uvs, depth)
+    tw = out["twist"][0].cpu().numpy()
+    assert np.abs(tw - tw_ref).max() <= 1e-9 * np.abs(tw_ref).max()
+    if np.array_equal(out["sel_tok"][0].cpu().numpy(), ref["chosen"]):
+        rel = np.abs(tw - ref["twist"]).max() / np.abs(ref["twist"]).max()
+        print(f"[{model_type}] identical selection, twist rel err {rel:.2e}")
+        assert rel <= 1e-3                                                   # twist relative error <= 1e-3
+    eng.close()
+
+
+@pytest.mark.parametrize("T,d", [(4096, 384), (2304, 768)])
+def test_matching_sweep_large_grid(T, d):
+    """BASELINE config 5: i.i.d. Gaussian descriptors, planted permutation + noise, unbinned."""
+    from vitvs_b200 import Engine, ServoConfig
+    eng = Engine(ServoConfig(model_type="dinov2_vits14"), max_images=2, max_match_tokens=2 * T, max_match_dim=d)
+    a, b, perm = synth.descriptor_sets(T, d, seed=7, noise=0.5)
+    r = eng.match(torch.stack([a, a]), torch.stack([b, b]), num_pairs=24)          # two identical episodes
+    torch.cuda.synchronize()
+    S = servo.cosine_similarity_matrix(a[None, None], b[None, None])[0, 0]
+    m = servo.match(S)
+    nn1, nn2 = r["nn1"][0].cpu().numpy(), r["nn2"][0].cpu().numpy()
+    assert (nn1 == m.nn1).mean() >= 0.99 and (nn2 == m.nn2).mean() >= 0.99
+    inv = np.empty(T, dtype=np.int64)
+    inv[perm.numpy()] = np.arange(T)
+    assert (nn1 == inv).mean() >= 0.99                                           # the planted matches are recovered
+    assert torch.equal(r["nn1"][0], r["nn1"][1]) and torch.equal(r["uv"][0], r["uv"][1])
+    grid = int(np.sqrt(T))
+    uv = r["uv"][0].cpu().numpy()
+    assert uv[:, 0].max() < 640 and uv[:, 1].max() < 480 and uv.min() >= 0
+    eng.close()
