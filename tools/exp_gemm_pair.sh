@@ -1,0 +1,6 @@
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -q -x -p no:cacheprovider > gpurun_out/tests2.log 2>&1; echo "exit $?" >> gpurun_out/tests2.log
+tail -5 gpurun_out/tests2.log
+timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/bench_2cta.log 2>&1; echo "exit $?" >> gpurun_out/bench_2cta.log
+VITVS_GEMM_CTAS=1 timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/bench_1cta.log 2>&1; echo "exit $?" >> gpurun_out/bench_1cta.log
+tail -c 600 gpurun_out/bench_2cta.log

@@ -4,6 +4,10 @@
 //   with the consumer of C fused into the epilogue (bias / GELU / SwiGLU / LayerScale+residual /
 //   patch-embed row remap + pos-embed / similarity arg-max).
 //
+// Default: CTA PAIRS (cluster of 2 = one TPC) compute 256 x BN tiles with tcgen05.mma.cta_group::2 - each CTA
+// stages its own 128 rows of A and half of the B tile, the leader CTA issues the MMAs, both CTAs run the
+// epilogue on their own 128 accumulator rows in their own TMEM.  VITVS_GEMM_CTAS=1 keeps the 1-CTA kernels.
+//
 // Structure (one persistent CTA per SM, 320 threads):
 //   warp 0  lane 0 : TMA producer   - 128x64 A box + BNx64 B box per stage, SWIZZLE_128B, mbarrier tx
 //   warp 1  lane 0 : MMA issuer     - 4 x tcgen05.mma (M128, N=BN, K16) per stage, commit -> empty[stage]
@@ -14,6 +18,7 @@
 #include <cuda.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <string>
 
 #include "ptx.cuh"
@@ -44,11 +49,15 @@ struct GemmDev {
   int best_pitch;
 };
 
-template <int BN>
+// NCTA = 2: a CTA pair (cluster of 2 on one TPC) computes a 256 x BN tile with cta_group::2 MMAs; each CTA
+// stages its own 128 rows of A and HALF of the B tile, so the L2 -> SM operand traffic per flop drops by a
+// third against the 1-CTA 128 x 256 tile (measured: the 1-CTA kernel saturates the L2 -> SM fabric at
+// ~13-15 TB/s while the tensor pipe idles).
+template <int BN, int NCTA>
 struct Cfg {
-  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kStages = (NCTA == 2) ? 6 : ((BN == 256) ? 4 : 6);
   static constexpr uint32_t kABytes = BM * BK * 2;
-  static constexpr uint32_t kBBytes = BN * BK * 2;
+  static constexpr uint32_t kBBytes = (BN / NCTA) * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr uint32_t kTmemCols = 2 * BN;
   static constexpr uint32_t kStagingBytes = 8 * 4096;   // one 32-row x 128-byte transpose buffer per epilogue warp
@@ -80,10 +89,10 @@ __device__ __forceinline__ uint32_t ord_f32(float f) {
 }
 
 
-template <int BN, int EPI>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+template <int BN, int EPI, int NCTA>
+__global__ void __cluster_dims__(NCTA, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmDev p) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, NCTA>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + C::kStages * C::kStageBytes;
@@ -95,44 +104,61 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = (NCTA == 2) ? cluster_ctarank() : 0u;   // 0 = leader (issues the MMAs)
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     for (int s = 0; s < C::kStages; ++s) {
-      mbar_init(&full[s], 1);
+      mbar_init(&full[s], 1);     // pair: only the leader's is used; its expect_tx covers both CTAs' boxes
       mbar_init(&empty[s], 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 8);
+      mbar_init(&tempty[a], 8 * NCTA);   // pair: the peer's epilogue warps arrive on the leader's barrier
     }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc<C::kTmemCols>(tmem_slot);
+  if (warp == 1) {
+    if constexpr (NCTA == 2) tmem_alloc_2sm<C::kTmemCols>(tmem_slot);
+    else tmem_alloc<C::kTmemCols>(tmem_slot);
+  }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (NCTA == 2) cluster_sync_all();   // peer barriers initialised before any remote arrive / TMA signal
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // p.m_tiles counts (128 * NCTA)-row tiles; this CTA owns 128-row block m_tile * NCTA + cta_rank of each
   const int tiles_per_batch = p.m_tiles * p.n_tiles;
   const int total_tiles = p.batch * tiles_per_batch;
+  const int first_tile = blockIdx.x / NCTA;
+  const int tile_step = gridDim.x / NCTA;
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const uint32_t full0 = (NCTA == 2) ? mapa_shared(smem_u32(&full[0]), 0) : 0u;   // leader's full[] in cluster space
+      for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
         const int b = tile / tiles_per_batch;
         const int r = tile - b * tiles_per_batch;
-        const int m_blk = r / p.n_tiles;
-        const int n_blk = r - m_blk * p.n_tiles;
+        const int m_blk = (r / p.n_tiles) * NCTA + static_cast<int>(cta_rank);
+        const int n_blk = r % p.n_tiles;
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
-          mbar_expect_tx(&full[stage], C::kStageBytes);
-          tma_load_3d(sa, &tmA, &full[stage], kb * BK, m_blk * BM, b, kEvictNormal);
-          tma_load_3d(sa + C::kABytes, &tmB, &full[stage], kb * BK, n_blk * BN, p.b_batched ? b : 0, kEvictLast);
+          if constexpr (NCTA == 2) {
+            if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
+            const uint32_t fb = full0 + stage * 8;
+            tma_load_3d_2sm(sa, &tmA, fb, kb * BK, m_blk * BM, b, kEvictNormal);
+            tma_load_3d_2sm(sa + C::kABytes, &tmB, fb, kb * BK, n_blk * BN + static_cast<int>(cta_rank) * (BN / 2),
+                            p.b_batched ? b : 0, kEvictLast);
+          } else {
+            mbar_expect_tx(&full[stage], C::kStageBytes);
+            tma_load_3d(sa, &tmA, &full[stage], kb * BK, m_blk * BM, b, kEvictNormal);
+            tma_load_3d(sa + C::kABytes, &tmB, &full[stage], kb * BK, n_blk * BN, p.b_batched ? b : 0, kEvictLast);
+          }
           if (++stage == C::kStages) {
             stage = 0;
             phase ^= 1;
@@ -143,10 +169,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN, false);
+    if (lane == 0 && cta_rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM * NCTA, BN, false);
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -157,16 +183,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t b_addr = a_addr + C::kABytes;
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            umma_bf16(d_tmem, umma_smem_desc(a_addr + k * 32, 16, 1024), umma_smem_desc(b_addr + k * 32, 16, 1024),
-                      idesc, (kb | k) != 0 ? 1u : 0u);
+            const uint64_t da = umma_smem_desc(a_addr + k * 32, 16, 1024), db = umma_smem_desc(b_addr + k * 32, 16, 1024);
+            if constexpr (NCTA == 2) umma_bf16_2sm(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            else umma_bf16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
           }
-          umma_commit(&empty[stage]);
+          if constexpr (NCTA == 2) umma_commit_2sm(&empty[stage], 3);   // frees the stage in both CTAs
+          else umma_commit(&empty[stage]);
           if (++stage == C::kStages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(&tfull[acc]);
+        if constexpr (NCTA == 2) umma_commit_2sm(&tfull[acc], 3);
+        else umma_commit(&tfull[acc]);
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
@@ -182,11 +211,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const uint32_t lane_field = static_cast<uint32_t>(quarter * 32) << 16;
     constexpr int NC = BN / 32;               // chunks per tile
     uint32_t acc = 0, acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    const uint32_t tempty0 = (NCTA == 2) ? mapa_shared(smem_u32(&tempty[0]), 0) : 0u;   // leader's tempty[]
+    for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
       const int b = tile / tiles_per_batch;
       const int r = tile - b * tiles_per_batch;
-      const int m_blk = r / p.n_tiles;
-      const int n_blk = r - m_blk * p.n_tiles;
+      const int m_blk = (r / p.n_tiles) * NCTA + static_cast<int>(cta_rank);
+      const int n_blk = r % p.n_tiles;
       const int row = m_blk * BM + quarter * 32 + lane;     // row inside batch b
       const bool row_ok = row < p.M;
       const size_t grow = static_cast<size_t>(b) * p.M + row;
@@ -429,15 +459,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[acc]);
+      if (lane == 0) {
+        if constexpr (NCTA == 2) mbar_arrive_cluster(tempty0 + acc * 8);
+        else mbar_arrive(&tempty[acc]);
+      }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
   }
 
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc<C::kTmemCols>(tmem_base);
+  if constexpr (NCTA == 2) {
+    cluster_sync_all();   // the peer may still be reading operands / signalling barriers of this CTA
+    if (warp == 1) tmem_dealloc_2sm<C::kTmemCols>(tmem_base);
+  } else {
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<C::kTmemCols>(tmem_base);
+  }
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -458,33 +496,33 @@ EncodeTiledFn get_encode_fn(std::string* err) {
   return fn;
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, int NCTA>
 int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmDev& d, int grid, cudaStream_t stream,
                std::string* err) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, NCTA>;
   static bool attr_set = false;
   if (!attr_set) {
-    VVS_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    VVS_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      static_cast<int>(C::kSmemBytes)),
                 err);
     attr_set = true;
   }
-  gemm_tc_kernel<BN, EPI><<<grid, kGemmThreads, C::kSmemBytes, stream>>>(tmA, tmB, d);
+  gemm_tc_kernel<BN, EPI, NCTA><<<grid, kGemmThreads, C::kSmemBytes, stream>>>(tmA, tmB, d);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }
 
-template <int BN>
+template <int BN, int NCTA>
 int dispatch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmDev& d, int grid,
                  cudaStream_t stream, std::string* err) {
   switch (epi) {
-    case EPI_BIAS_BF16: return launch_one<BN, EPI_BIAS_BF16>(tmA, tmB, d, grid, stream, err);
-    case EPI_GELU_BF16: return launch_one<BN, EPI_GELU_BF16>(tmA, tmB, d, grid, stream, err);
-    case EPI_RESID_F32: return launch_one<BN, EPI_RESID_F32>(tmA, tmB, d, grid, stream, err);
-    case EPI_PATCH_F32: return launch_one<BN, EPI_PATCH_F32>(tmA, tmB, d, grid, stream, err);
-    case EPI_SWIGLU_BF16: return launch_one<BN, EPI_SWIGLU_BF16>(tmA, tmB, d, grid, stream, err);
-    case EPI_SIM: return launch_one<BN, EPI_SIM>(tmA, tmB, d, grid, stream, err);
-    case EPI_STORE_F32: return launch_one<BN, EPI_STORE_F32>(tmA, tmB, d, grid, stream, err);
+    case EPI_BIAS_BF16: return launch_one<BN, EPI_BIAS_BF16, NCTA>(tmA, tmB, d, grid, stream, err);
+    case EPI_GELU_BF16: return launch_one<BN, EPI_GELU_BF16, NCTA>(tmA, tmB, d, grid, stream, err);
+    case EPI_RESID_F32: return launch_one<BN, EPI_RESID_F32, NCTA>(tmA, tmB, d, grid, stream, err);
+    case EPI_PATCH_F32: return launch_one<BN, EPI_PATCH_F32, NCTA>(tmA, tmB, d, grid, stream, err);
+    case EPI_SWIGLU_BF16: return launch_one<BN, EPI_SWIGLU_BF16, NCTA>(tmA, tmB, d, grid, stream, err);
+    case EPI_SIM: return launch_one<BN, EPI_SIM, NCTA>(tmA, tmB, d, grid, stream, err);
+    case EPI_STORE_F32: return launch_one<BN, EPI_STORE_F32, NCTA>(tmA, tmB, d, grid, stream, err);
     default: set_error(err, "launch_gemm: unknown epilogue"); return VVS_ERR_INVALID;
   }
 }
@@ -537,6 +575,11 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
     return VVS_ERR_INVALID;
   }
   const int bn = gemm_block_n(a.N);
+  // CTA pairs by default; VITVS_GEMM_CTAS=1 selects the single-CTA kernels (A/B experiments)
+  static const int ncta = []() {
+    const char* e = getenv("VITVS_GEMM_CTAS");
+    return (e && e[0] == '1') ? 1 : 2;
+  }();
   if (a.epilogue == EPI_SWIGLU_BF16 && a.N % bn) {
     set_error(err, "launch_gemm: SwiGLU needs N to be a multiple of the N tile");
     return VVS_ERR_INVALID;
@@ -545,20 +588,25 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   int rc = make_tmap_bf16(&tmA, a.A, a.K, a.M, a.batch, a.lda, a.a_batch_pitch, BM, err);
   if (rc) return rc;
   const bool b_batched = a.b_batch_pitch != 0;
-  rc = make_tmap_bf16(&tmB, a.B, a.K, a.N, b_batched ? a.batch : 1, a.ldb, a.b_batch_pitch, bn, err);
+  rc = make_tmap_bf16(&tmB, a.B, a.K, a.N, b_batched ? a.batch : 1, a.ldb, a.b_batch_pitch, bn / ncta, err);
   if (rc) return rc;
   GemmDev d;
   d.M = a.M; d.N = a.N; d.K = a.K; d.batch = a.batch; d.b_batched = b_batched ? 1 : 0;
-  d.m_tiles = (a.M + BM - 1) / BM;
+  d.m_tiles = (a.M + BM * ncta - 1) / (BM * ncta);
   d.n_tiles = (a.N + bn - 1) / bn;
   d.num_kb = (a.K + BK - 1) / BK;
   d.bias = a.bias; d.gamma = a.gamma; d.x_f32 = a.x_f32; d.out_bf16 = a.out_bf16; d.ldo = a.ldo;
   d.q_cols = a.q_cols; d.q_scale = a.q_scale; d.pos = a.pos; d.T = a.T;
   d.row_best = a.row_best; d.col_best = a.col_best; d.best_pitch = a.best_pitch;
   const long long tiles = static_cast<long long>(d.batch) * d.m_tiles * d.n_tiles;
+  if (ncta == 2) {
+    const int grid = 2 * static_cast<int>(std::min<long long>(tiles, num_sms / 2));
+    if (bn == 256) return dispatch_epi<256, 2>(a.epilogue, tmA, tmB, d, grid, stream, err);
+    return dispatch_epi<128, 2>(a.epilogue, tmA, tmB, d, grid, stream, err);
+  }
   const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
-  if (bn == 256) return dispatch_epi<256>(a.epilogue, tmA, tmB, d, grid, stream, err);
-  return dispatch_epi<128>(a.epilogue, tmA, tmB, d, grid, stream, err);
+  if (bn == 256) return dispatch_epi<256, 1>(a.epilogue, tmA, tmB, d, grid, stream, err);
+  return dispatch_epi<128, 1>(a.epilogue, tmA, tmB, d, grid, stream, err);
 }
 
 }  // namespace vvs
