@@ -73,6 +73,36 @@ def test_gemm_bias_bf16_qscale(eng, M, N, K):
     assert rel < 1e-2                     # bf16 output rounding (2^-9)
 
 
+def test_gemm_bias_bf16_ragged_tails(eng):
+    """M and N tails of the TMA-store epilogue: 37 rows (one partial 32-row slab), N = 96 (half-filled slab)."""
+    M, N, K = 37, 96, 128
+    A = _rand((M, K), 50, dtype=torch.bfloat16)
+    B = _rand((N, K), 51, 0.05, dtype=torch.bfloat16)
+    bias = _rand((N,), 52, 0.1)
+    out = torch.full((M + 3, N), 9.0, dtype=torch.bfloat16, device="cuda")      # 3 guard rows
+    eng.dbg_gemm(A, B, _lib.EPI_BIAS_BF16, bias=bias, out_bf16=out, ldo=N, q_cols=0, q_scale=1.0)
+    torch.cuda.synchronize()
+    _, rel = _report("gemm bias bf16 tails", out[:M], A.float() @ B.float().T + bias)
+    assert rel < 1e-2
+    assert torch.all(out[M:] == 9.0)              # rows past M untouched (TMA clips)
+
+
+def test_gemm_residual_f32_exact_add(eng):
+    """The residual epilogue reduce-adds d = gamma*(acc+bias) into x at the L2: with x = 0 the result must be
+    exactly d, and adding into a non-zero x must equal fp32 x + d bit for bit."""
+    M, N, K = 300, 768, 256
+    A = _rand((M, K), 53, dtype=torch.bfloat16)
+    B = _rand((N, K), 54, 0.05, dtype=torch.bfloat16)
+    bias, gamma = _rand((N,), 55, 0.1), _rand((N,), 56)
+    d = torch.zeros(M, N, device="cuda")
+    eng.dbg_gemm(A, B, _lib.EPI_RESID_F32, bias=bias, gamma=gamma, x_f32=d, ldo=N)
+    x0 = _rand((M, N), 57)
+    x = x0.clone()
+    eng.dbg_gemm(A, B, _lib.EPI_RESID_F32, bias=bias, gamma=gamma, x_f32=x, ldo=N)
+    torch.cuda.synchronize()
+    assert torch.equal(x, x0 + d)
+
+
 def test_gemm_gelu_bf16(eng):
     M, N, K = 970, 1536, 384
     A = _rand((M, K), 8, dtype=torch.bfloat16)
