@@ -10,10 +10,11 @@
 // sequence at the default 485 tokens - sharing every K / V block (64 keys) of a 4-stage TMA ring:
 //   warps 0-15   four softmax warpgroups, one per query tile (thread = query row = TMEM lane)
 //   warps 16-19  one MMA issuer thread per tile (issuer 0 is also the TMA producer)
-// The kernel is bound by MUFU.EX2 (N^2 exponentials per head) and by the TMEM read of S (64 B/clk/SM),
-// both ~512 clk per 128 x 64 block, not by the tensor pipe; what matters is keeping those two busy.  Four
+// The kernel is not tensor-bound: per 128 x 64 block the MMAs need ~64 clk, the 8192 exponentials 512 clk of
+// MUFU, and the softmax instruction stream (~350 warp instructions per block and warp) several times that
+// (measured: removing every MUFU.EX2 shortens the kernel by 9 %, removing the TMEM reads by nothing).  Four
 // softmax warps per SM sub-partition (one from each warpgroup) give the scheduler something to issue while
-// a warp waits on TMEM / MUFU / an mbarrier, and the MMA warp runs S one block ahead of every warpgroup:
+// a warp waits on a dependency / MUFU / an mbarrier, and each tile's S runs one block ahead of its warpgroup:
 //   S_t(j+1) = Q_t K(j+1)^T is issued as soon as warpgroup t has pulled S_t(j) into registers;
 //   softmax t: max / exp2 / sum on the row in registers (packed fp32x2 FMA / ADD), bf16 P -> swizzled smem;
 //   O_t += P_t V(j) (V consumed MN-major from its row-major tile), O accumulated in TMEM across blocks and
@@ -243,14 +244,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       uint32_t pk0[16];
 #pragma unroll
       for (int i = 0; i < 32; i += 4) {
-        float a0, a1, a2, a3;
-        f2_unpack(f2_fma(f2_pack(__uint_as_float(sc[0][i + 0]), __uint_as_float(sc[0][i + 1])), log2e2, neg_m2), a0, a1);
-        f2_unpack(f2_fma(f2_pack(__uint_as_float(sc[0][i + 2]), __uint_as_float(sc[0][i + 3])), log2e2, neg_m2), a2, a3);
-        const float e0 = ex2_approx(a0), e1 = ex2_approx(a1), e2 = ex2_approx(a2), e3 = ex2_approx(a3);
-        ps01 = f2_add(ps01, f2_pack(e0, e1));
-        ps23 = f2_add(ps23, f2_pack(e2, e3));
-        pk0[i / 2] = pack_bf16x2(e0, e1);
-        pk0[i / 2 + 1] = pack_bf16x2(e2, e3);
+        const f32x2 e01 = f2_ex2(f2_fma(f2_pack(__uint_as_float(sc[0][i + 0]), __uint_as_float(sc[0][i + 1])), log2e2, neg_m2));
+        const f32x2 e23 = f2_ex2(f2_fma(f2_pack(__uint_as_float(sc[0][i + 2]), __uint_as_float(sc[0][i + 3])), log2e2, neg_m2));
+        ps01 = f2_add(ps01, e01);
+        ps23 = f2_add(ps23, e23);
+        pk0[i / 2] = f2_to_bf16x2(e01);
+        pk0[i / 2 + 1] = f2_to_bf16x2(e23);
       }
       if (j >= 1) {
         mbar_wait(&pv_done[t], (j - 1) & 1);    // PV(j-1) has finished: P buffer free, O quiescent
@@ -278,14 +277,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int i = q * 8 + h * 4;
-          float a0, a1, a2, a3;
-          f2_unpack(f2_fma(f2_pack(__uint_as_float(sc[1][i + 0]), __uint_as_float(sc[1][i + 1])), log2e2, neg_m2), a0, a1);
-          f2_unpack(f2_fma(f2_pack(__uint_as_float(sc[1][i + 2]), __uint_as_float(sc[1][i + 3])), log2e2, neg_m2), a2, a3);
-          const float e0 = ex2_approx(a0), e1 = ex2_approx(a1), e2 = ex2_approx(a2), e3 = ex2_approx(a3);
-          ps01 = f2_add(ps01, f2_pack(e0, e1));
-          ps23 = f2_add(ps23, f2_pack(e2, e3));
-          pk[h * 2 + 0] = pack_bf16x2(e0, e1);
-          pk[h * 2 + 1] = pack_bf16x2(e2, e3);
+          const f32x2 e01 = f2_ex2(f2_fma(f2_pack(__uint_as_float(sc[1][i + 0]), __uint_as_float(sc[1][i + 1])), log2e2, neg_m2));
+          const f32x2 e23 = f2_ex2(f2_fma(f2_pack(__uint_as_float(sc[1][i + 2]), __uint_as_float(sc[1][i + 3])), log2e2, neg_m2));
+          ps01 = f2_add(ps01, e01);
+          ps23 = f2_add(ps23, e23);
+          pk[h * 2 + 0] = f2_to_bf16x2(e01);
+          pk[h * 2 + 1] = f2_to_bf16x2(e23);
         }
         st_shared_v4(p_row_s + ((static_cast<uint32_t>(4 + q) ^ sw) << 4), pk[0], pk[1], pk[2], pk[3]);
       }

@@ -38,24 +38,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 // A wait that lasts seconds is a protocol bug (lost arrive / wrong parity): trap instead of hanging the GPU.
-#ifndef VVS_WAIT_TIMEOUT_CYCLES
-#define VVS_WAIT_TIMEOUT_CYCLES 6000000000ll
-#endif
+// The fast path is one try_wait; the slow path counts failed polls (no clock reads, no printf: both cost
+// registers and instructions in the callers' hot loops) and traps after ~2^28 of them.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
 #ifdef VVS_NO_WAIT_TRAP
   while (!mbar_try_wait(bar, parity)) {
   }
-  return;
-#endif
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
+#else
+  uint32_t polls = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > VVS_WAIT_TIMEOUT_CYCLES) {
-      printf("vitvs_b200: mbarrier wait timed out (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y, blockIdx.z,
-             threadIdx.x);
-      __trap();
-    }
+    if (++polls == (1u << 28)) __trap();
   }
+#endif
 }
 
 // ----------------------------------------------------------------------------- TMA
@@ -210,6 +205,28 @@ __device__ __forceinline__ f32x2 f2_fma(f32x2 a, f32x2 b, f32x2 c) {
   f32x2 d;
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
   return d;
+}
+// two MUFU.EX2 on a register pair, result again a pair (no repacking moves)
+__device__ __forceinline__ f32x2 f2_ex2(f32x2 a) {
+  f32x2 d;
+  asm("{\n\t.reg .f32 lo, hi;\n\t"
+      "mov.b64 {lo, hi}, %1;\n\t"
+      "ex2.approx.ftz.f32 lo, lo;\n\t"
+      "ex2.approx.ftz.f32 hi, hi;\n\t"
+      "mov.b64 %0, {lo, hi};\n\t}"
+      : "=l"(d)
+      : "l"(a));
+  return d;
+}
+// bf16x2 of a pair (low half -> low 16 bits)
+__device__ __forceinline__ uint32_t f2_to_bf16x2(f32x2 a) {
+  uint32_t r;
+  asm("{\n\t.reg .f32 lo, hi;\n\t"
+      "mov.b64 {lo, hi}, %1;\n\t"
+      "cvt.rn.bf16x2.f32 %0, hi, lo;\n\t}"
+      : "=r"(r)
+      : "l"(a));
+  return r;
 }
 __device__ __forceinline__ f32x2 f2_add(f32x2 a, f32x2 b) {
   f32x2 d;
