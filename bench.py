@@ -253,6 +253,29 @@ def run_ours(args):
     barrier()
     ms_e2e = e2.elapsed_time(e3)
 
+    # ---- p50 single frame-pair latency (the metric's second half): one pair per call through the same
+    # host-buffer C-ABI call (H2D + device path as one CUDA-graph replay + D2H + sync), wall clock per call
+    latency = None
+    if rank == 0:
+        eng1 = Engine(cfg, max_images=2)
+        eng1.load_weights(random_state_dict(args.model, seed=0, max_block=cfg.layer))
+        g1, c1, d1 = (t[:1].clone().pin_memory() for t in sets_host[0])
+        tw1 = torch.empty(1, 6, dtype=torch.float64).pin_memory()
+        ns1 = torch.empty(1, dtype=torch.int32).pin_memory()
+        for _ in range(20):
+            eng1.frame_pairs_to_twist_host(g1, c1, d1, tw1, ns1)
+        lat = []
+        for _ in range(200):
+            t0 = time.perf_counter()
+            eng1.frame_pairs_to_twist_host(g1, c1, d1, tw1, ns1)
+            lat.append((time.perf_counter() - t0) * 1e3)
+        lat.sort()
+        latency = {"p50_ms": round(lat[len(lat) // 2], 4), "p95_ms": round(lat[int(len(lat) * 0.95)], 4),
+                   "min_ms": round(lat[0], 4), "calls": len(lat), "warmup": 20, "pairs_per_call": 1,
+                   "timing": "host wall clock around vvs_frame_pairs_to_twist_host (pinned buffers; H2D, device "
+                             "path replayed as one CUDA graph, D2H, stream sync)"}
+        eng1.close()
+
     if world > 1:
         t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -308,6 +331,7 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": UNIT,
                     "h2d_bytes_per_step": B * (2 * S * S * 3 + cfg.u_max * cfg.v_max * 2),
                     "d2h_bytes_per_step": B * (6 * 8 + 4 + 4), "ms_per_step": ms_e2e / args.steps},
+            "latency": latency,
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "tensor", "kernel": f"gemm_tc_kernel ({dom})", "achieved": round(achieved, 1),

@@ -116,6 +116,13 @@ struct vvs_ctx {
   std::vector<cudaEvent_t> prof_events;
   std::vector<int> prof_class;      // class of the i-th (start, stop) event pair
   size_t prof_used = 0;
+  // host-buffer entry point: own stream (graphs cannot be captured on the legacy default stream) and one
+  // instantiated CUDA graph of the whole device path per batch size (launch-bound at small batches)
+  cudaStream_t own_stream = nullptr;
+  struct GraphEntry { int n_pairs; int want_mean; cudaGraphExec_t exec; };
+  std::vector<GraphEntry> graphs;
+  std::vector<int> eager_calls;      // n_pairs values that already ran eagerly once (lazy init done)
+  bool graphs_enabled = true;
 };
 
 namespace {
@@ -473,12 +480,20 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
     vvs_destroy(c);
     return VVS_ERR_CUDA;
   }
+  if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    g_create_error = "vvs_create: cudaStreamCreateWithFlags failed";
+    vvs_destroy(c);
+    return VVS_ERR_CUDA;
+  }
+  if (const char* e = getenv("VITVS_GRAPHS")) c->graphs_enabled = e[0] != '0';
   *out = c;
   return VVS_OK;
 }
 
 int vvs_destroy(vvs_handle c) {
   if (!c) return VVS_OK;
+  for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
   void* ptrs[] = {c->pe_w, c->pe_b, c->cls, c->pos, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
                   c->nn1, c->nn2, c->sim1, c->cand, c->mean_sim1, c->n_cand, c->n_sel, c->flags, c->mean_sel,
                   c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth};
@@ -667,6 +682,9 @@ int vvs_frame_pairs_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8
     return fail(c, VVS_ERR_INVALID, "vvs_frame_pairs_to_twist_host: null argument");
   if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // the legacy default stream cannot be captured into a graph: the call is synchronous anyway, so it runs on
+  // the handle's own stream in that case
+  if (s == nullptr || s == cudaStreamLegacy) s = c->own_stream;
   const size_t img_bytes = static_cast<size_t>(c->cfg.image_size) * c->cfg.image_size * 3;
   const size_t depth_elems = static_cast<size_t>(c->cfg.frame_width) * c->cfg.frame_height;
   VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img, goal, n_pairs * img_bytes, cudaMemcpyHostToDevice, s), &c->err);
@@ -678,8 +696,40 @@ int vvs_frame_pairs_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8
   memset(&o, 0, sizeof(o));
   o.twist = c->twist;
   o.mean_sim_sel = mean_sim_sel ? c->mean_sel : nullptr;
-  int rc = pairs_to_twist(c, c->stage_img, c->stage_img + n_pairs * img_bytes, c->stage_depth, n_pairs, &o, s);
-  if (rc) return rc;
+  const int want_mean = mean_sim_sel ? 1 : 0;
+  int rc = VVS_OK;
+  // Every pointer of the device path is now a workspace address, so the ~100 launches replay as one graph.
+  // First call per batch size runs eagerly (lazy function attributes), the second is captured.
+  cudaGraphExec_t exec = nullptr;
+  if (c->graphs_enabled && !c->prof_on) {
+    for (auto& g : c->graphs)
+      if (g.n_pairs == n_pairs && g.want_mean == want_mean) exec = g.exec;
+    const bool warmed = std::find(c->eager_calls.begin(), c->eager_calls.end(), n_pairs) != c->eager_calls.end();
+    if (!exec && warmed && c->graphs.size() < 16) {
+      cudaGraph_t graph = nullptr;
+      if (cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+        rc = pairs_to_twist(c, c->stage_img, c->stage_img + n_pairs * img_bytes, c->stage_depth, n_pairs, &o, s);
+        const cudaError_t e = cudaStreamEndCapture(s, &graph);
+        if (rc == VVS_OK && e == cudaSuccess && graph &&
+            cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess) {
+          c->graphs.push_back({n_pairs, want_mean, exec});
+        } else {
+          exec = nullptr;
+          c->graphs_enabled = false;   // fall back to eager launches for good
+          cudaGetLastError();
+          rc = VVS_OK;
+        }
+        if (graph) cudaGraphDestroy(graph);
+      }
+    }
+    if (!warmed) c->eager_calls.push_back(n_pairs);
+  }
+  if (exec) {
+    VVS_CUDA_OK(cudaGraphLaunch(exec, s), &c->err);
+  } else {
+    rc = pairs_to_twist(c, c->stage_img, c->stage_img + n_pairs * img_bytes, c->stage_depth, n_pairs, &o, s);
+    if (rc) return rc;
+  }
   VVS_CUDA_OK(cudaMemcpyAsync(twist, c->twist, n_pairs * 6 * sizeof(double), cudaMemcpyDeviceToHost, s), &c->err);
   if (n_selected)
     VVS_CUDA_OK(cudaMemcpyAsync(n_selected, c->n_sel, n_pairs * sizeof(int32_t), cudaMemcpyDeviceToHost, s), &c->err);
