@@ -9,7 +9,7 @@ from vitvs_b200 import Engine, ServoConfig, _lib
 which = sys.argv[1] if len(sys.argv) > 1 else "all"
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 eng = Engine(ServoConfig(model_type="dinov2_vitb14"), max_images=2)
-n_img, n_tok, heads, D, H = 128, 485, 12, 768, 3072
+n_img, n_tok, heads, D, H = 128, int(os.environ.get('NTOK', '485')), 12, 768, 3072
 M = n_img * n_tok
 g = torch.Generator(device="cuda").manual_seed(0)
 

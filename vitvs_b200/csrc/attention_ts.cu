@@ -1,0 +1,411 @@
+// tcgen05 flash-attention forward, generation 7: P never leaves the tensor-core datapath.
+// (reference semantics: dino_patch/attention.py:70-80 - non-causal SDPA, scale hd^-0.5,
+// head dim 64, no mask, eval.)
+//
+// Input is the fused-QKV GEMM output [n_img * n_tok, 3*D] bf16 exactly as the reference's
+// `qkv(x).reshape(B, N, 3, H, hd)` lays it out (q already multiplied by hd^-0.5 in that GEMM's epilogue):
+// the Q / K / V tiles of (image, head) are 64-column TMA boxes of that matrix.  Output goes straight into
+// the [n_img * n_tok, D] layout attn.proj reads.
+//
+// One CTA = TWO 128-row query tiles of one (image, head); TWO CTAs are resident per SM (256 TMEM columns,
+// ~98 KB of shared memory and 256 threads each), so the prologue (descriptor fetch, Q / K loads) and the
+// epilogue (O / l, global stores) of one CTA hide behind the main loop of the other:
+//   warps 0-7   two softmax warpgroups, one per query tile (thread = query row = TMEM lane); lane 0 of each
+//               tile's first warp also issues that tile's MMAs (tile 0's: the TMA loads of the K / V ring too)
+// Per tile and 64-key block:
+//   S = Q K^T              (SS MMA, fp32 S in TMEM columns [0, 64) of the tile)
+//   softmax warpgroup: S -> registers (one TMEM pass), row max, p = exp2(s log2e - m) (packed fp32x2 FMA, one
+//   MUFU.EX2 per element), bf16 P written back with tcgen05.st over the first 32 columns of S
+//   O += P V               (TS MMA: A = P straight from TMEM, B = V consumed MN-major from its row-major tile)
+// so P costs no shared-memory store, no generic->async proxy fence and no smem operand bandwidth (an SS MMA
+// with N = 64 reads 6 KB of operands per 32-clk step - over the 128 B/clk shared-memory port; the TS form reads 2 KB).
+// S(j+1) is issued right behind PV(j) by the same thread: tcgen05.mma executes in issue order, which is
+// what makes overwriting P(j) with S(j+1) safe, and one commit (s_full) tells the warpgroup both "S(j+1) is
+// there" and "PV(j) is done" (O may be rescaled / read).  O accumulates in TMEM across blocks and is lazily
+// rescaled only when the running max grows by more than 2^8;  O / l once at the end.
+// TMEM: tile t owns columns [128 t, 128 t + 64) for S / P and [128 t + 64, 128 t + 128) for O.
+// Keys past n_tok (the next image's rows or TMA zero fill) are masked to p = 0.
+#include <cuda.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+
+#include "ptx.cuh"
+#include "vvs_internal.h"
+
+namespace vvs {
+namespace {
+
+constexpr int kBQ = 128;   // query rows per tile (one TMEM lane per row)
+constexpr int kBKV = 64;   // keys per block
+constexpr int kHD = 64;    // head dim (every DINOv2 size)
+constexpr int kQT = 2;     // query tiles per CTA
+constexpr int kThreads = kQT * 4 * 32;   // 256: 8 warps, two per SM sub-partition
+constexpr int kKVStages = 4;
+constexpr uint32_t kQBytes = kBQ * kHD * 2;      // 16 KB
+constexpr uint32_t kKVBytes = kBKV * kHD * 2;    // 8 KB: one K or V block
+constexpr uint32_t kOffQ = 0, kOffK = kOffQ + kQT * kQBytes, kOffV = kOffK + kKVStages * kKVBytes,
+                   kOffBar = kOffV + kKVStages * kKVBytes;
+constexpr uint32_t kSmem = kOffBar + 256 + 1024;   // + barriers + alignment slack
+constexpr uint32_t kTmemCols = 256;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kRescaleLog2 = 8.0f;
+
+__device__ __forceinline__ float ex2_approx(float x) {   // single MUFU.EX2; ex2(-inf) = 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// D[tmem] (+)= A[tmem] * B[smem]: A = 128 lanes x (K bf16 packed two per 32-bit column)
+__device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// 16 exponentials of a row segment: p = exp2(s * log2e - m), packed to bf16 pairs, row sum accumulated
+__device__ __forceinline__ void exp_pack16(const uint32_t* s, f32x2 log2e2, f32x2 neg_m2, f32x2& sum01, f32x2& sum23,
+                                           uint32_t* pk) {
+#pragma unroll
+  for (int i = 0; i < 16; i += 4) {
+    const f32x2 e01 = f2_ex2(f2_fma(f2_pack(__uint_as_float(s[i + 0]), __uint_as_float(s[i + 1])), log2e2, neg_m2));
+    const f32x2 e23 = f2_ex2(f2_fma(f2_pack(__uint_as_float(s[i + 2]), __uint_as_float(s[i + 3])), log2e2, neg_m2));
+    sum01 = f2_add(sum01, e01);
+    sum23 = f2_add(sum23, e23);
+    pk[i / 2] = f2_to_bf16x2(e01);
+    pk[i / 2 + 1] = f2_to_bf16x2(e23);
+  }
+}
+
+#ifdef VVS_ATT_TRACE   // timing experiment: per-block clock64 stamps of a few CTAs (tools/att_trace.py)
+__device__ long long g_att_trace[4 * 3 * 16 * 8];
+#define VVS_TR(ev)                                                                                         \
+  do {                                                                                                     \
+    if (tr_slot >= 0 && lane == 0 && j < 16) g_att_trace[((tr_slot * 3 + tr_warp) * 16 + j) * 8 + (ev)] = clock64(); \
+  } while (0)
+#else
+#define VVS_TR(ev) do { } while (0)
+#endif
+
+__global__ void __launch_bounds__(kThreads, 2)
+attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
+                    bf16* __restrict__ out, int n_tok, int D) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
+  uint64_t* q_full = bars;                       // kQT
+  uint64_t* k_full = q_full + kQT;               // kKVStages
+  uint64_t* v_full = k_full + kKVStages;
+  uint64_t* k_empty = v_full + kKVStages;
+  uint64_t* v_empty = k_empty + kKVStages;
+  uint64_t* s_full = v_empty + kKVStages;        // kQT: S_t(j) is in TMEM and PV_t(j-1) has completed
+  uint64_t* p_full = s_full + kQT;               // kQT: P_t(j) is in TMEM, O_t rescaled if needed (4 warp arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_full + kQT);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+  const int qt0 = blockIdx.x * kQT;               // first query tile of this CTA
+  const int head = blockIdx.y;
+  const int img = blockIdx.z;
+  const int row_base = img * n_tok;               // first row of this image in the qkv matrix
+  const int nblk = (n_tok + kBKV - 1) / kBKV;
+  const int n_qt = min(kQT, (n_tok + kBQ - 1) / kBQ - qt0);   // active tiles (last CTA of a sequence)
+  const int colQ = head * kHD, colK = D + head * kHD, colV = 2 * D + head * kHD;
+
+  if (tid == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmKV);
+    for (int i = 0; i < kKVStages; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&k_empty[i], n_qt);    // one commit per tile's issuer
+      mbar_init(&v_empty[i], n_qt);
+    }
+    for (int i = 0; i < kQT; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0) tmem_alloc<kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int t = warp >> 2;                          // query tile of this warpgroup
+  if (t < n_qt) {
+    const int wq = warp & 3;                          // TMEM lane quarter of this warp
+    const int row = wq * 32 + lane;                   // row inside the tile = TMEM lane
+    const uint32_t lane_field = static_cast<uint32_t>(wq * 32) << 16;
+    const uint32_t tS = tmem_base + t * 128 + lane_field;
+    const uint32_t tO = tS + 64;
+
+    // ---- MMA issue + TMA (lane 0 of the tile's first warp; tile 0's also feeds the K / V ring) -------------
+    // A CTA is exactly 8 warps: registers are allocated per SM sub-partition, and a ninth and tenth warp would
+    // cost a second resident CTA.  The issuing warp is on the tile's critical path either way.
+    const bool issuer = (wq == 0) && (lane == 0);
+    const bool producer = issuer && (t == 0);
+    constexpr uint32_t idescS = umma_idesc_bf16(128, kBKV, false);
+    constexpr uint32_t idescPV = umma_idesc_bf16(128, kHD, true);
+    const uint32_t sbase = smem_u32(smem);
+    const uint32_t qa = sbase + kOffQ + t * kQBytes;
+    const uint32_t tSi = tmem_base + t * 128, tOi = tSi + 64;   // lane field 0: MMA operands address the whole tile
+    int next_load = 0;
+    // loads are issued in the order K(0) V(0) K(1) V(1) ... whenever their stage is free (never blocking)
+    auto pump = [&]() {
+      while (next_load < 2 * nblk) {
+        const int b = next_load >> 1, st = b % kKVStages;
+        const bool is_v = next_load & 1;
+        uint64_t* empty = is_v ? &v_empty[st] : &k_empty[st];
+        if (!mbar_test_wait(empty, ((b / kKVStages) & 1) ^ 1)) return;   // never suspends
+        uint64_t* full = is_v ? &v_full[st] : &k_full[st];
+        mbar_expect_tx(full, kKVBytes);
+        tma_load_3d(smem + (is_v ? kOffV : kOffK) + st * kKVBytes, &tmKV, full, is_v ? colV : colK,
+                    row_base + b * kBKV, 0, kEvictLast);
+        ++next_load;
+      }
+    };
+    auto wait_pump = [&](uint64_t* bar, uint32_t parity) {   // issuer lanes only
+      uint32_t polls = 0;
+      while (!mbar_try_wait(bar, parity)) {
+        if (producer) pump();
+        if (++polls == (1u << 26)) __trap();
+      }
+    };
+    auto issue_S = [&](int b) {     // S_t(b) = Q_t K(b)^T
+      const int st = b % kKVStages;
+      wait_pump(&k_full[st], (b / kKVStages) & 1);
+      tc_fence_after();
+      const uint32_t ka = sbase + kOffK + st * kKVBytes;
+#ifndef VVS_EXP_NOMMA
+#pragma unroll
+      for (int k = 0; k < kHD / 16; ++k)
+        umma_bf16(tSi, umma_smem_desc(qa + k * 32, 16, 1024), umma_smem_desc(ka + k * 32, 16, 1024), idescS, k != 0);
+#endif
+      umma_commit(&k_empty[st]);
+    };
+    if (issuer) {
+      if (producer) {
+        for (int u = 0; u < n_qt; ++u) {
+          mbar_expect_tx(&q_full[u], kQBytes);
+          tma_load_3d(smem + kOffQ + u * kQBytes, &tmQ, &q_full[u], colQ, row_base + (qt0 + u) * kBQ, 0, kEvictNormal);
+          if (u == 0) pump();
+        }
+        pump();
+      }
+      wait_pump(&q_full[t], 0);
+      issue_S(0);
+      umma_commit(&s_full[t]);
+    }
+    __syncwarp();
+
+    float m_run = -INFINITY;   // reference max of the exponentials, already multiplied by log2(e)
+    float l_run = 0.f;
+    const f32x2 log2e2 = f2_pack(kLog2e, kLog2e);
+#ifdef VVS_ATT_TRACE
+    const int tr_slot = (blockIdx.z == 5 && blockIdx.y == 3) ? static_cast<int>(blockIdx.x)
+                        : (blockIdx.z == 100 && blockIdx.y == 7) ? 2 + static_cast<int>(blockIdx.x) : -1;
+    const int tr_warp = warp == 0 ? 0 : warp == 1 ? 1 : warp == 4 ? 2 : -1;
+    const int tr_ok = tr_warp >= 0 ? tr_slot : -1;
+#undef VVS_TR
+#define VVS_TR(ev)                                                                                         \
+  do {                                                                                                     \
+    if (tr_ok >= 0 && tr_ok < 4 && lane == 0 && j < 16) g_att_trace[((tr_ok * 3 + tr_warp) * 16 + j) * 8 + (ev)] = clock64(); \
+  } while (0)
+#endif
+
+    for (int j = 0; j < nblk; ++j) {
+      VVS_TR(0);
+      mbar_wait(&s_full[t], j & 1);
+      tc_fence_after();
+      VVS_TR(1);
+      uint32_t sc[2][32];                   // the row of S (fp32 bits)
+      tmem_ld32(tS, sc[0]);
+      tmem_ld32(tS + 32, sc[1]);
+      tmem_ld_wait();
+      VVS_TR(2);
+#ifdef VVS_EXP_NOMATH   // timing experiment: MMA + hand-off chain only (wrong numerics)
+      {
+        uint32_t pk[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) pk[i] = sc[0][i] ^ sc[1][i + 8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) tmem_st8(tS + q * 8, pk);
+        l_run = 1.f;
+      }
+#else
+      const int valid = n_tok - j * kBKV;   // keys [0, valid) of this block exist
+      if (valid < kBKV) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (c * 32 + i >= valid) sc[c][i] = 0xff800000u;      // -inf: ignored by the max, exp2 -> 0
+      }
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          mx0 = fmaxf(mx0, __uint_as_float(sc[c][i]));
+          mx1 = fmaxf(mx1, __uint_as_float(sc[c][i + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(sc[c][i + 2]));
+          mx3 = fmaxf(mx3, __uint_as_float(sc[c][i + 3]));
+        }
+      const float m_blk = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * kLog2e;
+      // Lazy rescale: the reference max only moves when a block exceeds it by more than 2^8; until then
+      // p = exp2(s - m_run) may exceed 1 (<= 256: exact in the fp32 sum, representable in bf16) and O / l
+      // is unchanged mathematically.  Always true for j == 0 (m_run = -inf).
+      const bool raise = m_blk > m_run + kRescaleLog2;
+      const float alpha = raise ? ex2_approx(m_run - m_blk) : 1.0f;
+      if (raise) m_run = m_blk;
+      if (j >= 1 && __any_sync(0xffffffffu, raise)) {   // PV(j-1) has completed (s_full(j)): O is quiescent
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          uint32_t ov[16];
+          tmem_ld16(tO + h * 16, ov);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) ov[i] = __float_as_uint(__uint_as_float(ov[i]) * alpha);
+          tmem_st16(tO + h * 16, ov);
+        }
+      }
+      const f32x2 neg_m2 = f2_pack(-m_run, -m_run);
+      f32x2 ps01 = f2_pack(0.f, 0.f), ps23 = ps01;
+      // P(j) overwrites columns [0, 32) of S(j) (this thread's own lane only: its S row is in registers)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint32_t pk[8];
+        exp_pack16(&sc[q >> 1][(q & 1) * 16], log2e2, neg_m2, ps01, ps23, pk);
+        tmem_st8(tS + q * 8, pk);
+      }
+      float s0, s1;
+      f2_unpack(f2_add(ps01, ps23), s0, s1);
+      l_run = l_run * alpha + (s0 + s1);
+#endif
+      VVS_TR(3);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[t]);
+      VVS_TR(4);
+      if (wq == 0) {
+        if (issuer) {
+          const int st = j % kKVStages;
+          wait_pump(&v_full[st], (j / kKVStages) & 1);
+          VVS_TR(5);
+          wait_pump(&p_full[t], j & 1);               // all four warps: P_t(j) in TMEM, O_t rescaled if it had to be
+          tc_fence_after();
+          VVS_TR(6);
+          const uint32_t va = sbase + kOffV + st * kKVBytes;
+#ifndef VVS_EXP_NOMMA
+#pragma unroll
+          for (int kk = 0; kk < kBKV / 16; ++kk)
+            umma_bf16_ts(tOi, tSi + kk * 8, umma_smem_desc(va + kk * 2048, 1024, 1024),   // MN-major V: 16 keys = 2 x 1024 B
+                         idescPV, (j > 0 || kk != 0) ? 1u : 0u);                          // O accumulates across key blocks
+#endif
+          umma_commit(&v_empty[st]);
+          if (j + 1 < nblk) issue_S(j + 1);           // in order behind PV(j): may overwrite P(j)
+          umma_commit(&s_full[t]);                    // S(j+1) ready and PV(j) done (last block: O final)
+          if (producer) pump();
+          VVS_TR(7);
+        }
+        __syncwarp();
+      }
+    }
+
+    mbar_wait(&s_full[t], nblk & 1);      // PV(nblk - 1) has completed
+    tc_fence_after();
+    const int q = (qt0 + t) * kBQ + row;
+    const float inv = 1.0f / l_run;
+    uint4* dst = reinterpret_cast<uint4*>(out + static_cast<size_t>(row_base + q) * D + head * kHD);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      uint32_t ov[32];
+      tmem_ld32(tO + h * 32, ov);
+      tmem_ld_wait();
+      if (q < n_tok) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 w;
+          w.x = pack_bf16x2(__uint_as_float(ov[g * 8 + 0]) * inv, __uint_as_float(ov[g * 8 + 1]) * inv);
+          w.y = pack_bf16x2(__uint_as_float(ov[g * 8 + 2]) * inv, __uint_as_float(ov[g * 8 + 3]) * inv);
+          w.z = pack_bf16x2(__uint_as_float(ov[g * 8 + 4]) * inv, __uint_as_float(ov[g * 8 + 5]) * inv);
+          w.w = pack_bf16x2(__uint_as_float(ov[g * 8 + 6]) * inv, __uint_as_float(ov[g * 8 + 7]) * inv);
+          dst[h * 4 + g] = w;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc<kTmemCols>(tmem_base);
+}
+
+}  // namespace
+
+#ifdef VVS_ATT_TRACE
+extern "C" __attribute__((visibility("default"))) int vvs_dbg_att_trace(long long* out) {
+  return static_cast<int>(cudaMemcpyFromSymbol(out, g_att_trace, sizeof(g_att_trace)));
+}
+#endif
+
+int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
+                        std::string* err) {
+  const int D = heads * kHD;
+  CUtensorMap tmq, tmkv;
+  const uint64_t rows = static_cast<uint64_t>(n_img) * n_tok;
+  int rc = make_tmap_bf16(&tmq, qkv, 3ull * D, rows, 1, 3ull * D, 0, kBQ, err);
+  if (rc) return rc;
+  rc = make_tmap_bf16(&tmkv, qkv, 3ull * D, rows, 1, 3ull * D, 0, kBKV, err);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    VVS_CUDA_OK(cudaFuncSetAttribute(attention_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     static_cast<int>(kSmem)),
+                err);
+    VVS_CUDA_OK(cudaFuncSetAttribute(attention_ts_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared),
+                err);
+    if (getenv("VITVS_DEBUG")) {
+      int nb = 0;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, attention_ts_kernel, kThreads, kSmem);
+      fprintf(stderr, "[vitvs] attention_ts_kernel: %d CTAs/SM (smem %u B, %d threads)\n", nb, kSmem, kThreads);
+      cudaFuncAttributes fa;
+      cudaFuncGetAttributes(&fa, attention_ts_kernel);
+      int dev = 0, smem_sm = 0, regs_sm = 0, resv = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+      cudaDeviceGetAttribute(&regs_sm, cudaDevAttrMaxRegistersPerMultiprocessor, dev);
+      cudaDeviceGetAttribute(&resv, cudaDevAttrReservedSharedMemoryPerBlock, dev);
+      fprintf(stderr, "[vitvs] regs %d static smem %zu maxdyn %d carveout %d | SM: smem %d regs %d reserved/block %d\n",
+              fa.numRegs, fa.sharedSizeBytes, fa.maxDynamicSharedSizeBytes, fa.preferredShmemCarveout, smem_sm, regs_sm, resv);
+      for (int th = 32; th <= 256; th += 32) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, attention_ts_kernel, th, 1024);
+        fprintf(stderr, "[vitvs]   threads %d, dyn smem 1024 -> %d CTAs/SM\n", th, nb);
+      }
+      for (int sm = 10000; sm <= 99584; sm += 10000) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, attention_ts_kernel, 128, sm);
+        fprintf(stderr, "[vitvs]   threads 128, dyn smem %d -> %d CTAs/SM\n", sm, nb);
+      }
+    }
+    attr_set = true;
+  }
+  const int q_tiles = (n_tok + kBQ - 1) / kBQ;
+  dim3 grid((q_tiles + kQT - 1) / kQT, heads, n_img);
+  attention_ts_kernel<<<grid, kThreads, kSmem, stream>>>(tmq, tmkv, out, n_tok, D);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+}  // namespace vvs

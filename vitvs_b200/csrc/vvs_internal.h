@@ -77,6 +77,9 @@ int gemm_block_n(int N);   // the N tile the launcher picks for this N (128 or 2
 // qkv: [n_img * n_tok, 3*D] bf16 (q pre-scaled by hd^-0.5), out: [n_img * n_tok, D] bf16
 int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
                      std::string* err);
+// generation 7 (attention_ts.cu): P stays in TMEM (TS MMA), two CTAs per SM; launch_attention dispatches to it
+int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
+                        std::string* err);
 
 // ---- bandwidth-bound kernels -------------------------------------------------------------------
 int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err);
