@@ -9,6 +9,16 @@ using namespace vvs;
 
 template <int MODE>
 __global__ void __launch_bounds__(512, 1) k(float* out, int iters, float seed) {
+  __shared__ uint32_t tmem_slot;
+  uint32_t tbase = 0;
+  if (MODE >= 4) {
+    if (threadIdx.x < 32) tmem_alloc<512>(&tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    // warp w may touch lanes 32 (w % 4) ..; give every warp its own 32-column slice
+    tbase = tmem_slot + ((uint32_t)((threadIdx.x >> 5) & 3) * 32 << 16) + (threadIdx.x >> 7) * 128;
+  }
   float s[64];
 #pragma unroll
   for (int i = 0; i < 64; ++i) s[i] = seed * (i + 1) + threadIdx.x * 1e-3f;
@@ -46,7 +56,25 @@ __global__ void __launch_bounds__(512, 1) k(float* out, int iters, float seed) {
         pk[i / 2] = f2_to_bf16x2(e01);
         pk[i / 2 + 1] = f2_to_bf16x2(e23);
       }
-      if (MODE == 3) {   // + the P hand-off of generation 6: 8 x STS.128 into this thread's row
+      if (MODE >= 4) {   // + the P hand-off of generation 7/8: 4 x tcgen05.st x8 (+ wait::st)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint32_t p8[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) p8[i] = pk[q * 8 + i];
+          tmem_st8(tbase + q * 8, p8);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        if (MODE == 5) {   // + S from TMEM: 2 x tcgen05.ld x32
+          uint32_t a[32], b[32];
+          tmem_ld32(tbase + 32, a);
+          tmem_ld32(tbase + 64, b);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) { s[i] = __uint_as_float(a[i] & 0x3fffffff); s[32 + i] = __uint_as_float(b[i] & 0x3fffffff); }
+        }
+      } else if (MODE == 3) {   // + the P hand-off of generation 6: 8 x STS.128 into this thread's row
         extern __shared__ uint4 sm[];
 #pragma unroll
         for (int q = 0; q < 8; ++q) sm[threadIdx.x * 8 + ((q ^ (threadIdx.x & 7)))] = make_uint4(pk[q * 4], pk[q * 4 + 1], pk[q * 4 + 2], pk[q * 4 + 3]);
@@ -67,6 +95,11 @@ __global__ void __launch_bounds__(512, 1) k(float* out, int iters, float seed) {
   for (int i = 0; i < 64; ++i) r += s[i];
   out[blockIdx.x * blockDim.x + threadIdx.x] = r;
   if (threadIdx.x == 0 && blockIdx.x == 0) out[1 << 20] = float(t1 - t0);
+  if (MODE >= 4) {
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc<512>(tmem_slot);
+  }
 }
 
 template <int MODE>
@@ -96,5 +129,7 @@ int main() {
   run<1>("exp body (+64 FFMA feed)", d);
   run<2>("max + exp body (+64 FFMA)", d);
   run<3>("max + exp body + 8 STS.128", d);
+  run<4>("max + exp body + 4 STTM.x8", d);
+  run<5>("  ... + 2 LDTM.x32", d);
   return 0;
 }
