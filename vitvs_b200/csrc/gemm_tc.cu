@@ -122,7 +122,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
-  const int warp = threadIdx.x >> 5;
+  // shuffle broadcast: warp-uniform for the compiler too, so descriptors / barrier addresses stay on the uniform
+  // datapath (a plain threadIdx.x >> 5 wraps every tcgen05.mma / TMA issue in an ELECT + R2UR waterfall loop)
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
   const uint32_t cta_rank = (NCTA == 2) ? cluster_ctarank() : 0u;   // 0 = leader (issues the MMAs)
 
@@ -148,7 +150,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if constexpr (NCTA == 2) cluster_sync_all();   // peer barriers initialised before any remote arrive / TMA signal
   else __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   // p.m_tiles counts (128 * NCTA)-row tiles; this CTA owns 128-row block m_tile * NCTA + cta_rank of each
   const int tiles_per_batch = p.m_tiles * p.n_tiles;
@@ -158,7 +160,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    // The whole warp walks the loop (stage / phase / tile stay warp-uniform values on the uniform datapath);
+    // only the issue instructions themselves are predicated on lane 0.
+    {
       uint32_t stage = 0, phase = 0;
       const uint32_t full0 = (NCTA == 2) ? mapa_shared(smem_u32(&full[0]), 0) : 0u;   // leader's full[] in cluster space
       for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
@@ -169,17 +173,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
-          if constexpr (NCTA == 2) {
-            if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
-            const uint32_t fb = full0 + stage * 8;
-            tma_load_3d_2sm(sa, &tmA, fb, kb * BK, m_blk * BM, b, kEvictNormal);
-            tma_load_3d_2sm(sa + C::kABytes, &tmB, fb, kb * BK, n_blk * BN + static_cast<int>(cta_rank) * (BN / 2),
-                            p.b_batched ? b : 0, kEvictLast);
-          } else {
-            mbar_expect_tx(&full[stage], C::kStageBytes);
-            tma_load_3d(sa, &tmA, &full[stage], kb * BK, m_blk * BM, b, kEvictNormal);
-            tma_load_3d(sa + C::kABytes, &tmB, &full[stage], kb * BK, n_blk * BN, p.b_batched ? b : 0, kEvictLast);
+          if (lane == 0) {
+            if constexpr (NCTA == 2) {
+              if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
+              const uint32_t fb = full0 + stage * 8;
+              tma_load_3d_2sm(sa, &tmA, fb, kb * BK, m_blk * BM, b, kEvictNormal);
+              tma_load_3d_2sm(sa + C::kABytes, &tmB, fb, kb * BK, n_blk * BN + static_cast<int>(cta_rank) * (BN / 2),
+                              p.b_batched ? b : 0, kEvictLast);
+            } else {
+              mbar_expect_tx(&full[stage], C::kStageBytes);
+              tma_load_3d(sa, &tmA, &full[stage], kb * BK, m_blk * BM, b, kEvictNormal);
+              tma_load_3d(sa + C::kABytes, &tmB, &full[stage], kb * BK, n_blk * BN, p.b_batched ? b : 0, kEvictLast);
+            }
           }
+          __syncwarp();
           if (++stage == C::kStages) {
             stage = 0;
             phase ^= 1;
@@ -187,10 +194,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
     }
-    __syncwarp();
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0 && cta_rank == 0) {
+    // ------------------------------------------------------------------ MMA issuer (whole warp walks, lane 0 issues)
+    if (cta_rank == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(BM * NCTA, BN, false);
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
       for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
@@ -202,26 +208,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + stage * C::kStageBytes);
           const uint32_t b_addr = a_addr + C::kABytes;
+          if (lane == 0) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t da = umma_smem_desc(a_addr + k * 32, 16, 1024), db = umma_smem_desc(b_addr + k * 32, 16, 1024);
-            if constexpr (NCTA == 2) umma_bf16_2sm(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
-            else umma_bf16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = umma_smem_desc(a_addr + k * 32, 16, 1024), db = umma_smem_desc(b_addr + k * 32, 16, 1024);
+              if constexpr (NCTA == 2) umma_bf16_2sm(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+              else umma_bf16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            if constexpr (NCTA == 2) umma_commit_2sm(&empty[stage], 3);   // frees the stage in both CTAs
+            else umma_commit(&empty[stage]);
           }
-          if constexpr (NCTA == 2) umma_commit_2sm(&empty[stage], 3);   // frees the stage in both CTAs
-          else umma_commit(&empty[stage]);
+          __syncwarp();
           if (++stage == C::kStages) {
             stage = 0;
             phase ^= 1;
           }
         }
-        if constexpr (NCTA == 2) umma_commit_2sm(&tfull[acc], 3);
-        else umma_commit(&tfull[acc]);
+        if (lane == 0) {
+          if constexpr (NCTA == 2) umma_commit_2sm(&tfull[acc], 3);
+          else umma_commit(&tfull[acc]);
+        }
+        __syncwarp();
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
     }
-    __syncwarp();
   } else {
     // ------------------------------------------------------------------ epilogue (8 warps)
     // Two warps per TMEM lane quarter; each owns half of the tile's 32-column chunks.  TMEM loads are
