@@ -119,7 +119,10 @@ struct vvs_ctx {
   // host-buffer entry point: own stream (graphs cannot be captured on the legacy default stream) and one
   // instantiated CUDA graph of the whole device path per batch size (launch-bound at small batches)
   cudaStream_t own_stream = nullptr;
-  struct GraphEntry { int n_pairs; int want_mean; cudaGraphExec_t exec; };
+  cudaStream_t copy_stream = nullptr;   // depth H2D overlaps the forward pass (depth is only read by the IBVS stage)
+  cudaEvent_t depth_ready = nullptr;
+  // execA: images (workspace) -> tokens -> descriptors -> matches;  execB: depth (workspace) -> twist
+  struct GraphEntry { int n_pairs; int want_mean; cudaGraphExec_t execA; cudaGraphExec_t execB; };
   std::vector<GraphEntry> graphs;
   std::vector<int> eager_calls;      // n_pairs values that already ran eagerly once (lazy init done)
   bool graphs_enabled = true;
@@ -370,11 +373,50 @@ int run_ibvs(vvs_ctx* c, const int32_t* uv, const int32_t* uv_star, const uint16
   return launch_ibvs(a, s, &c->err);
 }
 
+// part A: images [goal.. | current..] -> tokens -> unit descriptors -> matches / keypoints (workspace outputs)
+int pairs_forward_match(vvs_ctx* c, const uint8_t* images, int n_pairs, const vvs_match_out* match, cudaStream_t s) {
+  const vvs_config& f = c->cfg;
+  int rc = forward_tokens(c, images, VVS_IMAGE_U8_HWC, 2 * n_pairs, f.layer, s);
+  if (rc) return rc;
+  const int parts = f.use_feature_binning ? 9 : 1;
+  { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
+    rc = launch_descriptors_unit_bf16(c->x, c->desc, c->sqn, 2 * n_pairs, c->grid, c->grid, f.dim,
+                                      f.use_feature_binning, s, &c->err); }
+  if (rc) return rc;
+  c->launch_count += 2;
+  return match_on_desc(c, n_pairs, c->T, parts * f.dim, c->grid, f.num_pairs, match, s);
+}
+
+// part B: keypoints (workspace) + depth -> twist (+ mean similarity of the selected pairs), workspace outputs
+int pairs_control(vvs_ctx* c, const uint16_t* depth, int n_pairs, bool want_mean, cudaStream_t s) {
+  const vvs_config& f = c->cfg;
+  int rc = run_ibvs(c, c->uv, c->uv_star, depth, n_pairs, f.num_pairs, c->twist, nullptr, nullptr, nullptr, s);
+  if (rc) return rc;
+  if (want_mean) {
+    mean_selected_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(c->sel_sim, c->n_sel, f.num_pairs, c->mean_sel, n_pairs);
+    VVS_CUDA_OK(cudaGetLastError(), &c->err);
+    ++c->launch_count;
+  }
+  return VVS_OK;
+}
+
+// workspace results -> caller's device buffers
+int copy_pair_results(vvs_ctx* c, int n_pairs, const vvs_pair_out* out, cudaStream_t s) {
+  if (out->twist != c->twist)
+    VVS_CUDA_OK(cudaMemcpyAsync(out->twist, c->twist, n_pairs * 6 * sizeof(double), cudaMemcpyDeviceToDevice, s), &c->err);
+  if (out->n_selected)
+    VVS_CUDA_OK(cudaMemcpyAsync(out->n_selected, c->n_sel, n_pairs * sizeof(int32_t), cudaMemcpyDeviceToDevice, s),
+                &c->err);
+  if (out->mean_sim_sel && out->mean_sim_sel != c->mean_sel)
+    VVS_CUDA_OK(cudaMemcpyAsync(out->mean_sim_sel, c->mean_sel, n_pairs * sizeof(float), cudaMemcpyDeviceToDevice, s),
+                &c->err);
+  return VVS_OK;
+}
+
+// eager launches straight from the caller's buffers
 int pairs_to_twist(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth, int n_pairs,
                    const vvs_pair_out* out, cudaStream_t s) {
   const vvs_config& f = c->cfg;
-  if (n_pairs < 1 || 2 * n_pairs > f.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
-  if (!out || !out->twist) return fail(c, VVS_ERR_INVALID, "out->twist is required");
   c->launch_count = 0;
   const size_t img_bytes = static_cast<size_t>(f.image_size) * f.image_size * 3;
   const uint8_t* images = goal;
@@ -385,28 +427,56 @@ int pairs_to_twist(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const ui
                 &c->err);
     images = c->stage_img;
   }
-  int rc = forward_tokens(c, images, VVS_IMAGE_U8_HWC, 2 * n_pairs, f.layer, s);
+  int rc = pairs_forward_match(c, images, n_pairs, &out->match, s);
   if (rc) return rc;
-  const int parts = f.use_feature_binning ? 9 : 1;
-  { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
-    rc = launch_descriptors_unit_bf16(c->x, c->desc, c->sqn, 2 * n_pairs, c->grid, c->grid, f.dim,
-                                      f.use_feature_binning, s, &c->err); }
+  rc = pairs_control(c, depth, n_pairs, out->mean_sim_sel != nullptr, s);
   if (rc) return rc;
-  c->launch_count += 2;
-  rc = match_on_desc(c, n_pairs, c->T, parts * f.dim, c->grid, f.num_pairs, &out->match, s);
-  if (rc) return rc;
-  rc = run_ibvs(c, c->uv, c->uv_star, depth, n_pairs, f.num_pairs, out->twist, nullptr, nullptr, nullptr, s);
-  if (rc) return rc;
-  if (out->n_selected)
-    VVS_CUDA_OK(cudaMemcpyAsync(out->n_selected, c->n_sel, n_pairs * sizeof(int32_t), cudaMemcpyDeviceToDevice, s),
-                &c->err);
-  if (out->mean_sim_sel) {
-    mean_selected_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(c->sel_sim, c->n_sel, f.num_pairs, out->mean_sim_sel,
-                                                               n_pairs);
-    VVS_CUDA_OK(cudaGetLastError(), &c->err);
-    ++c->launch_count;
+  return copy_pair_results(c, n_pairs, out, s);
+}
+
+// The ~100 launches of the device path replayed as two CUDA graphs whose every pointer is a workspace address
+// (launch gaps are ~10 % of a 64-pair step when launched eagerly).  The first call per batch size runs eagerly
+// (lazy function attributes), the second is captured - on the handle's own stream, which executes nothing, so
+// the caller's stream may be the legacy default one.  Returns null when graphs are off / unavailable.
+const vvs_ctx::GraphEntry* graphs_for(vvs_ctx* c, int n_pairs, bool want_mean) {
+  if (!c->graphs_enabled || c->prof_on) return nullptr;
+  for (auto& g : c->graphs)
+    if (g.n_pairs == n_pairs && g.want_mean == (want_mean ? 1 : 0)) return &g;
+  const bool warmed = std::find(c->eager_calls.begin(), c->eager_calls.end(), n_pairs) != c->eager_calls.end();
+  if (!warmed) {
+    c->eager_calls.push_back(n_pairs);
+    return nullptr;
   }
-  return VVS_OK;
+  if (c->graphs.size() >= 16) return nullptr;
+  const size_t img_bytes = static_cast<size_t>(c->cfg.image_size) * c->cfg.image_size * 3;
+  cudaStream_t cs = c->own_stream;
+  cudaGraphExec_t exec[2] = {nullptr, nullptr};
+  bool ok = true;
+  for (int part = 0; part < 2 && ok; ++part) {
+    cudaGraph_t graph = nullptr;
+    if (cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+      ok = false;
+      break;
+    }
+    const int saved = c->launch_count;
+    if (part == 0) c->launch_count = 0;
+    const int rc = part == 0 ? pairs_forward_match(c, c->stage_img, n_pairs, nullptr, cs)
+                             : pairs_control(c, c->stage_depth, n_pairs, want_mean, cs);
+    (void)saved;
+    (void)img_bytes;
+    const cudaError_t e = cudaStreamEndCapture(cs, &graph);
+    ok = rc == VVS_OK && e == cudaSuccess && graph && cudaGraphInstantiate(&exec[part], graph, 0) == cudaSuccess;
+    if (graph) cudaGraphDestroy(graph);
+  }
+  if (!ok) {
+    for (auto& e : exec)
+      if (e) cudaGraphExecDestroy(e);
+    c->graphs_enabled = false;   // eager launches for good
+    cudaGetLastError();
+    return nullptr;
+  }
+  c->graphs.push_back({n_pairs, want_mean ? 1 : 0, exec[0], exec[1]});
+  return &c->graphs.back();
 }
 
 }  // namespace
@@ -480,7 +550,9 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
     vvs_destroy(c);
     return VVS_ERR_CUDA;
   }
-  if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+  if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->depth_ready, cudaEventDisableTiming) != cudaSuccess) {
     g_create_error = "vvs_create: cudaStreamCreateWithFlags failed";
     vvs_destroy(c);
     return VVS_ERR_CUDA;
@@ -492,8 +564,13 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
 
 int vvs_destroy(vvs_handle c) {
   if (!c) return VVS_OK;
-  for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);
+  for (auto& g : c->graphs) {
+    cudaGraphExecDestroy(g.execA);
+    cudaGraphExecDestroy(g.execB);
+  }
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+  if (c->depth_ready) cudaEventDestroy(c->depth_ready);
   void* ptrs[] = {c->pe_w, c->pe_b, c->cls, c->pos, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
                   c->nn1, c->nn2, c->sim1, c->cand, c->mean_sim1, c->n_cand, c->n_sel, c->flags, c->mean_sel,
                   c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth};
@@ -672,7 +749,29 @@ int vvs_ibvs_terms(vvs_handle c, const int32_t* uv, const int32_t* uv_star, cons
 int vvs_frame_pairs_to_twist(vvs_handle c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth,
                              int32_t n_pairs, const vvs_pair_out* out, vvs_stream stream) {
   if (!c || !goal || !cur || !depth) return fail(c, VVS_ERR_INVALID, "vvs_frame_pairs_to_twist: null argument");
-  return pairs_to_twist(c, goal, cur, depth, n_pairs, out, static_cast<cudaStream_t>(stream));
+  if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
+  if (!out || !out->twist) return fail(c, VVS_ERR_INVALID, "out->twist is required");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // the per-token match outputs are a test / inspection feature: those calls launch eagerly
+  const vvs_match_out& m = out->match;
+  const bool wants_match = m.nn1 || m.nn2 || m.sim1 || m.candidate || m.mean_sim1 || m.n_candidates || m.n_selected ||
+                           m.flags || m.sel_tok || m.sel_sim || m.uv_star || m.uv;
+  const bool want_mean = out->mean_sim_sel != nullptr;
+  const vvs_ctx::GraphEntry* g = wants_match ? nullptr : graphs_for(c, n_pairs, want_mean);
+  if (!g) return pairs_to_twist(c, goal, cur, depth, n_pairs, out, s);
+  // inputs -> workspace (device-to-device, ~25 us for 64 pairs), then the two graphs
+  const size_t img_bytes = static_cast<size_t>(c->cfg.image_size) * c->cfg.image_size * 3;
+  const size_t depth_bytes = static_cast<size_t>(c->cfg.frame_width) * c->cfg.frame_height * sizeof(uint16_t);
+  if (goal != c->stage_img)
+    VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img, goal, n_pairs * img_bytes, cudaMemcpyDeviceToDevice, s), &c->err);
+  if (cur != c->stage_img + n_pairs * img_bytes)
+    VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img + n_pairs * img_bytes, cur, n_pairs * img_bytes, cudaMemcpyDeviceToDevice, s),
+                &c->err);
+  if (depth != c->stage_depth)
+    VVS_CUDA_OK(cudaMemcpyAsync(c->stage_depth, depth, n_pairs * depth_bytes, cudaMemcpyDeviceToDevice, s), &c->err);
+  VVS_CUDA_OK(cudaGraphLaunch(g->execA, s), &c->err);
+  VVS_CUDA_OK(cudaGraphLaunch(g->execB, s), &c->err);
+  return copy_pair_results(c, n_pairs, out, s);
 }
 
 int vvs_frame_pairs_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth,
@@ -682,53 +781,31 @@ int vvs_frame_pairs_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8
     return fail(c, VVS_ERR_INVALID, "vvs_frame_pairs_to_twist_host: null argument");
   if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  // the legacy default stream cannot be captured into a graph: the call is synchronous anyway, so it runs on
-  // the handle's own stream in that case
+  // the call is synchronous; on the legacy default stream it runs on the handle's own stream instead
   if (s == nullptr || s == cudaStreamLegacy) s = c->own_stream;
   const size_t img_bytes = static_cast<size_t>(c->cfg.image_size) * c->cfg.image_size * 3;
   const size_t depth_elems = static_cast<size_t>(c->cfg.frame_width) * c->cfg.frame_height;
+  const bool want_mean = mean_sim_sel != nullptr;
+  // depth is read by the IBVS stage only: its copy (half of the input bytes) runs on a second stream under the
+  // forward pass.  The previous call synchronised, so the workspace is free.
+  VVS_CUDA_OK(cudaMemcpyAsync(c->stage_depth, depth, n_pairs * depth_elems * sizeof(uint16_t), cudaMemcpyHostToDevice,
+                              c->copy_stream),
+              &c->err);
+  VVS_CUDA_OK(cudaEventRecord(c->depth_ready, c->copy_stream), &c->err);
   VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img, goal, n_pairs * img_bytes, cudaMemcpyHostToDevice, s), &c->err);
   VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img + n_pairs * img_bytes, cur, n_pairs * img_bytes, cudaMemcpyHostToDevice, s),
               &c->err);
-  VVS_CUDA_OK(cudaMemcpyAsync(c->stage_depth, depth, n_pairs * depth_elems * sizeof(uint16_t), cudaMemcpyHostToDevice, s),
-              &c->err);
-  vvs_pair_out o;
-  memset(&o, 0, sizeof(o));
-  o.twist = c->twist;
-  o.mean_sim_sel = mean_sim_sel ? c->mean_sel : nullptr;
-  const int want_mean = mean_sim_sel ? 1 : 0;
-  int rc = VVS_OK;
-  // Every pointer of the device path is now a workspace address, so the ~100 launches replay as one graph.
-  // First call per batch size runs eagerly (lazy function attributes), the second is captured.
-  cudaGraphExec_t exec = nullptr;
-  if (c->graphs_enabled && !c->prof_on) {
-    for (auto& g : c->graphs)
-      if (g.n_pairs == n_pairs && g.want_mean == want_mean) exec = g.exec;
-    const bool warmed = std::find(c->eager_calls.begin(), c->eager_calls.end(), n_pairs) != c->eager_calls.end();
-    if (!exec && warmed && c->graphs.size() < 16) {
-      cudaGraph_t graph = nullptr;
-      if (cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
-        rc = pairs_to_twist(c, c->stage_img, c->stage_img + n_pairs * img_bytes, c->stage_depth, n_pairs, &o, s);
-        const cudaError_t e = cudaStreamEndCapture(s, &graph);
-        if (rc == VVS_OK && e == cudaSuccess && graph &&
-            cudaGraphInstantiate(&exec, graph, 0) == cudaSuccess) {
-          c->graphs.push_back({n_pairs, want_mean, exec});
-        } else {
-          exec = nullptr;
-          c->graphs_enabled = false;   // fall back to eager launches for good
-          cudaGetLastError();
-          rc = VVS_OK;
-        }
-        if (graph) cudaGraphDestroy(graph);
-      }
-    }
-    if (!warmed) c->eager_calls.push_back(n_pairs);
-  }
-  if (exec) {
-    VVS_CUDA_OK(cudaGraphLaunch(exec, s), &c->err);
+  const vvs_ctx::GraphEntry* g = graphs_for(c, n_pairs, want_mean);
+  int rc;
+  if (g) {
+    VVS_CUDA_OK(cudaGraphLaunch(g->execA, s), &c->err);
+    VVS_CUDA_OK(cudaStreamWaitEvent(s, c->depth_ready, 0), &c->err);
+    VVS_CUDA_OK(cudaGraphLaunch(g->execB, s), &c->err);
   } else {
-    rc = pairs_to_twist(c, c->stage_img, c->stage_img + n_pairs * img_bytes, c->stage_depth, n_pairs, &o, s);
-    if (rc) return rc;
+    c->launch_count = 0;
+    if ((rc = pairs_forward_match(c, c->stage_img, n_pairs, nullptr, s))) return rc;
+    VVS_CUDA_OK(cudaStreamWaitEvent(s, c->depth_ready, 0), &c->err);
+    if ((rc = pairs_control(c, c->stage_depth, n_pairs, want_mean, s))) return rc;
   }
   VVS_CUDA_OK(cudaMemcpyAsync(twist, c->twist, n_pairs * 6 * sizeof(double), cudaMemcpyDeviceToHost, s), &c->err);
   if (n_selected)
