@@ -166,6 +166,15 @@ def workload_name(model: str, pairs: int) -> str:
     return f"DINOv2 {nice} batch of {pairs} frame pairs per GPU (S=308, layer 11, 3x3-binned descriptors, K=24)"
 
 
+def ncu_traffic(cls):
+    """DRAM bytes per launch of a kernel class from the committed ncu capture (ViT-B, 64 pairs only), else None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1c_traffic.json")) as fh:
+            return json.load(fh)["bytes_per_launch"].get(cls)
+    except Exception:
+        return None
+
+
 def flops_per_pair(dim, tokens, layers, bin_parts):
     n = tokens + 1
     vit = 2.0 * 588 * dim * tokens + layers * (24.0 * n * dim * dim + 4.0 * n * n * dim)
@@ -336,7 +345,9 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": {"bound": "tensor", "kernel": f"gemm_tc_kernel ({dom})", "achieved": round(achieved, 1),
                          "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": round(achieved / pk["tf_sustained"], 3),
-                         "traffic": None, "peak_source": pk["source"] + ", sustained figure (kernel timed inside a long step)",
+                         "traffic": ncu_traffic(dom) if (args.model == "dinov2_vitb14" and B == 64) else None,
+                         "traffic_unit": "DRAM bytes per launch (profiles/r1c_traffic.json, one ncu --set full capture)",
+                         "peak_source": pk["source"] + ", sustained figure (kernel timed inside a long step)",
                          "avg_launch_ms": round(dom_ms, 4), "flops_per_launch": dom_fl},
             "kernels": kernels,
         }

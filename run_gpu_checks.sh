@@ -9,7 +9,7 @@ echo "exit $?" >> gpurun_out/bench.log
 if [ "$1" = "profile" ]; then
   CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline"
   $CMD > gpurun_out/plain.log 2>&1 &&
-  ncu --metrics gpu__time_duration.sum --clock-control none -s 279 -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
+  ncu --metrics gpu__time_duration.sum --clock-control none -s 420 -c 330 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
   $CMD > gpurun_out/plain2.log 2>&1 &&
   ncu --set full --clock-control none --import-source on -k regex:"gemm_tc|attention" -s 100 -c 5 -f -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
 fi

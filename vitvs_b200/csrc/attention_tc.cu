@@ -328,12 +328,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 }  // namespace
 
 int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
-                     std::string* err) {
+                     std::string* err, bool pdl) {
   static const bool use_v6 = []() {
     const char* e = getenv("VITVS_ATTN");
     return e && e[0] == '6';
   }();
-  if (!use_v6) return launch_attention_ts(qkv, out, n_img, n_tok, heads, stream, err);
+  if (!use_v6) return launch_attention_ts(qkv, out, n_img, n_tok, heads, stream, err, pdl);
   const int D = heads * kHD;
   CUtensorMap tmq, tmkv;
   const uint64_t rows = static_cast<uint64_t>(n_img) * n_tok;

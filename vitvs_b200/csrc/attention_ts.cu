@@ -143,6 +143,8 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  pdl_launch_dependents();   // the prologue above may overlap the previous kernel's tail
+  pdl_wait();
 
   const int t = warp >> 2;                          // query tile of this warpgroup
   if (t < n_qt) {
@@ -364,7 +366,7 @@ extern "C" __attribute__((visibility("default"))) int vvs_dbg_att_trace(long lon
 #endif
 
 int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
-                        std::string* err) {
+                        std::string* err, bool pdl) {
   const int D = heads * kHD;
   CUtensorMap tmq, tmkv;
   const uint64_t rows = static_cast<uint64_t>(n_img) * n_tok;
@@ -384,8 +386,7 @@ int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int he
   }
   const int q_tiles = (n_tok + kBQ - 1) / kBQ;
   dim3 grid((q_tiles + kQT - 1) / kQT, heads, n_img);
-  attention_ts_kernel<<<grid, kThreads, kSmem, stream>>>(tmq, tmkv, out, n_tok, D);
-  VVS_CUDA_OK(cudaGetLastError(), err);
+  VVS_CUDA_OK(launch_kernel(attention_ts_kernel, grid, kThreads, kSmem, stream, pdl, tmq, tmkv, out, n_tok, D), err);
   return VVS_OK;
 }
 

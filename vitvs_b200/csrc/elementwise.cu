@@ -3,6 +3,7 @@
 // Vectorised (128-bit) coalesced access, one warp per row with shuffle reductions; no tensor work.
 #include <string>
 
+#include "ptx.cuh"
 #include "vvs_internal.h"
 
 namespace vvs {
@@ -84,6 +85,8 @@ __global__ void __launch_bounds__(256)
 layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                  bf16* __restrict__ out, int rows, float eps) {
   constexpr int D = NV * 128;
+  pdl_launch_dependents();
+  pdl_wait();   // x is the previous kernel's output
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
@@ -245,16 +248,17 @@ int launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int
 }
 
 int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, int rows, int D, float eps,
-                     cudaStream_t s, std::string* err) {
+                     cudaStream_t s, std::string* err, bool pdl) {
   const int grid = (rows + 7) / 8;
+  cudaError_t e;
   switch (D) {
-    case 384: layernorm_kernel<3><<<grid, 256, 0, s>>>(x, w, b, out, rows, eps); break;
-    case 768: layernorm_kernel<6><<<grid, 256, 0, s>>>(x, w, b, out, rows, eps); break;
-    case 1024: layernorm_kernel<8><<<grid, 256, 0, s>>>(x, w, b, out, rows, eps); break;
-    case 1536: layernorm_kernel<12><<<grid, 256, 0, s>>>(x, w, b, out, rows, eps); break;
+    case 384: e = launch_kernel(layernorm_kernel<3>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps); break;
+    case 768: e = launch_kernel(layernorm_kernel<6>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps); break;
+    case 1024: e = launch_kernel(layernorm_kernel<8>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps); break;
+    case 1536: e = launch_kernel(layernorm_kernel<12>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps); break;
     default: set_error(err, "layernorm: unsupported width (384/768/1024/1536)"); return VVS_ERR_INVALID;
   }
-  VVS_CUDA_OK(cudaGetLastError(), err);
+  VVS_CUDA_OK(e, err);
   return VVS_OK;
 }
 

@@ -151,6 +151,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  // everything above (barriers, TMEM, descriptor prefetch) may overlap the previous kernel's tail
+  pdl_launch_dependents();
+  pdl_wait();
 
   // p.m_tiles counts (128 * NCTA)-row tiles; this CTA owns 128-row block m_tile * NCTA + cta_rank of each
   const int tiles_per_batch = p.m_tiles * p.n_tiles;
@@ -510,7 +513,7 @@ EncodeTiledFn get_encode_fn(std::string* err) {
 
 template <int BN, int EPI, int NCTA>
 int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const GemmDev& d, int grid,
-               cudaStream_t stream, std::string* err) {
+               cudaStream_t stream, bool pdl, std::string* err) {
   using C = Cfg<BN, NCTA>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -519,22 +522,22 @@ int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap
                 err);
     attr_set = true;
   }
-  gemm_tc_kernel<BN, EPI, NCTA><<<grid, kGemmThreads, C::kSmemBytes, stream>>>(tmA, tmB, tmOut, d);
-  VVS_CUDA_OK(cudaGetLastError(), err);
+  VVS_CUDA_OK(launch_kernel(gemm_tc_kernel<BN, EPI, NCTA>, grid, kGemmThreads, C::kSmemBytes, stream, pdl, tmA, tmB, tmOut, d),
+              err);
   return VVS_OK;
 }
 
 template <int BN, int NCTA>
 int dispatch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const GemmDev& d,
-                 int grid, cudaStream_t stream, std::string* err) {
+                 int grid, cudaStream_t stream, bool pdl, std::string* err) {
   switch (epi) {
-    case EPI_BIAS_BF16: return launch_one<BN, EPI_BIAS_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, err);
-    case EPI_GELU_BF16: return launch_one<BN, EPI_GELU_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, err);
-    case EPI_RESID_F32: return launch_one<BN, EPI_RESID_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, err);
-    case EPI_PATCH_F32: return launch_one<BN, EPI_PATCH_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, err);
-    case EPI_SWIGLU_BF16: return launch_one<BN, EPI_SWIGLU_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, err);
-    case EPI_SIM: return launch_one<BN, EPI_SIM, NCTA>(tmA, tmB, tmOut, d, grid, stream, err);
-    case EPI_STORE_F32: return launch_one<BN, EPI_STORE_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, err);
+    case EPI_BIAS_BF16: return launch_one<BN, EPI_BIAS_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_GELU_BF16: return launch_one<BN, EPI_GELU_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_RESID_F32: return launch_one<BN, EPI_RESID_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_PATCH_F32: return launch_one<BN, EPI_PATCH_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_SWIGLU_BF16: return launch_one<BN, EPI_SWIGLU_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_SIM: return launch_one<BN, EPI_SIM, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_STORE_F32: return launch_one<BN, EPI_STORE_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
     default: set_error(err, "launch_gemm: unknown epilogue"); return VVS_ERR_INVALID;
   }
 }
@@ -651,12 +654,12 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   const long long tiles = static_cast<long long>(d.batch) * d.m_tiles * d.n_tiles;
   if (ncta == 2) {
     const int grid = 2 * static_cast<int>(std::min<long long>(tiles, num_sms / 2));
-    if (bn == 256) return dispatch_epi<256, 2>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, err);
-    return dispatch_epi<128, 2>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, err);
+    if (bn == 256) return dispatch_epi<256, 2>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
+    return dispatch_epi<128, 2>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
   }
   const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
-  if (bn == 256) return dispatch_epi<256, 1>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, err);
-  return dispatch_epi<128, 1>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, err);
+  if (bn == 256) return dispatch_epi<256, 1>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
+  return dispatch_epi<128, 1>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
 }
 
 }  // namespace vvs

@@ -65,6 +65,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 #endif
 }
 
+// ----------------------------------------------------------------------------- programmatic dependent launch
+// A kernel launched with the programmatic-stream-serialization attribute may start while its predecessor is
+// still running: pdl_launch_dependents() (early) lets the NEXT kernel's CTAs take free SMs and run their prologue;
+// pdl_wait() blocks until every predecessor grid has completed and flushed.  Both are no-ops in a normal launch.
+// Every kernel of a PDL chain must execute pdl_wait() before it exits (completion order stays transitive).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ----------------------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");

@@ -30,6 +30,25 @@ void set_error(std::string* slot, const std::string& msg);
     }                                                                                                   \
   } while (0)
 
+// ---- launches ------------------------------------------------------------------------------------
+// <<< >>> with an optional programmatic-dependent-launch attribute (ptx.cuh: pdl_wait / pdl_launch_dependents)
+bool pdl_enabled();   // VITVS_PDL=1 turns it on (off by default, see api.cu)
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl,
+                                 Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (pdl && pdl_enabled()) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ---- TMA tensor maps ---------------------------------------------------------------------------
 // bf16 tensor [batch, rows, cols] (cols contiguous, row pitch ld elements, batch pitch in elements),
 // box = {64 cols, box_rows, 1}, SWIZZLE_128B, zero fill out of bounds.
@@ -69,6 +88,7 @@ struct GemmArgs {
   unsigned long long* row_best;   // [batch, best_pitch] (EPI_SIM)
   unsigned long long* col_best;   // [batch, best_pitch]
   int best_pitch;
+  int pdl;               // launch with the programmatic-dependent-launch attribute (predecessor is a PDL-aware kernel)
 };
 int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string* err);
 int gemm_block_n(int N);   // the N tile the launcher picks for this N (128 or 256)
@@ -76,10 +96,10 @@ int gemm_block_n(int N);   // the N tile the launcher picks for this N (128 or 2
 // ---- attention ---------------------------------------------------------------------------------
 // qkv: [n_img * n_tok, 3*D] bf16 (q pre-scaled by hd^-0.5), out: [n_img * n_tok, D] bf16
 int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
-                     std::string* err);
+                     std::string* err, bool pdl = false);
 // generation 7 (attention_ts.cu): P stays in TMEM (TS MMA), two CTAs per SM; launch_attention dispatches to it
 int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
-                        std::string* err);
+                        std::string* err, bool pdl = false);
 
 // ---- bandwidth-bound kernels -------------------------------------------------------------------
 int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err);
@@ -87,7 +107,7 @@ int launch_im2col_f32(const float* img, bf16* out, int n_img, int size, int kpad
 int launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int n_tok, int D, cudaStream_t s,
                     std::string* err);
 int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, int rows, int D, float eps,
-                     cudaStream_t s, std::string* err);
+                     cudaStream_t s, std::string* err, bool pdl = false);
 // residual stream [n_img, 1+T, D] -> descriptors (CLS dropped, optional 3x3 log-binning)
 int launch_descriptors_f32(const float* x, float* out, int n_img, int hp, int wp, int D, int bin, cudaStream_t s,
                            std::string* err);
