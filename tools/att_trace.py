@@ -16,16 +16,14 @@ lib = ctypes.CDLL(os.environ["VITVS_LIB"])
 buf = np.zeros(4 * 3 * 16 * 8, dtype=np.int64)
 rc = lib.vvs_dbg_att_trace(buf.ctypes.data_as(ctypes.c_void_p))
 tr = buf.reshape(4, 3, 16, 8)
-names = ["top", "half", "nextS", "exps", "arrive"]
-t0 = tr[0, 0, 0, 0]
-for w, wn in enumerate(["warp0 (tile0)", "warp1 (tile0)", "warp4 (tile1)"]):
-    print(wn, "(CTA 17, first 64 blocks of the tile; clk relative to warp 0's first block)")
-    prev = None
-    for g in range(64):
-        ev = tr[g >> 4, w, g & 15]
-        if not ev[0]:
-            continue
-        rel = [int(e - t0) for e in ev[:5]]
-        dt = "" if prev is None else f"  (+{rel[0] - prev})"
-        prev = rel[0]
-        print(f"  g={g:2d} " + "  ".join(f"{n}:{r}" for n, r in zip(names, rel)) + dt)
+nblk = (n_tok + 63) // 64
+names = ["top", "s_full", "Sregs", "math", "arrive", "p_full ok", "PV issued", "S issued"]
+for slot in range(4):
+    t0 = tr[slot, 0, 0, 0]
+    print(f"--- CTA slot {slot} (rc {rc}); clk relative to warp 0 loop start")
+    for w, wn in enumerate(["warp0 (tile0 issuer)", "warp1 (tile0)", "warp4 (tile1 issuer)"]):
+        print(" ", wn)
+        for j in range(nblk):
+            ev = tr[slot, w, j]
+            rel = [int(e - t0) if e else -1 for e in ev]
+            print(f"    j={j:2d} " + "  ".join(f"{n}:{r}" for n, r in zip(names, rel) if r >= 0 or True))

@@ -51,6 +51,9 @@ constexpr uint32_t kSmem = kOffBar + 256 + 1024;   // + barriers + alignment sla
 constexpr uint32_t kTmemCols = 256;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kRescaleLog2 = 8.0f;
+#ifndef VVS_ATT_STAGGER
+#define VVS_ATT_STAGGER 0
+#endif
 
 __device__ __forceinline__ float ex2_approx(float x) {   // single MUFU.EX2; ex2(-inf) = 0
   float y;
@@ -116,7 +119,9 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const int lane = tid & 31;
   const int qt0 = blockIdx.x * kQT;               // first query tile of this CTA
   const int head = blockIdx.y;
-  const int img = blockIdx.z;
+  // the QKV GEMM wrote the matrix in ascending row order and it is larger than L2: start with the images that
+  // are still resident
+  const int img = static_cast<int>(gridDim.z) - 1 - static_cast<int>(blockIdx.z);
   const int row_base = img * n_tok;               // first row of this image in the qkv matrix
   const int nblk = (n_tok + kBKV - 1) / kBKV;
   const int n_qt = min(kQT, (n_tok + kBQ - 1) / kBQ - qt0);   // active tiles (last CTA of a sequence)
@@ -186,9 +191,9 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         if (++polls == (1u << 26)) __trap();
       }
     };
-    auto issue_S = [&](int b) {     // S_t(b) = Q_t K(b)^T
+    auto issue_S = [&](int b, bool k_ready) {     // S_t(b) = Q_t K(b)^T
       const int st = b % kKVStages;
-      wait_pump(&k_full[st], (b / kKVStages) & 1);
+      if (!k_ready) wait_pump(&k_full[st], (b / kKVStages) & 1);
       tc_fence_after();
       const uint32_t ka = sbase + kOffK + st * kKVBytes;
 #ifndef VVS_EXP_NOMMA
@@ -208,7 +213,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         pump();
       }
       wait_pump(&q_full[t], 0);
-      issue_S(0);
+      issue_S(0, false);
       umma_commit(&s_full[t]);
     }
     __syncwarp();
@@ -232,10 +237,26 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       VVS_TR(0);
       mbar_wait(&s_full[t], j & 1);
       tc_fence_after();
+#if VVS_ATT_STAGGER > 0
+      // The tiles sharing an SM sub-partition's MUFU tend to run in lock step (all in their exponentials, then all
+      // in their hand-offs); a one-off offset of the second tile lets one fill the other's gaps.
+      if (j == 0 && t == 1) {
+        const long long t0 = clock64();
+        while (clock64() - t0 < VVS_ATT_STAGGER) {
+        }
+      }
+#endif
       VVS_TR(1);
       uint32_t sc[2][32];                   // the row of S (fp32 bits)
       tmem_ld32(tS, sc[0]);
       tmem_ld32(tS + 32, sc[1]);
+      // the operands of this block's MMAs landed long ago, but an mbarrier wait costs 100-250 clk even then: probe
+      // now, look at the answers after the exponentials
+      bool v_ready = false, k_ready = false;
+      if (issuer) {
+        v_ready = mbar_test_wait(&v_full[j % kKVStages], (j / kKVStages) & 1);
+        if (j + 1 < nblk) k_ready = mbar_test_wait(&k_full[(j + 1) % kKVStages], ((j + 1) / kKVStages) & 1);
+      }
       tmem_ld_wait();
       VVS_TR(2);
 #ifdef VVS_EXP_NOMATH   // timing experiment: MMA + hand-off chain only (wrong numerics)
@@ -306,11 +327,10 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       if (wq == 0) {
         if (issuer) {
           const int st = j % kKVStages;
-          wait_pump(&v_full[st], (j / kKVStages) & 1);
-          VVS_TR(5);
+          if (!v_ready) wait_pump(&v_full[st], (j / kKVStages) & 1);
           wait_pump(&p_full[t], j & 1);               // all four warps: P_t(j) in TMEM, O_t rescaled if it had to be
           tc_fence_after();
-          VVS_TR(6);
+          VVS_TR(5);
           const uint32_t va = sbase + kOffV + st * kKVBytes;
 #ifndef VVS_EXP_NOMMA
 #pragma unroll
@@ -319,10 +339,11 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                          idescPV, (j > 0 || kk != 0) ? 1u : 0u);                          // O accumulates across key blocks
 #endif
           umma_commit(&v_empty[st]);
-          if (j + 1 < nblk) issue_S(j + 1);           // in order behind PV(j): may overwrite P(j)
+          VVS_TR(6);
+          if (j + 1 < nblk) issue_S(j + 1, k_ready);   // in order behind PV(j): may overwrite P(j)
           umma_commit(&s_full[t]);                    // S(j+1) ready and PV(j) done (last block: O final)
-          if (producer) pump();
           VVS_TR(7);
+          if (producer) pump();
         }
         __syncwarp();
       }
