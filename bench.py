@@ -212,15 +212,21 @@ def run_ours(args):
     # synthetic inputs: 8 distinct pairs tiled to the batch, NSETS rotated input sets (rank-offset seeds)
     NSETS = 4
     base = rank * 1000
-    sets_host, sets_dev = [], []
+    import numpy as np
+    sets_host, sets_dev, raw_host = [], [], []
+    NRAW = 2                                   # un-resized 640x480 camera-frame sets for the e2e_frames leg
     for s in range(NSETS):
-        prs = [synth.frame_pair(base + 8 * s + i, S) for i in range(8)]
+        raw = [synth.raw_frame_pair(base + 8 * s + i) for i in range(8)]
+        prs = [(synth.resize_square(gr, S), synth.resize_square(cr, S), dr) for gr, cr, dr in raw]
         idx = [i % 8 for i in range(B)]
-        g = torch.from_numpy(__import__("numpy").stack([prs[j][0] for j in idx]))
-        c = torch.from_numpy(__import__("numpy").stack([prs[j][1] for j in idx]))
-        d = torch.from_numpy(__import__("numpy").stack([prs[j][2] for j in idx]))
+        g = torch.from_numpy(np.stack([prs[j][0] for j in idx]))
+        c = torch.from_numpy(np.stack([prs[j][1] for j in idx]))
+        d = torch.from_numpy(np.stack([prs[j][2] for j in idx]))
         sets_host.append((g.pin_memory(), c.pin_memory(), d.pin_memory()))
         sets_dev.append((g.to(dev), c.to(dev), d.to(dev)))
+        if s < NRAW:
+            raw_host.append((torch.from_numpy(np.stack([raw[j][0] for j in idx])).pin_memory(),
+                             torch.from_numpy(np.stack([raw[j][1] for j in idx])).pin_memory(), sets_host[-1][2]))
     stream = torch.cuda.current_stream(dev)
 
     def barrier():
@@ -262,6 +268,19 @@ def run_ours(args):
     barrier()
     ms_e2e = e2.elapsed_time(e3)
 
+    # ---- the same from the un-resized 640x480 camera frames: PIL-exact bicubic resize on the GPU
+    for i in range(min(args.warmup, 3)):
+        eng.frames_to_twist_host(*raw_host[i % NRAW], tw, ns, msim)
+    barrier()
+    e4, e5 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e4.record(stream)
+    for i in range(args.steps):
+        eng.frames_to_twist_host(*raw_host[i % NRAW], tw, ns, msim)
+    e5.record(stream)
+    barrier()
+    ms_e2e_frames = e4.elapsed_time(e5)
+    launches_frames = eng.last_launch_count()
+
     # ---- p50 single frame-pair latency (the metric's second half): one pair per call through the same
     # host-buffer C-ABI call (H2D + device path as one CUDA-graph replay + D2H + sync), wall clock per call
     latency = None
@@ -286,18 +305,20 @@ def run_ours(args):
         eng1.close()
 
     if world > 1:
-        t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+        t = torch.tensor([ms, ms_e2e, ms_e2e_frames], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, ms_e2e = t.tolist()
+        ms, ms_e2e, ms_e2e_frames = t.tolist()
 
     # ---- per-kernel-class device time, live, on the launching stream (2 extra profiled steps)
     prof = None
     if rank == 0:
         eng.profile(True)
         PS = 2
+        raw_dev = tuple(t.to(dev) for t in raw_host[0])
         for i in range(PS):
-            eng.frame_pairs_to_twist(*sets_dev[i % NSETS])
+            eng.frames_to_twist(*raw_dev)          # resize (both frames of every pair) + the pre-resized path
         torch.cuda.synchronize(dev)
+        del raw_dev
         prof = eng.profile_read()
         eng.profile(False)
         prof = {k: (v[0] / PS, v[1] // PS) for k, v in prof.items()}
@@ -340,6 +361,12 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": UNIT,
                     "h2d_bytes_per_step": B * (2 * S * S * 3 + cfg.u_max * cfg.v_max * 2),
                     "d2h_bytes_per_step": B * (6 * 8 + 4 + 4), "ms_per_step": ms_e2e / args.steps},
+            "e2e_frames": {"value": total_pairs / (ms_e2e_frames / 1e3), "unit": UNIT,
+                           "h2d_bytes_per_step": B * (2 * cfg.u_max * cfg.v_max * 3 + cfg.u_max * cfg.v_max * 2),
+                           "d2h_bytes_per_step": B * (6 * 8 + 4 + 4), "ms_per_step": ms_e2e_frames / args.steps,
+                           "gpu_launches_per_step": launches_frames,
+                           "what": "vvs_frames_to_twist_host: un-resized 640x480 RGB frames in pinned host memory; the "
+                                   "PIL-exact bicubic resize (vitvs_v2.py:474-475) runs on the GPU"},
             "latency": latency,
             "gpu_launches": launches,
             "clocks": clocks,

@@ -41,7 +41,7 @@ enum vvs_status {
 
 enum vvs_dtype { VVS_F32 = 0, VVS_BF16 = 1 };
 enum vvs_image_kind {
-  VVS_IMAGE_U8_HWC = 0,  /* [n, S, S, 3] uint8 RGB, already resized (vitvs_v2.py:474-475 stays on the host) */
+  VVS_IMAGE_U8_HWC = 0,  /* [n, S, S, 3] uint8 RGB, already resized (vitvs_v2.py:474-475; see vvs_resize_frames) */
   VVS_IMAGE_F32_NCHW = 1 /* [n, 3, S, S] fp32, output of ViTExtractor.preprocess_pil (dinov2_extractor.py:177-191) */
 };
 
@@ -159,14 +159,31 @@ VVS_API int vvs_frame_pairs_to_twist(vvs_handle h, const uint8_t* goal, const ui
 VVS_API int vvs_frame_pairs_to_twist_host(vvs_handle h, const uint8_t* goal_host, const uint8_t* current_host,
                                   const uint16_t* depth_host, int32_t n_pairs, double* twist_host,
                                   int32_t* n_selected_host, float* mean_sim_sel_host, vvs_stream stream);
-/* number of kernels the last vvs_frame_pairs_to_twist* call launched (bench.py gpu_launches). */
+
+/* replaces: PIL `Image.resize((S, S))` of the goal / current camera frame (vitvs_v2.py:474-475; Pillow default
+ * filter = antialiased BICUBIC, 8-bit fixed point, horizontal pass then vertical pass).  frames
+ * [n, frame_height, frame_width, 3] uint8 RGB (device) -> out [n, S, S, 3] uint8 (device), bit-identical to
+ * Pillow 12.2 (integer arithmetic).  n <= max_images. */
+VVS_API int vvs_resize_frames(vvs_handle h, const uint8_t* frames, int32_t n, uint8_t* out, vvs_stream stream);
+/* vvs_frame_pairs_to_twist on raw camera frames: goal / current [n_pairs, frame_height, frame_width, 3] uint8
+ * (device); the resize of vitvs_v2.py:474-475 runs on the GPU ahead of the patch embedding. */
+VVS_API int vvs_frames_to_twist(vvs_handle h, const uint8_t* goal_frames, const uint8_t* current_frames,
+                        const uint16_t* depth, int32_t n_pairs, const vvs_pair_out* out, vvs_stream stream);
+/* same with HOST buffers (the whole of one Controller.ibvs() iteration from the camera callbacks' buffers,
+ * vitvs_v2.py:455-462 -> :622): H2D, resize, the whole path, D2H, stream synchronise.  Like
+ * vvs_frame_pairs_to_twist_host the batch is processed in sub-batches so that the H2D copies of one run under
+ * the compute of the previous one. */
+VVS_API int vvs_frames_to_twist_host(vvs_handle h, const uint8_t* goal_frames_host, const uint8_t* current_frames_host,
+                             const uint16_t* depth_host, int32_t n_pairs, double* twist_host,
+                             int32_t* n_selected_host, float* mean_sim_sel_host, vvs_stream stream);
+/* number of kernels the last vvs_frame_pairs_to_twist* / vvs_frames_to_twist* call launched (bench.py gpu_launches). */
 VVS_API int vvs_last_launch_count(vvs_handle h);
 
 /* ---- per-kernel-class device timing (CUDA events on the launching stream around every launch) -------- */
 enum vvs_kernel_class {
   VVS_K_OTHER = 0, VVS_K_IM2COL = 1, VVS_K_PATCH_GEMM = 2, VVS_K_LAYERNORM = 3, VVS_K_QKV_GEMM = 4,
   VVS_K_ATTENTION = 5, VVS_K_PROJ_GEMM = 6, VVS_K_FFN1_GEMM = 7, VVS_K_FFN2_GEMM = 8, VVS_K_DESCRIPTORS = 9,
-  VVS_K_SIM_GEMM = 10, VVS_K_SELECT = 11, VVS_K_IBVS = 12, VVS_K_COUNT = 13
+  VVS_K_SIM_GEMM = 10, VVS_K_SELECT = 11, VVS_K_IBVS = 12, VVS_K_RESIZE = 13, VVS_K_COUNT = 14
 };
 VVS_API int vvs_profile_enable(vvs_handle h, int32_t on);
 /* sums (ms) and launch counts per vvs_kernel_class since the last read; synchronises on the events. */

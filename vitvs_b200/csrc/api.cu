@@ -119,6 +119,11 @@ struct vvs_ctx {
   double* twist = nullptr;
   uint8_t* stage_img = nullptr;    // [max_images, S, S, 3]
   uint16_t* stage_depth = nullptr; // [max_pairs, H, W]
+  // camera-frame front end (created on first use): Pillow-exact bicubic resize tables + staging
+  bool rz_ready = false;
+  ResizeAxis rz_w, rz_h;           // frame_width -> S (horizontal pass), frame_height -> S (vertical pass)
+  uint8_t* stage_frames = nullptr; // [max_images, H, W, 3] raw frames (also the H2D landing zone of the host entries)
+  uint8_t* rz_tmp = nullptr;       // [max_images, H, S, 3] output of the horizontal pass
   int last_n_img = 0;
   int launch_count = 0;
   // optional per-kernel-class CUDA-event profiler (vvs_profile_*)
@@ -132,7 +137,10 @@ struct vvs_ctx {
   cudaStream_t copy_stream = nullptr;   // depth H2D overlaps the forward pass (depth is only read by the IBVS stage)
   cudaEvent_t depth_ready = nullptr;
   // execA: images (workspace) -> tokens -> descriptors -> matches;  execB: depth (workspace) -> twist
-  struct GraphEntry { int n_pairs; int want_mean; cudaGraphExec_t execA; cudaGraphExec_t execB; };
+  struct GraphEntry { int n_pairs; int want_mean; cudaGraphExec_t execA; cudaGraphExec_t execB; int launchesA; int launches; };
+  std::vector<cudaEvent_t> chunk_events;   // host pipeline: [2 * chunk] frames landed / depth landed
+  int host_chunks = 0;                     // sub-batches of a host-buffer call (H2D of chunk j+1 under the compute of chunk j);
+                                           // 0 = default: 2 for camera frames (3.2x the bytes), 1 for pre-resized images
   std::vector<GraphEntry> graphs;
   std::vector<int> eager_calls;      // n_pairs values that already ran eagerly once (lazy init done)
   bool graphs_enabled = true;
@@ -463,22 +471,20 @@ const vvs_ctx::GraphEntry* graphs_for(vvs_ctx* c, int n_pairs, bool want_mean) {
     return nullptr;
   }
   if (c->graphs.size() >= 16) return nullptr;
-  const size_t img_bytes = static_cast<size_t>(c->cfg.image_size) * c->cfg.image_size * 3;
   cudaStream_t cs = c->own_stream;
   cudaGraphExec_t exec[2] = {nullptr, nullptr};
   bool ok = true;
+  int launches_a = 0;
   for (int part = 0; part < 2 && ok; ++part) {
     cudaGraph_t graph = nullptr;
     if (cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
       ok = false;
       break;
     }
-    const int saved = c->launch_count;
     if (part == 0) c->launch_count = 0;
     const int rc = part == 0 ? pairs_forward_match(c, c->stage_img, n_pairs, nullptr, cs)
                              : pairs_control(c, c->stage_depth, n_pairs, want_mean, cs);
-    (void)saved;
-    (void)img_bytes;
+    if (part == 0) launches_a = c->launch_count;
     const cudaError_t e = cudaStreamEndCapture(cs, &graph);
     ok = rc == VVS_OK && e == cudaSuccess && graph && cudaGraphInstantiate(&exec[part], graph, 0) == cudaSuccess;
     if (graph) cudaGraphDestroy(graph);
@@ -490,8 +496,128 @@ const vvs_ctx::GraphEntry* graphs_for(vvs_ctx* c, int n_pairs, bool want_mean) {
     cudaGetLastError();
     return nullptr;
   }
-  c->graphs.push_back({n_pairs, want_mean ? 1 : 0, exec[0], exec[1]});
+  c->graphs.push_back({n_pairs, want_mean ? 1 : 0, exec[0], exec[1], launches_a, c->launch_count});
   return &c->graphs.back();
+}
+
+// camera-frame front end: resize tables (pure functions of the geometry) and staging, created on first use
+int ensure_frontend(vvs_ctx* c) {
+  if (c->rz_ready) return VVS_OK;
+  const vvs_config& f = c->cfg;
+  if (f.frame_width < 1 || f.frame_height < 1) return fail(c, VVS_ERR_INVALID, "frame_width / frame_height not set");
+  int rc = make_resize_axis(&c->rz_w, f.frame_width, f.image_size, &c->err);
+  if (!rc) rc = make_resize_axis(&c->rz_h, f.frame_height, f.image_size, &c->err);
+  const size_t frame_bytes = static_cast<size_t>(f.frame_width) * f.frame_height * 3;
+  if (!rc) rc = dev_alloc(c, &c->stage_frames, static_cast<size_t>(f.max_images) * frame_bytes);
+  if (!rc) rc = dev_alloc(c, &c->rz_tmp, static_cast<size_t>(f.max_images) * f.frame_height * f.image_size * 3);
+  if (rc) return rc;
+  c->rz_ready = true;
+  return VVS_OK;
+}
+
+// frames [n, H, W, 3] u8 -> out [n, S, S, 3] u8, both passes of PIL Image.resize (a pass that would not change the
+// size is skipped, as Pillow does)
+int resize_frames(vvs_ctx* c, const uint8_t* frames, int n, uint8_t* out, cudaStream_t s) {
+  const vvs_config& f = c->cfg;
+  const int S = f.image_size;
+  const bool need_h = f.frame_width != S, need_v = f.frame_height != S;
+  if (!need_h && !need_v) {
+    VVS_CUDA_OK(cudaMemcpyAsync(out, frames, static_cast<size_t>(n) * S * S * 3, cudaMemcpyDeviceToDevice, s), &c->err);
+    return VVS_OK;
+  }
+  int rc = VVS_OK;
+  const uint8_t* v_in = frames;
+  if (need_h) {
+    uint8_t* h_out = need_v ? c->rz_tmp : out;
+    ProfScope ps(c, VVS_K_RESIZE, s);
+    rc = launch_resize_h(frames, h_out, n * f.frame_height, c->rz_w, s, &c->err);
+    ++c->launch_count;
+    v_in = h_out;
+  }
+  if (!rc && need_v) {
+    ProfScope ps(c, VVS_K_RESIZE, s);
+    rc = launch_resize_v(v_in, out, n, S * 3, c->rz_h, s, &c->err);
+    ++c->launch_count;
+  }
+  return rc;
+}
+
+// Host-buffer calls, pipelined: the batch is cut into sub-batches; the H2D copies of sub-batch j+1 (copy stream) run
+// under the device path of sub-batch j (compute stream).  Inputs land in stage_frames / stage_depth at their natural
+// offsets; each sub-batch is resized (camera frames) or copied (pre-resized images) into the [goal.. | current..]
+// block at the head of stage_img that the captured graph reads.  from_frames: inputs are [n, H, W, 3] camera frames.
+int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth, int n_pairs, bool from_frames,
+                  double* twist, int32_t* n_selected, float* mean_sim_sel, cudaStream_t s) {
+  const vvs_config& f = c->cfg;
+  int rc = ensure_frontend(c);
+  if (rc) return rc;
+  const size_t img_bytes = static_cast<size_t>(f.image_size) * f.image_size * 3;
+  const size_t frame_bytes = static_cast<size_t>(f.frame_width) * f.frame_height * 3;
+  const size_t in_bytes = from_frames ? frame_bytes : img_bytes;
+  const size_t depth_elems = static_cast<size_t>(f.frame_width) * f.frame_height;
+  const bool want_mean = mean_sim_sel != nullptr;
+  if (!from_frames && img_bytes > frame_bytes)
+    return fail(c, VVS_ERR_STATE, "image_size larger than the camera frame: host staging too small");
+  const int want_chunks = c->host_chunks > 0 ? c->host_chunks : (from_frames ? 2 : 1);
+  int chunks = std::max(1, std::min(want_chunks, n_pairs / 8));
+  const int per = (n_pairs + chunks - 1) / chunks;
+  chunks = (n_pairs + per - 1) / per;
+  while (c->chunk_events.size() < static_cast<size_t>(2 * chunks)) {
+    cudaEvent_t e;
+    VVS_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), &c->err);
+    c->chunk_events.push_back(e);
+  }
+  uint8_t* land_goal = c->stage_frames;
+  uint8_t* land_cur = c->stage_frames + static_cast<size_t>(n_pairs) * in_bytes;
+  // the previous call synchronised, so every staging buffer is free
+  for (int j = 0; j < chunks; ++j) {
+    const int p0 = j * per, nc = std::min(per, n_pairs - p0);
+    VVS_CUDA_OK(cudaMemcpyAsync(land_goal + p0 * in_bytes, goal + p0 * in_bytes, nc * in_bytes, cudaMemcpyHostToDevice,
+                                c->copy_stream), &c->err);
+    VVS_CUDA_OK(cudaMemcpyAsync(land_cur + p0 * in_bytes, cur + p0 * in_bytes, nc * in_bytes, cudaMemcpyHostToDevice,
+                                c->copy_stream), &c->err);
+    VVS_CUDA_OK(cudaEventRecord(c->chunk_events[2 * j], c->copy_stream), &c->err);
+    VVS_CUDA_OK(cudaMemcpyAsync(c->stage_depth + p0 * depth_elems, depth + p0 * depth_elems,
+                                nc * depth_elems * sizeof(uint16_t), cudaMemcpyHostToDevice, c->copy_stream), &c->err);
+    VVS_CUDA_OK(cudaEventRecord(c->chunk_events[2 * j + 1], c->copy_stream), &c->err);
+  }
+  int launches = 0;
+  for (int j = 0; j < chunks; ++j) {
+    const int p0 = j * per, nc = std::min(per, n_pairs - p0);
+    VVS_CUDA_OK(cudaStreamWaitEvent(s, c->chunk_events[2 * j], 0), &c->err);
+    c->launch_count = 0;
+    if (from_frames) {
+      if ((rc = resize_frames(c, land_goal + p0 * in_bytes, nc, c->stage_img, s))) return rc;
+      if ((rc = resize_frames(c, land_cur + p0 * in_bytes, nc, c->stage_img + nc * img_bytes, s))) return rc;
+    } else {
+      VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img, land_goal + p0 * in_bytes, nc * img_bytes, cudaMemcpyDeviceToDevice, s),
+                  &c->err);
+      VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img + nc * img_bytes, land_cur + p0 * in_bytes, nc * img_bytes,
+                                  cudaMemcpyDeviceToDevice, s), &c->err);
+    }
+    launches += c->launch_count;
+    const vvs_ctx::GraphEntry* g = graphs_for(c, nc, want_mean);
+    if (g) {
+      VVS_CUDA_OK(cudaGraphLaunch(g->execA, s), &c->err);
+      launches += g->launchesA;
+    } else {
+      c->launch_count = 0;
+      if ((rc = pairs_forward_match(c, c->stage_img, nc, nullptr, s))) return rc;
+      launches += c->launch_count;
+    }
+    VVS_CUDA_OK(cudaStreamWaitEvent(s, c->chunk_events[2 * j + 1], 0), &c->err);
+    c->launch_count = 0;
+    if ((rc = pairs_control(c, c->stage_depth + p0 * depth_elems, nc, want_mean, s))) return rc;
+    launches += c->launch_count;
+    VVS_CUDA_OK(cudaMemcpyAsync(twist + p0 * 6, c->twist, nc * 6 * sizeof(double), cudaMemcpyDeviceToHost, s), &c->err);
+    if (n_selected)
+      VVS_CUDA_OK(cudaMemcpyAsync(n_selected + p0, c->n_sel, nc * sizeof(int32_t), cudaMemcpyDeviceToHost, s), &c->err);
+    if (mean_sim_sel)
+      VVS_CUDA_OK(cudaMemcpyAsync(mean_sim_sel + p0, c->mean_sel, nc * sizeof(float), cudaMemcpyDeviceToHost, s), &c->err);
+  }
+  c->launch_count = launches;
+  VVS_CUDA_OK(cudaStreamSynchronize(s), &c->err);
+  return VVS_OK;
 }
 
 }  // namespace
@@ -573,6 +699,7 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
     return VVS_ERR_CUDA;
   }
   if (const char* e = getenv("VITVS_GRAPHS")) c->graphs_enabled = e[0] != '0';
+  if (const char* e = getenv("VITVS_HOST_CHUNKS")) c->host_chunks = std::max(1, atoi(e));
   *out = c;
   return VVS_OK;
 }
@@ -586,9 +713,13 @@ int vvs_destroy(vvs_handle c) {
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->depth_ready) cudaEventDestroy(c->depth_ready);
+  for (cudaEvent_t e : c->chunk_events) cudaEventDestroy(e);
+  free_resize_axis(&c->rz_w);
+  free_resize_axis(&c->rz_h);
   void* ptrs[] = {c->pe_w, c->pe_b, c->cls, c->pos, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
                   c->nn1, c->nn2, c->sim1, c->cand, c->mean_sim1, c->n_cand, c->n_sel, c->flags, c->mean_sel,
-                  c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth};
+                  c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth, c->stage_frames,
+                  c->rz_tmp};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : c->prof_events) cudaEventDestroy(e);
@@ -786,6 +917,7 @@ int vvs_frame_pairs_to_twist(vvs_handle c, const uint8_t* goal, const uint8_t* c
     VVS_CUDA_OK(cudaMemcpyAsync(c->stage_depth, depth, n_pairs * depth_bytes, cudaMemcpyDeviceToDevice, s), &c->err);
   VVS_CUDA_OK(cudaGraphLaunch(g->execA, s), &c->err);
   VVS_CUDA_OK(cudaGraphLaunch(g->execB, s), &c->err);
+  c->launch_count = g->launches;
   return copy_pair_results(c, n_pairs, out, s);
 }
 
@@ -798,37 +930,44 @@ int vvs_frame_pairs_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // the call is synchronous; on the legacy default stream it runs on the handle's own stream instead
   if (s == nullptr || s == cudaStreamLegacy) s = c->own_stream;
+  return host_pipeline(c, goal, cur, depth, n_pairs, /*from_frames=*/false, twist, n_selected, mean_sim_sel, s);
+}
+
+int vvs_resize_frames(vvs_handle c, const uint8_t* frames, int32_t n, uint8_t* out, vvs_stream stream) {
+  if (!c || !frames || !out) return fail(c, VVS_ERR_INVALID, "vvs_resize_frames: null argument");
+  if (n < 1 || n > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "vvs_resize_frames: n outside [1, max_images]");
+  int rc = ensure_frontend(c);
+  if (rc) return rc;
+  c->launch_count = 0;
+  return resize_frames(c, frames, n, out, static_cast<cudaStream_t>(stream));
+}
+
+int vvs_frames_to_twist(vvs_handle c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth, int32_t n_pairs,
+                        const vvs_pair_out* out, vvs_stream stream) {
+  if (!c || !goal || !cur || !depth) return fail(c, VVS_ERR_INVALID, "vvs_frames_to_twist: null argument");
+  if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
+  if (!out || !out->twist) return fail(c, VVS_ERR_INVALID, "out->twist is required");
+  int rc = ensure_frontend(c);
+  if (rc) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
   const size_t img_bytes = static_cast<size_t>(c->cfg.image_size) * c->cfg.image_size * 3;
-  const size_t depth_elems = static_cast<size_t>(c->cfg.frame_width) * c->cfg.frame_height;
-  const bool want_mean = mean_sim_sel != nullptr;
-  // depth is read by the IBVS stage only: its copy (half of the input bytes) runs on a second stream under the
-  // forward pass.  The previous call synchronised, so the workspace is free.
-  VVS_CUDA_OK(cudaMemcpyAsync(c->stage_depth, depth, n_pairs * depth_elems * sizeof(uint16_t), cudaMemcpyHostToDevice,
-                              c->copy_stream),
-              &c->err);
-  VVS_CUDA_OK(cudaEventRecord(c->depth_ready, c->copy_stream), &c->err);
-  VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img, goal, n_pairs * img_bytes, cudaMemcpyHostToDevice, s), &c->err);
-  VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img + n_pairs * img_bytes, cur, n_pairs * img_bytes, cudaMemcpyHostToDevice, s),
-              &c->err);
-  const vvs_ctx::GraphEntry* g = graphs_for(c, n_pairs, want_mean);
-  int rc;
-  if (g) {
-    VVS_CUDA_OK(cudaGraphLaunch(g->execA, s), &c->err);
-    VVS_CUDA_OK(cudaStreamWaitEvent(s, c->depth_ready, 0), &c->err);
-    VVS_CUDA_OK(cudaGraphLaunch(g->execB, s), &c->err);
-  } else {
-    c->launch_count = 0;
-    if ((rc = pairs_forward_match(c, c->stage_img, n_pairs, nullptr, s))) return rc;
-    VVS_CUDA_OK(cudaStreamWaitEvent(s, c->depth_ready, 0), &c->err);
-    if ((rc = pairs_control(c, c->stage_depth, n_pairs, want_mean, s))) return rc;
-  }
-  VVS_CUDA_OK(cudaMemcpyAsync(twist, c->twist, n_pairs * 6 * sizeof(double), cudaMemcpyDeviceToHost, s), &c->err);
-  if (n_selected)
-    VVS_CUDA_OK(cudaMemcpyAsync(n_selected, c->n_sel, n_pairs * sizeof(int32_t), cudaMemcpyDeviceToHost, s), &c->err);
-  if (mean_sim_sel)
-    VVS_CUDA_OK(cudaMemcpyAsync(mean_sim_sel, c->mean_sel, n_pairs * sizeof(float), cudaMemcpyDeviceToHost, s), &c->err);
-  VVS_CUDA_OK(cudaStreamSynchronize(s), &c->err);
-  return VVS_OK;
+  c->launch_count = 0;
+  if ((rc = resize_frames(c, goal, n_pairs, c->stage_img, s))) return rc;
+  if ((rc = resize_frames(c, cur, n_pairs, c->stage_img + n_pairs * img_bytes, s))) return rc;
+  const int resize_launches = c->launch_count;
+  rc = vvs_frame_pairs_to_twist(c, c->stage_img, c->stage_img + n_pairs * img_bytes, depth, n_pairs, out, stream);
+  c->launch_count += resize_launches;
+  return rc;
+}
+
+int vvs_frames_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth,
+                             int32_t n_pairs, double* twist, int32_t* n_selected, float* mean_sim_sel,
+                             vvs_stream stream) {
+  if (!c || !goal || !cur || !depth || !twist) return fail(c, VVS_ERR_INVALID, "vvs_frames_to_twist_host: null argument");
+  if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (s == nullptr || s == cudaStreamLegacy) s = c->own_stream;
+  return host_pipeline(c, goal, cur, depth, n_pairs, /*from_frames=*/true, twist, n_selected, mean_sim_sel, s);
 }
 
 int vvs_profile_enable(vvs_handle c, int32_t on) {

@@ -101,6 +101,20 @@ int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads
 int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
                         std::string* err, bool pdl = false);
 
+// ---- camera frame -> ViT input: Pillow-exact 8-bit bicubic resize (resize.cu) ---------------------
+struct ResizeAxis {          // one separable pass: per output index the first tap, the tap count and the 22-bit taps
+  int in_size = 0, out_size = 0, ksize = 0;
+  int32_t* bounds = nullptr; // [out_size, 2] device
+  int32_t* kk = nullptr;     // [out_size, ksize] device
+};
+int make_resize_axis(ResizeAxis* ax, int in_size, int out_size, std::string* err);
+void free_resize_axis(ResizeAxis* ax);
+// in [n_rows, ax.in_size, 3] -> out [n_rows, ax.out_size, 3]
+int launch_resize_h(const uint8_t* in, uint8_t* out, int n_rows, const ResizeAxis& ax, cudaStream_t s, std::string* err);
+// in [n_img, ax.in_size, row_bytes] -> out [n_img, ax.out_size, row_bytes]
+int launch_resize_v(const uint8_t* in, uint8_t* out, int n_img, int row_bytes, const ResizeAxis& ax, cudaStream_t s,
+                    std::string* err);
+
 // ---- bandwidth-bound kernels -------------------------------------------------------------------
 int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err);
 int launch_im2col_f32(const float* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err);

@@ -257,6 +257,50 @@ class Engine:
             _ptr(mean_sim_out), _stream(self.device)), "vvs_frame_pairs_to_twist_host")
         self._n_img = 2 * B
 
+    # ------------------------------------------------------------------ camera frames (resize on the GPU)
+    def resize_frames(self, frames: torch.Tensor) -> torch.Tensor:
+        """PIL ``Image.resize((S, S))`` (vitvs_v2.py:474-475) of uint8 [n, v_max, u_max, 3] frames on this
+        device -> uint8 [n, S, S, 3], bit-identical to Pillow's antialiased bicubic."""
+        S = self.cfg.dino_input_size
+        assert frames.dtype == torch.uint8 and frames.shape[1:] == (self.cfg.v_max, self.cfg.u_max, 3), frames.shape
+        frames = frames.to(self.device).contiguous()
+        out = torch.empty(frames.shape[0], S, S, 3, dtype=torch.uint8, device=self.device)
+        self._check(self.lib.vvs_resize_frames(self._h, _ptr(frames), frames.shape[0], _ptr(out), _stream(self.device)),
+                    "vvs_resize_frames")
+        return out
+
+    def frames_to_twist(self, goal_frames: torch.Tensor, current_frames: torch.Tensor, depth: torch.Tensor,
+                        want_match: bool = False) -> dict:
+        """frame_pairs_to_twist on raw camera frames: uint8 [B, v_max, u_max, 3] x2 + depth uint16 [B, v_max, u_max]."""
+        B = goal_frames.shape[0]
+        K = self.cfg.num_pairs
+        goal_frames, current_frames, depth = goal_frames.contiguous(), current_frames.contiguous(), depth.contiguous()
+        assert goal_frames.shape[1:] == (self.cfg.v_max, self.cfg.u_max, 3) and goal_frames.shape == current_frames.shape
+        out = dict(twist=torch.empty(B, 6, dtype=torch.float64, device=self.device),
+                   n_selected=torch.empty(B, dtype=torch.int32, device=self.device),
+                   mean_sim_sel=torch.empty(B, dtype=torch.float32, device=self.device))
+        po = _lib.PairOut(twist=out["twist"].data_ptr(), n_selected=out["n_selected"].data_ptr(),
+                          mean_sim_sel=out["mean_sim_sel"].data_ptr())
+        if want_match:
+            bufs, mo = self._match_buffers(B, self.tokens, K)
+            po.match = mo
+            out.update(bufs)
+        self._check(self.lib.vvs_frames_to_twist(self._h, _ptr(goal_frames), _ptr(current_frames), _ptr(depth), B,
+                                                 C.byref(po), _stream(self.device)), "vvs_frames_to_twist")
+        self._n_img = 2 * B
+        return out
+
+    def frames_to_twist_host(self, goal_frames: torch.Tensor, current_frames: torch.Tensor, depth: torch.Tensor,
+                             twist_out: torch.Tensor, n_selected_out: torch.Tensor | None = None,
+                             mean_sim_out: torch.Tensor | None = None) -> None:
+        """Same through HOST buffers (pinned for async copies); synchronises before returning."""
+        assert not goal_frames.is_cuda and not current_frames.is_cuda and not depth.is_cuda and not twist_out.is_cuda
+        B = goal_frames.shape[0]
+        self._check(self.lib.vvs_frames_to_twist_host(
+            self._h, _ptr(goal_frames), _ptr(current_frames), _ptr(depth), B, _ptr(twist_out), _ptr(n_selected_out),
+            _ptr(mean_sim_out), _stream(self.device)), "vvs_frames_to_twist_host")
+        self._n_img = 2 * B
+
     def profile(self, on: bool) -> None:
         self._check(self.lib.vvs_profile_enable(self._h, int(on)), "vvs_profile_enable")
 

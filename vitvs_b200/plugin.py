@@ -140,23 +140,23 @@ class DinoServoMixin:
             self.ema_velocities[index] = a * new_value + (1 - a) * self.ema_velocities[index]
         return self.ema_velocities[index]
 
-    def _resized_pair_u8(self):
-        S = self.cfg.dino_input_size                                                 # vitvs_v2.py:474-475 (host, PIL bicubic)
-        g = np.asarray(self.goal_image.resize((S, S)))
-        c = np.asarray(self.latest_pil_image.resize((S, S)))
-        return g, c
+    def _camera_frame_u8(self, pil_image) -> np.ndarray:
+        """RGB bytes of a PIL frame in the camera geometry the engine was built for (u_max x v_max)."""
+        if pil_image.size != (self.cfg.u_max, self.cfg.v_max):
+            raise ValueError(f"frame size {pil_image.size} != configured camera ({self.cfg.u_max}, {self.cfg.v_max})")
+        return np.array(pil_image.convert("RGB"), copy=True)
 
     def detect_features(self):
         """vitvs_v2.py:464-523: ``((s_uv_star, s_uv), sim)`` or ``(None, None)``; RuntimeError after 10
-        consecutive failures (:500-508).  One fused GPU call (forward x2, descriptors, matching, keypoints)."""
+        consecutive failures (:500-508).  One fused GPU call: PIL-exact resize of both frames (:474-475),
+        forward x2, descriptors, matching, keypoints."""
         if getattr(self, "latest_pil_image", None) is None:
             return None, None
-        g, c = self._resized_pair_u8()
         dev = self.engine.device
-        goal = torch.from_numpy(np.array(g, copy=True))[None].to(dev)
-        cur = torch.from_numpy(np.array(c, copy=True))[None].to(dev)
+        goal = torch.from_numpy(self._camera_frame_u8(self.goal_image))[None].to(dev)
+        cur = torch.from_numpy(self._camera_frame_u8(self.latest_pil_image))[None].to(dev)
         depth = torch.from_numpy(np.array(self.latest_image_depth, copy=True))[None].to(dev)
-        out = self.engine.frame_pairs_to_twist(goal, cur, depth, want_match=True)
+        out = self.engine.frames_to_twist(goal, cur, depth, want_match=True)
         self._last_fused = out
         n = int(out["n_selected"][0].item())
         if n == 0:

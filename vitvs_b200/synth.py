@@ -9,7 +9,8 @@ so that both sides of every parity check see identical bytes.
                     +-10 % scale, +-40 px shift, small perspective terms; seed 4321+i) + N(0, 2/255)
   * depth         : u16 millimetres, plane at 0.61 m (vitvs_v2.py:1391 desired height) tilted
                     +-10 deg, 2 % of the pixels zeroed (exercises the Z=100 branch, vitvs_v2.py:582-584)
-  * resize        : PIL bicubic 640x480 -> SxS exactly as vitvs_v2.py:474-475 (host stage a2)
+  * resize        : PIL bicubic 640x480 -> SxS exactly as vitvs_v2.py:474-475 (input generation for the
+                    pre-resized entry points; the product resizes raw frames on the GPU, csrc/resize.cu)
   * perturbed     : generate_perturbed_models.py:66-105 recipe on the current frame
                     (RandomErasing / ColorJitter / Gaussian 0.05, seed 489+i), BASELINE config 4
 """
@@ -101,6 +102,24 @@ def frame_pair(i: int, size: int = 308, perturbed: bool = False):
     if perturbed:
         c = perturb(c, i)
     return resize_square(g, size), resize_square(c, size), depth_frame(i)
+
+
+def raw_frame_pair(i: int, perturbed: bool = False):
+    """-> goal_u8[480,640,3], cur_u8[480,640,3], depth_u16[480,640]: the camera frames before vitvs_v2.py:474-475."""
+    g = goal_frame(i)
+    c = current_frame(i, g)
+    if perturbed:
+        c = perturb(c, i)
+    return g, c, depth_frame(i)
+
+
+def raw_frame_batch(n: int, perturbed: bool = False, distinct: int | None = None):
+    """n pairs of un-resized camera frames as stacked arrays (``distinct`` as in frame_batch)."""
+    distinct = n if distinct is None else min(distinct, n)
+    pairs = [raw_frame_pair(i, perturbed) for i in range(distinct)]
+    idx = [i % distinct for i in range(n)]
+    return (np.stack([pairs[j][0] for j in idx]), np.stack([pairs[j][1] for j in idx]),
+            np.stack([pairs[j][2] for j in idx]))
 
 
 def frame_batch(n: int, size: int = 308, perturbed: bool = False, distinct: int | None = None):
