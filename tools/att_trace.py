@@ -21,7 +21,7 @@ names = ["top", "s_full", "Sregs", "math", "arrive", "p_full ok", "PV issued", "
 for slot in range(4):
     t0 = tr[slot, 0, 0, 0]
     print(f"--- CTA slot {slot} (rc {rc}); clk relative to warp 0 loop start")
-    for w, wn in enumerate(["warp0 (tile0 issuer)", "warp1 (tile0)", "warp4 (tile1 issuer)"]):
+    for w, wn in enumerate(["warp0 (tile0)", "warp1 (tile0)", "warp8 issuer, tile 0: 0=p_full seen 1=v ready 2=PV issued 3=S issued"]):
         print(" ", wn)
         for j in range(nblk):
             ev = tr[slot, w, j]

@@ -41,7 +41,8 @@ constexpr int kBQ = 128;   // query rows per tile (one TMEM lane per row)
 constexpr int kBKV = 64;   // keys per block
 constexpr int kHD = 64;    // head dim (every DINOv2 size)
 constexpr int kQT = 2;     // query tiles per CTA
-constexpr int kThreads = kQT * 4 * 32;   // 256: 8 warps, two per SM sub-partition
+constexpr int kSoftmaxWarps = kQT * 4;   // 8 warps, two per SM sub-partition
+constexpr int kThreads = (kSoftmaxWarps + kQT) * 32;   // + warps 8, 9: MMA issuers of tile 0 / 1 (warp 8 also feeds the K / V ring)
 constexpr int kKVStages = 4;
 constexpr uint32_t kQBytes = kBQ * kHD * 2;      // 16 KB
 constexpr uint32_t kKVBytes = kBKV * kHD * 2;    // 8 KB: one K or V block
@@ -151,72 +152,119 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   pdl_launch_dependents();   // the prologue above may overlap the previous kernel's tail
   pdl_wait();
 
+  if (warp >= kSoftmaxWarps) {
+    // ---- warps 8 / 9: MMA issuer of tile 0 / tile 1; warp 8 also feeds the K / V ring.  The whole warp walks the
+    // loops (every value warp-uniform => uniform datapath, no ELECT / R2UR waterfalls); only the issue instructions
+    // are predicated on lane 0.  A softmax warp never issues: its timeline is wait S -> TMEM load -> max / exp ->
+    // TMEM store -> arrive.  The issuer's serial chain per block is: see P -> 4 TS MMAs -> 4 SS MMAs -> one commit;
+    // operand arrival is waited for right AFTER a block was issued (a free ~1000 clk), and the K / V stages are
+    // released by the softmax side (below), not by extra commits here. -------------------------------------------
+    const int u = warp - kSoftmaxWarps;            // the tile this warp issues for
+    if (u < n_qt) {
+      constexpr uint32_t idescS = umma_idesc_bf16(128, kBKV, false);
+      constexpr uint32_t idescPV = umma_idesc_bf16(128, kHD, true);
+      const uint32_t sbase = smem_u32(smem);
+      const bool producer = (u == 0);
+      int next_load = 0;
+      // loads are issued in the order K(0) V(0) K(1) V(1) ... whenever their stage is free (never blocking)
+      auto pump = [&]() {
+        while (next_load < 2 * nblk) {
+          const int b = next_load >> 1, st = b % kKVStages;
+          const bool is_v = next_load & 1;
+          uint64_t* empty = is_v ? &v_empty[st] : &k_empty[st];
+          if (!mbar_test_wait(empty, ((b / kKVStages) & 1) ^ 1)) return;   // never suspends
+          if (lane == 0) {
+            uint64_t* full = is_v ? &v_full[st] : &k_full[st];
+            mbar_expect_tx(full, kKVBytes);
+            tma_load_3d(smem + (is_v ? kOffV : kOffK) + st * kKVBytes, &tmKV, full, is_v ? colV : colK,
+                        row_base + b * kBKV, 0, kEvictLast);
+          }
+          __syncwarp();
+          ++next_load;
+        }
+      };
+      // the producer keeps the ring fed while it waits (a lagging sibling tile must never starve it of loads)
+      auto wait_feed = [&](uint64_t* bar, uint32_t parity) {
+        if (!producer) {
+          mbar_wait(bar, parity);
+          return;
+        }
+        uint32_t polls = 0;
+        while (!mbar_try_wait(bar, parity)) {
+          pump();
+          if (++polls == (1u << 26)) __trap();
+        }
+      };
+      if (producer) {
+        if (lane == 0) {
+          for (int q = 0; q < n_qt; ++q) {
+            mbar_expect_tx(&q_full[q], kQBytes);
+            tma_load_3d(smem + kOffQ + q * kQBytes, &tmQ, &q_full[q], colQ, row_base + (qt0 + q) * kBQ, 0, kEvictNormal);
+          }
+        }
+        __syncwarp();
+        pump();
+      }
+      const uint32_t tSi = tmem_base + u * 128, tOi = tSi + 64;   // lane field 0: operands address the whole tile
+      const uint64_t qd = umma_smem_desc(sbase + kOffQ + u * kQBytes, 16, 1024);
+      const uint64_t kd = umma_smem_desc(sbase + kOffK, 16, 1024);
+      const uint64_t vd = umma_smem_desc(sbase + kOffV, 1024, 1024);   // MN-major V: 16 keys = 2 x 1024 B
+      auto issue_S = [&](int b) {     // S_u(b) = Q_u K(b)^T   (lane 0)
+        const uint64_t kb = kd + (((b % kKVStages) * kKVBytes) >> 4);
+#pragma unroll
+        for (int k = 0; k < kHD / 16; ++k) umma_bf16(tSi, qd + 2 * k, kb + 2 * k, idescS, k != 0);   // +32 B per k step
+      };
+      wait_feed(&q_full[u], 0);
+      wait_feed(&k_full[0], 0);
+      tc_fence_after();
+      if (lane == 0) {
+        issue_S(0);
+        umma_commit(&s_full[u]);
+      }
+      __syncwarp();
+      wait_feed(&v_full[0], 0);
+      if (nblk > 1) wait_feed(&k_full[1 % kKVStages], (1 / kKVStages) & 1);
+#ifdef VVS_ATT_TRACE
+      const int tr8 = (blockIdx.z == 5 && blockIdx.y == 3) ? static_cast<int>(blockIdx.x)
+                      : (blockIdx.z == 100 && blockIdx.y == 7) ? 2 + static_cast<int>(blockIdx.x) : -1;
+#define VVS_TR8(ev)                                                                                            \
+  do {                                                                                                         \
+    if (tr8 >= 0 && tr8 < 4 && u == 0 && lane == 0 && j < 16) g_att_trace[((tr8 * 3 + 2) * 16 + j) * 8 + (ev)] = clock64(); \
+  } while (0)
+#else
+#define VVS_TR8(ev) do { } while (0)
+#endif
+      // PV_u(j), then S_u(j+1) right behind it (tcgen05.mma executes in issue order, which is what makes overwriting
+      // P(j) with S(j+1) safe); one commit tells the warpgroup both "S(j+1) is there" and "PV(j) is done"
+      for (int j = 0; j < nblk; ++j) {
+        mbar_wait(&p_full[u], j & 1);       // V(j) and K(j+1) have landed (waited for below, one block ahead)
+        VVS_TR8(0);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint64_t vb = vd + (((j % kKVStages) * kKVBytes) >> 4);
+#pragma unroll
+          for (int kk = 0; kk < kBKV / 16; ++kk)
+            umma_bf16_ts(tOi, tSi + kk * 8, vb + kk * (2048 >> 4), idescPV, (j > 0 || kk != 0) ? 1u : 0u);   // O accumulates
+          if (j + 1 < nblk) issue_S(j + 1);
+          umma_commit(&s_full[u]);                    // S(j+1) ready and PV(j) done (last block: O final)
+        }
+        __syncwarp();
+        VVS_TR8(1);
+        if (producer) pump();
+        if (j + 1 < nblk) wait_feed(&v_full[(j + 1) % kKVStages], ((j + 1) / kKVStages) & 1);
+        if (j + 2 < nblk) wait_feed(&k_full[(j + 2) % kKVStages], ((j + 2) / kKVStages) & 1);
+        VVS_TR8(2);
+      }
+    }
+  }
+
   const int t = warp >> 2;                          // query tile of this warpgroup
-  if (t < n_qt) {
+  if (warp < kSoftmaxWarps && t < n_qt) {
     const int wq = warp & 3;                          // TMEM lane quarter of this warp
     const int row = wq * 32 + lane;                   // row inside the tile = TMEM lane
     const uint32_t lane_field = static_cast<uint32_t>(wq * 32) << 16;
     const uint32_t tS = tmem_base + t * 128 + lane_field;
     const uint32_t tO = tS + 64;
-
-    // ---- MMA issue + TMA (lane 0 of the tile's first warp; tile 0's also feeds the K / V ring) -------------
-    // A CTA is exactly 8 warps: registers are allocated per SM sub-partition, and a ninth and tenth warp would
-    // cost a second resident CTA.  The issuing warp is on the tile's critical path either way.
-    const bool issuer = (wq == 0) && (lane == 0);
-    const bool producer = issuer && (t == 0);
-    constexpr uint32_t idescS = umma_idesc_bf16(128, kBKV, false);
-    constexpr uint32_t idescPV = umma_idesc_bf16(128, kHD, true);
-    const uint32_t sbase = smem_u32(smem);
-    const uint32_t qa = sbase + kOffQ + t * kQBytes;
-    const uint32_t tSi = tmem_base + t * 128, tOi = tSi + 64;   // lane field 0: MMA operands address the whole tile
-    int next_load = 0;
-    // loads are issued in the order K(0) V(0) K(1) V(1) ... whenever their stage is free (never blocking)
-    auto pump = [&]() {
-      while (next_load < 2 * nblk) {
-        const int b = next_load >> 1, st = b % kKVStages;
-        const bool is_v = next_load & 1;
-        uint64_t* empty = is_v ? &v_empty[st] : &k_empty[st];
-        if (!mbar_test_wait(empty, ((b / kKVStages) & 1) ^ 1)) return;   // never suspends
-        uint64_t* full = is_v ? &v_full[st] : &k_full[st];
-        mbar_expect_tx(full, kKVBytes);
-        tma_load_3d(smem + (is_v ? kOffV : kOffK) + st * kKVBytes, &tmKV, full, is_v ? colV : colK,
-                    row_base + b * kBKV, 0, kEvictLast);
-        ++next_load;
-      }
-    };
-    auto wait_pump = [&](uint64_t* bar, uint32_t parity) {   // issuer lanes only
-      uint32_t polls = 0;
-      while (!mbar_try_wait(bar, parity)) {
-        if (producer) pump();
-        if (++polls == (1u << 26)) __trap();
-      }
-    };
-    auto issue_S = [&](int b, bool k_ready) {     // S_t(b) = Q_t K(b)^T
-      const int st = b % kKVStages;
-      if (!k_ready) wait_pump(&k_full[st], (b / kKVStages) & 1);
-      tc_fence_after();
-      const uint32_t ka = sbase + kOffK + st * kKVBytes;
-#ifndef VVS_EXP_NOMMA
-#pragma unroll
-      for (int k = 0; k < kHD / 16; ++k)
-        umma_bf16(tSi, umma_smem_desc(qa + k * 32, 16, 1024), umma_smem_desc(ka + k * 32, 16, 1024), idescS, k != 0);
-#endif
-      umma_commit(&k_empty[st]);
-    };
-    if (issuer) {
-      if (producer) {
-        for (int u = 0; u < n_qt; ++u) {
-          mbar_expect_tx(&q_full[u], kQBytes);
-          tma_load_3d(smem + kOffQ + u * kQBytes, &tmQ, &q_full[u], colQ, row_base + (qt0 + u) * kBQ, 0, kEvictNormal);
-          if (u == 0) pump();
-        }
-        pump();
-      }
-      wait_pump(&q_full[t], 0);
-      issue_S(0, false);
-      umma_commit(&s_full[t]);
-    }
-    __syncwarp();
 
     float m_run = -INFINITY;   // reference max of the exponentials, already multiplied by log2(e)
     float l_run = 0.f;
@@ -224,7 +272,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #ifdef VVS_ATT_TRACE
     const int tr_slot = (blockIdx.z == 5 && blockIdx.y == 3) ? static_cast<int>(blockIdx.x)
                         : (blockIdx.z == 100 && blockIdx.y == 7) ? 2 + static_cast<int>(blockIdx.x) : -1;
-    const int tr_warp = warp == 0 ? 0 : warp == 1 ? 1 : warp == 4 ? 2 : -1;
+    const int tr_warp = warp == 0 ? 0 : warp == 1 ? 1 : -1;
     const int tr_ok = tr_warp >= 0 ? tr_slot : -1;
 #undef VVS_TR
 #define VVS_TR(ev)                                                                                         \
@@ -237,6 +285,11 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       VVS_TR(0);
       mbar_wait(&s_full[t], j & 1);
       tc_fence_after();
+      // S(j) complete => its K block is free; PV(j-1) complete => its V block is free (one arrival per tile)
+      if (wq == 0 && lane == 0) {
+        mbar_arrive(&k_empty[j % kKVStages]);
+        if (j >= 1) mbar_arrive(&v_empty[(j - 1) % kKVStages]);
+      }
 #if VVS_ATT_STAGGER > 0
       // The tiles sharing an SM sub-partition's MUFU tend to run in lock step (all in their exponentials, then all
       // in their hand-offs); a one-off offset of the second tile lets one fill the other's gaps.
@@ -250,13 +303,6 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       uint32_t sc[2][32];                   // the row of S (fp32 bits)
       tmem_ld32(tS, sc[0]);
       tmem_ld32(tS + 32, sc[1]);
-      // the operands of this block's MMAs landed long ago, but an mbarrier wait costs 100-250 clk even then: probe
-      // now, look at the answers after the exponentials
-      bool v_ready = false, k_ready = false;
-      if (issuer) {
-        v_ready = mbar_test_wait(&v_full[j % kKVStages], (j / kKVStages) & 1);
-        if (j + 1 < nblk) k_ready = mbar_test_wait(&k_full[(j + 1) % kKVStages], ((j + 1) / kKVStages) & 1);
-      }
       tmem_ld_wait();
       VVS_TR(2);
 #ifdef VVS_EXP_NOMATH   // timing experiment: MMA + hand-off chain only (wrong numerics)
@@ -324,29 +370,6 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[t]);
       VVS_TR(4);
-      if (wq == 0) {
-        if (issuer) {
-          const int st = j % kKVStages;
-          if (!v_ready) wait_pump(&v_full[st], (j / kKVStages) & 1);
-          wait_pump(&p_full[t], j & 1);               // all four warps: P_t(j) in TMEM, O_t rescaled if it had to be
-          tc_fence_after();
-          VVS_TR(5);
-          const uint32_t va = sbase + kOffV + st * kKVBytes;
-#ifndef VVS_EXP_NOMMA
-#pragma unroll
-          for (int kk = 0; kk < kBKV / 16; ++kk)
-            umma_bf16_ts(tOi, tSi + kk * 8, umma_smem_desc(va + kk * 2048, 1024, 1024),   // MN-major V: 16 keys = 2 x 1024 B
-                         idescPV, (j > 0 || kk != 0) ? 1u : 0u);                          // O accumulates across key blocks
-#endif
-          umma_commit(&v_empty[st]);
-          VVS_TR(6);
-          if (j + 1 < nblk) issue_S(j + 1, k_ready);   // in order behind PV(j): may overwrite P(j)
-          umma_commit(&s_full[t]);                    // S(j+1) ready and PV(j) done (last block: O final)
-          VVS_TR(7);
-          if (producer) pump();
-        }
-        __syncwarp();
-      }
     }
 
     mbar_wait(&s_full[t], nblk & 1);      // PV(nblk - 1) has completed

@@ -35,6 +35,13 @@ __device__ __forceinline__ float normalize_px(uint8_t v, int c) {
 // One thread = 8 consecutive k of one patch row -> one 16-byte store.
 template <bool kU8>
 __global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ out, int n_img, int S, int kpad) {
+  // u8 input: the 3 x 256 possible outputs of ToTensor + Normalize, evaluated once per block with the exact
+  // arithmetic above (two IEEE divisions each) - the per-element work is then a table lookup
+  __shared__ float lut[3][256];
+  if (kU8) {
+    for (int i = threadIdx.x; i < 768; i += blockDim.x) lut[i >> 8][i & 255] = normalize_px(static_cast<uint8_t>(i & 255), i >> 8);
+    __syncthreads();
+  }
   const int gp = S / kPatch;
   const int T = gp * gp;
   const int k8_per_row = kpad / 8;
@@ -57,7 +64,7 @@ __global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ 
         const int y = py * kPatch + ky, x = px * kPatch + kx;
         if (kU8) {
           const uint8_t* img8 = static_cast<const uint8_t*>(img_);
-          v[e] = normalize_px(img8[((static_cast<size_t>(img) * S + y) * S + x) * 3 + c], c);
+          v[e] = lut[c][img8[((static_cast<size_t>(img) * S + y) * S + x) * 3 + c]];
         } else {
           const float* imgf = static_cast<const float*>(img_);
           v[e] = imgf[((static_cast<size_t>(img) * 3 + c) * S + y) * S + x];
@@ -88,8 +95,11 @@ layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const
   pdl_launch_dependents();
   pdl_wait();   // x is the previous kernel's output
   const int lane = threadIdx.x & 31;
-  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (row >= rows) return;
+  // The producer (a persistent GEMM) wrote x in ascending row order and x is larger than L2: walk the rows from
+  // the end so that the reads start on the lines that are still resident; the consumer GEMM starts at row 0,
+  // which is then the part of the output written last.
+  const int row = rows - 1 - (blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5));
+  if (row < 0) return;
   const float4* xr = reinterpret_cast<const float4*>(x + static_cast<size_t>(row) * D);
   float4 v[NV];
   float s = 0.f;
