@@ -1,4 +1,4 @@
-// tcgen05 flash-attention forward, generation 7: P never leaves the tensor-core datapath.
+// tcgen05 flash-attention forward, generations 7-8: P never leaves the tensor-core datapath; dedicated issuer warps.
 // (reference semantics: dino_patch/attention.py:70-80 - non-causal SDPA, scale hd^-0.5,
 // head dim 64, no mask, eval.)
 //
@@ -8,10 +8,15 @@
 // the [n_img * n_tok, D] layout attn.proj reads.
 //
 // One CTA = TWO 128-row query tiles of one (image, head); TWO CTAs are resident per SM (256 TMEM columns,
-// ~98 KB of shared memory and 256 threads each), so the prologue (descriptor fetch, Q / K loads) and the
+// ~98 KB of shared memory and 320 threads each), so the prologue (descriptor fetch, Q / K loads) and the
 // epilogue (O / l, global stores) of one CTA hide behind the main loop of the other:
-//   warps 0-7   two softmax warpgroups, one per query tile (thread = query row = TMEM lane); lane 0 of each
-//               tile's first warp also issues that tile's MMAs (tile 0's: the TMA loads of the K / V ring too)
+//   warps 0-7   two softmax warpgroups, one per query tile (thread = query row = TMEM lane); they never issue an
+//               MMA or a TMA: wait S -> TMEM load -> max / exp -> TMEM store -> arrive
+//   warps 8, 9  MMA issuer of tile 0 / tile 1 (generation 8).  The whole warp walks the loop so that every address
+//               and descriptor lives on the uniform datapath; lane 0 issues.  Warp 8 also feeds the K / V ring.
+//               Measured with the per-block clock trace (tools/att_trace.py): when a softmax lane issued, its
+//               serial chain (poll P, poll V, 4 + 4 MMAs at ~75 clk each through ELECT / R2UR waterfalls, three
+//               commits, TMA pump) cost 1500-2500 clk per block on the tile's critical path; now ~600.
 // Per tile and 64-key block:
 //   S = Q K^T              (SS MMA, fp32 S in TMEM columns [0, 64) of the tile)
 //   softmax warpgroup: S -> registers (one TMEM pass), row max, p = exp2(s log2e - m) (packed fp32x2 FMA, one
@@ -73,13 +78,39 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, u
       : "memory");
 }
 
+// exp2 on the FMA pipe (the MUFU pipe is the kernel's tightest resource: 4 lanes / clk / sub-partition): round to
+// nearest integer with the 1.5 * 2^23 trick, degree-3 polynomial of 2^r on [-0.5, 0.5] (relative error 7.7e-5, far
+// below the bf16 rounding of P), integer part added to the exponent bits.  Inputs are clamped at -125.
+__device__ __forceinline__ f32x2 f2_ex2_poly(f32x2 x) {
+  float x0, x1;
+  f2_unpack(x, x0, x1);
+  x = f2_pack(fmaxf(x0, -125.0f), fmaxf(x1, -125.0f));
+  const f32x2 magic = f2_pack(12582912.0f, 12582912.0f), neg_magic = f2_pack(-12582912.0f, -12582912.0f);
+  const f32x2 t = f2_add(x, magic);
+  const f32x2 r = f2_fma(f2_add(t, neg_magic), f2_pack(-1.0f, -1.0f), x);
+  f32x2 p = f2_fma(f2_pack(0.05508868396282196f, 0.05508868396282196f), r, f2_pack(0.24260404706001282f, 0.24260404706001282f));
+  p = f2_fma(p, r, f2_pack(0.6932762265205383f, 0.6932762265205383f));
+  p = f2_fma(p, r, f2_pack(0.9999289512634277f, 0.9999289512634277f));
+  float p0, p1, t0, t1;
+  f2_unpack(p, p0, p1);
+  f2_unpack(t, t0, t1);
+  return f2_pack(__uint_as_float(__float_as_uint(p0) + (__float_as_uint(t0) << 23)),
+                 __uint_as_float(__float_as_uint(p1) + (__float_as_uint(t1) << 23)));
+}
+
+#ifndef VVS_ATT_POLY_MASK
+#define VVS_ATT_POLY_MASK 0x00   // bit i: pair i of every 8 pairs (16 elements) takes the polynomial instead of MUFU.EX2
+#endif
+
 // 16 exponentials of a row segment: p = exp2(s * log2e - m), packed to bf16 pairs, row sum accumulated
 __device__ __forceinline__ void exp_pack16(const uint32_t* s, f32x2 log2e2, f32x2 neg_m2, f32x2& sum01, f32x2& sum23,
                                            uint32_t* pk) {
 #pragma unroll
   for (int i = 0; i < 16; i += 4) {
-    const f32x2 e01 = f2_ex2(f2_fma(f2_pack(__uint_as_float(s[i + 0]), __uint_as_float(s[i + 1])), log2e2, neg_m2));
-    const f32x2 e23 = f2_ex2(f2_fma(f2_pack(__uint_as_float(s[i + 2]), __uint_as_float(s[i + 3])), log2e2, neg_m2));
+    const f32x2 a01 = f2_fma(f2_pack(__uint_as_float(s[i + 0]), __uint_as_float(s[i + 1])), log2e2, neg_m2);
+    const f32x2 a23 = f2_fma(f2_pack(__uint_as_float(s[i + 2]), __uint_as_float(s[i + 3])), log2e2, neg_m2);
+    const f32x2 e01 = ((VVS_ATT_POLY_MASK >> (i / 2)) & 1) ? f2_ex2_poly(a01) : f2_ex2(a01);
+    const f32x2 e23 = ((VVS_ATT_POLY_MASK >> (i / 2 + 1)) & 1) ? f2_ex2_poly(a23) : f2_ex2(a23);
     sum01 = f2_add(sum01, e01);
     sum23 = f2_add(sum23, e23);
     pk[i / 2] = f2_to_bf16x2(e01);
@@ -128,13 +159,17 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const int n_qt = min(kQT, (n_tok + kBQ - 1) / kBQ - qt0);   // active tiles (last CTA of a sequence)
   const int colQ = head * kHD, colK = D + head * kHD, colV = 2 * D + head * kHD;
 
-  if (tid == 0) {
+  // The producer lane sets the barriers up and starts the first loads (Q tiles, the first kKVStages K / V blocks:
+  // their stages are trivially free) BEFORE the TMEM allocation and the CTA-wide sync, so that the ~2000 clk
+  // HBM / L2 latency of the first operands overlaps the rest of the prologue.
+  const int n_early = min(nblk, kKVStages);
+  if (tid == kSoftmaxWarps * 32) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmKV);
     for (int i = 0; i < kKVStages; ++i) {
       mbar_init(&k_full[i], 1);
       mbar_init(&v_full[i], 1);
-      mbar_init(&k_empty[i], n_qt);    // one commit per tile's issuer
+      mbar_init(&k_empty[i], n_qt);    // one arrival per tile (its softmax warpgroup)
       mbar_init(&v_empty[i], n_qt);
     }
     for (int i = 0; i < kQT; ++i) {
@@ -143,6 +178,23 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       mbar_init(&p_full[i], 4);
     }
     fence_mbar_init();
+    pdl_wait();                        // qkv is the previous kernel's output
+    for (int q = 0; q < n_qt; ++q) {
+      mbar_expect_tx(&q_full[q], kQBytes);
+      tma_load_3d(smem + kOffQ + q * kQBytes, &tmQ, &q_full[q], colQ, row_base + (qt0 + q) * kBQ, 0, kEvictNormal);
+      if (q == 0) {                    // K(0) right behind Q(0): S_0(0) needs nothing else
+        mbar_expect_tx(&k_full[0], kKVBytes);
+        tma_load_3d(smem + kOffK, &tmKV, &k_full[0], colK, row_base, 0, kEvictLast);
+      }
+    }
+    for (int b = 0; b < n_early; ++b) {
+      if (b > 0) {
+        mbar_expect_tx(&k_full[b], kKVBytes);
+        tma_load_3d(smem + kOffK + b * kKVBytes, &tmKV, &k_full[b], colK, row_base + b * kBKV, 0, kEvictLast);
+      }
+      mbar_expect_tx(&v_full[b], kKVBytes);
+      tma_load_3d(smem + kOffV + b * kKVBytes, &tmKV, &v_full[b], colV, row_base + b * kBKV, 0, kEvictLast);
+    }
   }
   if (warp == 0) tmem_alloc<kTmemCols>(tmem_slot);
   tc_fence_before();
@@ -165,8 +217,8 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       constexpr uint32_t idescPV = umma_idesc_bf16(128, kHD, true);
       const uint32_t sbase = smem_u32(smem);
       const bool producer = (u == 0);
-      int next_load = 0;
-      // loads are issued in the order K(0) V(0) K(1) V(1) ... whenever their stage is free (never blocking)
+      int next_load = 2 * n_early;     // the prologue issued K / V blocks [0, n_early)
+      // loads are issued in the order K(b) V(b) K(b+1) V(b+1) ... whenever their stage is free (never blocking)
       auto pump = [&]() {
         while (next_load < 2 * nblk) {
           const int b = next_load >> 1, st = b % kKVStages;
@@ -195,16 +247,6 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           if (++polls == (1u << 26)) __trap();
         }
       };
-      if (producer) {
-        if (lane == 0) {
-          for (int q = 0; q < n_qt; ++q) {
-            mbar_expect_tx(&q_full[q], kQBytes);
-            tma_load_3d(smem + kOffQ + q * kQBytes, &tmQ, &q_full[q], colQ, row_base + (qt0 + q) * kBQ, 0, kEvictNormal);
-          }
-        }
-        __syncwarp();
-        pump();
-      }
       const uint32_t tSi = tmem_base + u * 128, tOi = tSi + 64;   // lane field 0: operands address the whole tile
       const uint64_t qd = umma_smem_desc(sbase + kOffQ + u * kQBytes, 16, 1024);
       const uint64_t kd = umma_smem_desc(sbase + kOffK, 16, 1024);
