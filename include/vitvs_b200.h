@@ -178,12 +178,18 @@ VVS_API int vvs_frames_to_twist_host(vvs_handle h, const uint8_t* goal_frames_ho
                              int32_t* n_selected_host, float* mean_sim_sel_host, vvs_stream stream);
 /* number of kernels the last vvs_frame_pairs_to_twist* / vvs_frames_to_twist* call launched (bench.py gpu_launches). */
 VVS_API int vvs_last_launch_count(vvs_handle h);
+/* 1 when the fused frame-pair path matches 3x3-binned descriptors as a 9-point stencil over the token Gram matrix
+ * (the [T, 9*dim] descriptors of dinov2_extractor.py:265-311 are then never written and the similarity product of
+ * vitvs_v2.py:49-56 runs with K = dim): same cosine similarities up to fp32 summation order.  0 = the binned
+ * descriptors are materialised: the default (the stencil form is opt-in through VITVS_GRAM=1 in the environment
+ * at vvs_create time; it trades 0.3 points of arg-max agreement with the fp32 reference for 1.3 % of a step). */
+VVS_API int vvs_uses_gram_stencil(vvs_handle h);
 
 /* ---- per-kernel-class device timing (CUDA events on the launching stream around every launch) -------- */
 enum vvs_kernel_class {
   VVS_K_OTHER = 0, VVS_K_IM2COL = 1, VVS_K_PATCH_GEMM = 2, VVS_K_LAYERNORM = 3, VVS_K_QKV_GEMM = 4,
   VVS_K_ATTENTION = 5, VVS_K_PROJ_GEMM = 6, VVS_K_FFN1_GEMM = 7, VVS_K_FFN2_GEMM = 8, VVS_K_DESCRIPTORS = 9,
-  VVS_K_SIM_GEMM = 10, VVS_K_SELECT = 11, VVS_K_IBVS = 12, VVS_K_RESIZE = 13, VVS_K_COUNT = 14
+  VVS_K_SIM_GEMM = 10, VVS_K_SELECT = 11, VVS_K_IBVS = 12, VVS_K_RESIZE = 13, VVS_K_STENCIL = 14, VVS_K_COUNT = 15
 };
 VVS_API int vvs_profile_enable(vvs_handle h, int32_t on);
 /* sums (ms) and launch counts per vvs_kernel_class since the last read; synchronises on the events. */

@@ -63,6 +63,7 @@ SYMBOLS = {
     "vvs_frames_to_twist": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, C.POINTER(PairOut), c_vp]),
     "vvs_frames_to_twist_host": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "vvs_last_launch_count": (c_i32, [c_vp]),
+    "vvs_uses_gram_stencil": (c_i32, [c_vp]),
     "vvs_profile_enable": (c_i32, [c_vp, c_i32]),
     "vvs_profile_read": (c_i32, [c_vp, C.POINTER(c_f64), C.POINTER(c_i32), c_i32]),
     "vvs_dbg_gemm": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32,
@@ -72,7 +73,7 @@ SYMBOLS = {
 }
 
 KERNEL_CLASSES = ["other", "im2col", "patch_gemm", "layernorm", "qkv_gemm", "attention", "proj_gemm", "ffn1_gemm",
-                  "ffn2_gemm", "descriptors", "sim_gemm", "select", "ibvs", "resize"]
+                  "ffn2_gemm", "descriptors", "sim_gemm", "select", "ibvs", "resize", "stencil"]
 
 _lib = None
 

@@ -107,6 +107,8 @@ struct vvs_ctx {
   bf16* desc = nullptr;      // unit-norm descriptors
   size_t desc_elems = 0;
   float* sqn = nullptr;      // [max_images * T]
+  float* inv_norm = nullptr; // [max_images * T] inverse norms of the binned descriptors (Gram-stencil matching)
+  bool gram_stencil = false; // binned matching as a 9-point stencil over the token Gram matrix (gram_stencil.cu)
   unsigned long long* row_best = nullptr;
   unsigned long long* col_best = nullptr;
   size_t match_cap = 0;      // tokens (summed over pairs) the match outputs hold
@@ -309,28 +311,10 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
   return VVS_OK;
 }
 
-// similarity arg-max + selection on unit-norm bf16 descriptors already in c->desc:
-// goal sets at desc[0 .. n_pairs), current sets at desc[n_pairs .. 2 n_pairs), each [T, dpad].
-int match_on_desc(vvs_ctx* c, int n_pairs, int T, int dpad, int grid_w, int K, const vvs_match_out* out,
-                  cudaStream_t s) {
-  if (static_cast<size_t>(n_pairs) * T > c->match_cap)
-    return fail(c, VVS_ERR_STATE, "match workspace too small (raise max_images / max_match_tokens)");
-  if (K > c->k_cap || n_pairs > c->max_pairs)
-    return fail(c, VVS_ERR_STATE, "num_pairs / n_pairs beyond the workspace of this handle");
+// packed row / column arg-max keys (workspace) -> matches, candidates, top-K keypoints (+ copies to the caller)
+int match_tail(vvs_ctx* c, int n_pairs, int T, int grid_w, int K, const vvs_match_out* out, cudaStream_t s) {
   const size_t keys = static_cast<size_t>(n_pairs) * T;
-  VVS_CUDA_OK(cudaMemsetAsync(c->row_best, 0, keys * sizeof(unsigned long long), s), &c->err);
-  VVS_CUDA_OK(cudaMemsetAsync(c->col_best, 0, keys * sizeof(unsigned long long), s), &c->err);
-  GemmArgs g;
-  memset(&g, 0, sizeof(g));
-  g.A = c->desc;
-  g.B = c->desc + static_cast<size_t>(n_pairs) * T * dpad;
-  g.M = T; g.N = T; g.K = dpad; g.lda = dpad; g.ldb = dpad; g.batch = n_pairs;
-  g.a_batch_pitch = static_cast<long long>(T) * dpad;
-  g.b_batch_pitch = static_cast<long long>(T) * dpad;
-  g.epilogue = EPI_SIM;
-  g.row_best = c->row_best; g.col_best = c->col_best; g.best_pitch = T;
-  int rc = gemm(c, g, s, VVS_K_SIM_GEMM);
-  if (rc) return rc;
+  int rc;
   SelectArgs a;
   memset(&a, 0, sizeof(a));
   a.row_best = c->row_best; a.col_best = c->col_best; a.best_pitch = T;
@@ -368,6 +352,31 @@ int match_on_desc(vvs_ctx* c, int n_pairs, int T, int dpad, int grid_w, int K, c
   return VVS_OK;
 }
 
+
+// similarity arg-max + selection on unit-norm bf16 descriptors already in c->desc:
+// goal sets at desc[0 .. n_pairs), current sets at desc[n_pairs .. 2 n_pairs), each [T, dpad].
+int match_on_desc(vvs_ctx* c, int n_pairs, int T, int dpad, int grid_w, int K, const vvs_match_out* out,
+                  cudaStream_t s) {
+  if (static_cast<size_t>(n_pairs) * T > c->match_cap)
+    return fail(c, VVS_ERR_STATE, "match workspace too small (raise max_images / max_match_tokens)");
+  if (K > c->k_cap || n_pairs > c->max_pairs)
+    return fail(c, VVS_ERR_STATE, "num_pairs / n_pairs beyond the workspace of this handle");
+  const size_t keys = static_cast<size_t>(n_pairs) * T;
+  VVS_CUDA_OK(cudaMemsetAsync(c->row_best, 0, keys * sizeof(unsigned long long), s), &c->err);
+  VVS_CUDA_OK(cudaMemsetAsync(c->col_best, 0, keys * sizeof(unsigned long long), s), &c->err);
+  GemmArgs g;
+  memset(&g, 0, sizeof(g));
+  g.A = c->desc;
+  g.B = c->desc + static_cast<size_t>(n_pairs) * T * dpad;
+  g.M = T; g.N = T; g.K = dpad; g.lda = dpad; g.ldb = dpad; g.batch = n_pairs;
+  g.a_batch_pitch = static_cast<long long>(T) * dpad;
+  g.b_batch_pitch = static_cast<long long>(T) * dpad;
+  g.epilogue = EPI_SIM;
+  g.row_best = c->row_best; g.col_best = c->col_best; g.best_pitch = T;
+  int rc = gemm(c, g, s, VVS_K_SIM_GEMM);
+  if (rc) return rc;
+  return match_tail(c, n_pairs, T, grid_w, K, out, s);
+}
 int normalise_caller_descriptors(vvs_ctx* c, const float* d1, const float* d2, int n_pairs, int T, int d, int* dpad_out,
                                  cudaStream_t s) {
   const int dpad = (d + 7) / 8 * 8;
@@ -402,6 +411,39 @@ int pairs_forward_match(vvs_ctx* c, const uint8_t* images, int n_pairs, const vv
   int rc = forward_tokens(c, images, VVS_IMAGE_U8_HWC, 2 * n_pairs, f.layer, s);
   if (rc) return rc;
   const int parts = f.use_feature_binning ? 9 : 1;
+  if (c->gram_stencil) {
+    // binned matching as a 9-point stencil over the token Gram matrix (gram_stencil.cu): the 9D-wide descriptors are
+    // never written and the similarity GEMM has K = D instead of 9D.  Workspace: bf16 tokens at the head of the
+    // descriptor buffer, the fp32 Gram matrices behind them (fixed offsets: the graph replays these addresses).
+    const int T = c->T, D = f.dim;
+    bf16* tb = c->desc;
+    float* G = reinterpret_cast<float*>(c->desc + static_cast<size_t>(f.max_images) * T * D);
+    if (static_cast<size_t>(n_pairs) * T > c->match_cap || n_pairs > c->max_pairs)
+      return fail(c, VVS_ERR_STATE, "match workspace too small for this batch");
+    { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
+      rc = launch_tokens_bf16_sqnorm(c->x, tb, c->sqn, 2 * n_pairs, T, D, s, &c->err); }
+    if (rc) return rc;
+    { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
+      rc = launch_binned_inv_norm(c->sqn, c->inv_norm, 2 * n_pairs, c->grid, c->grid, s, &c->err); }
+    if (rc) return rc;
+    c->launch_count += 2;
+    GemmArgs g;
+    memset(&g, 0, sizeof(g));
+    g.A = tb;
+    g.B = tb + static_cast<size_t>(n_pairs) * T * D;
+    g.M = T; g.N = T; g.K = D; g.lda = D; g.ldb = D; g.batch = n_pairs;
+    g.a_batch_pitch = static_cast<long long>(T) * D;
+    g.b_batch_pitch = static_cast<long long>(T) * D;
+    g.epilogue = EPI_STORE_F32;
+    g.x_f32 = G; g.ldo = T;
+    if ((rc = gemm(c, g, s, VVS_K_SIM_GEMM))) return rc;
+    VVS_CUDA_OK(cudaMemsetAsync(c->col_best, 0, static_cast<size_t>(n_pairs) * T * sizeof(unsigned long long), s), &c->err);
+    { ProfScope ps(c, VVS_K_STENCIL, s);
+      rc = launch_gram_stencil_argmax(G, c->inv_norm, c->row_best, c->col_best, n_pairs, c->grid, c->grid, T, s, &c->err); }
+    if (rc) return rc;
+    ++c->launch_count;
+    return match_tail(c, n_pairs, T, c->grid, f.num_pairs, match, s);
+  }
   { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
     rc = launch_descriptors_unit_bf16(c->x, c->desc, c->sqn, 2 * n_pairs, c->grid, c->grid, f.dim,
                                       f.use_feature_binning, s, &c->err); }
@@ -668,6 +710,7 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
   rc |= dev_alloc(c, &c->big, c->big_elems);
   rc |= dev_alloc(c, &c->desc, c->desc_elems);
   rc |= dev_alloc(c, &c->sqn, static_cast<size_t>(cfg->max_images) * c->T);
+  rc |= dev_alloc(c, &c->inv_norm, static_cast<size_t>(cfg->max_images) * c->T);
   rc |= dev_alloc(c, &c->row_best, c->match_cap);
   rc |= dev_alloc(c, &c->col_best, c->match_cap);
   rc |= dev_alloc(c, &c->nn1, c->match_cap);
@@ -699,6 +742,19 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
     return VVS_ERR_CUDA;
   }
   if (const char* e = getenv("VITVS_GRAPHS")) c->graphs_enabled = e[0] != '0';
+  // Gram-stencil matching (opt-in: VITVS_GRAM=1) needs the binned layout, a token count the stencil kernel covers and
+  // room for the bf16 tokens + fp32 Gram matrices inside the descriptor workspace.  Measured on B200 (ViT-B, 64
+  // pairs): descriptors + similarity 0.44 ms -> 0.26 ms per step, but the bf16 rounding of a token is then shared by
+  // the nine stencil terms instead of being drawn nine times, and the arg-max agreement with the fp32 oracle drops
+  // from 99.6 % to 99.3 % (tests/test_gpu_gram.py) - parity margin is worth more than 1.3 % of a step, so the
+  // materialised descriptors stay the default.
+  {
+    const size_t need = static_cast<size_t>(cfg->max_images) * c->T * D * sizeof(bf16) +
+                        static_cast<size_t>(c->max_pairs) * c->T * c->T * sizeof(float);
+    const char* e = getenv("VITVS_GRAM");
+    c->gram_stencil = e && e[0] == '1' && cfg->use_feature_binning != 0 && gram_stencil_supports(c->T) &&
+                      need <= c->desc_elems * sizeof(bf16);
+  }
   if (const char* e = getenv("VITVS_HOST_CHUNKS")) c->host_chunks = std::max(1, atoi(e));
   *out = c;
   return VVS_OK;
@@ -717,7 +773,7 @@ int vvs_destroy(vvs_handle c) {
   free_resize_axis(&c->rz_w);
   free_resize_axis(&c->rz_h);
   void* ptrs[] = {c->pe_w, c->pe_b, c->cls, c->pos, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
-                  c->nn1, c->nn2, c->sim1, c->cand, c->mean_sim1, c->n_cand, c->n_sel, c->flags, c->mean_sel,
+                  c->inv_norm, c->nn1, c->nn2, c->sim1, c->cand, c->mean_sim1, c->n_cand, c->n_sel, c->flags, c->mean_sel,
                   c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth, c->stage_frames,
                   c->rz_tmp};
   for (void* p : ptrs)
@@ -736,6 +792,7 @@ int vvs_destroy(vvs_handle c) {
 const char* vvs_last_error(vvs_handle c) { return c ? c->err.c_str() : g_create_error.c_str(); }
 int vvs_num_sms(vvs_handle c) { return c ? c->num_sms : 0; }
 int vvs_last_launch_count(vvs_handle c) { return c ? c->launch_count : 0; }
+int vvs_uses_gram_stencil(vvs_handle c) { return (c && c->gram_stencil) ? 1 : 0; }
 
 int vvs_set_weight(vvs_handle c, const char* name_c, const void* p, int32_t dtype, const int64_t* shape, int32_t rank,
                    vvs_stream stream) {

@@ -131,6 +131,15 @@ int launch_descriptors_unit_bf16(const float* x, bf16* out, float* sqnorm_scratc
 int launch_normalize_rows_bf16(const float* in, bf16* out, int rows, int d, int dpad, cudaStream_t s,
                                std::string* err);
 
+// ---- Gram-stencil matching on 3x3-binned descriptors without materialising them (gram_stencil.cu) ----
+int launch_tokens_bf16_sqnorm(const float* x, bf16* tb, float* n2, int n_img, int T, int D, cudaStream_t s,
+                              std::string* err);
+int launch_binned_inv_norm(const float* n2, float* inv, int n_img, int hp, int wp, cudaStream_t s, std::string* err);
+bool gram_stencil_supports(int T);
+int launch_gram_stencil_argmax(const float* G, const float* inv, unsigned long long* row_best,
+                               unsigned long long* col_best, int n_pairs, int hp, int wp, int best_pitch, cudaStream_t s,
+                               std::string* err);
+
 // ---- matching tail + control law ----------------------------------------------------------------
 struct Camera {
   int width, height;      // u_max, v_max

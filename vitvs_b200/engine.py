@@ -312,6 +312,11 @@ class Engine:
         self._check(self.lib.vvs_profile_read(self._h, ms, cnt, n), "vvs_profile_read")
         return {k: (ms[i], cnt[i]) for i, k in enumerate(_lib.KERNEL_CLASSES) if cnt[i]}
 
+    @property
+    def gram_stencil(self) -> bool:
+        """True when the fused path matches binned descriptors through the token Gram matrix (never materialised)."""
+        return bool(self.lib.vvs_uses_gram_stencil(self._h))
+
     def last_launch_count(self) -> int:
         return self.lib.vvs_last_launch_count(self._h)
 
