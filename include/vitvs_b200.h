@@ -185,6 +185,19 @@ VVS_API int vvs_last_launch_count(vvs_handle h);
  * at vvs_create time; it trades 0.3 points of arg-max agreement with the fp32 reference for 1.3 % of a step). */
 VVS_API int vvs_uses_gram_stencil(vvs_handle h);
 
+/* ---- the step AFTER the path: twist -> next camera frame, headless ------------------------------- */
+/* replaces: the simulated RealSense D435 of the reference's Gazebo world looking at its textured poster - a
+ * plane_w x plane_h metre plane (models/viso/meshes/resized.dae:113: 0.8 x 0.6) in z = 0 of the world frame,
+ * centred on the origin, texture [tex_h, tex_w, 3] uint8 (x right, y down) - through the pinhole camera of the
+ * handle's config (frame_width x frame_height, f_x, f_y, c_x, c_y).  cam_to_world [n, 12] fp64 (device): rotation
+ * R row-major then translation t; a camera at (0, 0, -h) with R = I looks along +z at the poster from h metres.
+ * rgb_out [n, frame_height, frame_width, 3] uint8 (bilinear texture fetch, grey 128 off the poster), depth_out
+ * [n, frame_height, frame_width] uint16 millimetres, 0 outside [0.2, 10] m (RealSensePlugin.cpp:252-262).  Device
+ * buffers only: no window, no graphics API.  fp64, bit-identical to the CPU restatement in oracle/render.py. */
+VVS_API int vvs_render_plane(vvs_handle h, const uint8_t* texture, int32_t tex_h, int32_t tex_w, double plane_w,
+                     double plane_h, const double* cam_to_world, int32_t n, uint8_t* rgb_out, uint16_t* depth_out,
+                     vvs_stream stream);
+
 /* ---- per-kernel-class device timing (CUDA events on the launching stream around every launch) -------- */
 enum vvs_kernel_class {
   VVS_K_OTHER = 0, VVS_K_IM2COL = 1, VVS_K_PATCH_GEMM = 2, VVS_K_LAYERNORM = 3, VVS_K_QKV_GEMM = 4,

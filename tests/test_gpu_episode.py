@@ -1,0 +1,96 @@
+"""SURVEY §8f N3 + N2: the headless planar-scene camera is bit-identical to its CPU restatement (oracle/render.py),
+and closed-loop servo episodes driven by the hot path's own twists converge on the goal view - the end-to-end check
+that every sign and frame convention of a9-a16 (keypoint order, interaction matrix, v = -lambda L+ e) is the
+reference's: a wrong one makes the loop diverge."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import dinov2, render  # noqa: E402  (the checker)
+from vitvs_b200 import episode  # noqa: E402
+
+
+def _texture(seed=0, th=600, tw=800):
+    """band-limited noise poster (same recipe as synth.goal_frame, texture-sized)"""
+    g = torch.Generator().manual_seed(seed)
+    low = torch.rand(1, 3, 75, 100, generator=g)
+    img = torch.nn.functional.interpolate(low, size=(th, tw), mode="bicubic", align_corners=False)
+    return (img[0].clamp(0, 1) * 255).round().byte().permute(1, 2, 0).contiguous().numpy()
+
+
+@pytest.fixture(scope="module")
+def vits():
+    return dinov2.build("dinov2_vits14", seed=0)
+
+
+@pytest.fixture(scope="module")
+def eng(vits):
+    from vitvs_b200 import Engine, ServoConfig
+    e = Engine(ServoConfig(model_type="dinov2_vits14", lambda_=0.5), max_images=16)
+    e.load_weights(vits)
+    yield e
+    e.close()
+
+
+def test_render_bit_exact_vs_oracle(eng):
+    tex = _texture()
+    poses = np.stack([
+        episode.make_pose((0.0, 0.0, -0.61)),                                   # the goal view
+        episode.make_pose((0.05, -0.03, -0.70), (0.05, -0.08, 0.3)),            # tilted, rotated, partly off the poster
+        episode.make_pose((0.3, 0.25, -0.25), (0.0, 0.0, -1.0)),                # close: bilinear magnification
+        episode.make_pose((0.0, 0.0, -0.15)),                                    # nearer than 0.2 m: depth 0
+        episode.make_pose((0.0, 0.0, -0.61), (np.pi / 2 + 0.2, 0.0, 0.0)),       # looking past the plane: rays that miss
+    ])
+    rgb, depth = eng.render_plane(torch.from_numpy(tex).cuda(), torch.from_numpy(poses))
+    rgb, depth = rgb.cpu().numpy(), depth.cpu().numpy()
+    for i, p in enumerate(poses):
+        r, d = render.render_plane(tex, p)
+        assert np.array_equal(depth[i], d), f"depth, pose {i}"
+        assert np.array_equal(rgb[i], r), f"rgb, pose {i}: {np.count_nonzero(rgb[i] != r)} bytes differ"
+    assert depth[0].min() == 610 and depth[0].max() == 610 and depth[3].max() == 0
+    assert (rgb[4] == 128).any()
+
+
+def test_kinematics_match_oracle():
+    rng = np.random.default_rng(0)
+    pose = episode.make_pose((0.02, -0.04, -0.6), (0.1, -0.2, 0.3))
+    for _ in range(20):
+        tw = rng.normal(size=6) * 0.05
+        a, b = episode.integrate_twist(pose, tw, 0.7), render.integrate_twist(pose, tw, 0.7)
+        assert np.allclose(a, b, rtol=0, atol=1e-15)
+        pose = a
+    R = pose[:9].reshape(3, 3)
+    assert np.allclose(R @ R.T, np.eye(3), atol=1e-12)
+    et, er = episode.end_error(pose, episode.make_pose((0, 0, -0.61)))
+    ot, orr = render.pose_error(pose, episode.make_pose((0, 0, -0.61)))
+    assert abs(et - 100 * ot) < 1e-9 and abs(er - orr) < 1e-9
+
+
+def test_closed_loop_episodes_converge(eng, tmp_path):
+    tex = _texture(1)
+    goal = episode.make_pose((0.0, 0.0, -0.61))
+    starts = [episode.make_pose((0.04, -0.03, -0.66), (0.0, 0.0, 0.12)),
+              episode.make_pose((-0.05, 0.02, -0.58), (0.03, -0.02, -0.15)),
+              episode.make_pose((0.02, 0.05, -0.70), (-0.04, 0.03, 0.08)),
+              episode.make_pose((0.0, 0.0, -0.61))]                                 # starts at the goal: same-image branch
+    batch = episode.EpisodeBatch(eng, tex, goal, starts, dt=0.3, min_iterations=60, max_iterations=100)
+    res = batch.run()
+    for r in res[:3]:
+        print(f"[episode] {r['initial_position_error_cm']:.2f} cm / {r['initial_orientation_error_deg']:.2f} deg -> "
+              f"{r['position_error_cm']:.3f} cm / {r['orientation_error_deg']:.3f} deg in {r['iterations']} iterations "
+              f"(converged {r['converged']})")
+        # random-init weights and 14-px patch-centre keypoints bound the final accuracy; a sign or frame error in
+        # a9-a16 would make the error GROW (the 2x divergence abort of vitvs_v2.py:359 would fire)
+        assert r["position_error_cm"] < 0.5 * r["initial_position_error_cm"]
+        assert r["orientation_error_deg"] < 0.5 * r["initial_orientation_error_deg"]
+    assert res[3]["position_error_cm"] < 0.5                                       # stays at the goal
+    path = str(tmp_path / "results.npz")
+    batch.save_npz(path)
+    z = np.load(path, allow_pickle=True)
+    for key in ("initial_positions", "final_positions", "final_quaternions", "convergence_flags", "position_errors",
+                "orientation_errors", "all_position_histories", "all_iteration_histories", "lowest_position_errors",
+                "all_applied_velocity_x", "all_applied_velocity_yaw", "total_execution_time"):
+        assert key in z.files
+    assert z["final_positions"].shape == (4, 3) and z["convergence_flags"].shape == (4,)

@@ -1,0 +1,125 @@
+"""CPU tests of the episode driver's host logic and of the oracle renderer's geometry: kinematics,
+EMA, clipping, the stopping rule of vitvs_v2.py:345-421 and the results file, with a stand-in engine whose twist
+is an ideal pose-error controller (no GPU, no kernels)."""
+import numpy as np
+import torch
+
+from oracle import render
+from vitvs_b200 import ServoConfig, episode
+
+
+class _IdealEngine:
+    """render_plane / frames_to_twist with the shapes of Engine; the twist drives the pose error to zero."""
+    device = torch.device("cpu")
+    max_images = 64
+
+    def __init__(self, goal_pose, gain=0.2, fail_from=None, noise=0.0):
+        self.cfg = ServoConfig()
+        self.goal = goal_pose
+        self.gain, self.fail_from, self.calls = gain, fail_from, 0
+        self._poses = None
+        self.noise, self.rng = noise, np.random.default_rng(3)
+
+    def render_plane(self, texture, poses, plane_w=0.8, plane_h=0.6):
+        self._poses = poses.numpy()
+        n = poses.shape[0]
+        return torch.zeros(n, 4, 4, 3, dtype=torch.uint8), torch.zeros(n, 4, 4, dtype=torch.uint16)
+
+    def frames_to_twist(self, goal, cur, depth, want_match=False):
+        self.calls += 1
+        tw = []
+        for p in self._poses:
+            R, t = p[:9].reshape(3, 3), p[9:]
+            Rg, tg = self.goal[:9].reshape(3, 3), self.goal[9:]
+            v = R.T @ (tg - t) * self.gain
+            dR = R.T @ Rg
+            w = np.array([dR[2, 1] - dR[1, 2], dR[0, 2] - dR[2, 0], dR[1, 0] - dR[0, 1]]) / 2 * self.gain
+            tw.append(np.concatenate([v, w]) + self.noise * self.rng.normal(size=6))
+        n = len(tw)
+        nsel = 24 if self.fail_from is None or self.calls < self.fail_from else 0
+        return dict(twist=torch.from_numpy(np.array(tw)), n_selected=torch.full((n,), nsel, dtype=torch.int32),
+                    mean_sim_sel=torch.ones(n))
+
+
+def test_kinematics_and_errors_match_oracle():
+    rng = np.random.default_rng(1)
+    pose = episode.make_pose((0.02, -0.04, -0.6), (0.1, -0.2, 0.3))
+    goal = episode.make_pose((0, 0, -0.61))
+    for _ in range(10):
+        tw = rng.normal(size=6) * 0.05
+        a, b = episode.integrate_twist(pose, tw, 0.5), render.integrate_twist(pose, tw, 0.5)
+        assert np.allclose(a, b, rtol=0, atol=1e-15)
+        pose = a
+    et, er = episode.end_error(pose, goal)
+    ot, orr = render.pose_error(pose, goal)
+    assert abs(et - 100 * ot) < 1e-9 and abs(er - orr) < 1e-9
+    q = episode.quaternion_xyzw(pose)
+    assert abs(np.linalg.norm(q) - 1) < 1e-12
+
+
+def test_ideal_controller_converges_and_stops_by_rule(tmp_path):
+    goal = episode.make_pose((0, 0, -0.61))
+    starts = [episode.make_pose((0.05, -0.03, -0.7), (0.02, -0.03, 0.2)), episode.make_pose((-0.04, 0.04, -0.55), (0, 0, -0.3))]
+    eng = _IdealEngine(goal)
+    b = episode.EpisodeBatch(eng, np.zeros((4, 4, 3), np.uint8), goal, starts, dt=1.0, min_iterations=300, max_iterations=400)
+    res = b.run()
+    for r in res:
+        # a noiseless controller's velocity only ever falls, so the velocity-trend stop (second window above the
+        # first, :402-405) never fires: the episode ends at max_iterations, converged by the 90 % rule (:408-414)
+        assert r["converged"] and r["iterations"] == 400
+        assert r["position_error_cm"] < 0.01 and r["orientation_error_deg"] < 0.01
+    # with a noise floor the velocity-trend rule stops the episode after the 300-iteration floor
+    eng2 = _IdealEngine(goal, noise=1e-4)
+    b2 = episode.EpisodeBatch(eng2, np.zeros((4, 4, 3), np.uint8), goal, starts, dt=1.0, min_iterations=300, max_iterations=2000)
+    for r in b2.run():
+        assert r["converged"] and 300 <= r["iterations"] < 2000
+    e = b.episodes[0]
+    assert len(e.velocity_vector_history) == e.iteration_count == len(e.applied)
+    # EMA (vitvs_v2.py:329-343): first sample copied, then alpha * new + (1 - alpha) * old
+    a = ServoConfig().ema_alpha
+    assert a == 0.8
+    # ROS twist re-mapping of publish_twist (vitvs_v2.py:668-676)
+    v = e.velocity_vector_history[5]
+    assert np.allclose(e.applied[5], [v[2], -v[0], -v[1], v[5], -v[3], -v[4]])
+    path = str(tmp_path / "r.npz")
+    b.save_npz(path, 1.5)
+    z = np.load(path, allow_pickle=True)
+    assert z["convergence_flags"].all() and z["all_position_histories"].shape == (2,)
+    assert float(z["total_execution_time"]) == 1.5
+
+
+def test_divergence_and_feature_failure_abort():
+    goal = episode.make_pose((0, 0, -0.61))
+    start = [episode.make_pose((0.05, 0.0, -0.61))]
+    eng = _IdealEngine(goal, gain=-0.05)                                    # wrong sign: error grows
+    b = episode.EpisodeBatch(eng, np.zeros((4, 4, 3), np.uint8), goal, start, dt=1.0, min_iterations=5, max_iterations=500)
+    r = b.run()[0]
+    assert not r["converged"] and r["position_error_cm"] > 2 * r["initial_position_error_cm"]   # :359 abort
+    eng = _IdealEngine(goal, fail_from=3)
+    b = episode.EpisodeBatch(eng, np.zeros((4, 4, 3), np.uint8), goal, start, dt=1.0, min_iterations=5, max_iterations=500)
+    b.run()
+    assert b.episodes[0].aborted == "Persistent feature detection failure" and b.episodes[0].iteration_count == 12
+
+
+def test_velocity_clip():
+    goal = episode.make_pose((0, 0, -0.61))
+    eng = _IdealEngine(goal, gain=50.0)
+    eng.cfg.max_velocity = 0.1
+    b = episode.EpisodeBatch(eng, np.zeros((4, 4, 3), np.uint8), goal, [episode.make_pose((0.3, 0, -0.61))], dt=0.1,
+                             min_iterations=1, max_iterations=3, cfg=eng.cfg)
+    b.step()
+    assert np.abs(b.episodes[0].velocity_vector_history[0]).max() <= 0.1 + 1e-15
+
+
+def test_oracle_render_geometry():
+    tex = np.zeros((60, 80, 3), np.uint8)
+    tex[:, :40] = 200                                                         # left half bright
+    rgb, depth = render.render_plane(tex, episode.make_pose((0, 0, -0.61)))
+    assert depth.min() == 610 and depth.max() == 610
+    assert rgb[240, 100, 0] == 200 and rgb[240, 540, 0] == 0                  # left of the image = left of the poster
+    # moving the camera to +x shifts the scene to the left in the image
+    rgb2, _ = render.render_plane(tex, episode.make_pose((0.1, 0, -0.61)))
+    assert (rgb2[240] == 200).sum() < (rgb[240] == 200).sum()
+    # farther away: the poster no longer fills the frame, grey background appears; depth grows
+    rgb3, depth3 = render.render_plane(tex, episode.make_pose((0, 0, -1.5)))
+    assert (rgb3 == 128).any() and depth3.max() == 1500

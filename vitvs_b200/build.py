@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libvitvs_b200.so")
-SOURCES = ["api.cu", "gemm_tc.cu", "attention_tc.cu", "attention_ts.cu", "elementwise.cu", "match_ibvs.cu", "resize.cu", "gram_stencil.cu"]
+SOURCES = ["api.cu", "gemm_tc.cu", "attention_tc.cu", "attention_ts.cu", "elementwise.cu", "match_ibvs.cu", "resize.cu", "gram_stencil.cu", "render.cu"]
 HEADERS = ["ptx.cuh", "vvs_internal.h", os.path.join("..", "..", "include", "vitvs_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

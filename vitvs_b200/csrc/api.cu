@@ -1027,6 +1027,20 @@ int vvs_frames_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8_t* c
   return host_pipeline(c, goal, cur, depth, n_pairs, /*from_frames=*/true, twist, n_selected, mean_sim_sel, s);
 }
 
+int vvs_render_plane(vvs_handle c, const uint8_t* texture, int32_t tex_h, int32_t tex_w, double plane_w, double plane_h,
+                     const double* cam_to_world, int32_t n, uint8_t* rgb_out, uint16_t* depth_out, vvs_stream stream) {
+  if (!c || !texture || !cam_to_world || !rgb_out || !depth_out)
+    return fail(c, VVS_ERR_INVALID, "vvs_render_plane: null argument");
+  if (n < 1 || tex_h < 1 || tex_w < 1 || !(plane_w > 0.0) || !(plane_h > 0.0))
+    return fail(c, VVS_ERR_INVALID, "vvs_render_plane: empty problem");
+  Camera cam;
+  cam.width = c->cfg.frame_width; cam.height = c->cfg.frame_height;
+  cam.fx = c->cfg.f_x; cam.fy = c->cfg.f_y; cam.cx = c->cfg.c_x; cam.cy = c->cfg.c_y;
+  ++c->launch_count;
+  return launch_render_plane(texture, tex_h, tex_w, plane_w, plane_h, cam_to_world, n, cam, rgb_out, depth_out,
+                             static_cast<cudaStream_t>(stream), &c->err);
+}
+
 int vvs_profile_enable(vvs_handle c, int32_t on) {
   if (!c) return VVS_ERR_INVALID;
   c->prof_on = on != 0;

@@ -145,6 +145,10 @@ struct Camera {
   int width, height;      // u_max, v_max
   double fx, fy, cx, cy;
 };
+// headless planar-scene RGB-D camera (render.cu): poses [n, 12] = camera-to-world R (row-major) + t, device memory
+int launch_render_plane(const uint8_t* tex, int th, int tw, double plane_w, double plane_h, const double* poses, int n,
+                        const Camera& cam, uint8_t* rgb, uint16_t* depth, cudaStream_t s, std::string* err);
+
 struct SelectArgs {
   const unsigned long long* row_best;
   const unsigned long long* col_best;

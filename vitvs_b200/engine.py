@@ -301,6 +301,23 @@ class Engine:
             _ptr(mean_sim_out), _stream(self.device)), "vvs_frames_to_twist_host")
         self._n_img = 2 * B
 
+    # ------------------------------------------------------------------ headless planar-scene camera (N3)
+    def render_plane(self, texture: torch.Tensor, cam_to_world: torch.Tensor, plane_w: float = 0.8,
+                     plane_h: float = 0.6):
+        """texture uint8 [th, tw, 3] and poses fp64 [n, 12] (R row-major + t, camera-to-world) on this device ->
+        (rgb uint8 [n, v_max, u_max, 3], depth uint16 [n, v_max, u_max]) as the reference's Gazebo camera would."""
+        assert texture.dtype == torch.uint8 and texture.dim() == 3 and texture.shape[2] == 3 and texture.is_cuda
+        poses = cam_to_world.to(self.device, torch.float64).contiguous()
+        assert poses.dim() == 2 and poses.shape[1] == 12
+        n = poses.shape[0]
+        rgb = torch.empty(n, self.cfg.v_max, self.cfg.u_max, 3, dtype=torch.uint8, device=self.device)
+        depth = torch.empty(n, self.cfg.v_max, self.cfg.u_max, dtype=torch.uint16, device=self.device)
+        texture = texture.contiguous()
+        self._check(self.lib.vvs_render_plane(self._h, _ptr(texture), texture.shape[0], texture.shape[1], plane_w,
+                                              plane_h, _ptr(poses), n, _ptr(rgb), _ptr(depth), _stream(self.device)),
+                    "vvs_render_plane")
+        return rgb, depth
+
     def profile(self, on: bool) -> None:
         self._check(self.lib.vvs_profile_enable(self._h, int(on)), "vvs_profile_enable")
 

@@ -1,0 +1,234 @@
+"""Closed-loop servo episodes, batched on one GPU (SURVEY §8f N2 + N3): the callers of the hot path.
+
+Mirrors the reference's servo loop around ``Controller.ibvs()`` - EMA smoothing (vitvs_v2.py:329-343, :623),
+velocity clipping (:668-676), the stopping rule of ``is_visual_servoing_done`` (:345-421) and the per-sample
+records ``run()`` returns (:700-842) - but B episodes advance together: every iteration is ONE
+``vvs_render_plane`` call (the headless stand-in for the Gazebo camera) and ONE ``vvs_frames_to_twist`` call for
+all episodes still running.  Host code here is bookkeeping only (poses, histories, stopping rule); the frames
+never leave the device.  ``save_npz`` writes the keys the reference's results file holds (:1493-1516) so that
+``src/eval/*.py`` can read it.
+
+Pose convention (csrc/render.cu): camera-to-world [R | t] as 12 doubles; the poster lies in z = 0; the camera at
+(0, 0, -h) with R = I looks straight at it from h metres.  The twist is the camera-frame velocity
+v_c = (vx, vy, vz, wx, wy, wz) the control law returns (vitvs_v2.py:622).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from .config import ServoConfig
+
+
+# ----------------------------------------------------------------------------------------- rigid-body kinematics
+def _skew(w):
+    return np.array([[0.0, -w[2], w[1]], [w[2], 0.0, -w[0]], [-w[1], w[0], 0.0]])
+
+
+def rotation_from_rotvec(w) -> np.ndarray:
+    th = float(np.linalg.norm(w))
+    K = _skew(w)
+    if th < 1e-12:
+        return np.eye(3) + K
+    return np.eye(3) + (np.sin(th) / th) * K + ((1.0 - np.cos(th)) / (th * th)) * (K @ K)
+
+
+def make_pose(position, rotvec=(0.0, 0.0, 0.0)) -> np.ndarray:
+    """camera-to-world pose [12] from a camera position and a rotation vector (world frame)."""
+    return np.concatenate([rotation_from_rotvec(np.asarray(rotvec, float)).reshape(-1), np.asarray(position, float)])
+
+
+def integrate_twist(pose: np.ndarray, twist: np.ndarray, dt: float) -> np.ndarray:
+    """Apply the camera-frame twist for dt seconds (what gazebo_vel_broadcaster.py:32-46 asks Gazebo to do)."""
+    R, t = pose[:9].reshape(3, 3), pose[9:]
+    return np.concatenate([(R @ rotation_from_rotvec(twist[3:] * dt)).reshape(-1), t + R @ (twist[:3] * dt)])
+
+
+def end_error(pose: np.ndarray, goal: np.ndarray):
+    """Controller.calculate_end_error (vitvs_v2.py:843-861): (position error in cm, orientation error in degrees)."""
+    Ra, Rb = pose[:9].reshape(3, 3), goal[:9].reshape(3, 3)
+    c = (np.trace(Ra.T @ Rb) - 1.0) / 2.0
+    return float(np.linalg.norm(pose[9:] - goal[9:]) * 100.0), float(np.degrees(np.arccos(np.clip(c, -1.0, 1.0))))
+
+
+def quaternion_xyzw(pose: np.ndarray) -> np.ndarray:
+    R = pose[:9].reshape(3, 3)
+    w = np.sqrt(max(0.0, 1.0 + R[0, 0] + R[1, 1] + R[2, 2])) / 2.0
+    if w > 1e-8:
+        return np.array([(R[2, 1] - R[1, 2]) / (4 * w), (R[0, 2] - R[2, 0]) / (4 * w), (R[1, 0] - R[0, 1]) / (4 * w), w])
+    i = int(np.argmax(np.diag(R)))
+    j, k = (i + 1) % 3, (i + 2) % 3
+    s = np.sqrt(max(0.0, 1.0 + R[i, i] - R[j, j] - R[k, k])) * 2.0
+    q = np.zeros(4)
+    q[i] = s / 4.0
+    q[j] = (R[j, i] + R[i, j]) / s
+    q[k] = (R[k, i] + R[i, k]) / s
+    q[3] = (R[k, j] - R[j, k]) / s
+    return q
+
+
+# ----------------------------------------------------------------------------------------- per-episode state
+@dataclass
+class Episode:
+    pose: np.ndarray
+    start_pose: np.ndarray
+    ema: list = field(default_factory=lambda: [None] * 6)         # Controller.initialize_ema (vitvs_v2.py:325-327)
+    iteration_count: int = 0
+    failures: int = 0                                              # feature_failure_count (:500-508)
+    done: bool = False
+    converged: bool = False
+    aborted: str = ""
+    velocity_vector_history: list = field(default_factory=list)
+    position_history: list = field(default_factory=list)
+    orientation_history: list = field(default_factory=list)
+    applied: list = field(default_factory=list)                    # clipped, re-mapped twist published on /camera_vel
+    lowest_position_error: float = float("inf")
+    lowest_orientation_error: float = float("inf")
+    initial_error_translation: float = 0.0
+    initial_error_rotation: float = 0.0
+
+
+class EpisodeBatch:
+    """B closed-loop servo episodes against one goal view, advanced together on one Engine."""
+
+    def __init__(self, engine, texture_u8, goal_pose: np.ndarray, start_poses, dt: float = 1.0,
+                 min_iterations: int = 300, max_iterations: int = 2000, cfg: ServoConfig | None = None):
+        self.engine = engine
+        self.cfg = cfg or engine.cfg
+        self.dt, self.min_iterations, self.max_iterations = dt, min_iterations, max_iterations
+        dev = engine.device
+        self.texture = torch.as_tensor(np.ascontiguousarray(texture_u8)).to(dev)
+        self.goal_pose = np.asarray(goal_pose, float)
+        self.episodes = [Episode(pose=np.asarray(p, float).copy(), start_pose=np.asarray(p, float).copy())
+                         for p in start_poses]
+        if 2 * len(self.episodes) > engine.max_images:
+            raise ValueError("engine.max_images must be >= 2 x the number of episodes")
+        for e in self.episodes:
+            e.initial_error_translation, e.initial_error_rotation = end_error(e.pose, self.goal_pose)
+        # the goal view never changes: rendered once (the reference loads goalrgb.jpg once, vitvs_v2.py:255)
+        self.goal_frame, _ = engine.render_plane(self.texture, torch.from_numpy(self.goal_pose[None]))
+
+    # -- vitvs_v2.py:329-343
+    def _update_ema(self, e: Episode, i: int, v: float) -> float:
+        a = self.cfg.ema_alpha
+        e.ema[i] = v if e.ema[i] is None else a * v + (1 - a) * e.ema[i]
+        return e.ema[i]
+
+    # -- vitvs_v2.py:345-421, with the iteration floor as a parameter (300 in the reference)
+    def _is_done(self, e: Episode):
+        if e.iteration_count < self.min_iterations:
+            return False, False
+        err_t, err_r = end_error(e.pose, self.goal_pose)
+        if err_t > 2 * e.initial_error_translation:
+            return True, False
+        reduced = (err_t / max(e.initial_error_translation, 1e-12) < 0.1 and
+                   err_r / max(e.initial_error_rotation, 1e-12) < 0.1)
+        if len(e.velocity_vector_history) >= 200:
+            recent = np.array(e.velocity_vector_history[-200:])
+            first, second = recent[:100], recent[100:]
+            ft = np.linalg.norm(first[:, :3] * 1000.0, axis=1).mean()
+            fr = np.linalg.norm(np.degrees(first[:, 3:]), axis=1).mean()
+            st = np.linalg.norm(second[:, :3] * 1000.0, axis=1).mean()
+            sr = np.linalg.norm(np.degrees(second[:, 3:]), axis=1).mean()
+            if ft < 1.0 and fr < 0.1 and st > ft and sr > fr:
+                return True, reduced
+        if e.iteration_count >= self.max_iterations:
+            return True, reduced
+        return False, False
+
+    def step(self) -> int:
+        """One iteration of every running episode; returns how many are still running."""
+        live = [e for e in self.episodes if not e.done]
+        if not live:
+            return 0
+        n = len(live)
+        poses = torch.from_numpy(np.stack([e.pose for e in live]))
+        frames, depth = self.engine.render_plane(self.texture, poses)
+        goal = self.goal_frame.expand(n, -1, -1, -1).contiguous()
+        out = self.engine.frames_to_twist(goal, frames, depth)
+        twist = out["twist"].cpu().numpy()
+        n_sel = out["n_selected"].cpu().numpy()
+        mv = self.cfg.max_velocity
+        for k, e in enumerate(live):
+            e.iteration_count += 1
+            if n_sel[k] == 0:                                     # detect_features failure (:500-508)
+                e.failures += 1
+                if e.failures >= 10:
+                    e.done, e.aborted = True, "Persistent feature detection failure"
+                continue
+            e.failures = 0
+            if n_sel[k] < 4:                                       # ibvs() returns early (:602-605)
+                continue
+            v_c = np.array([self._update_ema(e, i, float(v)) for i, v in enumerate(twist[k])])
+            v_c = np.clip(v_c, -mv, mv)                            # publish_twist clips every component (:668-676)
+            e.applied.append([v_c[2], -v_c[0], -v_c[1], v_c[5], -v_c[3], -v_c[4]])
+            e.velocity_vector_history.append(v_c.copy())
+            e.pose = integrate_twist(e.pose, v_c, self.dt)
+            err_t, err_r = end_error(e.pose, self.goal_pose)
+            e.position_history.append(e.pose[9:].copy())
+            e.orientation_history.append(quaternion_xyzw(e.pose))
+            e.lowest_position_error = min(e.lowest_position_error, err_t)
+            e.lowest_orientation_error = min(e.lowest_orientation_error, err_r)
+            done, conv = self._is_done(e)
+            if done:
+                e.done, e.converged = True, bool(conv)
+        return sum(not e.done for e in self.episodes)
+
+    def run(self) -> list[dict]:
+        while self.step():
+            pass
+        return self.results()
+
+    def results(self) -> list[dict]:
+        out = []
+        for e in self.episodes:
+            err_t, err_r = end_error(e.pose, self.goal_pose)
+            out.append(dict(converged=e.converged, aborted=e.aborted, iterations=e.iteration_count,
+                            position_error_cm=err_t, orientation_error_deg=err_r,
+                            initial_position_error_cm=e.initial_error_translation,
+                            initial_orientation_error_deg=e.initial_error_rotation,
+                            lowest_position_error_cm=e.lowest_position_error,
+                            lowest_orientation_error_deg=e.lowest_orientation_error))
+        return out
+
+    def save_npz(self, path: str, total_execution_time: float = 0.0) -> None:
+        """The keys of the reference's results file (vitvs_v2.py:1493-1516)."""
+        E = self.episodes
+
+        def obj(rows):                      # ragged per-episode histories: a 1-D object array, one entry per episode
+            a = np.empty(len(rows), dtype=object)
+            for i, r in enumerate(rows):
+                a[i] = np.asarray(r)
+            return a
+        res = self.results()
+        applied = [np.asarray(e.applied).reshape(-1, 6) for e in E]
+        vel = [np.asarray(e.velocity_vector_history).reshape(-1, 6) for e in E]
+
+        def window_mean(v, w):
+            return np.array([v[max(0, i - w + 1): i + 1].mean(axis=0) for i in range(len(v))]).reshape(-1, 6)
+        np.savez(path,
+                 initial_positions=np.array([e.start_pose[9:] for e in E]),
+                 initial_orientations=np.array([quaternion_xyzw(e.start_pose) for e in E]),
+                 final_positions=np.array([e.pose[9:] for e in E]),
+                 final_quaternions=np.array([quaternion_xyzw(e.pose) for e in E]),
+                 convergence_flags=np.array([e.converged for e in E]),
+                 position_errors=np.array([r["position_error_cm"] for r in res]),
+                 orientation_errors=np.array([r["orientation_error_deg"] for r in res]),
+                 best_poses=obj([e.start_pose for e in E]),
+                 all_position_histories=obj([e.position_history for e in E]),
+                 all_orientation_histories=obj([e.orientation_history for e in E]),
+                 all_iteration_histories=np.array([e.iteration_count for e in E]),
+                 lowest_position_errors=np.array([e.lowest_position_error for e in E]),
+                 lowest_orientation_errors=np.array([e.lowest_orientation_error for e in E]),
+                 all_average_velocities=obj([v.mean(axis=0) if len(v) else np.zeros(6) for v in vel]),
+                 all_velocity_mean_100=obj([window_mean(v, 100) for v in vel]),
+                 all_velocity_mean_10=obj([window_mean(v, 10) for v in vel]),
+                 all_applied_velocity_x=obj([a[:, 0] for a in applied]),
+                 all_applied_velocity_y=obj([a[:, 1] for a in applied]),
+                 all_applied_velocity_z=obj([a[:, 2] for a in applied]),
+                 all_applied_velocity_roll=obj([a[:, 3] for a in applied]),
+                 all_applied_velocity_pitch=obj([a[:, 4] for a in applied]),
+                 all_applied_velocity_yaw=obj([a[:, 5] for a in applied]),
+                 total_execution_time=total_execution_time)
