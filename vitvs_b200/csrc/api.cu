@@ -142,7 +142,7 @@ struct vvs_ctx {
   struct GraphEntry { int n_pairs; int want_mean; cudaGraphExec_t execA; cudaGraphExec_t execB; int launchesA; int launches; };
   std::vector<cudaEvent_t> chunk_events;   // host pipeline: [2 * chunk] frames landed / depth landed
   int host_chunks = 0;                     // sub-batches of a host-buffer call (H2D of chunk j+1 under the compute of chunk j);
-                                           // 0 = default: 2 for camera frames (3.2x the bytes), 1 for pre-resized images
+                                           // 0 = default: see host_pipeline
   std::vector<GraphEntry> graphs;
   std::vector<int> eager_calls;      // n_pairs values that already ran eagerly once (lazy init done)
   bool graphs_enabled = true;
@@ -600,10 +600,23 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
   const bool want_mean = mean_sim_sel != nullptr;
   if (!from_frames && img_bytes > frame_bytes)
     return fail(c, VVS_ERR_STATE, "image_size larger than the camera frame: host staging too small");
-  const int want_chunks = c->host_chunks > 0 ? c->host_chunks : (from_frames ? 2 : 1);
-  int chunks = std::max(1, std::min(want_chunks, n_pairs / 8));
-  const int per = (n_pairs + chunks - 1) / chunks;
-  chunks = (n_pairs + per - 1) / per;
+  // Sub-batches: {p0, nc}.  Default for camera frames: a SMALL first sub-batch (an eighth of the batch) whose H2D is
+  // the only copy left exposed, then the rest in one piece - its 3.2x larger copy runs under the first one's
+  // compute, and only an eighth of the work pays the wave-quantisation cost of a small GEMM.  Pre-resized images
+  // (36 MB for 64 pairs) are not worth splitting (measured).  VITVS_HOST_CHUNKS=n forces n equal sub-batches.
+  std::vector<std::pair<int, int>> parts;
+  if (c->host_chunks > 0) {
+    int chunks = std::max(1, std::min(c->host_chunks, n_pairs / 8));
+    const int per = (n_pairs + chunks - 1) / chunks;
+    for (int p0 = 0; p0 < n_pairs; p0 += per) parts.emplace_back(p0, std::min(per, n_pairs - p0));
+  } else if (from_frames && n_pairs >= 32) {
+    const int first = n_pairs / 8;
+    parts.emplace_back(0, first);
+    parts.emplace_back(first, n_pairs - first);
+  } else {
+    parts.emplace_back(0, n_pairs);
+  }
+  const int chunks = static_cast<int>(parts.size());
   while (c->chunk_events.size() < static_cast<size_t>(2 * chunks)) {
     cudaEvent_t e;
     VVS_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), &c->err);
@@ -611,21 +624,25 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
   }
   uint8_t* land_goal = c->stage_frames;
   uint8_t* land_cur = c->stage_frames + static_cast<size_t>(n_pairs) * in_bytes;
-  // the previous call synchronised, so every staging buffer is free
+  // the previous call synchronised, so every staging buffer is free.  Copy order: the frames of every sub-batch
+  // first, the depth maps (read only by the control law at the end of a sub-batch) behind them.
   for (int j = 0; j < chunks; ++j) {
-    const int p0 = j * per, nc = std::min(per, n_pairs - p0);
+    const int p0 = parts[j].first, nc = parts[j].second;
     VVS_CUDA_OK(cudaMemcpyAsync(land_goal + p0 * in_bytes, goal + p0 * in_bytes, nc * in_bytes, cudaMemcpyHostToDevice,
                                 c->copy_stream), &c->err);
     VVS_CUDA_OK(cudaMemcpyAsync(land_cur + p0 * in_bytes, cur + p0 * in_bytes, nc * in_bytes, cudaMemcpyHostToDevice,
                                 c->copy_stream), &c->err);
     VVS_CUDA_OK(cudaEventRecord(c->chunk_events[2 * j], c->copy_stream), &c->err);
+  }
+  for (int j = 0; j < chunks; ++j) {
+    const int p0 = parts[j].first, nc = parts[j].second;
     VVS_CUDA_OK(cudaMemcpyAsync(c->stage_depth + p0 * depth_elems, depth + p0 * depth_elems,
                                 nc * depth_elems * sizeof(uint16_t), cudaMemcpyHostToDevice, c->copy_stream), &c->err);
     VVS_CUDA_OK(cudaEventRecord(c->chunk_events[2 * j + 1], c->copy_stream), &c->err);
   }
   int launches = 0;
   for (int j = 0; j < chunks; ++j) {
-    const int p0 = j * per, nc = std::min(per, n_pairs - p0);
+    const int p0 = parts[j].first, nc = parts[j].second;
     VVS_CUDA_OK(cudaStreamWaitEvent(s, c->chunk_events[2 * j], 0), &c->err);
     c->launch_count = 0;
     if (from_frames) {
