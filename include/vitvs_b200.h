@@ -178,6 +178,9 @@ VVS_API int vvs_frames_to_twist_host(vvs_handle h, const uint8_t* goal_frames_ho
                              int32_t* n_selected_host, float* mean_sim_sel_host, vvs_stream stream);
 /* number of kernels the last vvs_frame_pairs_to_twist* / vvs_frames_to_twist* call launched (bench.py gpu_launches). */
 VVS_API int vvs_last_launch_count(vvs_handle h);
+/* replaces: `controller.num_pairs = 48` / restore around the best-pose search (vitvs_v2.py:1156-1158, 1179): changes
+ * the K of the fused frame-pair entry points, 1 <= num_pairs <= max(num_pairs at creation, 64). */
+VVS_API int vvs_set_num_pairs(vvs_handle h, int32_t num_pairs);
 /* 1 when the fused frame-pair path matches 3x3-binned descriptors as a 9-point stencil over the token Gram matrix
  * (the [T, 9*dim] descriptors of dinov2_extractor.py:265-311 are then never written and the similarity product of
  * vitvs_v2.py:49-56 runs with K = dim): same cosine similarities up to fp32 summation order.  0 = the binned

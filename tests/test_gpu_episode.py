@@ -94,3 +94,29 @@ def test_closed_loop_episodes_converge(eng, tmp_path):
                 "all_applied_velocity_x", "all_applied_velocity_yaw", "total_execution_time"):
         assert key in z.files
     assert z["final_positions"].shape == (4, 3) and z["convergence_flags"].shape == (4,)
+
+
+def test_best_pose_search_and_num_pairs(eng):
+    """find_and_set_best_pose (vitvs_v2.py:1151-1189), batched: starts turned by a multiple of 90 degrees about the
+    optical axis are turned back by the search; num_pairs is 48 during the search and restored after it."""
+    tex = torch.from_numpy(_texture(2)).cuda()
+    goal_pose = episode.make_pose((0.0, 0.0, -0.61))
+    goal_frame, _ = eng.render_plane(tex, torch.from_numpy(goal_pose[None]))
+    base = [episode.make_pose((0.02, -0.01, -0.63), (0.0, 0.0, 0.05)), episode.make_pose((-0.03, 0.02, -0.60), (0.01, 0.0, -0.04))]
+    turned = np.stack([episode.rotate_about_optical_axis(base[0], 180), episode.rotate_about_optical_axis(base[1], 90),
+                       base[0]])
+    assert eng.cfg.num_pairs == 24
+    best = episode.find_best_poses(eng, tex, goal_frame, turned)
+    assert eng.cfg.num_pairs == 24
+    for b, want in zip(best, (base[0], base[1], base[0])):
+        _, err_deg = episode.end_error(b, want)
+        assert err_deg < 1e-6, err_deg
+    # K really changes: 48 keypoints come back while it is raised
+    eng.set_num_pairs(48)
+    frames, depth = eng.render_plane(tex, torch.from_numpy(np.stack(base)))
+    out = eng.frames_to_twist(goal_frame.expand(2, -1, -1, -1).contiguous(), frames, depth, want_match=True)
+    assert out["uv"].shape == (2, 48, 2) and int(out["n_selected"].max()) > 24
+    eng.set_num_pairs(24)
+    from vitvs_b200 import VvsError
+    with pytest.raises(VvsError):
+        eng.set_num_pairs(1000)

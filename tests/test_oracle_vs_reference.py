@@ -83,3 +83,43 @@ def test_cyclic_distance_bit_equal_to_pairwise_distance():
     ref = torch.nn.PairwiseDistance(p=2)(a, torch.zeros_like(a)).numpy()
     mine = servo.cyclic_distance_f32(dr.reshape(-1).numpy(), dc.reshape(-1).numpy())
     assert np.array_equal(ref, mine)
+
+
+def test_experiment_sampling_equals_reference():
+    """vitvs_b200.episode restates the start-pose sampling of the reference's main() (vitvs_v2.py:1385-1418): same
+    numbers from the same seed, then mapped into the renderer's camera convention."""
+    from vitvs_b200 import episode
+    V = ref_loader.vitvs()
+    n, circles, aug = 40, 4, 0.08
+    np.random.seed(41)
+    pos_r = V.sample_camera_positions(np.array([1.2, 1.2, 0.3]), n, np.array([0, 0, 0.61]))
+    foc_r = V.sample_focal_points_original(n, np.array([0.0, 0.0, 0.01]), circles, aug)
+    mats_r, _ = V.calculate_look_at_orientation(pos_r, foc_r)
+    quat_r = V.apply_z_axis_rotation(mats_r, circles, n // circles)
+    np.random.seed(41)
+    pos = episode.sample_camera_positions(np.array([1.2, 1.2, 0.3]), n, np.array([0, 0, 0.61]))
+    foc = episode.sample_focal_points(n, np.array([0.0, 0.0, 0.01]), circles, aug)
+    mats = episode.look_at_matrices(pos, foc)
+    rot = episode.apply_optical_axis_rotation(mats, circles, n // circles)
+    assert np.array_equal(pos, pos_r) and np.array_equal(foc, foc_r) and np.array_equal(mats, mats_r)
+    from scipy.spatial.transform import Rotation as R
+    assert np.allclose(R.from_matrix(rot).as_quat(), quat_r, atol=1e-12)
+    poses = episode.sample_start_poses(n, circles, aug, seed=41)
+    assert poses.shape == (n, 12)
+    for i in range(n):
+        assert np.allclose(poses[i], episode.to_camera_pose(pos_r[i], R.from_quat(quat_r[i]).as_matrix()), atol=1e-12)
+    # the reference's desired pose (position (0,0,0.61), quaternion [0, .7071068, 0, .7071068]: vitvs_v2.py:1391-1392)
+    # is the renderer's goal view: identity rotation, 0.61 m in front of the poster
+    goal = episode.to_camera_pose([0, 0, 0.61], R.from_quat([0, 0.7071068, 0, 0.7071068]).as_matrix())
+    assert np.allclose(goal, episode.make_pose((0, 0, -0.61)), atol=1e-7)
+    # every sampled camera looks at the poster: its optical axis hits z = 0 within the circles' radius
+    for p in poses:
+        Rm, t = p[:9].reshape(3, 3), p[9:]
+        s = -t[2] / Rm[2, 2]
+        hit = t + s * Rm[:, 2]
+        assert s > 0 and np.hypot(hit[0], hit[1]) < circles * aug + 0.02
+    # rotate_camera_x_axis (:1125-1148) == a rotation about our optical axis
+    q0 = quat_r[3]
+    for ang in (90, 180, 270):
+        ref_pose = episode.to_camera_pose(pos_r[3], R.from_quat(V.rotate_camera_x_axis(q0, ang)).as_matrix())
+        assert np.allclose(episode.rotate_about_optical_axis(poses[3], ang), ref_pose, atol=1e-12)

@@ -65,6 +65,7 @@ SYMBOLS = {
     "vvs_render_plane": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_f64, c_f64, c_vp, c_i32, c_vp, c_vp, c_vp]),
     "vvs_last_launch_count": (c_i32, [c_vp]),
     "vvs_uses_gram_stencil": (c_i32, [c_vp]),
+    "vvs_set_num_pairs": (c_i32, [c_vp, c_i32]),
     "vvs_profile_enable": (c_i32, [c_vp, c_i32]),
     "vvs_profile_read": (c_i32, [c_vp, C.POINTER(c_f64), C.POINTER(c_i32), c_i32]),
     "vvs_dbg_gemm": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32,

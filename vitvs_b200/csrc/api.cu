@@ -809,6 +809,20 @@ int vvs_destroy(vvs_handle c) {
 const char* vvs_last_error(vvs_handle c) { return c ? c->err.c_str() : g_create_error.c_str(); }
 int vvs_num_sms(vvs_handle c) { return c ? c->num_sms : 0; }
 int vvs_last_launch_count(vvs_handle c) { return c ? c->launch_count : 0; }
+int vvs_set_num_pairs(vvs_handle c, int32_t num_pairs) {
+  if (!c) return VVS_ERR_INVALID;
+  if (num_pairs < 1 || num_pairs > c->k_cap)
+    return fail(c, VVS_ERR_INVALID, "vvs_set_num_pairs: outside [1, max(num_pairs at creation, 64)]");
+  if (num_pairs == c->cfg.num_pairs) return VVS_OK;
+  c->cfg.num_pairs = num_pairs;
+  for (auto& g : c->graphs) {      // K is baked into the captured launches
+    cudaGraphExecDestroy(g.execA);
+    cudaGraphExecDestroy(g.execB);
+  }
+  c->graphs.clear();
+  c->eager_calls.clear();
+  return VVS_OK;
+}
 int vvs_uses_gram_stencil(vvs_handle c) { return (c && c->gram_stencil) ? 1 : 0; }
 
 int vvs_set_weight(vvs_handle c, const char* name_c, const void* p, int32_t dtype, const int64_t* shape, int32_t rank,

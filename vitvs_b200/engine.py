@@ -334,6 +334,11 @@ class Engine:
         """True when the fused path matches binned descriptors through the token Gram matrix (never materialised)."""
         return bool(self.lib.vvs_uses_gram_stencil(self._h))
 
+    def set_num_pairs(self, num_pairs: int) -> None:
+        """`controller.num_pairs = K` (vitvs_v2.py:1158): K of the fused entry points from now on."""
+        self._check(self.lib.vvs_set_num_pairs(self._h, int(num_pairs)), "vvs_set_num_pairs")
+        self.cfg.num_pairs = int(num_pairs)
+
     def last_launch_count(self) -> int:
         return self.lib.vvs_last_launch_count(self._h)
 

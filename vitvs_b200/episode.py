@@ -69,6 +69,117 @@ def quaternion_xyzw(pose: np.ndarray) -> np.ndarray:
     return q
 
 
+# ----------------------------------------------------------------------------------------- experiment sampling
+# The reference samples in ITS world / body frames (Z up, camera body x = optical axis; vitvs_v2.py:1391-1418) - the
+# functions below restate that sampling number for number (numpy legacy RNG, seed 41) and map the result into the
+# optical camera-to-world convention of csrc/render.cu.
+_REF_WORLD_TO_OURS = np.array([[0.0, -1.0, 0.0], [-1.0, 0.0, 0.0], [0.0, 0.0, -1.0]])   # x = -Y_ref, y = -X_ref, z = -Z_ref
+_OPTICAL_IN_BODY = np.array([[0.0, 0.0, 1.0], [-1.0, 0.0, 0.0], [0.0, -1.0, 0.0]])      # columns: optical x, y, z in body axes
+
+
+def sample_camera_positions(volume_dimensions, num_samples, desired_position):
+    """vitvs_v2.py:959-978: uniform positions in a box centred on the desired position (uses np.random's global state)."""
+    half = np.asarray(volume_dimensions, float) / 2
+    return np.random.uniform(np.asarray(desired_position) - half, np.asarray(desired_position) + half, size=(num_samples, 3))
+
+
+def sample_focal_points(num_samples, reference_point, num_circles, circle_radius_aug):
+    """vitvs_v2.py:981-1010: looked-at points on concentric circles around the poster centre."""
+    per = num_samples // num_circles
+    pts = np.empty((num_samples, 3))
+    for cn in range(num_circles):
+        radius = circle_radius_aug * (cn + 1)
+        theta = np.random.uniform(-np.pi, np.pi, size=per)
+        pts[cn * per:(cn + 1) * per] = np.column_stack((np.cos(theta) * radius + reference_point[0],
+                                                        np.sin(theta) * radius + reference_point[1],
+                                                        np.repeat(reference_point[2], per)))
+    return pts
+
+
+def look_at_matrices(camera_positions, focal_points):
+    """vitvs_v2.py:1253-1292: body-to-world rotations, body x = forward, world_up = (-1, 0, 0)."""
+    out = np.empty((len(camera_positions), 3, 3))
+    for i in range(len(camera_positions)):
+        forward = focal_points[i] - camera_positions[i]
+        forward = forward / np.linalg.norm(forward)
+        right = -np.cross(forward, np.array([-1, 0, 0]))
+        right = right / np.linalg.norm(right)
+        up = np.cross(right, forward)
+        out[i] = np.column_stack((forward, -right, up))
+    return out
+
+
+def apply_optical_axis_rotation(rotation_matrices, num_circles, samples_per_circle, rz_max=np.radians(120)):
+    """vitvs_v2.py:1295-1342: per circle, rotations about the body x axis swept linearly over [-rz_max, rz_max]."""
+    out = []
+    for cn in range(num_circles):
+        rz_values = np.linspace(-rz_max, rz_max, num=samples_per_circle)
+        for i in range(samples_per_circle):
+            idx = cn * samples_per_circle + i
+            if idx >= len(rotation_matrices):
+                break
+            c, s_ = np.cos(rz_values[i]), np.sin(rz_values[i])
+            out.append(np.dot(rotation_matrices[idx], np.array([[1, 0, 0], [0, c, -s_], [0, s_, c]])))
+    return np.array(out)
+
+
+def to_camera_pose(position_ref, body_to_world_ref) -> np.ndarray:
+    """A reference (world Z-up, body-frame) camera pose -> our camera-to-world [R | t] (optical axes, poster in z = 0)."""
+    R = _REF_WORLD_TO_OURS @ np.asarray(body_to_world_ref, float) @ _OPTICAL_IN_BODY
+    return np.concatenate([R.reshape(-1), _REF_WORLD_TO_OURS @ np.asarray(position_ref, float)])
+
+
+def sample_start_poses(num_samples=500, num_circles=4, circle_radius_aug=0.08, seed=41,
+                       desired_position=(0.0, 0.0, 0.61), box_sample_size=(1.2, 1.2, 0.3),
+                       reference_point=(0.0, 0.0, 0.01)) -> np.ndarray:
+    """The start poses of the reference's experiment (main(), vitvs_v2.py:1385-1418; config.yaml num_samples /
+    num_circles / circle_radius_aug; np.random.seed(41)) as [n, 12] camera-to-world poses in our convention."""
+    per = num_samples // num_circles
+    n = num_circles * per
+    np.random.seed(seed)
+    pos = sample_camera_positions(np.array(box_sample_size), n, np.array(desired_position))
+    foc = sample_focal_points(n, np.array(reference_point), num_circles, circle_radius_aug)
+    rot = apply_optical_axis_rotation(look_at_matrices(pos, foc), num_circles, per)
+    return np.stack([to_camera_pose(pos[i], rot[i]) for i in range(n)])
+
+
+def rotate_about_optical_axis(pose: np.ndarray, angle_degrees: float) -> np.ndarray:
+    """rotate_camera_x_axis (vitvs_v2.py:1125-1148): the body x axis is the optical axis = our camera z."""
+    a = np.radians(angle_degrees)
+    Rz = np.array([[np.cos(a), -np.sin(a), 0.0], [np.sin(a), np.cos(a), 0.0], [0.0, 0.0, 1.0]])
+    return np.concatenate([(pose[:9].reshape(3, 3) @ Rz).reshape(-1), pose[9:]])
+
+
+def find_best_poses(engine, texture, goal_frame, poses, search_num_pairs: int = 48) -> np.ndarray:
+    """find_and_set_best_pose (vitvs_v2.py:1151-1189), batched: every start pose is tried at 0 / 90 / 180 / 270 degrees
+    about the optical axis with num_pairs raised to 48; the rotation whose selected pairs have the highest mean
+    similarity wins (the first of equals, as the reference's strict `>`); a rotation with no match is skipped and a
+    pose with none keeps its initial orientation.  One render + one frames_to_twist call per rotation."""
+    poses = np.asarray(poses, float)
+    n = len(poses)
+    best_mean = np.full(n, -np.inf)
+    best = poses.copy()
+    K0 = engine.cfg.num_pairs
+    engine.set_num_pairs(search_num_pairs)
+    try:
+        for angle in (0, 90, 180, 270):
+            cand = poses if angle == 0 else np.stack([rotate_about_optical_axis(p, angle) for p in poses])
+            for i0 in range(0, n, engine.max_images // 2):
+                sl = slice(i0, min(n, i0 + engine.max_images // 2))
+                frames, depth = engine.render_plane(texture, torch.from_numpy(cand[sl]))
+                goal = goal_frame.expand(frames.shape[0], -1, -1, -1).contiguous()
+                out = engine.frames_to_twist(goal, frames, depth)
+                mean = out["mean_sim_sel"].double().cpu().numpy()
+                ok = out["n_selected"].cpu().numpy() > 0
+                better = ok & (mean > best_mean[sl])
+                idx = np.nonzero(better)[0] + i0
+                best_mean[idx] = mean[better]
+                best[idx] = cand[idx]
+    finally:
+        engine.set_num_pairs(K0)
+    return best
+
+
 # ----------------------------------------------------------------------------------------- per-episode state
 @dataclass
 class Episode:
