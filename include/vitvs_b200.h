@@ -102,6 +102,19 @@ VVS_API int vvs_get_tokens(vvs_handle h, float* tokens_out, int32_t n_img, vvs_s
  * desc_out [n_img, T, (bin ? 9 : 1) * dim] fp32. */
 VVS_API int vvs_descriptors(vvs_handle h, int32_t n_img, int32_t bin, float* desc_out, vvs_stream stream);
 
+/* replaces: ViTExtractor._extract_features with facet 'query' / 'key' / 'value' (dinov2_extractor.py:203-218): runs
+ * blocks[0..layer-1], then norm1 and the fused qkv projection of blocks[layer] - the tensor the reference's hook on
+ * `blocks[layer].attn` recomputes - and stops.  Invalidates vvs_get_tokens / vvs_descriptors until the next
+ * vvs_forward_tokens. */
+VVS_API int vvs_forward_facet(vvs_handle h, const void* images, int32_t image_kind, int32_t n_img, int32_t layer,
+                      vvs_stream stream);
+/* replaces: ViTExtractor.extract_descriptors(..., facet in {'query','key','value'}, bin, include_cls)
+ * (dinov2_extractor.py:313-337) on the last vvs_forward_facet pass.  facet: 0 query, 1 key, 2 value.  desc_out
+ * [n_img, T + include_cls, (bin ? 9 : 1) * dim] fp32, channels in the reference's order (head-dim major, head minor:
+ * `permute(0, 2, 3, 1).flatten(-2)`); values carry the bf16 rounding of the projection's output. */
+VVS_API int vvs_facet_descriptors(vvs_handle h, int32_t n_img, int32_t facet, int32_t bin, int32_t include_cls,
+                          float* desc_out, vvs_stream stream);
+
 typedef struct vvs_match_out { /* every pointer optional (NULL = not wanted), device memory */
   int32_t* nn1;          /* [n_pairs, T]   argmax_j S[i,j]         (vitvs_v2.py:80) */
   int32_t* nn2;          /* [n_pairs, T]   argmax_i S[i,j]         (vitvs_v2.py:81) */

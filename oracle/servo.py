@@ -80,6 +80,34 @@ def extract_descriptors(model, batch: torch.Tensor, layer: int = 11, bin: bool =
     return x.unsqueeze(1)
 
 
+@torch.no_grad()
+def extract_facet_descriptors(model, batch: torch.Tensor, layer: int = 11, facet: str = "key", bin: bool = False,
+                              include_cls: bool = False) -> torch.Tensor:
+    """dinov2_extractor.py:203-218 + :313-337 for facet in {'key','query','value'}: the hook on
+    ``blocks[layer].attn`` recomputes ``qkv(input)`` of that block's attention input (= norm1 of the residual
+    stream entering the block), takes q / k / v as [B, h, t, d], drops CLS unless asked to keep it, and flattens
+    to channel order (d major, h minor) - ``permute(0, 2, 3, 1).flatten(-2)`` - before the optional 3x3 binning.
+    -> [B, 1, t, d'] (PINNED: tests/test_oracle_vs_reference.py runs the reference's ViTExtractor against it)."""
+    idx = {"query": 0, "key": 1, "value": 2}[facet]
+    x = model.prepare_tokens(batch)
+    for blk in model.blocks[:layer]:
+        x = blk(x)
+    blk = model.blocks[layer]
+    inp = blk.norm1(x)
+    B, N, C = inp.shape
+    h = blk.attn.num_heads
+    qkv = blk.attn.qkv(inp).reshape(B, N, 3, h, C // h).permute(2, 0, 3, 1, 4)[idx]     # [B, h, t, d]
+    if not include_cls:
+        qkv = qkv[:, :, 1:, :]
+    else:
+        assert not bin
+    flat = qkv.permute(0, 2, 3, 1).flatten(start_dim=-2, end_dim=-1)                     # [B, t, d*h]
+    if bin:
+        hp, wp = batch.shape[2] // 14, batch.shape[3] // 14
+        flat = log_bin(flat, (hp, wp))
+    return flat.unsqueeze(1)
+
+
 # --------------------------------------------------------------------------- a9
 def cosine_similarity_matrix(desc1: torch.Tensor, desc2: torch.Tensor) -> torch.Tensor:
     """vitvs_v2.py:49-56 (chunk_cosine_sim): S[i,j] = cos(desc1[i], desc2[j]), eps 1e-8.

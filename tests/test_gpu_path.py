@@ -325,3 +325,37 @@ def test_plugin_surface(eng, vits):
     assert np.array_equal(Z, servo.get_depth(s_uv, s.latest_image_depth))
     s_xy, s_star = s.transform_to_real_world(s_uv, s_uv_star)
     assert np.allclose(s_xy, servo.to_normalised(s_uv), rtol=1e-15)
+
+
+# ------------------------------------------------------------------------------ N4: key / query / value facets
+def test_facet_descriptors_vs_oracle(eng, vits):
+    """dinov2_extractor.py:203-218, 313-337 for facet in {key, query, value}: the projection's output carries bf16
+    rounding (cosine >= 0.999 per descriptor, as for tokens); the channel permutation (head-dim major, head minor),
+    CLS handling and 3x3 binning are gathers and must land every value in the reference's slot."""
+    from vitvs_b200 import plugin
+    pairs = [synth.frame_pair(i) for i in range(2)]
+    imgs = np.stack([pairs[0][0], pairs[1][1]])
+    pre = torch.cat([servo.preprocess_u8(im) for im in imgs])
+    for layer in (11, 4):
+        eng.forward_facet(torch.from_numpy(imgs).cuda(), layer)
+        for facet in ("key", "query", "value"):
+            for bin_, cls_ in ((False, False), (True, False), (False, True)):
+                d = eng.facet_descriptors(facet, bin_, cls_).cpu()
+                ref = servo.extract_facet_descriptors(vits, pre, layer, facet, bin_, cls_)
+                assert d.shape == ref.shape, (facet, bin_, cls_)
+                cos = torch.nn.functional.cosine_similarity(d, ref, dim=-1)
+                assert cos.min() >= 0.999, (facet, bin_, cls_, cos.min())
+                # slot check: per-channel error small against the channel's own scale (a permutation bug shuffles them)
+                err = (d - ref).abs().max().item()
+                assert err <= 0.02 * ref.abs().max().item() + 1e-3, (facet, bin_, cls_, err)
+    from vitvs_b200 import VvsError
+    with pytest.raises(VvsError):
+        eng.tokens_out()                      # the residual stream is not blocks[layer]'s after a facet pass
+    # the extractor surface routes every facet
+    ex = plugin.B200ViTExtractor.__new__(plugin.B200ViTExtractor)
+    ex.engine, ex.p, ex.stride = eng, 14, (14, 14)
+    k = ex.extract_descriptors(pre.cuda(), layer=11, facet="key", bin=True)
+    assert k.shape == (2, 1, 484, 9 * 384) and ex.num_patches == (22, 22)
+    t = ex.extract_descriptors(pre.cuda(), layer=11, facet="token", include_cls=True)
+    assert t.shape == (2, 1, 485, 384)
+    assert torch.equal(t[:, 0, 1:], ex.extract_descriptors(pre.cuda(), layer=11, facet="token")[:, 0])

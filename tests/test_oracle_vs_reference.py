@@ -123,3 +123,16 @@ def test_experiment_sampling_equals_reference():
     for ang in (90, 180, 270):
         ref_pose = episode.to_camera_pose(pos_r[3], R.from_quat(V.rotate_camera_x_axis(q0, ang)).as_matrix())
         assert np.allclose(episode.rotate_about_optical_axis(poses[3], ang), ref_pose, atol=1e-12)
+
+
+def test_facet_descriptors_bit_equal(vits):
+    """key / query / value facets (dinov2_extractor.py:203-218), with and without binning / CLS."""
+    ex = ref_loader.make_extractor(vits, "dinov2_vits14")
+    batch = torch.randn(2, 3, 70, 98, generator=torch.Generator().manual_seed(2))     # 5 x 7 patches
+    with torch.no_grad(), warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        for facet in ("key", "query", "value"):
+            for bin_, cls_ in ((False, False), (True, False), (False, True)):
+                ref = ex.extract_descriptors(batch, layer=9, facet=facet, bin=bin_, include_cls=cls_)
+                mine = servo.extract_facet_descriptors(vits, batch, 9, facet, bin_, cls_)
+                assert torch.equal(ref, mine), (facet, bin_, cls_)

@@ -52,6 +52,8 @@ SYMBOLS = {
     "vvs_weights_ready": (c_i32, [c_vp]),
     "vvs_forward_tokens": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp]),
     "vvs_get_tokens": (c_i32, [c_vp, c_vp, c_i32, c_vp]),
+    "vvs_forward_facet": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp]),
+    "vvs_facet_descriptors": (c_i32, [c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp]),
     "vvs_descriptors": (c_i32, [c_vp, c_i32, c_i32, c_vp, c_vp]),
     "vvs_match": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, C.POINTER(MatchOut), c_vp]),
     "vvs_similarity": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp]),

@@ -127,6 +127,7 @@ struct vvs_ctx {
   uint8_t* stage_frames = nullptr; // [max_images, H, W, 3] raw frames (also the H2D landing zone of the host entries)
   uint8_t* rz_tmp = nullptr;       // [max_images, H, S, 3] output of the horizontal pass
   int last_n_img = 0;
+  int facet_n_img = 0;       // images whose qkv(norm1(x)) of the requested block sits in `big` (vvs_forward_facet)
   int launch_count = 0;
   // optional per-kernel-class CUDA-event profiler (vvs_profile_*)
   bool prof_on = false;
@@ -240,7 +241,8 @@ GemmArgs plain_gemm(const bf16* A, const bf16* B, int M, int N, int K, int epi) 
   return g;
 }
 
-int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int layer, cudaStream_t s) {
+int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int layer, cudaStream_t s,
+                   bool stop_after_qkv = false) {
   const vvs_config& f = c->cfg;
   if (n_img < 1 || n_img > f.max_images) return fail(c, VVS_ERR_INVALID, "n_img outside [1, max_images]");
   if (layer < 0 || layer >= f.depth) return fail(c, VVS_ERR_INVALID, "layer outside [0, depth)");
@@ -282,7 +284,15 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
       GemmArgs g = plain_gemm(c->h, w.qkv_w, M, 3 * D, D, EPI_BIAS_BF16);
       g.bias = w.qkv_b; g.out_bf16 = c->big; g.ldo = 3 * D; g.q_cols = D; g.q_scale = 0.125f;   // hd^-0.5, hd = 64
       g.pdl = pdl;
+      const bool facet_stop = stop_after_qkv && i == layer;   // key / query / value facet: the hook sees raw qkv(norm1(x))
+      if (facet_stop) g.q_scale = 1.0f;
       if ((rc = gemm(c, g, s, VVS_K_QKV_GEMM))) return rc;
+      if (facet_stop) {
+        ++c->launch_count;
+        c->last_n_img = 0;            // the residual stream is NOT that of blocks[layer]: token getters must refuse
+        c->facet_n_img = n_img;
+        return VVS_OK;
+      }
     }
     { ProfScope ps(c, VVS_K_ATTENTION, s);
       rc = launch_attention(c->big, c->h, n_img, N, f.heads, s, &c->err, pdl); }
@@ -308,6 +318,7 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
     c->launch_count += 3;   // 2 LayerNorms + attention
   }
   c->last_n_img = n_img;
+  c->facet_n_img = 0;
   return VVS_OK;
 }
 
@@ -904,6 +915,25 @@ int vvs_forward_tokens(vvs_handle c, const void* images, int32_t kind, int32_t n
   if (!c || !images) return fail(c, VVS_ERR_INVALID, "vvs_forward_tokens: null argument");
   c->launch_count = 0;
   return forward_tokens(c, images, kind, n_img, layer, static_cast<cudaStream_t>(stream));
+}
+
+int vvs_forward_facet(vvs_handle c, const void* images, int32_t kind, int32_t n_img, int32_t layer, vvs_stream stream) {
+  if (!c || !images) return fail(c, VVS_ERR_INVALID, "vvs_forward_facet: null argument");
+  c->launch_count = 0;
+  return forward_tokens(c, images, kind, n_img, layer, static_cast<cudaStream_t>(stream), /*stop_after_qkv=*/true);
+}
+
+int vvs_facet_descriptors(vvs_handle c, int32_t n_img, int32_t facet, int32_t bin, int32_t include_cls, float* out,
+                          vvs_stream stream) {
+  if (!c || !out) return fail(c, VVS_ERR_INVALID, "vvs_facet_descriptors: null argument");
+  if (facet < 0 || facet > 2) return fail(c, VVS_ERR_INVALID, "vvs_facet_descriptors: facet must be 0 (query), 1 (key) or 2 (value)");
+  if (bin && include_cls)
+    return fail(c, VVS_ERR_INVALID, "bin = True and include_cls = True are not supported together");   // dinov2_extractor.py:332
+  if (n_img < 1 || n_img > c->facet_n_img)
+    return fail(c, VVS_ERR_STATE, "vvs_facet_descriptors: no vvs_forward_facet pass holds that many images");
+  ++c->launch_count;
+  return launch_facet_descriptors_f32(c->big, out, n_img, c->grid, c->grid, c->cfg.dim, c->cfg.heads, facet, bin,
+                                      include_cls, static_cast<cudaStream_t>(stream), &c->err);
 }
 
 int vvs_get_tokens(vvs_handle c, float* out, int32_t n_img, vvs_stream stream) {

@@ -157,6 +157,38 @@ __global__ void descriptors_f32_kernel(const float* __restrict__ x, float* __res
   }
 }
 
+// facet descriptors (dinov2_extractor.py:203-218, 326-336): q / k / v of the block's attention input as
+// [B, h, t, d] -> permute(0, 2, 3, 1).flatten(-2): channel c = dd * heads + hh reads qkv column facet*D + hh*64 + dd.
+// Thread = one output channel of one (image, token, part): writes coalesced, reads gather from an L2-resident row.
+__global__ void facet_descriptors_f32_kernel(const bf16* __restrict__ qkv, float* __restrict__ out, int n_img, int hp,
+                                             int wp, int D, int heads, int facet, int parts, int include_cls) {
+  const int T = hp * wp;
+  const int rows_out = T + (include_cls ? 1 : 0);
+  const long long total = static_cast<long long>(n_img) * rows_out * parts * D;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>(idx % D);
+    long long r = idx / D;
+    const int part = static_cast<int>(r % parts);
+    r /= parts;
+    const int t = static_cast<int>(r % rows_out);
+    const int img = static_cast<int>(r / rows_out);
+    int src_tok;                                         // row inside the image's 1+T tokens
+    if (include_cls) {
+      src_tok = t;
+    } else {
+      int sy = t / wp, sx = t - sy * wp;
+      if (parts == 9) {
+        sy = clampi(sy + part / 3 - 1, 0, hp - 1);
+        sx = clampi(sx + part % 3 - 1, 0, wp - 1);
+      }
+      src_tok = 1 + sy * wp + sx;
+    }
+    const int dd = c / heads, hh = c - dd * heads;
+    out[idx] = __bfloat162float(qkv[(static_cast<size_t>(img) * (T + 1) + src_tok) * (3 * D) + facet * D + hh * 64 + dd]);
+  }
+}
+
 // squared L2 norm of every patch token (CLS skipped): one warp per token.
 __global__ void token_sqnorm_kernel(const float* __restrict__ x, float* __restrict__ n2, int n_img, int T, int D) {
   const int lane = threadIdx.x & 31;
@@ -277,6 +309,16 @@ int launch_descriptors_f32(const float* x, float* out, int n_img, int hp, int wp
   const int parts = bin ? 9 : 1;
   const long long items = static_cast<long long>(n_img) * hp * wp * parts * (D / 4);
   descriptors_f32_kernel<<<grid_for(items, 256), 256, 0, s>>>(x, out, n_img, hp, wp, D, parts);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_facet_descriptors_f32(const bf16* qkv, float* out, int n_img, int hp, int wp, int D, int heads, int facet,
+                                 int bin, int include_cls, cudaStream_t s, std::string* err) {
+  const int parts = bin ? 9 : 1;
+  const long long items = static_cast<long long>(n_img) * (hp * wp + (include_cls ? 1 : 0)) * parts * D;
+  facet_descriptors_f32_kernel<<<grid_for(items, 256), 256, 0, s>>>(qkv, out, n_img, hp, wp, D, heads, facet, parts,
+                                                                     include_cls);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }

@@ -58,7 +58,8 @@ class Engine:
         if self.cfg.stride != PATCH:
             raise NotImplementedError("only stride == patch size (14) is on the hot path (SURVEY §8f N4)")
         if self.cfg.facet != "token":
-            raise NotImplementedError("only facet 'token' is on the hot path (SURVEY §8f N4)")
+            raise NotImplementedError("the servo path matches 'token' descriptors (vitvs_v2.py:485); key / query / "
+                                      "value facets are served by forward_facet / facet_descriptors")
         dim, heads, depth, hidden, swiglu = ARCHS[self.cfg.model_type]
         self.dim, self.heads, self.depth, self.hidden, self.swiglu = dim, heads, depth, hidden, swiglu
         self.grid = self.cfg.dino_input_size // PATCH
@@ -142,6 +143,34 @@ class Engine:
         self._check(self.lib.vvs_forward_tokens(self._h, _ptr(images), kind, images.shape[0], layer,
                                                 _stream(self.device)), "vvs_forward_tokens")
         self._n_img = images.shape[0]
+
+    def forward_facet(self, images: torch.Tensor, layer: int | None = None) -> None:
+        """blocks[0..layer-1] + norm1 + qkv of blocks[layer]: what the key / query / value hooks see
+        (dinov2_extractor.py:203-218).  images as in forward_tokens."""
+        layer = min(self.cfg.layer, self.depth - 1) if layer is None else layer
+        S = self.cfg.dino_input_size
+        if images.dtype == torch.uint8:
+            assert images.shape[1:] == (S, S, 3), images.shape
+            kind = _lib.IMAGE_U8_HWC
+        elif images.dtype == torch.float32:
+            assert images.shape[1:] == (3, S, S), images.shape
+            kind = _lib.IMAGE_F32_NCHW
+        else:
+            raise TypeError("images must be uint8 HWC or float32 NCHW")
+        images = images.contiguous()
+        self._check(self.lib.vvs_forward_facet(self._h, _ptr(images), kind, images.shape[0], layer,
+                                               _stream(self.device)), "vvs_forward_facet")
+        self._n_facet = images.shape[0]
+
+    def facet_descriptors(self, facet: str, bin: bool = False, include_cls: bool = False) -> torch.Tensor:
+        """[n, 1, T (+1), d'] fp32 descriptors of the last forward_facet pass; facet in {'query','key','value'}."""
+        idx = {"query": 0, "key": 1, "value": 2}[facet]
+        n = self._n_facet
+        out = torch.empty(n, 1, self.tokens + int(include_cls), self.dim * (9 if bin else 1), device=self.device,
+                          dtype=torch.float32)
+        self._check(self.lib.vvs_facet_descriptors(self._h, n, idx, int(bin), int(include_cls), _ptr(out),
+                                                   _stream(self.device)), "vvs_facet_descriptors")
+        return out
 
     def tokens_out(self) -> torch.Tensor:
         out = torch.empty(self._n_img, self.tokens + 1, self.dim, device=self.device, dtype=torch.float32)

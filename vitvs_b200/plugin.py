@@ -65,19 +65,21 @@ class B200ViTExtractor:
                             include_cls: bool = False) -> torch.Tensor:
         """dinov2_extractor.py:313-337.  batch: [B,3,H,W] fp32 (or uint8 [B,H,W,3]) -> [B,1,T,d'] fp32 (cuda)."""
         assert facet in ["key", "query", "value", "token"], f"{facet} is not a supported facet for descriptors."
-        if facet != "token":
-            raise NotImplementedError("facet != 'token' is outside the dino hot path (SURVEY §8f N4)")
         if include_cls:
             assert not bin, "bin = True and include_cls = True are not supported together, set one of them False."
-            raise NotImplementedError("include_cls=True is outside the dino hot path")
         batch = batch.to(self.engine.device)
-        self.engine.forward_tokens(batch, layer)
         if batch.dtype == torch.uint8:
             H, W = batch.shape[1:3]
         else:
             H, W = batch.shape[2:4]
         self.load_size = (H, W)                                                        # dinov2_extractor.py:261
         self.num_patches = (1 + (H - self.p) // self.stride[0], 1 + (W - self.p) // self.stride[1])  # :262
+        if facet != "token":                                                           # :203-218 (SURVEY N4)
+            self.engine.forward_facet(batch, layer)
+            return self.engine.facet_descriptors(facet, bin, include_cls)
+        self.engine.forward_tokens(batch, layer)
+        if include_cls:
+            return self.engine.tokens_out().unsqueeze(1)                               # :328-334 with the CLS row kept
         return self.engine.descriptors(bin)
 
 
