@@ -55,7 +55,7 @@ typedef struct vvs_config {
   int32_t ffn_hidden;   /* 4*dim, or 4096 for the SwiGLU giant */
   int32_t swiglu;       /* 0 = Mlp(GELU), 1 = SwiGLUFFNFused */
   /* geometry */
-  int32_t image_size;   /* dino_input_size (308) - square ViT input, multiple of 14 */
+  int32_t image_size;   /* dino_input_size (308) - square ViT input; image_size - 14 a multiple of patch_stride */
   int32_t max_images;   /* workspace sizing: images in flight (= 2 x frame pairs per call) */
   /* camera / control (config.yaml) */
   int32_t frame_width;  /* u_max 640 */
@@ -70,6 +70,9 @@ typedef struct vvs_config {
   float same_image_threshold;  /* 0.99 (vitvs_v2.py:84) */
   int32_t max_match_tokens;    /* workspace for vvs_match on caller descriptors (0 => tokens of image_size) */
   int32_t max_match_dim;       /* (0 => 9*dim) */
+  int32_t patch_stride;        /* ViTExtractor stride (dinov2_extractor.py:25,123-144): 14 = non-overlapping patches
+                                  (vitvs_v2.py:250), a divisor of 14 = overlapping patches, 1 + (S-14)/stride tokens
+                                  per side; 0 => 14 */
 } vvs_config;
 
 /* replaces: Controller.__init__ -> ViTExtractor(...) model construction (vitvs_v2.py:249-250,

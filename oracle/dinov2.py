@@ -219,6 +219,43 @@ def build(model_type: str = "dinov2_vits14", seed: int = 0, rich: bool = True, m
     return m.eval()
 
 
+def with_stride(model: "DinoV2", stride: int) -> "DinoV2":
+    """ViTExtractor.patch_vit_resolution + _fix_pos_enc (dinov2_extractor.py:85-144) restated on a COPY of the model:
+    the patch-embedding convolution runs at ``stride`` (a divisor of 14: overlapping patches) and the positional
+    encoding is interpolated to the 1 + (S - 14) // stride grid with the same bicubic call (+0.1 offset).
+    PINNED: tests/test_oracle_vs_reference.py lets the reference's own ViTExtractor patch a copy and compares."""
+    import copy
+    import types
+    m = copy.deepcopy(model)
+    if stride == PATCH:
+        return m
+    assert (PATCH // stride) * stride == PATCH, f"stride {stride} should divide patch_size {PATCH}"
+    m.patch_embed.proj.stride = (stride, stride)
+
+    def interpolate_pos_encoding(self, x, w, h):
+        npatch = x.shape[1] - 1
+        N = self.pos_embed.shape[1] - 1
+        if npatch == N and w == h:
+            return self.pos_embed
+        class_pos_embed = self.pos_embed[:, 0]
+        patch_pos_embed = self.pos_embed[:, 1:]
+        dim = x.shape[-1]
+        w0 = 1 + (w - PATCH) // stride
+        h0 = 1 + (h - PATCH) // stride
+        assert w0 * h0 == npatch
+        w0, h0 = w0 + 0.1, h0 + 0.1
+        M = int(math.sqrt(N))
+        patch_pos_embed = F.interpolate(patch_pos_embed.reshape(1, M, M, dim).permute(0, 3, 1, 2),
+                                        scale_factor=(w0 / math.sqrt(N), h0 / math.sqrt(N)), mode="bicubic",
+                                        align_corners=False, recompute_scale_factor=False)
+        assert int(w0) == patch_pos_embed.shape[-2] and int(h0) == patch_pos_embed.shape[-1]
+        patch_pos_embed = patch_pos_embed.permute(0, 2, 3, 1).reshape(1, -1, dim)
+        return torch.cat((class_pos_embed.unsqueeze(0), patch_pos_embed), dim=1)
+
+    m.interpolate_pos_encoding = types.MethodType(interpolate_pos_encoding, m)
+    return m
+
+
 def flops_per_image(arch: Arch, tokens: int, layer: int) -> float:
     """2*588*D*T + (layer+1)*(24*N*D^2 + 4*N^2*D), N = T+1."""
     n = tokens + 1

@@ -359,3 +359,51 @@ def test_facet_descriptors_vs_oracle(eng, vits):
     t = ex.extract_descriptors(pre.cuda(), layer=11, facet="token", include_cls=True)
     assert t.shape == (2, 1, 485, 384)
     assert torch.equal(t[:, 0, 1:], ex.extract_descriptors(pre.cuda(), layer=11, facet="token")[:, 0])
+
+
+# ------------------------------------------------------------------------------ N4: stride < patch size
+def test_overlapping_patches_stride7(vits):
+    """dinov2_extractor.py:123-144: stride 7 => 1 + (S - 14) / 7 tokens per side, overlapping 14x14 patches, position
+    encoding interpolated to that grid.  Tokens against the oracle's stride-patched model (itself pinned against the
+    reference's own patching), descriptors as gathers of the tokens, and the fused path end to end."""
+    from vitvs_b200 import Engine, ServoConfig
+    S, stride = 112, 7
+    grid = 1 + (S - 14) // stride
+    e = Engine(ServoConfig(model_type="dinov2_vits14", stride=stride, dino_input_size=S), max_images=4)
+    e.load_weights(vits)
+    assert e.grid == grid and e.tokens == grid * grid
+    pairs = [synth.frame_pair(i, S) for i in range(2)]
+    imgs = np.stack([pairs[0][0], pairs[0][1], pairs[1][0], pairs[1][1]])
+    e.forward_tokens(torch.from_numpy(imgs).cuda())
+    tok = e.tokens_out().cpu()
+    m7 = dinov2.with_stride(vits, stride)
+    ref = torch.cat([servo.block_tokens(m7, servo.preprocess_u8(im), 11) for im in imgs])
+    assert tok.shape == ref.shape == (4, 1 + grid * grid, 384)
+    cos = torch.nn.functional.cosine_similarity(tok, ref, dim=-1)
+    print(f"[stride 7] tokens cosine min {cos.min():.6f}")
+    assert cos.min() >= 0.999
+    d = e.descriptors(True).cpu()
+    assert torch.equal(d[:, 0], servo.log_bin(tok[:, 1:], (grid, grid)))
+    out = e.frame_pairs_to_twist(torch.from_numpy(imgs[0::2].copy()).cuda(), torch.from_numpy(imgs[1::2].copy()).cuda(),
+                                 torch.from_numpy(np.stack([p[2] for p in pairs])).cuda(), want_match=True)
+    # matching against the oracle on the oracle's own tokens of the stride-7 model
+    for i in range(2):
+        d1 = servo.log_bin(ref[2 * i:2 * i + 1, 1:], (grid, grid)).unsqueeze(1)
+        d2 = servo.log_bin(ref[2 * i + 1:2 * i + 2, 1:], (grid, grid)).unsqueeze(1)
+        m = servo.match(servo.cosine_similarity_matrix(d1, d2)[0, 0])
+        agree = (out["nn1"][i].cpu().numpy() == m.nn1).mean()
+        print(f"[stride 7] pair {i} nn1 agreement {agree:.4f}")
+        assert agree >= 0.98
+    assert torch.isfinite(out["twist"]).all()
+    e.close()
+    with pytest.raises(ValueError):
+        Engine(ServoConfig(model_type="dinov2_vits14", stride=5), max_images=2)
+    # the default geometry at stride 7: 43 x 43 = 1849 tokens per image through the whole fused path
+    e = Engine(ServoConfig(model_type="dinov2_vits14", stride=7), max_images=2)
+    e.load_weights(vits)
+    g, c, dpt = synth.frame_pair(0)
+    out = e.frame_pairs_to_twist(torch.from_numpy(g[None]).cuda(), torch.from_numpy(c[None]).cuda(),
+                                 torch.from_numpy(dpt[None]).cuda(), want_match=True)
+    assert e.tokens == 1849 and out["nn1"].shape == (1, 1849) and torch.isfinite(out["twist"]).all()
+    assert int(out["n_selected"][0]) == 24
+    e.close()

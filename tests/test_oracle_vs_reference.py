@@ -136,3 +136,24 @@ def test_facet_descriptors_bit_equal(vits):
                 ref = ex.extract_descriptors(batch, layer=9, facet=facet, bin=bin_, include_cls=cls_)
                 mine = servo.extract_facet_descriptors(vits, batch, 9, facet, bin_, cls_)
                 assert torch.equal(ref, mine), (facet, bin_, cls_)
+
+
+def test_stride_patching_equals_reference(vits):
+    """stride < patch size (dinov2_extractor.py:85-144).  The reference's ViTExtractor patches a copy of
+    the oracle model itself (patch_vit_resolution + _fix_pos_enc); oracle.dinov2.with_stride must give the same tokens."""
+    import copy
+    batch = torch.randn(1, 3, 56, 56, generator=torch.Generator().manual_seed(4))
+    for stride in (7, 2):
+        ex = ref_loader.extractor().ViTExtractor(model_type="dinov2_vits14", stride=stride, model=copy.deepcopy(vits),
+                                                 device="cpu")
+        mine = dinov2.with_stride(vits, stride)
+        with torch.no_grad(), warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            ref = ex.extract_descriptors(batch, layer=3, facet="token", bin=False)
+            grid = 1 + (56 - 14) // stride
+            assert ex.num_patches == (grid, grid) and ref.shape == (1, 1, grid * grid, 384)
+            x = mine.prepare_tokens(batch)
+            for blk in mine.blocks[:4]:
+                x = blk(x)
+            assert torch.equal(ref[:, 0], x[:, 1:])
+    assert vits.patch_embed.proj.stride == (14, 14)          # the shared fixture was not patched

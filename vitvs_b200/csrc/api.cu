@@ -94,7 +94,7 @@ struct vvs_ctx {
   int device = 0;
   int num_sms = 148;
   std::string err;
-  int grid = 0, T = 0, N = 0;
+  int grid = 0, T = 0, N = 0, stride = 14;
   // embeddings
   bf16* pe_w = nullptr; float* pe_b = nullptr; float* cls = nullptr; float* pos = nullptr;
   unsigned emb_mask = 0;   // 4 bits
@@ -255,10 +255,12 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
   int rc;
   if (kind == VVS_IMAGE_U8_HWC)
   { ProfScope ps(c, VVS_K_IM2COL, s);
-    rc = launch_im2col_u8(static_cast<const uint8_t*>(images), c->big, n_img, f.image_size, kPatchKPad, s, &c->err); }
+    rc = launch_im2col_u8(static_cast<const uint8_t*>(images), c->big, n_img, f.image_size, kPatchKPad, c->grid, c->stride, s,
+                          &c->err); }
   else if (kind == VVS_IMAGE_F32_NCHW)
   { ProfScope ps(c, VVS_K_IM2COL, s);
-    rc = launch_im2col_f32(static_cast<const float*>(images), c->big, n_img, f.image_size, kPatchKPad, s, &c->err); }
+    rc = launch_im2col_f32(static_cast<const float*>(images), c->big, n_img, f.image_size, kPatchKPad, c->grid, c->stride, s,
+                           &c->err); }
   else
     return fail(c, VVS_ERR_INVALID, "unknown image_kind");
   if (rc) return rc;
@@ -707,16 +709,26 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
                 std::string("vvs_create: device '") + prop.name + "' is sm_" + std::to_string(prop.major) +
                     std::to_string(prop.minor) + "; the kernels are built for sm_100a only");
   if (cfg->dim % 128 || cfg->heads * 64 != cfg->dim || cfg->depth < 1 || cfg->ffn_hidden % 64 ||
-      cfg->image_size % kPatch || cfg->image_size < kPatch || cfg->max_images < 1 || cfg->num_pairs < 1 ||
+      cfg->image_size < kPatch || cfg->max_images < 1 || cfg->num_pairs < 1 ||
       cfg->num_pairs > 256 || cfg->layer < 0 || cfg->layer >= cfg->depth)
     return fail(nullptr, VVS_ERR_INVALID, "vvs_create: inconsistent vvs_config");
+  {
+    const int st = cfg->patch_stride > 0 ? cfg->patch_stride : kPatch;
+    if (kPatch % st != 0 || (cfg->image_size - kPatch) % st != 0)
+      return fail(nullptr, VVS_ERR_INVALID,
+                  "vvs_create: patch_stride must divide the patch size 14 (dinov2_extractor.py:136-137) and "
+                  "image_size - 14 must be a multiple of it");
+  }
   if (cfg->dim != 384 && cfg->dim != 768 && cfg->dim != 1024 && cfg->dim != 1536)
     return fail(nullptr, VVS_ERR_INVALID, "vvs_create: dim must be 384/768/1024/1536 (dinov2_vit{s,b,l,g}14)");
   vvs_ctx* c = new vvs_ctx();
   c->cfg = *cfg;
   c->device = dev;
   c->num_sms = prop.multiProcessorCount;
-  c->grid = cfg->image_size / kPatch;
+  // patch stride: 14 (non-overlapping) or a divisor of it (overlapping patches, dinov2_extractor.py:123-144);
+  // tokens per side = 1 + (S - 14) / stride (:262)
+  c->stride = cfg->patch_stride > 0 ? cfg->patch_stride : kPatch;
+  c->grid = 1 + (cfg->image_size - kPatch) / c->stride;
   c->T = c->grid * c->grid;
   c->N = c->T + 1;
   c->blocks.resize(cfg->depth);

@@ -34,7 +34,8 @@ __device__ __forceinline__ float normalize_px(uint8_t v, int c) {
 // A_pe[img*T + t][k], k = c*196 + ky*14 + kx (Conv2d weight [D,3,14,14] flattened), zero padded to kpad.
 // One thread = 8 consecutive k of one patch row -> one 16-byte store.
 template <bool kU8>
-__global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ out, int n_img, int S, int kpad) {
+__global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ out, int n_img, int S, int kpad, int gp,
+                              int stride) {
   // u8 input: the 3 x 256 possible outputs of ToTensor + Normalize, evaluated once per block with the exact
   // arithmetic above (two IEEE divisions each) - the per-element work is then a table lookup
   __shared__ float lut[3][256];
@@ -42,8 +43,7 @@ __global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ 
     for (int i = threadIdx.x; i < 768; i += blockDim.x) lut[i >> 8][i & 255] = normalize_px(static_cast<uint8_t>(i & 255), i >> 8);
     __syncthreads();
   }
-  const int gp = S / kPatch;
-  const int T = gp * gp;
+  const int T = gp * gp;                      // gp = 1 + (S - 14) / stride patches per side (dinov2_extractor.py:262)
   const int k8_per_row = kpad / 8;
   const long long total = static_cast<long long>(n_img) * T * k8_per_row;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
@@ -61,7 +61,7 @@ __global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ 
         const int c = k / (kPatch * kPatch);
         const int rem = k - c * kPatch * kPatch;
         const int ky = rem / kPatch, kx = rem - ky * kPatch;
-        const int y = py * kPatch + ky, x = px * kPatch + kx;
+        const int y = py * stride + ky, x = px * stride + kx;   // stride < 14: overlapping patches (:123-144)
         if (kU8) {
           const uint8_t* img8 = static_cast<const uint8_t*>(img_);
           v[e] = lut[c][img8[((static_cast<size_t>(img) * S + y) * S + x) * 3 + c]];
@@ -268,16 +268,18 @@ int grid_for(long long work_items, int block) {
 
 }  // namespace
 
-int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err) {
-  const long long items = static_cast<long long>(n_img) * (size / kPatch) * (size / kPatch) * (kpad / 8);
-  im2col_kernel<true><<<grid_for(items, 256), 256, 0, s>>>(img, out, n_img, size, kpad);
+int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpad, int grid, int stride, cudaStream_t s,
+                     std::string* err) {
+  const long long items = static_cast<long long>(n_img) * grid * grid * (kpad / 8);
+  im2col_kernel<true><<<grid_for(items, 256), 256, 0, s>>>(img, out, n_img, size, kpad, grid, stride);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }
 
-int launch_im2col_f32(const float* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err) {
-  const long long items = static_cast<long long>(n_img) * (size / kPatch) * (size / kPatch) * (kpad / 8);
-  im2col_kernel<false><<<grid_for(items, 256), 256, 0, s>>>(img, out, n_img, size, kpad);
+int launch_im2col_f32(const float* img, bf16* out, int n_img, int size, int kpad, int grid, int stride, cudaStream_t s,
+                      std::string* err) {
+  const long long items = static_cast<long long>(n_img) * grid * grid * (kpad / 8);
+  im2col_kernel<false><<<grid_for(items, 256), 256, 0, s>>>(img, out, n_img, size, kpad, grid, stride);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }

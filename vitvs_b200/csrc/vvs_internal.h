@@ -116,8 +116,10 @@ int launch_resize_v(const uint8_t* in, uint8_t* out, int n_img, int row_bytes, c
                     std::string* err);
 
 // ---- bandwidth-bound kernels -------------------------------------------------------------------
-int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err);
-int launch_im2col_f32(const float* img, bf16* out, int n_img, int size, int kpad, cudaStream_t s, std::string* err);
+int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpad, int grid, int stride, cudaStream_t s,
+                     std::string* err);
+int launch_im2col_f32(const float* img, bf16* out, int n_img, int size, int kpad, int grid, int stride, cudaStream_t s,
+                      std::string* err);
 int launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int n_tok, int D, cudaStream_t s,
                     std::string* err);
 int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, int rows, int D, float eps,

@@ -55,14 +55,15 @@ class Engine:
                                    (device if isinstance(device, int) else torch.device(device).index or 0))
         if self.cfg.model_type not in ARCHS:
             raise ValueError(f"unknown model_type {self.cfg.model_type}")
-        if self.cfg.stride != PATCH:
-            raise NotImplementedError("only stride == patch size (14) is on the hot path (SURVEY §8f N4)")
+        if PATCH % self.cfg.stride != 0 or (self.cfg.dino_input_size - PATCH) % self.cfg.stride != 0:
+            raise ValueError(f"stride {self.cfg.stride} should divide patch_size {PATCH} (dinov2_extractor.py:136-137) "
+                             f"and dino_input_size - {PATCH}")
         if self.cfg.facet != "token":
             raise NotImplementedError("the servo path matches 'token' descriptors (vitvs_v2.py:485); key / query / "
                                       "value facets are served by forward_facet / facet_descriptors")
         dim, heads, depth, hidden, swiglu = ARCHS[self.cfg.model_type]
         self.dim, self.heads, self.depth, self.hidden, self.swiglu = dim, heads, depth, hidden, swiglu
-        self.grid = self.cfg.dino_input_size // PATCH
+        self.grid = 1 + (self.cfg.dino_input_size - PATCH) // self.cfg.stride      # dinov2_extractor.py:262
         self.tokens = self.grid * self.grid
         self.max_images = max_images
         c = _lib.Config(
@@ -74,7 +75,7 @@ class Engine:
             num_pairs=self.cfg.num_pairs, layer=min(self.cfg.layer, depth - 1),
             use_feature_binning=int(self.cfg.use_feature_binning),
             same_image_threshold=self.cfg.same_image_threshold,
-            max_match_tokens=max_match_tokens, max_match_dim=max_match_dim)
+            max_match_tokens=max_match_tokens, max_match_dim=max_match_dim, patch_stride=self.cfg.stride)
         self._h = C.c_void_p()
         with torch.cuda.device(self.device):
             rc = self.lib.vvs_create(C.byref(c), C.byref(self._h))
