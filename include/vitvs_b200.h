@@ -105,6 +105,11 @@ VVS_API int vvs_get_tokens(vvs_handle h, float* tokens_out, int32_t n_img, vvs_s
  * desc_out [n_img, T, (bin ? 9 : 1) * dim] fp32. */
 VVS_API int vvs_descriptors(vvs_handle h, int32_t n_img, int32_t bin, float* desc_out, vvs_stream stream);
 
+/* replaces: ViTExtractor._log_bin(x, hierarchy) (dinov2_extractor.py:265-311) for hierarchy >= 1 on the tokens of the
+ * last vvs_forward_tokens call: level k = the 3x3 neighbourhood at distance 3^k of the 3^k x 3^k average-pooled token
+ * map (in-grid elements only), centre kept at k = 0 only, borders replicate-clamped.  desc_out
+ * [n_img, T, (1 + 8 * hierarchy) * dim] fp32; hierarchy 1 equals vvs_descriptors(bin = 1). */
+VVS_API int vvs_descriptors_hierarchy(vvs_handle h, int32_t n_img, int32_t hierarchy, float* desc_out, vvs_stream stream);
 /* replaces: ViTExtractor._extract_features with facet 'query' / 'key' / 'value' (dinov2_extractor.py:203-218): runs
  * blocks[0..layer-1], then norm1 and the fused qkv projection of blocks[layer] - the tensor the reference's hook on
  * `blocks[layer].attn` recomputes - and stops.  Invalidates vvs_get_tokens / vvs_descriptors until the next

@@ -70,6 +70,29 @@ def log_bin(tokens_no_cls: torch.Tensor, grid: tuple[int, int]) -> torch.Tensor:
     return torch.cat(parts, dim=-1).reshape(B, T, 9 * D)
 
 
+def log_bin_hierarchy(tokens_no_cls: torch.Tensor, grid: tuple[int, int], hierarchy: int) -> torch.Tensor:
+    """dinov2_extractor.py:265-311 for any ``hierarchy``: level k holds the 3x3 neighbourhood at
+    distance 3^k of the 3^k x 3^k average-pooled map (AvgPool2d stride 1, padding 3^k // 2, count_include_pad=False),
+    centre skipped for k > 0, out-of-grid neighbours replicate-clamped.  [B,T,D] -> [B,T,(1+8h)D], level-major then
+    (dy,dx) row-major.  PINNED against the reference's own _log_bin (tests/test_oracle_vs_reference.py)."""
+    B, T, D = tokens_no_cls.shape
+    hp, wp = grid
+    g = tokens_no_cls.reshape(B, hp, wp, D).permute(0, 3, 1, 2)                     # B D hp wp
+    parts = []
+    for k in range(hierarchy):
+        win = 3 ** k
+        pooled = torch.nn.AvgPool2d(win, stride=1, padding=win // 2, count_include_pad=False)(g)
+        for dy in (-win, 0, win):
+            for dx in (-win, 0, win):
+                if dy == 0 and dx == 0 and k != 0:
+                    continue
+                yy = (torch.arange(hp) + dy).clamp(0, hp - 1)
+                xx = (torch.arange(wp) + dx).clamp(0, wp - 1)
+                parts.append(pooled[:, :, yy][:, :, :, xx])
+    out = torch.cat(parts, dim=1)                                                    # B (bins*D) hp wp
+    return out.flatten(start_dim=-2).permute(0, 2, 1)
+
+
 @torch.no_grad()
 def extract_descriptors(model, batch: torch.Tensor, layer: int = 11, bin: bool = True) -> torch.Tensor:
     """dinov2_extractor.py:313-337 for facet='token', include_cls=False. -> [B,1,T,d']."""

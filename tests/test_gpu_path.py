@@ -407,3 +407,19 @@ def test_overlapping_patches_stride7(vits):
     assert e.tokens == 1849 and out["nn1"].shape == (1, 1849) and torch.isfinite(out["twist"]).all()
     assert int(out["n_selected"][0]) == 24
     e.close()
+
+
+# ------------------------------------------------------------------------------ N4: hierarchy > 1 log-binning
+def test_log_bin_hierarchy_vs_oracle(eng):
+    """dinov2_extractor.py:265-311 with hierarchy 1..3 on the GPU's own tokens: level 0 is a pure gather (bit-exact),
+    deeper levels average up to 9 / 81 tokens in fp32 (summation order differs from AvgPool2d: 1e-5 relative)."""
+    g, c, _ = synth.frame_pair(5)
+    eng.forward_tokens(torch.from_numpy(np.stack([g, c])).cuda())
+    tok = eng.tokens_out().cpu()[:, 1:]
+    for hierarchy in (1, 2, 3):
+        d = eng.descriptors_hierarchy(hierarchy).cpu()[:, 0]
+        ref = servo.log_bin_hierarchy(tok, (22, 22), hierarchy)
+        assert d.shape == ref.shape == (2, 484, (1 + 8 * hierarchy) * 384)
+        assert torch.equal(d[..., :9 * 384], ref[..., :9 * 384])
+        assert torch.allclose(d, ref, rtol=1e-5, atol=1e-5 * ref.abs().max().item())
+    assert torch.equal(eng.descriptors_hierarchy(1), eng.descriptors(True))

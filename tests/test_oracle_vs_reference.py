@@ -157,3 +157,18 @@ def test_stride_patching_equals_reference(vits):
                 x = blk(x)
             assert torch.equal(ref[:, 0], x[:, 1:])
     assert vits.patch_embed.proj.stride == (14, 14)          # the shared fixture was not patched
+
+
+def test_log_bin_hierarchy_equals_reference(vits):
+    """_log_bin with hierarchy > 1 (dinov2_extractor.py:265-311; only reachable by calling it directly)."""
+    ex = ref_loader.make_extractor(vits, "dinov2_vits14")
+    g = torch.Generator().manual_seed(7)
+    for hp, wp in ((7, 7), (5, 9), (2, 3)):
+        x = torch.randn(2, 1, hp * wp, 24, generator=g)            # B x h x t x d as the reference's hook delivers it
+        ex.num_patches = (hp, wp)
+        for hierarchy in (1, 2, 3):
+            ref = ex._log_bin(x, hierarchy)[:, 0]
+            mine = servo.log_bin_hierarchy(x[:, 0], (hp, wp), hierarchy)
+            assert ref.shape == mine.shape == (2, hp * wp, (1 + 8 * hierarchy) * 24)
+            assert torch.equal(ref, mine), (hp, wp, hierarchy)
+        assert torch.equal(servo.log_bin_hierarchy(x[:, 0], (hp, wp), 1), servo.log_bin(x[:, 0], (hp, wp)))

@@ -52,6 +52,7 @@ SYMBOLS = {
     "vvs_weights_ready": (c_i32, [c_vp]),
     "vvs_forward_tokens": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp]),
     "vvs_get_tokens": (c_i32, [c_vp, c_vp, c_i32, c_vp]),
+    "vvs_descriptors_hierarchy": (c_i32, [c_vp, c_i32, c_i32, c_vp, c_vp]),
     "vvs_forward_facet": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp]),
     "vvs_facet_descriptors": (c_i32, [c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp]),
     "vvs_descriptors": (c_i32, [c_vp, c_i32, c_i32, c_vp, c_vp]),

@@ -965,6 +965,16 @@ int vvs_descriptors(vvs_handle c, int32_t n_img, int32_t bin, float* out, vvs_st
                                 &c->err);
 }
 
+int vvs_descriptors_hierarchy(vvs_handle c, int32_t n_img, int32_t hierarchy, float* out, vvs_stream stream) {
+  if (!c || !out) return fail(c, VVS_ERR_INVALID, "vvs_descriptors_hierarchy: null argument");
+  if (hierarchy < 1 || hierarchy > 4) return fail(c, VVS_ERR_INVALID, "vvs_descriptors_hierarchy: hierarchy outside [1, 4]");
+  if (n_img < 1 || n_img > c->last_n_img)
+    return fail(c, VVS_ERR_STATE, "vvs_descriptors_hierarchy: no forward pass holds that many images");
+  ++c->launch_count;
+  return launch_descriptors_hier_f32(c->x, out, n_img, c->grid, c->grid, c->cfg.dim, hierarchy,
+                                     static_cast<cudaStream_t>(stream), &c->err);
+}
+
 int vvs_match(vvs_handle c, const float* d1, const float* d2, int32_t n_pairs, int32_t T, int32_t d, int32_t grid_w,
               int32_t num_pairs, const vvs_match_out* out, vvs_stream stream) {
   if (!c || !d1 || !d2) return fail(c, VVS_ERR_INVALID, "vvs_match: null argument");

@@ -157,6 +157,51 @@ __global__ void descriptors_f32_kernel(const float* __restrict__ x, float* __res
   }
 }
 
+// Log-binned descriptors with any hierarchy (dinov2_extractor.py:265-311): bin (k, dy, dx) of token
+// (y, x) = the 3^k x 3^k average (in-grid elements only: count_include_pad=False) around the replicate-clamped
+// neighbour (y + dy 3^k, x + dx 3^k); the centre bin exists at k = 0 only.  Bins level-major, then (dy, dx) row-major.
+// x: [n_img, 1+T, D] fp32 -> out [n_img, T, (1 + 8 h) D] fp32.  Thread = 4 channels of one bin of one token.
+__global__ void descriptors_hier_f32_kernel(const float* __restrict__ x, float* __restrict__ out, int n_img, int hp,
+                                            int wp, int D, int hierarchy) {
+  const int T = hp * wp;
+  const int bins = 1 + 8 * hierarchy;
+  const int d4 = D / 4;
+  const long long total = static_cast<long long>(n_img) * T * bins * d4;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c4 = static_cast<int>(idx % d4);
+    long long r = idx / d4;
+    const int bin = static_cast<int>(r % bins);
+    r /= bins;
+    const int t = static_cast<int>(r % T);
+    const int img = static_cast<int>(r / T);
+    int k = 0, slot = bin;                     // level 0 has 9 slots, deeper levels 8 (centre skipped)
+    if (bin >= 9) {
+      k = 1 + (bin - 9) / 8;
+      slot = (bin - 9) % 8;
+      if (slot >= 4) ++slot;                   // re-insert the skipped centre
+    }
+    int win = 1;
+    for (int i = 0; i < k; ++i) win *= 3;
+    const int y0 = t / wp, x0 = t - y0 * wp;
+    const int cy = clampi(y0 + (slot / 3 - 1) * win, 0, hp - 1);
+    const int cx = clampi(x0 + (slot % 3 - 1) * win, 0, wp - 1);
+    const int half = win / 2;
+    const int ya = max(cy - half, 0), yb = min(cy + half, hp - 1);
+    const int xa = max(cx - half, 0), xb = min(cx + half, wp - 1);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int yy = ya; yy <= yb; ++yy)
+      for (int xx = xa; xx <= xb; ++xx) {
+        const float4 v = *reinterpret_cast<const float4*>(x + (static_cast<size_t>(img) * (T + 1) + 1 + yy * wp + xx) * D +
+                                                          c4 * 4);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+    const float n = static_cast<float>((yb - ya + 1) * (xb - xa + 1));
+    if (win > 1) { acc.x /= n; acc.y /= n; acc.z /= n; acc.w /= n; }
+    *reinterpret_cast<float4*>(out + ((static_cast<size_t>(img) * T + t) * bins + bin) * D + c4 * 4) = acc;
+  }
+}
+
 // facet descriptors (dinov2_extractor.py:203-218, 326-336): q / k / v of the block's attention input as
 // [B, h, t, d] -> permute(0, 2, 3, 1).flatten(-2): channel c = dd * heads + hh reads qkv column facet*D + hh*64 + dd.
 // Thread = one output channel of one (image, token, part): writes coalesced, reads gather from an L2-resident row.
@@ -311,6 +356,14 @@ int launch_descriptors_f32(const float* x, float* out, int n_img, int hp, int wp
   const int parts = bin ? 9 : 1;
   const long long items = static_cast<long long>(n_img) * hp * wp * parts * (D / 4);
   descriptors_f32_kernel<<<grid_for(items, 256), 256, 0, s>>>(x, out, n_img, hp, wp, D, parts);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_descriptors_hier_f32(const float* x, float* out, int n_img, int hp, int wp, int D, int hierarchy,
+                                cudaStream_t s, std::string* err) {
+  const long long items = static_cast<long long>(n_img) * hp * wp * (1 + 8 * hierarchy) * (D / 4);
+  descriptors_hier_f32_kernel<<<grid_for(items, 256), 256, 0, s>>>(x, out, n_img, hp, wp, D, hierarchy);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }

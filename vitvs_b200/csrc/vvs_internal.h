@@ -127,6 +127,9 @@ int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, 
 // residual stream [n_img, 1+T, D] -> descriptors (CLS dropped, optional 3x3 log-binning)
 int launch_descriptors_f32(const float* x, float* out, int n_img, int hp, int wp, int D, int bin, cudaStream_t s,
                            std::string* err);
+// residual stream -> log-binned descriptors with `hierarchy` levels, [n_img, T, (1 + 8 h) D] fp32
+int launch_descriptors_hier_f32(const float* x, float* out, int n_img, int hp, int wp, int D, int hierarchy,
+                                cudaStream_t s, std::string* err);
 // qkv [n_img * (1+T), 3*D] bf16 (columns [facet][head][64]) -> key / query / value descriptors fp32
 // [n_img, T (+1 with CLS), parts * D] in the reference's channel order (d major, head minor)
 int launch_facet_descriptors_f32(const bf16* qkv, float* out, int n_img, int hp, int wp, int D, int heads, int facet,

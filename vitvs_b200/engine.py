@@ -185,6 +185,15 @@ class Engine:
                     "vvs_descriptors")
         return out
 
+    def descriptors_hierarchy(self, hierarchy: int) -> torch.Tensor:
+        """``_log_bin(x, hierarchy)`` (dinov2_extractor.py:265-311) of the last forward_tokens pass:
+        [n, 1, T, (1 + 8 * hierarchy) * dim] fp32."""
+        out = torch.empty(self._n_img, 1, self.tokens, self.dim * (1 + 8 * hierarchy), device=self.device,
+                          dtype=torch.float32)
+        self._check(self.lib.vvs_descriptors_hierarchy(self._h, self._n_img, int(hierarchy), _ptr(out),
+                                                       _stream(self.device)), "vvs_descriptors_hierarchy")
+        return out
+
     def _match_buffers(self, n_pairs: int, T: int, K: int):
         dev = self.device
         bufs = dict(
