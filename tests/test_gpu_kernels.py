@@ -130,18 +130,22 @@ def test_gemm_residual_f32(eng):
 
 
 def test_gemm_patch_embed_rows(eng):
+    """EPI_PATCH_F32: A carries one all-zero row per CLS slot, so GEMM row r is residual-stream row r and
+    x[r] = acc + bias + pos'[r % (T + 1)] leaves through a TMA store (ragged last tile: M = 150 rows)."""
     n_img, T, D, K = 3, 49, 384, 640
-    A = _rand((n_img * T, K), 16, dtype=torch.bfloat16)
+    A = _rand((n_img, T + 1, K), 16, dtype=torch.bfloat16)
+    A[:, 0] = 0
+    A = A.reshape(n_img * (T + 1), K).contiguous()
     B = _rand((D, K), 17, 0.05, dtype=torch.bfloat16)
     bias, pos = _rand((D,), 18, 0.1), _rand((T + 1, D), 19)
     x = torch.full((n_img * (T + 1), D), 7.0, device="cuda")
     eng.dbg_gemm(A, B, _lib.EPI_PATCH_F32, bias=bias, x_f32=x, ldo=D, pos=pos, T=T)
     torch.cuda.synchronize()
-    ref = (A.float() @ B.float().T + bias).reshape(n_img, T, D) + pos[1:]
+    ref = (A.float() @ B.float().T + bias).reshape(n_img, T + 1, D) + pos
     got = x.reshape(n_img, T + 1, D)
-    _, rel = _report("gemm patch rows", got[:, 1:], ref)
+    _, rel = _report("gemm patch rows", got, ref)
     assert rel < 1e-4
-    assert torch.all(got[:, 0] == 7.0)            # CLS rows untouched by this kernel
+    assert torch.equal(got[:, 0], (bias + pos[0]).expand(n_img, D))        # zero accumulator on the CLS rows
 
 
 def test_gemm_swiglu(eng):

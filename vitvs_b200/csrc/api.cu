@@ -97,6 +97,7 @@ struct vvs_ctx {
   int grid = 0, T = 0, N = 0, stride = 14;
   // embeddings
   bf16* pe_w = nullptr; float* pe_b = nullptr; float* cls = nullptr; float* pos = nullptr;
+  float* pos_prime = nullptr;   // pos with the CLS row folded in for the patch-embed epilogue (launch_pos_prime)
   unsigned emb_mask = 0;   // 4 bits
   std::vector<BlockW> blocks;
   // workspace
@@ -251,7 +252,7 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
     if (c->blocks[i].set_mask != 0x3FFF)
       return fail(c, VVS_ERR_STATE, "weights of blocks." + std::to_string(i) + " incomplete");
   const int D = f.dim, H = f.ffn_hidden, T = c->T, N = c->N;
-  const int M = n_img * N, Mp = n_img * T;
+  const int M = n_img * N;
   int rc;
   if (kind == VVS_IMAGE_U8_HWC)
   { ProfScope ps(c, VVS_K_IM2COL, s);
@@ -264,14 +265,12 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
   else
     return fail(c, VVS_ERR_INVALID, "unknown image_kind");
   if (rc) return rc;
-  { ProfScope ps(c, VVS_K_OTHER, s);
-    rc = launch_cls_rows(c->x, c->cls, c->pos, n_img, N, D, s, &c->err); }
-  if (rc) return rc;
-  c->launch_count += 2;
+  ++c->launch_count;
   {
-    GemmArgs g = plain_gemm(c->big, c->pe_w, Mp, D, kPatchKPad, EPI_PATCH_F32);
-    g.bias = c->pe_b; g.x_f32 = c->x; g.ldo = D; g.pos = c->pos; g.T = T;
-    g.pdl = 0;   // predecessor (cls_rows) is not PDL-aware
+    // A has one zero row per CLS slot, so GEMM row r is residual-stream row r: x = acc + bias + pos'[r % N]
+    GemmArgs g = plain_gemm(c->big, c->pe_w, M, D, kPatchKPad, EPI_PATCH_F32);
+    g.bias = c->pe_b; g.x_f32 = c->x; g.ldo = D; g.pos = c->pos_prime; g.T = T;
+    g.pdl = 0;   // predecessor (im2col) is not PDL-aware
     if ((rc = gemm(c, g, s, VVS_K_PATCH_GEMM))) return rc;
   }
   // inside the blocks every kernel is PDL-aware (LayerNorm, GEMMs, attention): programmatic dependent launches.
@@ -694,6 +693,18 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
 
 }  // namespace
 
+namespace {
+// pos' depends on patch_embed.proj.bias, cls_token and pos_embed_interp: refreshed whenever one of them is (re)set
+int refresh_pos_prime(vvs_ctx* c, cudaStream_t s) {
+  if ((c->emb_mask & 0xE) != 0xE) return VVS_OK;
+  if (!c->pos_prime) {
+    int rc = dev_alloc(c, &c->pos_prime, static_cast<size_t>(c->N) * c->cfg.dim);
+    if (rc) return rc;
+  }
+  return launch_pos_prime(c->pos, c->cls, c->pe_b, c->pos_prime, c->N, c->cfg.dim, s, &c->err);
+}
+}  // namespace
+
 // ------------------------------------------------------------------------------------------- C ABI
 extern "C" {
 
@@ -812,7 +823,7 @@ int vvs_destroy(vvs_handle c) {
   for (cudaEvent_t e : c->chunk_events) cudaEventDestroy(e);
   free_resize_axis(&c->rz_w);
   free_resize_axis(&c->rz_h);
-  void* ptrs[] = {c->pe_w, c->pe_b, c->cls, c->pos, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
+  void* ptrs[] = {c->pe_w, c->pe_b, c->cls, c->pos, c->pos_prime, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
                   c->inv_norm, c->nn1, c->nn2, c->sim1, c->cand, c->mean_sim1, c->n_cand, c->n_sel, c->flags, c->mean_sel,
                   c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth, c->stage_frames,
                   c->rz_tmp};
@@ -865,17 +876,20 @@ int vvs_set_weight(vvs_handle c, const char* name_c, const void* p, int32_t dtyp
   if (name == "patch_embed.proj.bias") {
     if (n != D) return bad_shape();
     c->emb_mask |= 2;
-    return upload_vector(c, &c->pe_b, p, dtype, D, 0, 0, s);
+    int rc = upload_vector(c, &c->pe_b, p, dtype, D, 0, 0, s);
+    return rc ? rc : refresh_pos_prime(c, s);
   }
   if (name == "cls_token") {
     if (n != D) return bad_shape();
     c->emb_mask |= 4;
-    return upload_vector(c, &c->cls, p, dtype, D, 0, 0, s);
+    int rc = upload_vector(c, &c->cls, p, dtype, D, 0, 0, s);
+    return rc ? rc : refresh_pos_prime(c, s);
   }
   if (name == "pos_embed_interp") {
     if (n != static_cast<long long>(c->N) * D) return bad_shape();
     c->emb_mask |= 8;
-    return upload_vector(c, &c->pos, p, dtype, c->N * D, 0, 0, s);
+    int rc = upload_vector(c, &c->pos, p, dtype, c->N * D, 0, 0, s);
+    return rc ? rc : refresh_pos_prime(c, s);
   }
   if (name.rfind("blocks.", 0) == 0) {
     const size_t dot = name.find('.', 7);

@@ -74,8 +74,24 @@ __global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ 
       }
     }
     uint4 w = make_uint4(pack2(v[0], v[1]), pack2(v[2], v[3]), pack2(v[4], v[5]), pack2(v[6], v[7]));
-    *reinterpret_cast<uint4*>(out + row * kpad + k8 * 8) = w;
+    // row img * (T + 1) + 1 + t: the matrix has one (all-zero) row per CLS slot, so that the patch-embed GEMM's rows
+    // are the residual stream's rows and its epilogue can leave through a plain 2-D TMA store
+    *reinterpret_cast<uint4*>(out + (row + img + 1) * kpad + k8 * 8) = w;
   }
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+       idx < static_cast<long long>(n_img) * k8_per_row; idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long img = idx / k8_per_row;
+    *reinterpret_cast<uint4*>(out + img * (T + 1) * kpad + (idx - img * k8_per_row) * 8) = make_uint4(0u, 0u, 0u, 0u);
+  }
+}
+
+// pos'[0] = cls + pos[0] - patch_bias (the CLS row of the patch-embed GEMM has a zero accumulator: acc + bias + pos'[0]
+// = cls + pos[0]); pos'[r] = pos[r] for the patch rows.
+__global__ void pos_prime_kernel(const float* __restrict__ pos, const float* __restrict__ cls,
+                                 const float* __restrict__ bias, float* __restrict__ out, int n_tok, int D) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_tok * D) return;
+  out[idx] = idx < D ? (cls[idx] + pos[idx]) - bias[idx] : pos[idx];
 }
 
 __global__ void cls_rows_kernel(float* __restrict__ x, const float* __restrict__ cls, const float* __restrict__ pos,
@@ -325,6 +341,13 @@ int launch_im2col_f32(const float* img, bf16* out, int n_img, int size, int kpad
                       std::string* err) {
   const long long items = static_cast<long long>(n_img) * grid * grid * (kpad / 8);
   im2col_kernel<false><<<grid_for(items, 256), 256, 0, s>>>(img, out, n_img, size, kpad, grid, stride);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_pos_prime(const float* pos, const float* cls, const float* bias, float* out, int n_tok, int D, cudaStream_t s,
+                     std::string* err) {
+  pos_prime_kernel<<<(n_tok * D + 255) / 256, 256, 0, s>>>(pos, cls, bias, out, n_tok, D);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }

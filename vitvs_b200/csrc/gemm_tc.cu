@@ -311,15 +311,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         float best_v = -INFINITY;
         int best_j = 0x7fffffff;
         const uint32_t row_tag = 0xFFFFFFFFu - static_cast<uint32_t>(row);
-        // EPI_PATCH_F32 row remap
-        size_t orow = grow;
+        // EPI_PATCH_F32: the positional row of this GEMM row (row r of image i is token r of the residual stream)
         const float* pos_row = nullptr;
-        if constexpr (EPI == EPI_PATCH_F32) {
-          const int img = row / p.T;
-          const int t = row - img * p.T;
-          orow = static_cast<size_t>(img) * (p.T + 1) + 1 + t;
-          pos_row = p.pos + static_cast<size_t>(1 + t) * p.ldo;
-        }
+        if constexpr (EPI == EPI_PATCH_F32) pos_row = p.pos + static_cast<size_t>(row_ok ? row % (p.T + 1) : 0) * p.ldo;
         uint32_t raw[2][32];
         tmem_ld32(t_acc + c_begin * 32, raw[0]);
 #pragma unroll
@@ -435,16 +429,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               bulk_commit();
             }
           } else if constexpr (EPI == EPI_PATCH_F32) {
-            if (row_ok) {
-              float4* x4 = reinterpret_cast<float4*>(p.x_f32 + orow * p.ldo + col0);
+            // x = acc + bias + pos': one 32-column fp32 chunk = one 128-byte-row slab, stored by TMA
+            if (lane == 0) bulk_wait_read0();
+            __syncwarp();
 #pragma unroll
-              for (int q = 0; q < 8; ++q) {
-                const float4 ps = __ldg(reinterpret_cast<const float4*>(pos_row + col0) + q);
-                x4[q] = make_float4(__uint_as_float(rw[q * 4 + 0]) + bq[q].x + ps.x,
-                                    __uint_as_float(rw[q * 4 + 1]) + bq[q].y + ps.y,
-                                    __uint_as_float(rw[q * 4 + 2]) + bq[q].z + ps.z,
-                                    __uint_as_float(rw[q * 4 + 3]) + bq[q].w + ps.w);
-              }
+            for (int q = 0; q < 8; ++q) {
+              const float4 ps = __ldg(reinterpret_cast<const float4*>(pos_row + col0) + q);
+              st_shared_v4f(my_row_s + ((static_cast<uint32_t>(q) ^ sw) << 4),
+                            __uint_as_float(rw[q * 4 + 0]) + bq[q].x + ps.x, __uint_as_float(rw[q * 4 + 1]) + bq[q].y + ps.y,
+                            __uint_as_float(rw[q * 4 + 2]) + bq[q].z + ps.z, __uint_as_float(rw[q * 4 + 3]) + bq[q].w + ps.w);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && tile_row0 < p.M) {
+              tma_store_2d(&tmOut, stg_s, col0, tile_row0);
+              bulk_commit();
             }
           } else if constexpr (EPI == EPI_STORE_F32) {
             if (row_ok) {
@@ -624,7 +623,7 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
     return VVS_ERR_INVALID;
   }
   const bool tma_out = a.epilogue == EPI_BIAS_BF16 || a.epilogue == EPI_GELU_BF16 || a.epilogue == EPI_SWIGLU_BF16 ||
-                       a.epilogue == EPI_RESID_F32;
+                       a.epilogue == EPI_RESID_F32 || a.epilogue == EPI_PATCH_F32;
   if (tma_out && a.batch != 1) {
     set_error(err, "launch_gemm: this epilogue stores through a 2-D tensor map (batch must be 1)");
     return VVS_ERR_INVALID;
@@ -636,7 +635,7 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   rc = make_tmap_bf16(&tmB, a.B, a.K, a.N, b_batched ? a.batch : 1, a.ldb, a.b_batch_pitch, bn / ncta, err);
   if (rc) return rc;
   CUtensorMap tmOut = tmA;   // unused by the epilogues that write with plain stores
-  if (a.epilogue == EPI_RESID_F32)
+  if (a.epilogue == EPI_RESID_F32 || a.epilogue == EPI_PATCH_F32)
     rc = make_tmap_out(&tmOut, a.x_f32, 4, a.N, a.M, a.ldo, 32, 32, err);
   else if (a.epilogue == EPI_SWIGLU_BF16)
     rc = make_tmap_out(&tmOut, a.out_bf16, 2, a.N / 2, a.M, a.ldo, 64, 32, err);

@@ -60,7 +60,7 @@ enum Epilogue : int {
   EPI_BIAS_BF16 = 0,   // out_bf16 = (acc + bias) * (col < q_cols ? q_scale : 1)              (qkv)
   EPI_GELU_BF16 = 1,   // out_bf16 = gelu_erf(acc + bias)                                      (mlp.fc1)
   EPI_RESID_F32 = 2,   // x_f32   += gamma * (acc + bias)                                      (attn.proj, mlp.fc2 / w3)
-  EPI_PATCH_F32 = 3,   // x_f32[img*(T+1)+1+t] = acc + bias + pos[1+t]                         (patch embed)
+  EPI_PATCH_F32 = 3,   // x_f32[r] = acc + bias + pos'[r % (T+1)], A has a zero row per CLS slot        (patch embed)
   EPI_SWIGLU_BF16 = 4, // out_bf16 = silu(acc1 + b1) * (acc2 + b2), weight rows tile-interleaved (mlp.w12)
   EPI_SIM = 5,         // packed row / column arg-max of the similarity tile, S never stored    (matching)
   EPI_STORE_F32 = 6    // out_f32 = acc  (plain fp32 store; unit tests / similarity dump)
@@ -83,7 +83,7 @@ struct GemmArgs {
   int ldo;
   int q_cols;
   float q_scale;
-  const float* pos;      // [T+1, ldo] (EPI_PATCH_F32)
+  const float* pos;      // [T+1, ldo] (EPI_PATCH_F32): pos' with the CLS row folded in (launch_pos_prime)
   int T;                 // patches per image (EPI_PATCH_F32)
   unsigned long long* row_best;   // [batch, best_pitch] (EPI_SIM)
   unsigned long long* col_best;   // [batch, best_pitch]
@@ -120,6 +120,8 @@ int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpa
                      std::string* err);
 int launch_im2col_f32(const float* img, bf16* out, int n_img, int size, int kpad, int grid, int stride, cudaStream_t s,
                       std::string* err);
+int launch_pos_prime(const float* pos, const float* cls, const float* bias, float* out, int n_tok, int D, cudaStream_t s,
+                     std::string* err);
 int launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int n_tok, int D, cudaStream_t s,
                     std::string* err);
 int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, int rows, int D, float eps,
