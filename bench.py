@@ -341,6 +341,18 @@ def run_ours(args):
             if fl:
                 ent["tflops"] = round(fl / (tot_ms / cnt * 1e-3) / 1e12, 1)
                 ent["frac_of_sustained_peak"] = round(ent["tflops"] / pk["tf_sustained"], 3)
+            # HBM-bound classes: ALGORITHMIC bytes per launch (SURVEY 8d / DESIGN.md 3) against the measured copy bandwidth
+            S_ = cfg.dino_input_size
+            by = {"layernorm": M * dim * (4 + 2) + 2 * dim * 4,
+                  "proj_gemm": M * dim * (2 + 4 + 4),                                   # h read, x read-modify-write
+                  "im2col": 2 * B * (S_ * S_ * 3 + (T + 1) * 640 * 2),
+                  "descriptors": 2 * B * T * (dim * 4 + parts * dim * 2 + 4),           # tokens read once, binned rows written
+                  "resize": B * (cfg.u_max * cfg.v_max * 3 + S_ * S_ * 3),              # per launch pair (H + V) of one frame set
+                  }.get(k)
+            if by:
+                launches = cnt if k != "resize" else max(cnt // 2, 1)
+                ent["gbps"] = round(by / (tot_ms / launches * 1e-3) / 1e9, 1)
+                ent["frac_of_hbm_peak"] = round(ent["gbps"] / pk["hbm"], 3)
             kernels[k] = ent
         dom = next(k for k in kernels if k.endswith("_gemm"))
         dom_fl = gemm_class_flops(dom, M, dim, hidden, Mp, T, B, sim_k)

@@ -54,13 +54,14 @@ __global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ 
     const int img = static_cast<int>(row / T);
     const int py = t / gp, px = t - py * gp;
     float v[8];
+    // (c, ky, kx) of the first element once, then carried: k = c * 196 + ky * 14 + kx
+    const int kfirst = k8 * 8;
+    int c = kfirst / (kPatch * kPatch);
+    int ky = (kfirst - c * kPatch * kPatch) / kPatch;
+    int kx = kfirst - c * kPatch * kPatch - ky * kPatch;
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      const int k = k8 * 8 + e;
-      if (k < kPatchK) {
-        const int c = k / (kPatch * kPatch);
-        const int rem = k - c * kPatch * kPatch;
-        const int ky = rem / kPatch, kx = rem - ky * kPatch;
+      if (kfirst + e < kPatchK) {
         const int y = py * stride + ky, x = px * stride + kx;   // stride < 14: overlapping patches (:123-144)
         if (kU8) {
           const uint8_t* img8 = static_cast<const uint8_t*>(img_);
@@ -71,6 +72,13 @@ __global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ 
         }
       } else {
         v[e] = 0.f;
+      }
+      if (++kx == kPatch) {
+        kx = 0;
+        if (++ky == kPatch) {
+          ky = 0;
+          ++c;
+        }
       }
     }
     uint4 w = make_uint4(pack2(v[0], v[1]), pack2(v[2], v[3]), pack2(v[4], v[5]), pack2(v[6], v[7]));
