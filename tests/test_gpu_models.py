@@ -74,3 +74,32 @@ def test_matching_sweep_large_grid(T, d):
     uv = r["uv"][0].cpu().numpy()
     assert uv[:, 0].max() < 640 and uv[:, 1].max() < 480 and uv.min() >= 0
     eng.close()
+
+
+@pytest.mark.parametrize("T,d", [(16384, 768), (8192, 3456)])
+def test_matching_maximum_grid(T, d):
+    """SURVEY §8d C5 at its largest sizes (128 x 128 tokens unbinned ViT-B; 8192 tokens with ViT-S binned width):
+    the similarity matrix (1 GiB at T = 16 384) is never written; arg-max parity against the CPU oracle computed in
+    row blocks, and the planted permutation must come back."""
+    from vitvs_b200 import Engine, ServoConfig
+    eng = Engine(ServoConfig(model_type="dinov2_vits14"), max_images=4, max_match_tokens=T, max_match_dim=d)
+    a, b, perm = synth.descriptor_sets(T, d, seed=7, noise=0.5)
+    r = eng.match(a[None], b[None], num_pairs=24)
+    torch.cuda.synchronize()
+    nn1, nn2 = r["nn1"][0].cpu().numpy(), r["nn2"][0].cpu().numpy()
+    inv = np.empty(T, dtype=np.int64)
+    inv[perm.numpy()] = np.arange(T)
+    assert (nn1 == inv).mean() >= 0.999 and (nn2 == perm.numpy()).mean() >= 0.999
+    # oracle arg-max (fp32 cosine similarity, vitvs_v2.py:49-56,80-81) in row blocks of 2048
+    an = a / a.norm(dim=1, keepdim=True).clamp_min(1e-8)
+    bn = b / b.norm(dim=1, keepdim=True).clamp_min(1e-8)
+    ref1 = torch.cat([(an[i:i + 2048] @ bn.T).argmax(dim=1) for i in range(0, T, 2048)]).numpy()
+    ref2 = torch.cat([(bn[i:i + 2048] @ an.T).argmax(dim=1) for i in range(0, T, 2048)]).numpy()
+    assert (nn1 == ref1).mean() >= 0.99 and (nn2 == ref2).mean() >= 0.99
+    # every selected pair is mutual and its key-points lie inside the frame
+    sel = r["sel_tok"][0].cpu().numpy()
+    sel = sel[sel >= 0]
+    assert len(sel) == 24 and (nn2[nn1[sel]] == sel).all()
+    uv = r["uv"][0].cpu().numpy()
+    assert uv[:, 0].max() < 640 and uv[:, 1].max() < 480 and uv.min() >= 0
+    eng.close()
