@@ -105,6 +105,7 @@ struct vvs_ctx {
   bf16* h = nullptr;         // LN out / attention out [max_images * N, D]
   bf16* big = nullptr;       // im2col / qkv / ffn hidden
   size_t big_elems = 0;
+  int x_pin_mb = 40;          // MB of the residual stream (its last rows) that every kernel asks L2 to keep; 0 = no hints
   bf16* desc = nullptr;      // unit-norm descriptors
   size_t desc_elems = 0;
   float* sqn = nullptr;      // [max_images * T]
@@ -253,6 +254,12 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
       return fail(c, VVS_ERR_STATE, "weights of blocks." + std::to_string(i) + " incomplete");
   const int D = f.dim, H = f.ffn_hidden, T = c->T, N = c->N;
   const int M = n_img * N;
+  // The residual stream (M x D fp32) is read or rewritten by four kernels per block and is larger than L2 at full
+  // batch; its last x_pin_mb megabytes carry the evict-last hint in every one of them (LayerNorm loads, the
+  // residual GEMMs' reduce-adds), the rest is read evict-first, so that a fixed part of it never leaves L2.
+  const long long pin_rows = static_cast<long long>(c->x_pin_mb) * 1000000ll / (static_cast<long long>(D) * 4);
+  const int pin_row0 = (c->x_pin_mb > 0 && static_cast<long long>(M) * D * 4 > 100000000ll)
+                           ? static_cast<int>(std::max<long long>(1, M - pin_rows)) : 0x7fffffff;
   int rc;
   if (kind == VVS_IMAGE_U8_HWC)
   { ProfScope ps(c, VVS_K_IM2COL, s);
@@ -269,7 +276,7 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
   {
     // A has one zero row per CLS slot, so GEMM row r is residual-stream row r: x = acc + bias + pos'[r % N]
     GemmArgs g = plain_gemm(c->big, c->pe_w, M, D, kPatchKPad, EPI_PATCH_F32);
-    g.bias = c->pe_b; g.x_f32 = c->x; g.ldo = D; g.pos = c->pos_prime; g.T = T;
+    g.bias = c->pe_b; g.x_f32 = c->x; g.ldo = D; g.pos = c->pos_prime; g.T = T; g.pin_row0 = pin_row0;
     g.pdl = 0;   // predecessor (im2col) is not PDL-aware
     if ((rc = gemm(c, g, s, VVS_K_PATCH_GEMM))) return rc;
   }
@@ -279,7 +286,7 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
   for (int i = 0; i <= layer; ++i) {
     const BlockW& w = c->blocks[i];
     { ProfScope ps(c, VVS_K_LAYERNORM, s);
-      rc = launch_layernorm(c->x, w.n1w, w.n1b, c->h, M, D, 1e-6f, s, &c->err, pdl); }
+      rc = launch_layernorm(c->x, w.n1w, w.n1b, c->h, M, D, 1e-6f, pin_row0, s, &c->err, pdl); }
     if (rc) return rc;
     {
       GemmArgs g = plain_gemm(c->h, w.qkv_w, M, 3 * D, D, EPI_BIAS_BF16);
@@ -300,11 +307,11 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
     if (rc) return rc;
     {
       GemmArgs g = plain_gemm(c->h, w.proj_w, M, D, D, EPI_RESID_F32);
-      g.bias = w.proj_b; g.gamma = w.ls1; g.x_f32 = c->x; g.ldo = D; g.pdl = pdl;
+      g.bias = w.proj_b; g.gamma = w.ls1; g.x_f32 = c->x; g.ldo = D; g.pdl = pdl; g.pin_row0 = pin_row0;
       if ((rc = gemm(c, g, s, VVS_K_PROJ_GEMM))) return rc;
     }
     { ProfScope ps(c, VVS_K_LAYERNORM, s);
-      rc = launch_layernorm(c->x, w.n2w, w.n2b, c->h, M, D, 1e-6f, s, &c->err, pdl); }
+      rc = launch_layernorm(c->x, w.n2w, w.n2b, c->h, M, D, 1e-6f, pin_row0, s, &c->err, pdl); }
     if (rc) return rc;
     {
       GemmArgs g = plain_gemm(c->h, w.ffn1_w, M, f.swiglu ? 2 * H : H, D, f.swiglu ? EPI_SWIGLU_BF16 : EPI_GELU_BF16);
@@ -313,7 +320,7 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
     }
     {
       GemmArgs g = plain_gemm(c->big, w.ffn2_w, M, D, H, EPI_RESID_F32);
-      g.bias = w.ffn2_b; g.gamma = w.ls2; g.x_f32 = c->x; g.ldo = D; g.pdl = pdl;
+      g.bias = w.ffn2_b; g.gamma = w.ls2; g.x_f32 = c->x; g.ldo = D; g.pdl = pdl; g.pin_row0 = pin_row0;
       if ((rc = gemm(c, g, s, VVS_K_FFN2_GEMM))) return rc;
     }
     c->launch_count += 3;   // 2 LayerNorms + attention
@@ -807,6 +814,7 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
                       need <= c->desc_elems * sizeof(bf16);
   }
   if (const char* e = getenv("VITVS_HOST_CHUNKS")) c->host_chunks = std::max(1, atoi(e));
+  if (const char* e = getenv("VITVS_XPIN_MB")) c->x_pin_mb = std::max(0, atoi(e));
   *out = c;
   return VVS_OK;
 }
@@ -1184,7 +1192,7 @@ int vvs_dbg_attention(vvs_handle c, const void* qkv, void* out, int32_t n_img, i
 int vvs_dbg_layernorm(vvs_handle c, const float* x, const float* w, const float* b, void* out, int32_t rows, int32_t dim,
                       vvs_stream stream) {
   if (!c || !x || !w || !b || !out) return fail(c, VVS_ERR_INVALID, "vvs_dbg_layernorm: null argument");
-  return launch_layernorm(x, w, b, static_cast<bf16*>(out), rows, dim, 1e-6f, static_cast<cudaStream_t>(stream), &c->err);
+  return launch_layernorm(x, w, b, static_cast<bf16*>(out), rows, dim, 1e-6f, 0x7fffffff, static_cast<cudaStream_t>(stream), &c->err);
 }
 
 }  // extern "C"

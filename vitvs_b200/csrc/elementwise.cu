@@ -114,7 +114,7 @@ __global__ void cls_rows_kernel(float* __restrict__ x, const float* __restrict__
 template <int NV>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
-                 bf16* __restrict__ out, int rows, float eps) {
+                 bf16* __restrict__ out, int rows, float eps, int pin_row0) {
   constexpr int D = NV * 128;
   pdl_launch_dependents();
   pdl_wait();   // x is the previous kernel's output
@@ -127,9 +127,12 @@ layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const
   const float4* xr = reinterpret_cast<const float4*>(x + static_cast<size_t>(row) * D);
   float4 v[NV];
   float s = 0.f;
+  // rows >= pin_row0 are the part of the residual stream every kernel asks L2 to keep (evict-last); the rest is
+  // dead until the next residual GEMM rewrites it: evict-first, so that it does not push the kept part out
+  const uint64_t pol = (row >= pin_row0) ? kEvictLast : kEvictFirst;
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
-    v[i] = xr[i * 32 + lane];
+    v[i] = (pin_row0 < rows) ? ld_global_v4_hint(xr + i * 32 + lane, pol) : xr[i * 32 + lane];
     s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
   }
   const float mean = warp_sum(s) * (1.0f / D);
@@ -367,15 +370,15 @@ int launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int
   return VVS_OK;
 }
 
-int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, int rows, int D, float eps,
+int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, int rows, int D, float eps, int pin_row0,
                      cudaStream_t s, std::string* err, bool pdl) {
   const int grid = (rows + 7) / 8;
   cudaError_t e;
   switch (D) {
-    case 384: e = launch_kernel(layernorm_kernel<3>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps); break;
-    case 768: e = launch_kernel(layernorm_kernel<6>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps); break;
-    case 1024: e = launch_kernel(layernorm_kernel<8>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps); break;
-    case 1536: e = launch_kernel(layernorm_kernel<12>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps); break;
+    case 384: e = launch_kernel(layernorm_kernel<3>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0); break;
+    case 768: e = launch_kernel(layernorm_kernel<6>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0); break;
+    case 1024: e = launch_kernel(layernorm_kernel<8>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0); break;
+    case 1536: e = launch_kernel(layernorm_kernel<12>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0); break;
     default: set_error(err, "layernorm: unsupported width (384/768/1024/1536)"); return VVS_ERR_INVALID;
   }
   VVS_CUDA_OK(e, err);

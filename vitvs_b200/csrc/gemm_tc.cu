@@ -47,6 +47,7 @@ struct GemmDev {
   unsigned long long* row_best;
   unsigned long long* col_best;
   int best_pitch;
+  int pin_row0;   // EPI_RESID_F32 / EPI_PATCH_F32: rows >= pin_row0 of x carry the L2 evict-last hint
 };
 
 // NCTA = 2: a CTA pair (cluster of 2 on one TPC) computes a 256 x BN tile with cta_group::2 MMAs; each CTA
@@ -425,7 +426,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0 && tile_row0 < p.M) {
-              tma_reduce_add_2d(&tmOut, stg_s, col0, tile_row0);
+              if (tile_row0 >= p.pin_row0) tma_reduce_add_2d_hint(&tmOut, stg_s, col0, tile_row0, kEvictLast);
+              else tma_reduce_add_2d(&tmOut, stg_s, col0, tile_row0);
               bulk_commit();
             }
           } else if constexpr (EPI == EPI_PATCH_F32) {
@@ -442,7 +444,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0 && tile_row0 < p.M) {
-              tma_store_2d(&tmOut, stg_s, col0, tile_row0);
+              if (tile_row0 >= p.pin_row0) tma_store_2d_hint(&tmOut, stg_s, col0, tile_row0, kEvictLast);
+              else tma_store_2d(&tmOut, stg_s, col0, tile_row0);
               bulk_commit();
             }
           } else if constexpr (EPI == EPI_STORE_F32) {
@@ -650,6 +653,7 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   d.bias = a.bias; d.gamma = a.gamma; d.x_f32 = a.x_f32; d.out_bf16 = a.out_bf16; d.ldo = a.ldo;
   d.q_cols = a.q_cols; d.q_scale = a.q_scale; d.pos = a.pos; d.T = a.T;
   d.row_best = a.row_best; d.col_best = a.col_best; d.best_pitch = a.best_pitch;
+  d.pin_row0 = a.pin_row0 > 0 ? a.pin_row0 : 0x7fffffff;
   const long long tiles = static_cast<long long>(d.batch) * d.m_tiles * d.n_tiles;
   if (ncta == 2) {
     const int grid = 2 * static_cast<int>(std::min<long long>(tiles, num_sms / 2));

@@ -204,6 +204,28 @@ __device__ __forceinline__ void tma_reduce_add_2d(const void* tmap, uint32_t sme
                "r"(smem_src), "r"(c0), "r"(c1)
                : "memory");
 }
+// the same with an L2 eviction-priority hint for the destination lines
+__device__ __forceinline__ void tma_reduce_add_2d_hint(const void* tmap, uint32_t smem_src, int c0, int c1, uint64_t policy) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(
+          reinterpret_cast<uint64_t>(tmap)),
+      "r"(smem_src), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_2d_hint(const void* tmap, uint32_t smem_src, int c0, int c1, uint64_t policy) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3}], [%1], %4;" ::"l"(
+                   reinterpret_cast<uint64_t>(tmap)),
+               "r"(smem_src), "r"(c0), "r"(c1), "l"(policy)
+               : "memory");
+}
+// 128-bit global load with an L2 eviction-priority hint
+__device__ __forceinline__ float4 ld_global_v4_hint(const float4* ptr, uint64_t policy) {
+  float4 v;
+  asm volatile("ld.global.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(ptr), "l"(policy));
+  return v;
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all of this thread's bulk stores have finished READING their smem source (the buffer may be rewritten)
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }

@@ -88,6 +88,7 @@ struct GemmArgs {
   unsigned long long* row_best;   // [batch, best_pitch] (EPI_SIM)
   unsigned long long* col_best;   // [batch, best_pitch]
   int best_pitch;
+  int pin_row0;          // EPI_RESID_F32: rows >= pin_row0 of x are reduce-added with the L2 evict-last hint (<= 0: no hint)
   int pdl;               // launch with the programmatic-dependent-launch attribute (predecessor is a PDL-aware kernel)
 };
 int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string* err);
@@ -124,7 +125,8 @@ int launch_pos_prime(const float* pos, const float* cls, const float* bias, floa
                      std::string* err);
 int launch_cls_rows(float* x, const float* cls, const float* pos, int n_img, int n_tok, int D, cudaStream_t s,
                     std::string* err);
-int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, int rows, int D, float eps,
+// rows >= pin_row0 are read with the L2 evict-last hint, the others evict-first (pin_row0 >= rows: no hints)
+int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, int rows, int D, float eps, int pin_row0,
                      cudaStream_t s, std::string* err, bool pdl = false);
 // residual stream [n_img, 1+T, D] -> descriptors (CLS dropped, optional 3x3 log-binning)
 int launch_descriptors_f32(const float* x, float* out, int n_img, int hp, int wp, int D, int bin, cudaStream_t s,
