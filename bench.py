@@ -65,9 +65,19 @@ class ClockSampler:
         for ln in self.proc.stdout:
             self.lines.append(ln.strip())
 
+    def wait_first(self, timeout_s: float = 5.0):
+        t0 = time.perf_counter()
+        while self.proc is not None and not self.lines and time.perf_counter() - t0 < timeout_s:
+            time.sleep(0.02)
+
+    def mark(self):
+        """Start of the timed region: samples taken before this belong to the warm-up."""
+        self.first = len(self.lines)
+
     def stop(self) -> dict:
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        last = len(self.lines)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
@@ -75,7 +85,10 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        first = getattr(self, "first", 0)
+        # the samples of the timed region; a region shorter than the sampling period borrows the one just before it
+        window = self.lines[first:last] or self.lines[max(first - 1, 0):last]
+        for ln in window:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -235,14 +248,16 @@ def run_ours(args):
         torch.cuda.synchronize(dev)
 
     # ---- device-resident throughput (value)
+    sampler = ClockSampler(local)          # running since before the warm-up: nvidia-smi takes a while to come up
+    if rank == 0:
+        sampler.start()
+        sampler.wait_first()
     for i in range(args.warmup):
         eng.frame_pairs_to_twist(*sets_dev[i % NSETS])
     barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    sampler.mark()
     e0.record(stream)
     for i in range(args.steps):
         out = eng.frame_pairs_to_twist(*sets_dev[i % NSETS])

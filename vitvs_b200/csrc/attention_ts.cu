@@ -1,4 +1,4 @@
-// tcgen05 flash-attention forward, generations 7-8: P never leaves the tensor-core datapath; dedicated issuer warps.
+// tcgen05 flash-attention forward, generations 7-9: P never leaves the tensor-core datapath; dedicated issuer warp.
 // (reference semantics: dino_patch/attention.py:70-80 - non-causal SDPA, scale hd^-0.5,
 // head dim 64, no mask, eval.)
 //
@@ -7,16 +7,22 @@
 // the Q / K / V tiles of (image, head) are 64-column TMA boxes of that matrix.  Output goes straight into
 // the [n_img * n_tok, D] layout attn.proj reads.
 //
-// One CTA = TWO 128-row query tiles of one (image, head); TWO CTAs are resident per SM (256 TMEM columns,
-// ~98 KB of shared memory and 320 threads each), so the prologue (descriptor fetch, Q / K loads) and the
-// epilogue (O / l, global stores) of one CTA hide behind the main loop of the other:
-//   warps 0-7   two softmax warpgroups, one per query tile (thread = query row = TMEM lane); they never issue an
-//               MMA or a TMA: wait S -> TMEM load -> max / exp -> TMEM store -> arrive
-//   warps 8, 9  MMA issuer of tile 0 / tile 1 (generation 8).  The whole warp walks the loop so that every address
-//               and descriptor lives on the uniform datapath; lane 0 issues.  Warp 8 also feeds the K / V ring.
-//               Measured with the per-block clock trace (tools/att_trace.py): when a softmax lane issued, its
-//               serial chain (poll P, poll V, 4 + 4 MMAs at ~75 clk each through ELECT / R2UR waterfalls, three
-//               commits, TMA pump) cost 1500-2500 clk per block on the tile's critical path; now ~600.
+// Generation 9 (the default, VVS_ATT_QT = 1): one CTA = ONE 128-row query tile of one (image, head), FOUR CTAs
+// resident per SM (128 TMEM columns, ~49 KB of shared memory and 160 threads each).  A sequence of 485 tokens is
+// only 8 key blocks long, so a CTA spends a third of its life outside its main loop - ~4500 clk until the first
+// S is there (barriers, TMEM allocation, first operands from HBM) and ~5000 clk after the last P (last PV, O
+// read-out, stores, teardown); measured with the per-block clock trace (tools/att_trace.py).  With four
+// independent CTAs per SM those phases fall under the main loops of three others instead of one (2 tiles per CTA,
+// 2 CTAs per SM: 180 us; 1 tile per CTA: 161 us), and the output leaves as one TMA store per tile from the tile's
+// own Q buffer instead of 8 row-strided 16-byte stores per thread (146 us).  VVS_ATT_QT = 2 restores generation 8:
+// two tiles per CTA sharing one K / V ring.
+//   warps 0-3 (per tile)  softmax warpgroup (thread = query row = TMEM lane); it never issues an MMA or a TMA:
+//               wait S -> TMEM load -> max / exp -> TMEM store -> arrive
+//   warp 4 (4 kQT + u)    MMA issuer of tile u (generation 8).  The whole warp walks the loop so that every address
+//               and descriptor lives on the uniform datapath; lane 0 issues.  The first issuer also feeds the K / V
+//               ring.  When a softmax lane issued, its serial chain (poll P, poll V, 4 + 4 MMAs at ~75 clk each
+//               through ELECT / R2UR waterfalls, three commits, TMA pump) cost 1500-2500 clk per block on the
+//               tile's critical path; now ~600.
 // Per tile and 64-key block:
 //   S = Q K^T              (SS MMA, fp32 S in TMEM columns [0, 64) of the tile)
 //   softmax warpgroup: S -> registers (one TMEM pass), row max, p = exp2(s log2e - m) (packed fp32x2 FMA, one
@@ -45,16 +51,26 @@ namespace {
 constexpr int kBQ = 128;   // query rows per tile (one TMEM lane per row)
 constexpr int kBKV = 64;   // keys per block
 constexpr int kHD = 64;    // head dim (every DINOv2 size)
-constexpr int kQT = 2;     // query tiles per CTA
-constexpr int kSoftmaxWarps = kQT * 4;   // 8 warps, two per SM sub-partition
-constexpr int kThreads = (kSoftmaxWarps + kQT) * 32;   // + warps 8, 9: MMA issuers of tile 0 / 1 (warp 8 also feeds the K / V ring)
-constexpr int kKVStages = 4;
+#ifndef VVS_ATT_QT
+#define VVS_ATT_QT 1
+#endif
+#ifndef VVS_ATT_STAGES
+#define VVS_ATT_STAGES (2 * VVS_ATT_QT)
+#endif
+#ifndef VVS_ATT_TMA_STORE
+#define VVS_ATT_TMA_STORE 1
+#endif
+
+constexpr int kQT = VVS_ATT_QT;     // query tiles per CTA
+constexpr int kSoftmaxWarps = kQT * 4;   // one warpgroup per tile
+constexpr int kThreads = (kSoftmaxWarps + kQT) * 32;   // + one MMA issuer warp per tile (the first also feeds the K / V ring)
+constexpr int kKVStages = VVS_ATT_STAGES;
 constexpr uint32_t kQBytes = kBQ * kHD * 2;      // 16 KB
 constexpr uint32_t kKVBytes = kBKV * kHD * 2;    // 8 KB: one K or V block
 constexpr uint32_t kOffQ = 0, kOffK = kOffQ + kQT * kQBytes, kOffV = kOffK + kKVStages * kKVBytes,
                    kOffBar = kOffV + kKVStages * kKVBytes;
 constexpr uint32_t kSmem = kOffBar + 256 + 1024;   // + barriers + alignment slack
-constexpr uint32_t kTmemCols = 256;
+constexpr uint32_t kTmemCols = 128 * kQT;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kRescaleLog2 = 8.0f;
 #ifndef VVS_ATT_STAGGER
@@ -128,9 +144,12 @@ __device__ long long g_att_trace[4 * 3 * 16 * 8];
 #define VVS_TR(ev) do { } while (0)
 #endif
 
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, 4 / kQT)
 attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
-                    bf16* __restrict__ out, int n_tok, int D) {
+                    const __grid_constant__ CUtensorMap tmO, bf16* __restrict__ out, int n_tok, int D) {
+#ifdef VVS_ATT_TRACE
+  const long long tr_entry = clock64();
+#endif
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
@@ -205,7 +224,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   pdl_wait();
 
   if (warp >= kSoftmaxWarps) {
-    // ---- warps 8 / 9: MMA issuer of tile 0 / tile 1; warp 8 also feeds the K / V ring.  The whole warp walks the
+    // ---- issuer warps: MMA issuer of tile u; the first one also feeds the K / V ring.  The whole warp walks the
     // loops (every value warp-uniform => uniform datapath, no ELECT / R2UR waterfalls); only the issue instructions
     // are predicated on lane 0.  A softmax warp never issues: its timeline is wait S -> TMEM load -> max / exp ->
     // TMEM store -> arrive.  The issuer's serial chain per block is: see P -> 4 TS MMAs -> 4 SS MMAs -> one commit;
@@ -418,6 +437,36 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     tc_fence_after();
     const int q = (qt0 + t) * kBQ + row;
     const float inv = 1.0f / l_run;
+#if VVS_ATT_TMA_STORE
+    // The tile's Q buffer is free (every S MMA has completed): the normalised bf16 rows go there in the 128-byte
+    // swizzled layout of the output tensor map and leave as ONE TMA store per tile (rows past n_tok are clipped by
+    // the map's per-image extent).  Per-thread global stores of a row each (32 distinct lines per instruction) kept
+    // the warps ~2000 clk longer.
+    {
+      const uint32_t stage = smem_u32(smem + kOffQ + t * kQBytes) + static_cast<uint32_t>(row) * 128u;
+      const uint32_t sw = static_cast<uint32_t>(row & 7);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint32_t ov[32];
+        tmem_ld32(tO + h * 32, ov);
+        tmem_ld_wait();
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          st_shared_v4(stage + ((static_cast<uint32_t>(h * 4 + g) ^ sw) << 4),
+                       pack_bf16x2(__uint_as_float(ov[g * 8 + 0]) * inv, __uint_as_float(ov[g * 8 + 1]) * inv),
+                       pack_bf16x2(__uint_as_float(ov[g * 8 + 2]) * inv, __uint_as_float(ov[g * 8 + 3]) * inv),
+                       pack_bf16x2(__uint_as_float(ov[g * 8 + 4]) * inv, __uint_as_float(ov[g * 8 + 5]) * inv),
+                       pack_bf16x2(__uint_as_float(ov[g * 8 + 6]) * inv, __uint_as_float(ov[g * 8 + 7]) * inv));
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(1 + t, 128);
+      if (wq == 0 && lane == 0) {
+        tma_store_3d(&tmO, smem_u32(smem + kOffQ + t * kQBytes), head * kHD, (qt0 + t) * kBQ, img);
+        bulk_commit();
+        bulk_wait_read0();     // the buffer must outlive the store's read of it
+      }
+    }
+#else
     uint4* dst = reinterpret_cast<uint4*>(out + static_cast<size_t>(row_base + q) * D + head * kHD);
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -436,11 +485,27 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         }
       }
     }
+#endif
   }
 
+#ifdef VVS_ATT_TRACE
+  const long long tr_loop_end = clock64();
+#endif
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc<kTmemCols>(tmem_base);
+#ifdef VVS_ATT_TRACE
+  {   // CTA lifetime: entry, end of this thread's role, exit (slot j = 15 of the issuer row is otherwise unused)
+    const int sl = (blockIdx.z == 5 && blockIdx.y == 3) ? static_cast<int>(blockIdx.x)
+                   : (blockIdx.z == 100 && blockIdx.y == 7) ? 2 + static_cast<int>(blockIdx.x) : -1;
+    if (sl >= 0 && sl < 4 && tid == 0) {
+      long long* o = &g_att_trace[((sl * 3 + 2) * 16 + 15) * 8];
+      o[5] = tr_entry;
+      o[6] = tr_loop_end;
+      o[7] = clock64();
+    }
+  }
+#endif
 }
 
 }  // namespace
@@ -460,6 +525,10 @@ int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int he
   if (rc) return rc;
   rc = make_tmap_bf16(&tmkv, qkv, 3ull * D, rows, 1, 3ull * D, 0, kBKV, err);
   if (rc) return rc;
+  CUtensorMap tmo;   // [n_img][n_tok][D]: the per-image row extent clips the last tile's rows past n_tok
+  rc = make_tmap_bf16(&tmo, out, static_cast<uint64_t>(D), static_cast<uint64_t>(n_tok), static_cast<uint64_t>(n_img),
+                      static_cast<uint64_t>(D), static_cast<uint64_t>(n_tok) * D, kBQ, err);
+  if (rc) return rc;
   static bool attr_set = false;
   if (!attr_set) {
     VVS_CUDA_OK(cudaFuncSetAttribute(attention_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -472,7 +541,7 @@ int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int he
   }
   const int q_tiles = (n_tok + kBQ - 1) / kBQ;
   dim3 grid((q_tiles + kQT - 1) / kQT, heads, n_img);
-  VVS_CUDA_OK(launch_kernel(attention_ts_kernel, grid, kThreads, kSmem, stream, pdl, tmq, tmkv, out, n_tok, D), err);
+  VVS_CUDA_OK(launch_kernel(attention_ts_kernel, grid, kThreads, kSmem, stream, pdl, tmq, tmkv, tmo, out, n_tok, D), err);
   return VVS_OK;
 }
 

@@ -98,7 +98,7 @@ int gemm_block_n(int N);   // the N tile the launcher picks for this N (128 or 2
 // qkv: [n_img * n_tok, 3*D] bf16 (q pre-scaled by hd^-0.5), out: [n_img * n_tok, D] bf16
 int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
                      std::string* err, bool pdl = false);
-// generation 7 (attention_ts.cu): P stays in TMEM (TS MMA), two CTAs per SM; launch_attention dispatches to it
+// generations 7-9 (attention_ts.cu): P stays in TMEM (TS MMA), one tile per CTA and four CTAs per SM; launch_attention dispatches to it
 int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
                         std::string* err, bool pdl = false);
 
