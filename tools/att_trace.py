@@ -24,7 +24,7 @@ for slot in range(4):
     print(f"--- CTA slot {slot}: entry {int(life[5] - t0)}  warp-0 role end {int(life[6] - t0)}  exit {int(life[7] - t0)}  "
           f"(lifetime {int(life[7] - life[5])} clk)")
     print(f"--- CTA slot {slot} (rc {rc}); clk relative to warp 0 loop start")
-    for w, wn in enumerate(["warp0 (tile0)", "warp1 (tile0)", "warp8 issuer, tile 0: 0=p_full seen 1=v ready 2=PV issued 3=S issued"]):
+    for w, wn in enumerate(["warp0 (tile0)", "warp1 (tile0)", "issuer warp, tile 0: top=p_full seen, s_full=PV+S issued, Sregs=next operands landed"]):
         print(" ", wn)
         for j in range(nblk):
             ev = tr[slot, w, j]

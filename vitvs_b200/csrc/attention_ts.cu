@@ -286,8 +286,8 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       wait_feed(&v_full[0], 0);
       if (nblk > 1) wait_feed(&k_full[1 % kKVStages], (1 / kKVStages) & 1);
 #ifdef VVS_ATT_TRACE
-      const int tr8 = (blockIdx.z == 5 && blockIdx.y == 3) ? static_cast<int>(blockIdx.x)
-                      : (blockIdx.z == 100 && blockIdx.y == 7) ? 2 + static_cast<int>(blockIdx.x) : -1;
+      const int tr8 = (blockIdx.z == 5 && blockIdx.y == 3 && blockIdx.x < 2) ? static_cast<int>(blockIdx.x)
+                      : (blockIdx.z == 100 && blockIdx.y == 7 && blockIdx.x < 2) ? 2 + static_cast<int>(blockIdx.x) : -1;
 #define VVS_TR8(ev)                                                                                            \
   do {                                                                                                         \
     if (tr8 >= 0 && tr8 < 4 && u == 0 && lane == 0 && j < 16) g_att_trace[((tr8 * 3 + 2) * 16 + j) * 8 + (ev)] = clock64(); \
@@ -331,8 +331,8 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     float l_run = 0.f;
     const f32x2 log2e2 = f2_pack(kLog2e, kLog2e);
 #ifdef VVS_ATT_TRACE
-    const int tr_slot = (blockIdx.z == 5 && blockIdx.y == 3) ? static_cast<int>(blockIdx.x)
-                        : (blockIdx.z == 100 && blockIdx.y == 7) ? 2 + static_cast<int>(blockIdx.x) : -1;
+    const int tr_slot = (blockIdx.z == 5 && blockIdx.y == 3 && blockIdx.x < 2) ? static_cast<int>(blockIdx.x)
+                        : (blockIdx.z == 100 && blockIdx.y == 7 && blockIdx.x < 2) ? 2 + static_cast<int>(blockIdx.x) : -1;
     const int tr_warp = warp == 0 ? 0 : warp == 1 ? 1 : -1;
     const int tr_ok = tr_warp >= 0 ? tr_slot : -1;
 #undef VVS_TR
@@ -496,8 +496,8 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   if (warp == 0) tmem_dealloc<kTmemCols>(tmem_base);
 #ifdef VVS_ATT_TRACE
   {   // CTA lifetime: entry, end of this thread's role, exit (slot j = 15 of the issuer row is otherwise unused)
-    const int sl = (blockIdx.z == 5 && blockIdx.y == 3) ? static_cast<int>(blockIdx.x)
-                   : (blockIdx.z == 100 && blockIdx.y == 7) ? 2 + static_cast<int>(blockIdx.x) : -1;
+    const int sl = (blockIdx.z == 5 && blockIdx.y == 3 && blockIdx.x < 2) ? static_cast<int>(blockIdx.x)
+                   : (blockIdx.z == 100 && blockIdx.y == 7 && blockIdx.x < 2) ? 2 + static_cast<int>(blockIdx.x) : -1;
     if (sl >= 0 && sl < 4 && tid == 0) {
       long long* o = &g_att_trace[((sl * 3 + 2) * 16 + 15) * 8];
       o[5] = tr_entry;
