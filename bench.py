@@ -182,7 +182,7 @@ def workload_name(model: str, pairs: int) -> str:
 def ncu_traffic(cls):
     """DRAM bytes per launch of a kernel class from the committed ncu capture (ViT-B, 64 pairs only), else None."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r1e_traffic.json")) as fh:
+        with open(os.path.join(ROOT, "profiles", "r1f_traffic.json")) as fh:
             return json.load(fh)["bytes_per_launch"].get(cls)
     except Exception:
         return None
@@ -404,7 +404,7 @@ def run_ours(args):
             "roofline": {"bound": "tensor", "kernel": f"gemm_tc_kernel ({dom})", "achieved": round(achieved, 1),
                          "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": round(achieved / pk["tf_sustained"], 3),
                          "traffic": ncu_traffic(dom) if (args.model == "dinov2_vitb14" and B == 64) else None,
-                         "traffic_unit": "DRAM bytes per launch (profiles/r1e_traffic.json, one ncu --set full capture)",
+                         "traffic_unit": "DRAM bytes per launch (profiles/r1f_traffic.json, one ncu --set full capture)",
                          "peak_source": pk["source"] + ", sustained figure (kernel timed inside a long step)",
                          "avg_launch_ms": round(dom_ms, 4), "flops_per_launch": dom_fl},
             "kernels": kernels,
