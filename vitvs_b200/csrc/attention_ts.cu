@@ -459,7 +459,9 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                        pack_bf16x2(__uint_as_float(ov[g * 8 + 6]) * inv, __uint_as_float(ov[g * 8 + 7]) * inv));
       }
       fence_proxy_async_smem();
-      named_bar_sync(1 + t, 128);
+      // immediate barrier ids: a run-time id makes the compiler reserve all 16 hardware barriers per CTA
+      if (kQT == 1 || t == 0) named_bar_sync<1>(128);
+      else named_bar_sync<2>(128);
       if (wq == 0 && lane == 0) {
         tma_store_3d(&tmO, smem_u32(smem + kOffQ + t * kQBytes), head * kHD, (qt0 + t) * kBQ, img);
         bulk_commit();

@@ -233,8 +233,9 @@ __device__ __forceinline__ float4 ld_global_v4_hint(const float4* ptr, uint64_t 
   return v;
 }
 // barrier among `count` threads (a multiple of 32) on hardware barrier `id` (1..15; 0 is __syncthreads)
-__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t count) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+template <int kId>
+__device__ __forceinline__ void named_bar_sync(uint32_t count) {
+  asm volatile("bar.sync %0, %1;" ::"n"(kId), "r"(count) : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all of this thread's bulk stores have finished READING their smem source (the buffer may be rewritten)
