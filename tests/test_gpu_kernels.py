@@ -193,3 +193,14 @@ def test_layernorm(eng, D):
     ref = torch.nn.functional.layer_norm(x, (D,), w, b, eps=1e-6)
     _, rel = _report(f"layernorm {D}", out, ref)
     assert rel < 6e-3
+
+
+def test_gemm_two_pair_clusters_with_multicast():
+    """VITVS_GEMM_CTAS=4 (experimental): clusters of two CTA pairs sharing the B tile through TMA multicast; the
+    parity script covers bias/bf16 and residual/fp32 epilogues at sizes that take that path, ragged M included."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, VITVS_GEMM_CTAS="4")
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "gemm_check.py")], capture_output=True, text=True,
+                       timeout=300, env=env, cwd=root)
+    assert r.returncode == 0 and r.stdout.strip().endswith("OK"), r.stdout[-1500:] + r.stderr[-1500:]

@@ -56,9 +56,10 @@ struct GemmDev {
 // ~13-15 TB/s while the tensor pipe idles).
 template <int BN, int NCTA>
 struct Cfg {
-  static constexpr int kStages = (NCTA == 2) ? 6 : ((BN == 256) ? 4 : 6);
+  static constexpr int kPair = NCTA >= 2 ? 2 : 1;   // CTAs per MMA (cta_group); NCTA = 4: two pairs sharing the B tile
+  static constexpr int kStages = (NCTA >= 2) ? 6 : ((BN == 256) ? 4 : 6);
   static constexpr uint32_t kABytes = BM * BK * 2;
-  static constexpr uint32_t kBBytes = (BN / NCTA) * BK * 2;
+  static constexpr uint32_t kBBytes = (BN / kPair) * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr uint32_t kTmemCols = 2 * BN;
   static constexpr uint32_t kStagingBytes = 8 * 4096;   // one 32-row x 128-byte transpose buffer per epilogue warp
@@ -127,7 +128,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   // datapath (a plain threadIdx.x >> 5 wraps every tcgen05.mma / TMA issue in an ELECT + R2UR waterfall loop)
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
-  const uint32_t cta_rank = (NCTA == 2) ? cluster_ctarank() : 0u;   // 0 = leader (issues the MMAs)
+  const uint32_t cta_rank = (NCTA >= 2) ? cluster_ctarank() : 0u;
+  const uint32_t pair_rank = cta_rank & 1u;          // 0 = leader of its pair (issues the MMAs)
+  const uint32_t leader_rank = cta_rank & ~1u;       // cluster rank of this CTA's pair leader
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -135,20 +138,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tma_prefetch_desc(&tmOut);
     for (int s = 0; s < C::kStages; ++s) {
       mbar_init(&full[s], 1);     // pair: only the leader's is used; its expect_tx covers both CTAs' boxes
-      mbar_init(&empty[s], 1);
+      mbar_init(&empty[s], NCTA == 4 ? 2 : 1);   // two pairs: a stage is free when BOTH have consumed it
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 8 * NCTA);   // pair: the peer's epilogue warps arrive on the leader's barrier
+      mbar_init(&tempty[a], 8 * C::kPair);   // pair: the peer's epilogue warps arrive on the leader's barrier
     }
     fence_mbar_init();
   }
   if (warp == 1) {
-    if constexpr (NCTA == 2) tmem_alloc_2sm<C::kTmemCols>(tmem_slot);
+    if constexpr (NCTA >= 2) tmem_alloc_2sm<C::kTmemCols>(tmem_slot);
     else tmem_alloc<C::kTmemCols>(tmem_slot);
   }
   tc_fence_before();
-  if constexpr (NCTA == 2) cluster_sync_all();   // peer barriers initialised before any remote arrive / TMA signal
+  if constexpr (NCTA >= 2) cluster_sync_all();   // peer barriers initialised before any remote arrive / TMA signal
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
@@ -168,7 +171,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // only the issue instructions themselves are predicated on lane 0.
     {
       uint32_t stage = 0, phase = 0;
-      const uint32_t full0 = (NCTA == 2) ? mapa_shared(smem_u32(&full[0]), 0) : 0u;   // leader's full[] in cluster space
+      const uint32_t full0 = (NCTA >= 2) ? mapa_shared(smem_u32(&full[0]), leader_rank) : 0u;   // leader's full[] in cluster space
       for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
         const int b = tile / tiles_per_batch;
         const int r = tile - b * tiles_per_batch;
@@ -178,7 +181,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
           if (lane == 0) {
-            if constexpr (NCTA == 2) {
+            if constexpr (NCTA == 4) {
+              // this CTA fetches ONE quarter of the B tile and multicasts it to the CTA of the same parity in the
+              // other pair: every CTA still receives its 128-row half, the L2 -> SM traffic per CTA drops by a quarter
+              if (pair_rank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
+              const uint32_t fb = full0 + stage * 8;
+              const int quarter = static_cast<int>(cta_rank >> 1);
+              tma_load_3d_2sm(sa, &tmA, fb, kb * BK, m_blk * BM, b, kEvictNormal);
+              tma_load_3d_2sm_mc(sa + C::kABytes + quarter * (BN / 4) * BK * 2, &tmB, fb, kb * BK,
+                                 n_blk * BN + static_cast<int>(pair_rank) * (BN / 2) + quarter * (BN / 4),
+                                 p.b_batched ? b : 0, static_cast<uint16_t>((1u << cta_rank) | (1u << (cta_rank ^ 2u))),
+                                 kEvictLast);
+            } else if constexpr (NCTA == 2) {
               if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
               const uint32_t fb = full0 + stage * 8;
               tma_load_3d_2sm(sa, &tmA, fb, kb * BK, m_blk * BM, b, kEvictNormal);
@@ -200,8 +214,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (whole warp walks, lane 0 issues)
-    if (cta_rank == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM * NCTA, BN, false);
+    if (pair_rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM * C::kPair, BN, false);
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
       for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
         mbar_wait(&tempty[acc], acc_phase ^ 1);
@@ -216,10 +230,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
               const uint64_t da = umma_smem_desc(a_addr + k * 32, 16, 1024), db = umma_smem_desc(b_addr + k * 32, 16, 1024);
-              if constexpr (NCTA == 2) umma_bf16_2sm(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+              if constexpr (NCTA >= 2) umma_bf16_2sm(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
               else umma_bf16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
             }
-            if constexpr (NCTA == 2) umma_commit_2sm(&empty[stage], 3);   // frees the stage in both CTAs
+            if constexpr (NCTA == 4) umma_commit_2sm(&empty[stage], 0xF);   // one of the two arrivals, in all four CTAs
+            else if constexpr (NCTA == 2) umma_commit_2sm(&empty[stage], 3);   // frees the stage in both CTAs
             else umma_commit(&empty[stage]);
           }
           __syncwarp();
@@ -229,7 +244,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
         if (lane == 0) {
-          if constexpr (NCTA == 2) umma_commit_2sm(&tfull[acc], 3);
+          if constexpr (NCTA >= 2) umma_commit_2sm(&tfull[acc], static_cast<uint16_t>(3u << leader_rank));
           else umma_commit(&tfull[acc]);
         }
         __syncwarp();
@@ -253,7 +268,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const uint32_t my_row_s = stg_s + lane * 128;
     const uint32_t sw = static_cast<uint32_t>(lane & 7);
     uint32_t acc = 0, acc_phase = 0;
-    const uint32_t tempty0 = (NCTA == 2) ? mapa_shared(smem_u32(&tempty[0]), 0) : 0u;   // leader's tempty[]
+    const uint32_t tempty0 = (NCTA >= 2) ? mapa_shared(smem_u32(&tempty[0]), leader_rank) : 0u;   // leader's tempty[]
     for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
       const int b = tile / tiles_per_batch;
       const int r = tile - b * tiles_per_batch;
@@ -476,7 +491,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
-        if constexpr (NCTA == 2) mbar_arrive_cluster(tempty0 + acc * 8);
+        if constexpr (NCTA >= 2) mbar_arrive_cluster(tempty0 + acc * 8);
         else mbar_arrive(&tempty[acc]);
       }
       acc ^= 1;
@@ -486,7 +501,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 
   tc_fence_before();
-  if constexpr (NCTA == 2) {
+  if constexpr (NCTA >= 2) {
     cluster_sync_all();   // the peer may still be reading operands / signalling barriers of this CTA
     if (warp == 1) tmem_dealloc_2sm<C::kTmemCols>(tmem_base);
   } else {
@@ -617,10 +632,13 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   }
   const int bn = gemm_block_n(a.N);
   // CTA pairs by default; VITVS_GEMM_CTAS=1 selects the single-CTA kernels (A/B experiments)
-  static const int ncta = []() {
+  // VITVS_GEMM_CTAS=4 (experiment): clusters of two pairs that share the B tile through TMA multicast
+  static const int ncta_env = []() {
     const char* e = getenv("VITVS_GEMM_CTAS");
-    return (e && e[0] == '1') ? 1 : 2;
+    return (e && e[0] == '1') ? 1 : (e && e[0] == '4') ? 4 : 2;
   }();
+  // two-pair clusters only where they pay: 256-wide tiles, one problem, at least a few 512-row cluster tiles
+  const int ncta = (ncta_env == 4 && !(bn == 256 && a.batch == 1 && a.M >= 4096)) ? 2 : ncta_env;
   if (a.epilogue == EPI_SWIGLU_BF16 && (bn != 256 || a.N % bn)) {
     set_error(err, "launch_gemm: SwiGLU needs N to be a multiple of the 256-wide N tile");
     return VVS_ERR_INVALID;
@@ -635,7 +653,7 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   int rc = make_tmap_bf16(&tmA, a.A, a.K, a.M, a.batch, a.lda, a.a_batch_pitch, BM, err);
   if (rc) return rc;
   const bool b_batched = a.b_batch_pitch != 0;
-  rc = make_tmap_bf16(&tmB, a.B, a.K, a.N, b_batched ? a.batch : 1, a.ldb, a.b_batch_pitch, bn / ncta, err);
+  rc = make_tmap_bf16(&tmB, a.B, a.K, a.N, b_batched ? a.batch : 1, a.ldb, a.b_batch_pitch, bn / ncta, err);   // pair: half, two pairs: quarter
   if (rc) return rc;
   CUtensorMap tmOut = tmA;   // unused by the epilogues that write with plain stores
   if (a.epilogue == EPI_RESID_F32 || a.epilogue == EPI_PATCH_F32)
@@ -655,6 +673,28 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   d.row_best = a.row_best; d.col_best = a.col_best; d.best_pitch = a.best_pitch;
   d.pin_row0 = a.pin_row0 > 0 ? a.pin_row0 : 0x7fffffff;
   const long long tiles = static_cast<long long>(d.batch) * d.m_tiles * d.n_tiles;
+  if (ncta == 4) {
+    // co-resident 4-CTA clusters (a GPC with an odd number of TPCs leaves one TPC out)
+    static int max_clusters = -1;
+    if (max_clusters < 0) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(4 * (num_sms / 4));
+      cfg.blockDim = dim3(kGemmThreads);
+      cfg.dynamicSmemBytes = Cfg<256, 4>::kSmemBytes;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = 4; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      cfg.attrs = at; cfg.numAttrs = 1;
+      cudaFuncSetAttribute(gemm_tc_kernel<256, EPI_BIAS_BF16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           static_cast<int>(Cfg<256, 4>::kSmemBytes));
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<256, EPI_BIAS_BF16, 4>, &cfg) != cudaSuccess || n < 1) n = num_sms / 4;
+      max_clusters = n;
+      if (getenv("VITVS_VERBOSE")) fprintf(stderr, "[vitvs] 4-CTA GEMM clusters co-resident: %d of %d\n", n, num_sms / 4);
+    }
+    const int grid = 4 * static_cast<int>(std::min<long long>(tiles, max_clusters));
+    return dispatch_epi<256, 4>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
+  }
   if (ncta == 2) {
     const int grid = 2 * static_cast<int>(std::min<long long>(tiles, num_sms / 2));
     if (bn == 256) return dispatch_epi<256, 2>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);

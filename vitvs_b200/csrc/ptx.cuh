@@ -327,6 +327,17 @@ __device__ __forceinline__ void tma_load_3d_2sm(void* smem_dst, const void* tmap
       "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2), "l"(hint)
       : "memory");
 }
+// the same, delivered to every CTA in `cta_mask` (same CTA-relative destination offset); measured
+// (tools/ubench/mcast_probe): the complete_tx lands on the barrier at `bar_cluster_addr`'s offset in EACH destination's
+// own pair leader, so a pair's MMA issuer still waits on one barrier.
+__device__ __forceinline__ void tma_load_3d_2sm_mc(void* smem_dst, const void* tmap, uint32_t bar_cluster_addr, int c0,
+                                                   int c1, int c2, uint16_t cta_mask, uint64_t hint) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+      ".L2::cache_hint [%0], [%1, {%3, %4, %5}], [%2], %6, %7;" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2), "h"(cta_mask), "l"(hint)
+      : "memory");
+}
 template <uint32_t kCols>
 __device__ __forceinline__ void tmem_alloc_2sm(uint32_t* smem_result) {  // one full warp in EACH CTA of the pair
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_result)),
