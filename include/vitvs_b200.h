@@ -10,7 +10,9 @@
  * says _host); the library owns only its workspace and its bf16 copies of the weights inside the
  * handle.  Every call returns 0 or a negative vvs_status (no exceptions cross the ABI) and
  * vvs_last_error() gives the message.  Calls are stream-ordered and asynchronous unless documented
- * otherwise.  One handle per device, re-entrant across handles, not thread-safe per handle.
+ * otherwise.  Any number of handles per process and per device (every call switches to its handle's device for
+ * its duration), re-entrant across handles, not thread-safe per handle.  A handle's workspace is shared by its
+ * calls: a call on a different stream than the previous one first waits (on the device) for that call to finish.
  * There is no CPU fallback: on a machine without an sm_100 GPU vvs_create() fails.
  */
 #ifndef VITVS_B200_H_
@@ -82,6 +84,9 @@ VVS_API int vvs_destroy(vvs_handle h);
 /* message of the last failing call on this handle (h may be NULL: last vvs_create failure). */
 VVS_API const char* vvs_last_error(vvs_handle h);
 VVS_API int vvs_num_sms(vvs_handle h);
+/* hash of the CUDA sources this library was compiled from (vitvs_b200/build.py computes it; smoke() compares it with
+ * the sources next to the .so, so a stale binary cannot pass for the tree it travels with). */
+VVS_API const char* vvs_build_id(void);
 
 /* replaces: the state_dict torch.hub.load() fills (dinov2_extractor.py:65-67).  `name` uses the upstream
  * DINOv2 parameter names: patch_embed.proj.{weight,bias}, cls_token, blocks.<i>.norm{1,2}.{weight,bias},
@@ -131,11 +136,18 @@ typedef struct vvs_match_out { /* every pointer optional (NULL = not wanted), de
   float* mean_sim1;      /* [n_pairs] */
   int32_t* n_candidates; /* [n_pairs] */
   int32_t* n_selected;   /* [n_pairs]   min(num_pairs, n_candidates) */
-  int32_t* flags;        /* [n_pairs]   bit 0: same-image branch taken (:84-101) */
+  int32_t* flags;        /* [n_pairs]   bit 0: same-image branch taken (:84-101); bit 1: a row / column of S had
+                            no comparable value (NaN descriptors) - its indices are reported as 0 */
   int32_t* sel_tok;      /* [n_pairs, num_pairs] chosen goal tokens, best similarity first, -1 padded */
   float* sel_sim;        /* [n_pairs, num_pairs] */
   int32_t* uv_star;      /* [n_pairs, num_pairs, 2] goal keypoints (u,v) in camera pixels (:511-553) */
   int32_t* uv;           /* [n_pairs, num_pairs, 2] current keypoints */
+  /* INPUT (optional): reference-faithful selection (vitvs_v2.py:139-141, :90-91).  NULL = the num_pairs best
+   * candidates by similarity (deterministic; the benchmark default).  Otherwise a priority list of goal tokens per
+   * pair [n_pairs, T] int32 - e.g. a host torch.randperm(T) - and the first num_pairs of its entries that are
+   * candidates are selected, in list order: a uniform random subset of the mutual-NN set like the reference's
+   * perm[:num_to_select]; in the same-image branch exactly perm[:num_points]. */
+  const int32_t* sel_order;
 } vvs_match_out;
 
 /* replaces: chunk_cosine_sim + find_correspondences_batch + calculate_uv (vitvs_v2.py:49-155, 511-553) on
@@ -156,6 +168,16 @@ VVS_API int vvs_similarity(vvs_handle h, const float* desc1, const float* desc2,
  * twist_raw (optional) is the value before smoothing. */
 VVS_API int vvs_ibvs(vvs_handle h, const int32_t* uv, const int32_t* uv_star, const uint16_t* depth, int32_t n_pairs,
              int32_t K, double* twist, double* twist_raw, double* ema_state, int32_t* ema_init, vvs_stream stream);
+
+/* replaces: Controller.transform_to_real_world(s_uv, s_uv_star) (vitvs_v2.py:634-648) with the reference's own
+ * arguments - no depth frame involved: uv / uv_star [n_points, 2] int32 -> xy / xy_star [n_points, 2] fp64
+ * (either pair may be NULL). */
+VVS_API int vvs_transform_to_real_world(vvs_handle h, const int32_t* uv, const int32_t* uv_star, int32_t n_points,
+                                double* xy, double* xy_star, vvs_stream stream);
+/* replaces: Controller.calculate_interaction_matrix(s_xy, Z) (vitvs_v2.py:650-659) with the reference's own
+ * arguments: xy [n_points, 2], z [n_points] fp64 -> L [2 * n_points, 6] fp64, bit-identical to numpy's IEEE result. */
+VVS_API int vvs_interaction_matrix(vvs_handle h, const double* xy, const double* z, int32_t n_points, double* L,
+                           vvs_stream stream);
 
 /* replaces, term by term: Controller.get_depth -> z [n_pairs,K]; transform_to_real_world -> xy / xy_star
  * [n_pairs,K,2]; calculate_interaction_matrix -> L [n_pairs,2K,6] (vitvs_v2.py:566-586, 634-659); any output

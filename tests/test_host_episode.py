@@ -13,8 +13,11 @@ class _IdealEngine:
     device = torch.device("cpu")
     max_images = 64
 
-    def __init__(self, goal_pose, gain=0.2, fail_from=None, noise=0.0):
+    tokens = 484
+
+    def __init__(self, goal_pose, gain=0.2, fail_from=None, noise=0.0, fail_until=None, fail_nsel=0):
         self.cfg = ServoConfig()
+        self.fail_until, self.fail_nsel = fail_until, fail_nsel
         self.goal = goal_pose
         self.gain, self.fail_from, self.calls = gain, fail_from, 0
         self._poses = None
@@ -25,8 +28,9 @@ class _IdealEngine:
         n = poses.shape[0]
         return torch.zeros(n, 4, 4, 3, dtype=torch.uint8), torch.zeros(n, 4, 4, dtype=torch.uint16)
 
-    def frames_to_twist(self, goal, cur, depth, want_match=False):
+    def frames_to_twist(self, goal, cur, depth, want_match=False, sel_order=None):
         self.calls += 1
+        self.last_order = sel_order
         tw = []
         for p in self._poses:
             R, t = p[:9].reshape(3, 3), p[9:]
@@ -37,6 +41,12 @@ class _IdealEngine:
             tw.append(np.concatenate([v, w]) + self.noise * self.rng.normal(size=6))
         n = len(tw)
         nsel = 24 if self.fail_from is None or self.calls < self.fail_from else 0
+        if self.fail_until is not None and self.fail_from <= self.calls < self.fail_until:
+            nsel = self.fail_nsel
+        elif self.fail_until is not None:
+            nsel = 24
+        if 0 < nsel < 4:
+            tw = [np.zeros(6) for _ in tw]            # the kernel's answer for 1 <= n < 4 pairs: all-zero key-points, zero twist
         return dict(twist=torch.from_numpy(np.array(tw)), n_selected=torch.full((n,), nsel, dtype=torch.int32),
                     mean_sim_sel=torch.ones(n))
 
@@ -74,13 +84,14 @@ def test_ideal_controller_converges_and_stops_by_rule(tmp_path):
     for r in b2.run():
         assert r["converged"] and 300 <= r["iterations"] < 2000
     e = b.episodes[0]
-    assert len(e.velocity_vector_history) == e.iteration_count == len(e.applied)
+    assert e.iteration_count == len(e.applied) == len(e.average_velocities) == 400
+    assert len(e.velocity_vector_history) == 200                    # trimmed at max_velocity_vector_history (:627-628)
     # EMA (vitvs_v2.py:329-343): first sample copied, then alpha * new + (1 - alpha) * old
     a = ServoConfig().ema_alpha
     assert a == 0.8
     # ROS twist re-mapping of publish_twist (vitvs_v2.py:668-676)
-    v = e.velocity_vector_history[5]
-    assert np.allclose(e.applied[5], [v[2], -v[0], -v[1], v[5], -v[3], -v[4]])
+    v = e.velocity_vector_history[-1]                               # the last iteration's twist (below the clip limit)
+    assert np.allclose(e.applied[-1], [v[2], -v[0], -v[1], v[5], -v[3], -v[4]])
     path = str(tmp_path / "r.npz")
     b.save_npz(path, 1.5)
     z = np.load(path, allow_pickle=True)
@@ -98,7 +109,66 @@ def test_divergence_and_feature_failure_abort():
     eng = _IdealEngine(goal, fail_from=3)
     b = episode.EpisodeBatch(eng, np.zeros((4, 4, 3), np.uint8), goal, start, dt=1.0, min_iterations=5, max_iterations=500)
     b.run()
-    assert b.episodes[0].aborted == "Persistent feature detection failure" and b.episodes[0].iteration_count == 12
+    # calls 1-2 succeed, calls 3-11 fail but the loop goes on with the last twist, the 10th failure (call 12) raises
+    # inside ibvs() BEFORE that iteration is counted (vitvs_v2.py:745-758)
+    assert b.episodes[0].aborted == "Persistent feature detection failure" and b.episodes[0].iteration_count == 11
+
+
+def test_feature_failure_keeps_the_camera_moving():
+    """vitvs_v2.py:740-793: a failed detection makes ibvs() return early, but run() still republishes the
+    previous self.v_c, integrates the pose, appends the histories and evaluates the stopping rule; only the failure
+    counter notices.  The velocity window of the stopping rule gets no new entry (it is appended inside ibvs())."""
+    goal = episode.make_pose((0, 0, -0.61))
+    start = [episode.make_pose((0.05, 0.0, -0.7))]
+    eng = _IdealEngine(goal, fail_from=3, fail_until=6)                       # calls 3, 4, 5 fail, then recover
+    b = episode.EpisodeBatch(eng, np.zeros((4, 4, 3), np.uint8), goal, start, dt=1.0, min_iterations=5, max_iterations=8)
+    e = b.episodes[0]
+    for _ in range(2):
+        b.step()
+    v_before, pose_before = e.v_c.copy(), e.pose.copy()
+    b.step()                                                                  # call 3: no features
+    assert e.failures == 1 and e.iteration_count == 3 and np.array_equal(e.v_c, v_before)
+    assert np.allclose(e.pose, episode.integrate_twist(pose_before, v_before, 1.0))     # moved by the PREVIOUS twist
+    assert len(e.velocity_vector_history) == 2 and len(e.applied) == 3 and len(e.position_history) == 3
+    b.step(); b.step()
+    assert e.failures == 3
+    b.step()                                                                  # call 6: features again
+    assert e.failures == 0 and len(e.velocity_vector_history) == 3 and not e.aborted
+    # a failure before any twist exists: run() trips over np.abs(None) and returns its error tuple (:762, :819-821)
+    eng = _IdealEngine(goal, fail_from=1)
+    b = episode.EpisodeBatch(eng, np.zeros((4, 4, 3), np.uint8), goal, start, dt=1.0, min_iterations=5, max_iterations=8)
+    b.step()
+    assert b.episodes[0].done and b.episodes[0].aborted.startswith("Error in run loop") and b.episodes[0].iteration_count == 0
+
+
+def test_fewer_than_four_pairs_is_a_zero_twist_through_the_ema():
+    """1 <= n < 4 matches: calculate_uv returns num_pairs all-zero rows (vitvs_v2.py:539-541), len >= 4 passes :603,
+    the error vector is zero, v = 0, and that zero goes through update_ema and is published."""
+    goal = episode.make_pose((0, 0, -0.61))
+    start = [episode.make_pose((0.05, 0.0, -0.7))]
+    eng = _IdealEngine(goal, fail_from=3, fail_until=4, fail_nsel=2)
+    b = episode.EpisodeBatch(eng, np.zeros((4, 4, 3), np.uint8), goal, start, dt=1.0, min_iterations=5, max_iterations=8)
+    e = b.episodes[0]
+    b.step(); b.step()
+    v2 = e.v_c.copy()
+    b.step()                                                                  # two pairs only
+    a = ServoConfig().ema_alpha
+    assert e.failures == 0 and np.allclose(e.v_c, (1 - a) * v2)               # alpha * 0 + (1 - alpha) * previous
+    assert len(e.velocity_vector_history) == 3 and e.iteration_count == 3
+
+
+def test_random_selection_hands_a_seeded_permutation_to_the_fused_call():
+    goal = episode.make_pose((0, 0, -0.61))
+    starts = [episode.make_pose((0.05, 0.0, -0.7)), episode.make_pose((0.0, 0.03, -0.6))]
+    orders = []
+    for _ in range(2):
+        eng = _IdealEngine(goal)
+        b = episode.EpisodeBatch(eng, np.zeros((4, 4, 3), np.uint8), goal, starts, random_selection=True)
+        b.step()
+        orders.append(eng.last_order.clone())
+    assert orders[0].shape == (2, 484) and orders[0].dtype == torch.int32 and torch.equal(orders[0], orders[1])
+    assert torch.equal(orders[0][0].sort().values, torch.arange(484, dtype=torch.int32))
+    assert not torch.equal(orders[0][0], orders[0][1])
 
 
 def test_velocity_clip():
@@ -108,7 +178,9 @@ def test_velocity_clip():
     b = episode.EpisodeBatch(eng, np.zeros((4, 4, 3), np.uint8), goal, [episode.make_pose((0.3, 0, -0.61))], dt=0.1,
                              min_iterations=1, max_iterations=3, cfg=eng.cfg)
     b.step()
-    assert np.abs(b.episodes[0].velocity_vector_history[0]).max() <= 0.1 + 1e-15
+    e = b.episodes[0]
+    assert np.abs(e.velocity_vector_history[0]).max() > 0.1          # the history keeps the UNCLIPPED EMA twist (:623-626)
+    assert np.abs(np.array(e.applied[0])).max() <= 0.1 + 1e-15       # what is published (and integrated) is clipped
 
 
 def test_oracle_render_geometry():

@@ -35,7 +35,7 @@ class Config(C.Structure):
 class MatchOut(C.Structure):
     _fields_ = [(n, c_vp) for n in (
         "nn1", "nn2", "sim1", "candidate", "mean_sim1", "n_candidates", "n_selected", "flags",
-        "sel_tok", "sel_sim", "uv_star", "uv")]
+        "sel_tok", "sel_sim", "uv_star", "uv", "sel_order")]
 
 
 class PairOut(C.Structure):
@@ -48,6 +48,9 @@ SYMBOLS = {
     "vvs_destroy": (c_i32, [c_vp]),
     "vvs_last_error": (C.c_char_p, [c_vp]),
     "vvs_num_sms": (c_i32, [c_vp]),
+    "vvs_build_id": (C.c_char_p, []),
+    "vvs_transform_to_real_world": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp]),
+    "vvs_interaction_matrix": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
     "vvs_set_weight": (c_i32, [c_vp, C.c_char_p, c_vp, c_i32, C.POINTER(c_i64), c_i32, c_vp]),
     "vvs_weights_ready": (c_i32, [c_vp]),
     "vvs_forward_tokens": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp]),

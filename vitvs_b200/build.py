@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libvitvs_b200.so")
-SOURCES = ["api.cu", "gemm_tc.cu", "attention_tc.cu", "attention_ts.cu", "elementwise.cu", "match_ibvs.cu", "resize.cu", "gram_stencil.cu", "render.cu"]
+SOURCES = ["api.cu", "gemm_tc.cu", "attention_ts.cu", "elementwise.cu", "match_ibvs.cu", "resize.cu", "gram_stencil.cu", "render.cu"]
 HEADERS = ["ptx.cuh", "vvs_internal.h", os.path.join("..", "..", "include", "vitvs_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -25,12 +25,31 @@ def _nvcc() -> str | None:
     return shutil.which("nvcc") or (os.path.exists("/usr/local/cuda/bin/nvcc") and "/usr/local/cuda/bin/nvcc") or None
 
 
+def source_id() -> str:
+    """sha256 (first 16 hex digits) over the CUDA sources and headers the library is compiled from, in a fixed order.
+    Compiled into the .so as vvs_build_id(); smoke() compares the two on the GPU box, so a binary built from other
+    (e.g. uncommitted, since edited) sources cannot pass for the tree it travels with."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in SOURCES + HEADERS:
+        with open(os.path.join(CSRC, f), "rb") as fh:
+            h.update(f.encode() + b"\0" + fh.read())
+    return h.hexdigest()[:16]
+
+
+def binary_id(path: str = LIB) -> str | None:
+    """The id compiled into an existing .so (read from the file, not by loading it)."""
+    try:
+        with open(path, "rb") as fh:
+            blob = fh.read()
+    except OSError:
+        return None
+    i = blob.find(b"VVSBUILD:")
+    return blob[i + 9:i + 25].decode("ascii", "replace") if i >= 0 else None
+
+
 def needs_build() -> bool:
-    if not os.path.exists(LIB):
-        return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS]
-    return any(os.path.getmtime(d) > t for d in deps)
+    return not os.path.exists(LIB) or binary_id() != source_id()
 
 
 def build_variant(name: str, defines: list[str]) -> str:
@@ -38,7 +57,8 @@ def build_variant(name: str, defines: list[str]) -> str:
     nvcc = _nvcc()
     out = os.path.join(HERE, f"libvitvs_b200_{name}.so")
     srcs = [os.path.join(CSRC, f) for f in SOURCES]
-    subprocess.check_call([nvcc, *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-shared", "-o", out, *srcs])
+    subprocess.check_call([nvcc, *NVCC_FLAGS, f'-DVVS_BUILD_ID="{source_id()}"', *[f"-D{d}" for d in defines], "-shared",
+                           "-o", out, *srcs])
     return out
 
 
@@ -57,7 +77,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     for src in SOURCES:
         obj = os.path.join(build_dir, src.replace(".cu", ".o"))
         objs.append(obj)
-        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc, *NVCC_FLAGS, f'-DVVS_BUILD_ID="{source_id()}"', "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

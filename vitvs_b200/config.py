@@ -26,6 +26,7 @@ class ServoConfig:
     use_feature_binning: bool = True
     ema_alpha: float = 0.8
     max_velocity: float = 1.0
+    max_velocity_vector_history: int = 200
     # hard-coded in the reference
     model_type: str = "dinov2_vits14"        # vitvs_v2.py:250
     stride: int = 14                          # vitvs_v2.py:250

@@ -149,6 +149,10 @@ struct vvs_ctx {
   std::vector<GraphEntry> graphs;
   std::vector<int> eager_calls;      // n_pairs values that already ran eagerly once (lazy init done)
   bool graphs_enabled = true;
+  // cross-call ordering of the shared workspace: recorded at the end of every call that touches it
+  cudaEvent_t ws_done = nullptr;
+  cudaStream_t ws_stream = nullptr;
+  bool ws_used = false;
 };
 
 namespace {
@@ -163,6 +167,37 @@ int fail(vvs_ctx* c, int code, const std::string& msg) {
   if (c) c->err = msg; else g_create_error = msg;
   return code;
 }
+
+// Every C-ABI entry runs on its handle's device whatever the caller's current device is (several handles on several
+// GPUs in one process), and restores the caller's device on return.
+struct DeviceGuard {
+  int prev = -1;
+  bool switched = false;
+  explicit DeviceGuard(const vvs_ctx* c) {
+    if (c && cudaGetDevice(&prev) == cudaSuccess && prev != c->device) switched = cudaSetDevice(c->device) == cudaSuccess;
+  }
+  ~DeviceGuard() {
+    if (switched) cudaSetDevice(prev);
+  }
+};
+
+// The workspace (x / h / big / desc / staging / match buffers) is shared by every call on a handle.  Calls are
+// stream-ordered and asynchronous, so a call on stream B must not start overwriting it while the previous call
+// on stream A still runs: each workspace-touching entry waits for the previous one's end-of-call event when the
+// stream changed, and records its own at the end.
+struct WorkspaceOrder {
+  vvs_ctx* c;
+  cudaStream_t s;
+  WorkspaceOrder(vvs_ctx* c_, cudaStream_t s_) : c(c_), s(s_) {
+    if (c->ws_used && c->ws_stream != s) cudaStreamWaitEvent(s, c->ws_done, 0);
+  }
+  ~WorkspaceOrder() {
+    if (cudaEventRecord(c->ws_done, s) == cudaSuccess) {
+      c->ws_used = true;
+      c->ws_stream = s;
+    }
+  }
+};
 
 // brackets one kernel launch with events on the launching stream when profiling is enabled
 struct ProfScope {
@@ -345,6 +380,7 @@ int match_tail(vvs_ctx* c, int n_pairs, int T, int grid_w, int K, const vvs_matc
   a.nn1 = c->nn1; a.nn2 = c->nn2; a.sim1 = c->sim1; a.candidate = c->cand;
   a.mean_sim1 = c->mean_sim1; a.n_candidates = c->n_cand; a.n_selected = c->n_sel; a.flags = c->flags;
   a.sel_tok = c->sel_tok; a.sel_sim = c->sel_sim; a.uv_star = c->uv_star; a.uv = c->uv;
+  a.sel_order = out ? out->sel_order : nullptr;
   { ProfScope ps(c, VVS_K_SELECT, s);
     rc = launch_select(a, s, &c->err); }
   if (rc) return rc;
@@ -643,7 +679,9 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
   }
   uint8_t* land_goal = c->stage_frames;
   uint8_t* land_cur = c->stage_frames + static_cast<size_t>(n_pairs) * in_bytes;
-  // the previous call synchronised, so every staging buffer is free.  Copy order: the frames of every sub-batch
+  // a previous (asynchronous, device-buffer) call may still be reading the staging buffers: the copies wait for it
+  if (c->ws_used) VVS_CUDA_OK(cudaStreamWaitEvent(c->copy_stream, c->ws_done, 0), &c->err);
+  // Copy order: the frames of every sub-batch
   // first, the depth maps (read only by the control law at the end of a sub-batch) behind them.
   for (int j = 0; j < chunks; ++j) {
     const int p0 = parts[j].first, nc = parts[j].second;
@@ -794,7 +832,8 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
   }
   if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
-      cudaEventCreateWithFlags(&c->depth_ready, cudaEventDisableTiming) != cudaSuccess) {
+      cudaEventCreateWithFlags(&c->depth_ready, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ws_done, cudaEventDisableTiming) != cudaSuccess) {
     g_create_error = "vvs_create: cudaStreamCreateWithFlags failed";
     vvs_destroy(c);
     return VVS_ERR_CUDA;
@@ -821,6 +860,8 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
 
 int vvs_destroy(vvs_handle c) {
   if (!c) return VVS_OK;
+  DeviceGuard dg(c);
+  cudaDeviceSynchronize();   // asynchronous calls may still be using the workspace
   for (auto& g : c->graphs) {
     cudaGraphExecDestroy(g.execA);
     cudaGraphExecDestroy(g.execB);
@@ -828,6 +869,7 @@ int vvs_destroy(vvs_handle c) {
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->depth_ready) cudaEventDestroy(c->depth_ready);
+  if (c->ws_done) cudaEventDestroy(c->ws_done);
   for (cudaEvent_t e : c->chunk_events) cudaEventDestroy(e);
   free_resize_axis(&c->rz_w);
   free_resize_axis(&c->rz_h);
@@ -850,12 +892,21 @@ int vvs_destroy(vvs_handle c) {
 
 const char* vvs_last_error(vvs_handle c) { return c ? c->err.c_str() : g_create_error.c_str(); }
 int vvs_num_sms(vvs_handle c) { return c ? c->num_sms : 0; }
+#ifndef VVS_BUILD_ID
+#define VVS_BUILD_ID "unknown"
+#endif
+// the "VVSBUILD:" marker lets build.py read the id of an existing binary without loading it
+const char* vvs_build_id(void) {
+  static const char tagged[] = "VVSBUILD:" VVS_BUILD_ID;
+  return tagged + 9;
+}
 int vvs_last_launch_count(vvs_handle c) { return c ? c->launch_count : 0; }
 int vvs_set_num_pairs(vvs_handle c, int32_t num_pairs) {
   if (!c) return VVS_ERR_INVALID;
   if (num_pairs < 1 || num_pairs > c->k_cap)
     return fail(c, VVS_ERR_INVALID, "vvs_set_num_pairs: outside [1, max(num_pairs at creation, 64)]");
   if (num_pairs == c->cfg.num_pairs) return VVS_OK;
+  DeviceGuard dg(c);
   c->cfg.num_pairs = num_pairs;
   for (auto& g : c->graphs) {      // K is baked into the captured launches
     cudaGraphExecDestroy(g.execA);
@@ -871,6 +922,7 @@ int vvs_set_weight(vvs_handle c, const char* name_c, const void* p, int32_t dtyp
                    vvs_stream stream) {
   if (!c || !name_c || !p || !shape) return fail(c, VVS_ERR_INVALID, "vvs_set_weight: null argument");
   if (dtype != VVS_F32 && dtype != VVS_BF16) return fail(c, VVS_ERR_INVALID, "vvs_set_weight: dtype must be f32 or bf16");
+  DeviceGuard dg(c);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const std::string name(name_c);
   const int D = c->cfg.dim, H = c->cfg.ffn_hidden;
@@ -947,12 +999,16 @@ int vvs_weights_ready(vvs_handle c) {
 
 int vvs_forward_tokens(vvs_handle c, const void* images, int32_t kind, int32_t n_img, int32_t layer, vvs_stream stream) {
   if (!c || !images) return fail(c, VVS_ERR_INVALID, "vvs_forward_tokens: null argument");
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, static_cast<cudaStream_t>(stream));
   c->launch_count = 0;
   return forward_tokens(c, images, kind, n_img, layer, static_cast<cudaStream_t>(stream));
 }
 
 int vvs_forward_facet(vvs_handle c, const void* images, int32_t kind, int32_t n_img, int32_t layer, vvs_stream stream) {
   if (!c || !images) return fail(c, VVS_ERR_INVALID, "vvs_forward_facet: null argument");
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, static_cast<cudaStream_t>(stream));
   c->launch_count = 0;
   return forward_tokens(c, images, kind, n_img, layer, static_cast<cudaStream_t>(stream), /*stop_after_qkv=*/true);
 }
@@ -965,6 +1021,8 @@ int vvs_facet_descriptors(vvs_handle c, int32_t n_img, int32_t facet, int32_t bi
     return fail(c, VVS_ERR_INVALID, "bin = True and include_cls = True are not supported together");   // dinov2_extractor.py:332
   if (n_img < 1 || n_img > c->facet_n_img)
     return fail(c, VVS_ERR_STATE, "vvs_facet_descriptors: no vvs_forward_facet pass holds that many images");
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, static_cast<cudaStream_t>(stream));
   ++c->launch_count;
   return launch_facet_descriptors_f32(c->big, out, n_img, c->grid, c->grid, c->cfg.dim, c->cfg.heads, facet, bin,
                                       include_cls, static_cast<cudaStream_t>(stream), &c->err);
@@ -973,6 +1031,8 @@ int vvs_facet_descriptors(vvs_handle c, int32_t n_img, int32_t facet, int32_t bi
 int vvs_get_tokens(vvs_handle c, float* out, int32_t n_img, vvs_stream stream) {
   if (!c || !out) return fail(c, VVS_ERR_INVALID, "vvs_get_tokens: null argument");
   if (n_img < 1 || n_img > c->last_n_img) return fail(c, VVS_ERR_STATE, "vvs_get_tokens: no forward pass holds that many images");
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, static_cast<cudaStream_t>(stream));
   VVS_CUDA_OK(cudaMemcpyAsync(out, c->x, static_cast<size_t>(n_img) * c->N * c->cfg.dim * sizeof(float),
                               cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)),
               &c->err);
@@ -982,6 +1042,8 @@ int vvs_get_tokens(vvs_handle c, float* out, int32_t n_img, vvs_stream stream) {
 int vvs_descriptors(vvs_handle c, int32_t n_img, int32_t bin, float* out, vvs_stream stream) {
   if (!c || !out) return fail(c, VVS_ERR_INVALID, "vvs_descriptors: null argument");
   if (n_img < 1 || n_img > c->last_n_img) return fail(c, VVS_ERR_STATE, "vvs_descriptors: no forward pass holds that many images");
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, static_cast<cudaStream_t>(stream));
   ++c->launch_count;
   return launch_descriptors_f32(c->x, out, n_img, c->grid, c->grid, c->cfg.dim, bin, static_cast<cudaStream_t>(stream),
                                 &c->err);
@@ -992,6 +1054,8 @@ int vvs_descriptors_hierarchy(vvs_handle c, int32_t n_img, int32_t hierarchy, fl
   if (hierarchy < 1 || hierarchy > 4) return fail(c, VVS_ERR_INVALID, "vvs_descriptors_hierarchy: hierarchy outside [1, 4]");
   if (n_img < 1 || n_img > c->last_n_img)
     return fail(c, VVS_ERR_STATE, "vvs_descriptors_hierarchy: no forward pass holds that many images");
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, static_cast<cudaStream_t>(stream));
   ++c->launch_count;
   return launch_descriptors_hier_f32(c->x, out, n_img, c->grid, c->grid, c->cfg.dim, hierarchy,
                                      static_cast<cudaStream_t>(stream), &c->err);
@@ -1003,6 +1067,8 @@ int vvs_match(vvs_handle c, const float* d1, const float* d2, int32_t n_pairs, i
   if (n_pairs < 1 || T < 1 || d < 1 || grid_w < 1 || num_pairs < 1)
     return fail(c, VVS_ERR_INVALID, "vvs_match: empty problem");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, s);
   c->launch_count = 0;
   int dpad = 0;
   int rc = normalise_caller_descriptors(c, d1, d2, n_pairs, T, d, &dpad, s);
@@ -1014,6 +1080,8 @@ int vvs_similarity(vvs_handle c, const float* d1, const float* d2, int32_t n_pai
                    vvs_stream stream) {
   if (!c || !d1 || !d2 || !S) return fail(c, VVS_ERR_INVALID, "vvs_similarity: null argument");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, s);
   int dpad = 0;
   int rc = normalise_caller_descriptors(c, d1, d2, n_pairs, T, d, &dpad, s);
   if (rc) return rc;
@@ -1035,14 +1103,38 @@ int vvs_ibvs(vvs_handle c, const int32_t* uv, const int32_t* uv_star, const uint
   if (n_pairs < 1 || K < 1) return fail(c, VVS_ERR_INVALID, "vvs_ibvs: empty problem");
   if ((ema_state == nullptr) != (ema_init == nullptr))
     return fail(c, VVS_ERR_INVALID, "vvs_ibvs: ema_state and ema_init go together");
+  DeviceGuard dg(c);
   return run_ibvs(c, uv, uv_star, depth, n_pairs, K, twist, twist_raw, ema_state, ema_init,
                   static_cast<cudaStream_t>(stream));
+}
+
+int vvs_transform_to_real_world(vvs_handle c, const int32_t* uv, const int32_t* uv_star, int32_t n_points, double* xy,
+                                double* xy_star, vvs_stream stream) {
+  if (!c || (!uv && !uv_star)) return fail(c, VVS_ERR_INVALID, "vvs_transform_to_real_world: null argument");
+  if ((uv && !xy) || (uv_star && !xy_star)) return fail(c, VVS_ERR_INVALID, "vvs_transform_to_real_world: output missing");
+  if (n_points < 1) return fail(c, VVS_ERR_INVALID, "vvs_transform_to_real_world: empty problem");
+  DeviceGuard dg(c);
+  Camera cam;
+  cam.width = c->cfg.frame_width; cam.height = c->cfg.frame_height;
+  cam.fx = c->cfg.f_x; cam.fy = c->cfg.f_y; cam.cx = c->cfg.c_x; cam.cy = c->cfg.c_y;
+  ++c->launch_count;
+  return launch_points(uv, uv_star, n_points, cam, xy, xy_star, static_cast<cudaStream_t>(stream), &c->err);
+}
+
+int vvs_interaction_matrix(vvs_handle c, const double* xy, const double* z, int32_t n_points, double* L,
+                           vvs_stream stream) {
+  if (!c || !xy || !z || !L) return fail(c, VVS_ERR_INVALID, "vvs_interaction_matrix: null argument");
+  if (n_points < 1) return fail(c, VVS_ERR_INVALID, "vvs_interaction_matrix: empty problem");
+  DeviceGuard dg(c);
+  ++c->launch_count;
+  return launch_interaction(xy, z, n_points, L, static_cast<cudaStream_t>(stream), &c->err);
 }
 
 int vvs_ibvs_terms(vvs_handle c, const int32_t* uv, const int32_t* uv_star, const uint16_t* depth, int32_t n_pairs,
                    int32_t K, double* twist, double* z, double* xy, double* xy_star, double* L, vvs_stream stream) {
   if (!c || !uv || !uv_star || !depth || !twist) return fail(c, VVS_ERR_INVALID, "vvs_ibvs_terms: null argument");
   if (n_pairs < 1 || K < 1) return fail(c, VVS_ERR_INVALID, "vvs_ibvs_terms: empty problem");
+  DeviceGuard dg(c);
   IbvsArgs a;
   memset(&a, 0, sizeof(a));
   a.uv = uv; a.uv_star = uv_star; a.depth = depth; a.n_pairs = n_pairs; a.K = K;
@@ -1060,10 +1152,12 @@ int vvs_frame_pairs_to_twist(vvs_handle c, const uint8_t* goal, const uint8_t* c
   if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
   if (!out || !out->twist) return fail(c, VVS_ERR_INVALID, "out->twist is required");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, s);
   // the per-token match outputs are a test / inspection feature: those calls launch eagerly
   const vvs_match_out& m = out->match;
   const bool wants_match = m.nn1 || m.nn2 || m.sim1 || m.candidate || m.mean_sim1 || m.n_candidates || m.n_selected ||
-                           m.flags || m.sel_tok || m.sel_sim || m.uv_star || m.uv;
+                           m.flags || m.sel_tok || m.sel_sim || m.uv_star || m.uv || m.sel_order;
   const bool want_mean = out->mean_sim_sel != nullptr;
   const vvs_ctx::GraphEntry* g = wants_match ? nullptr : graphs_for(c, n_pairs, want_mean);
   if (!g) return pairs_to_twist(c, goal, cur, depth, n_pairs, out, s);
@@ -1092,12 +1186,16 @@ int vvs_frame_pairs_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   // the call is synchronous; on the legacy default stream it runs on the handle's own stream instead
   if (s == nullptr || s == cudaStreamLegacy) s = c->own_stream;
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, s);
   return host_pipeline(c, goal, cur, depth, n_pairs, /*from_frames=*/false, twist, n_selected, mean_sim_sel, s);
 }
 
 int vvs_resize_frames(vvs_handle c, const uint8_t* frames, int32_t n, uint8_t* out, vvs_stream stream) {
   if (!c || !frames || !out) return fail(c, VVS_ERR_INVALID, "vvs_resize_frames: null argument");
   if (n < 1 || n > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "vvs_resize_frames: n outside [1, max_images]");
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, static_cast<cudaStream_t>(stream));
   int rc = ensure_frontend(c);
   if (rc) return rc;
   c->launch_count = 0;
@@ -1109,6 +1207,8 @@ int vvs_frames_to_twist(vvs_handle c, const uint8_t* goal, const uint8_t* cur, c
   if (!c || !goal || !cur || !depth) return fail(c, VVS_ERR_INVALID, "vvs_frames_to_twist: null argument");
   if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
   if (!out || !out->twist) return fail(c, VVS_ERR_INVALID, "out->twist is required");
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, static_cast<cudaStream_t>(stream));
   int rc = ensure_frontend(c);
   if (rc) return rc;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
@@ -1129,6 +1229,8 @@ int vvs_frames_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8_t* c
   if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (s == nullptr || s == cudaStreamLegacy) s = c->own_stream;
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, s);
   return host_pipeline(c, goal, cur, depth, n_pairs, /*from_frames=*/true, twist, n_selected, mean_sim_sel, s);
 }
 
@@ -1138,6 +1240,7 @@ int vvs_render_plane(vvs_handle c, const uint8_t* texture, int32_t tex_h, int32_
     return fail(c, VVS_ERR_INVALID, "vvs_render_plane: null argument");
   if (n < 1 || tex_h < 1 || tex_w < 1 || !(plane_w > 0.0) || !(plane_h > 0.0))
     return fail(c, VVS_ERR_INVALID, "vvs_render_plane: empty problem");
+  DeviceGuard dg(c);
   Camera cam;
   cam.width = c->cfg.frame_width; cam.height = c->cfg.frame_height;
   cam.fx = c->cfg.f_x; cam.fy = c->cfg.f_y; cam.cx = c->cfg.c_x; cam.cy = c->cfg.c_y;
@@ -1156,6 +1259,7 @@ int vvs_profile_enable(vvs_handle c, int32_t on) {
 
 int vvs_profile_read(vvs_handle c, double* total_ms, int32_t* launches, int32_t n_classes) {
   if (!c || !total_ms || !launches || n_classes < VVS_K_COUNT) return fail(c, VVS_ERR_INVALID, "vvs_profile_read: bad argument");
+  DeviceGuard dg(c);
   for (int i = 0; i < n_classes; ++i) {
     total_ms[i] = 0.0;
     launches[i] = 0;
@@ -1176,6 +1280,7 @@ int vvs_dbg_gemm(vvs_handle c, const void* A, const void* B, int32_t M, int32_t 
                  const float* bias, const float* gamma, float* x_f32, void* out_bf16, int32_t ldo, int32_t q_cols,
                  float q_scale, const float* pos, int32_t T, vvs_stream stream) {
   if (!c || !A || !B) return fail(c, VVS_ERR_INVALID, "vvs_dbg_gemm: null argument");
+  DeviceGuard dg(c);
   GemmArgs g = plain_gemm(static_cast<const bf16*>(A), static_cast<const bf16*>(B), M, N, K, epilogue);
   g.bias = bias; g.gamma = gamma; g.x_f32 = x_f32; g.out_bf16 = static_cast<bf16*>(out_bf16); g.ldo = ldo;
   g.q_cols = q_cols; g.q_scale = q_scale; g.pos = pos; g.T = T;
@@ -1185,6 +1290,7 @@ int vvs_dbg_gemm(vvs_handle c, const void* A, const void* B, int32_t M, int32_t 
 int vvs_dbg_attention(vvs_handle c, const void* qkv, void* out, int32_t n_img, int32_t n_tok, int32_t heads,
                       vvs_stream stream) {
   if (!c || !qkv || !out) return fail(c, VVS_ERR_INVALID, "vvs_dbg_attention: null argument");
+  DeviceGuard dg(c);
   return launch_attention(static_cast<const bf16*>(qkv), static_cast<bf16*>(out), n_img, n_tok, heads,
                           static_cast<cudaStream_t>(stream), &c->err);
 }
@@ -1192,6 +1298,7 @@ int vvs_dbg_attention(vvs_handle c, const void* qkv, void* out, int32_t n_img, i
 int vvs_dbg_layernorm(vvs_handle c, const float* x, const float* w, const float* b, void* out, int32_t rows, int32_t dim,
                       vvs_stream stream) {
   if (!c || !x || !w || !b || !out) return fail(c, VVS_ERR_INVALID, "vvs_dbg_layernorm: null argument");
+  DeviceGuard dg(c);
   return launch_layernorm(x, w, b, static_cast<bf16*>(out), rows, dim, 1e-6f, 0x7fffffff, static_cast<cudaStream_t>(stream), &c->err);
 }
 

@@ -518,7 +518,7 @@ extern "C" __attribute__((visibility("default"))) int vvs_dbg_att_trace(long lon
 }
 #endif
 
-int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
+int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
                         std::string* err, bool pdl) {
   const int D = heads * kHD;
   CUtensorMap tmq, tmkv;
@@ -531,16 +531,15 @@ int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int he
   rc = make_tmap_bf16(&tmo, out, static_cast<uint64_t>(D), static_cast<uint64_t>(n_tok), static_cast<uint64_t>(n_img),
                       static_cast<uint64_t>(D), static_cast<uint64_t>(n_tok) * D, kBQ, err);
   if (rc) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
-    VVS_CUDA_OK(cudaFuncSetAttribute(attention_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     static_cast<int>(kSmem)),
-                err);
-    VVS_CUDA_OK(cudaFuncSetAttribute(attention_ts_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                     cudaSharedmemCarveoutMaxShared),
-                err);
-    attr_set = true;
-  }
+  static PerDeviceOnce once;
+  VVS_CUDA_OK(once.run([] {
+                cudaError_t e = cudaFuncSetAttribute(attention_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                     static_cast<int>(kSmem));
+                if (e != cudaSuccess) return e;
+                return cudaFuncSetAttribute(attention_ts_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                            cudaSharedmemCarveoutMaxShared);
+              }),
+              err);
   const int q_tiles = (n_tok + kBQ - 1) / kBQ;
   dim3 grid((q_tiles + kQT - 1) / kQT, heads, n_img);
   VVS_CUDA_OK(launch_kernel(attention_ts_kernel, grid, kThreads, kSmem, stream, pdl, tmq, tmkv, tmo, out, n_tok, D), err);

@@ -532,13 +532,12 @@ template <int BN, int EPI, int NCTA>
 int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const GemmDev& d, int grid,
                cudaStream_t stream, bool pdl, std::string* err) {
   using C = Cfg<BN, NCTA>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    VVS_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     static_cast<int>(C::kSmemBytes)),
-                err);
-    attr_set = true;
-  }
+  static PerDeviceOnce once;
+  VVS_CUDA_OK(once.run([] {
+                return cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            static_cast<int>(C::kSmemBytes));
+              }),
+              err);
   VVS_CUDA_OK(launch_kernel(gemm_tc_kernel<BN, EPI, NCTA>, grid, kGemmThreads, C::kSmemBytes, stream, pdl, tmA, tmB, tmOut, d),
               err);
   return VVS_OK;
@@ -675,8 +674,11 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   const long long tiles = static_cast<long long>(d.batch) * d.m_tiles * d.n_tiles;
   if (ncta == 4) {
     // co-resident 4-CTA clusters (a GPC with an odd number of TPCs leaves one TPC out)
-    static int max_clusters = -1;
-    if (max_clusters < 0) {
+    static int max_clusters_dev[64];   // per device (0 = not queried yet)
+    int dev_id = 0;
+    cudaGetDevice(&dev_id);
+    int& max_clusters = max_clusters_dev[dev_id & 63];
+    if (max_clusters <= 0) {
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3(4 * (num_sms / 4));
       cfg.blockDim = dim3(kGemmThreads);

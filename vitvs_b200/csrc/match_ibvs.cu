@@ -55,16 +55,23 @@ __global__ void __launch_bounds__(256) select_kernel(const SelectArgs a) {
   uint8_t* cand = a.candidate + static_cast<size_t>(pair) * T;
 
   // 1. decode packed keys (value in the high word, ~index in the low word)
+  // A key that no atomicMax ever raised (still the memset 0) means the whole row / column of S was NaN - only
+  // possible with NaN / Inf in caller-supplied descriptors.  torch.max would return some index and carry on, so
+  // the index decodes to 0 (never out of bounds), the similarity to NaN, and flags bit 1 reports it.
   double ssum = 0.0;
+  int unset = 0;
   for (int i = threadIdx.x; i < T; i += blockDim.x) {
     const unsigned long long kr = rb[i], kc = cb[i];
-    nn1[i] = static_cast<int32_t>(0xFFFFFFFFu - static_cast<uint32_t>(kr));
-    const float s = unord_f32(static_cast<uint32_t>(kr >> 32));
+    const uint32_t i1 = 0xFFFFFFFFu - static_cast<uint32_t>(kr), i2 = 0xFFFFFFFFu - static_cast<uint32_t>(kc);
+    nn1[i] = (kr != 0ull && i1 < static_cast<uint32_t>(T)) ? static_cast<int32_t>(i1) : 0;
+    const float s = kr != 0ull ? unord_f32(static_cast<uint32_t>(kr >> 32)) : __int_as_float(0x7fc00000);
     sim1[i] = s;
     ssum += s;
-    nn2[i] = static_cast<int32_t>(0xFFFFFFFFu - static_cast<uint32_t>(kc));
+    nn2[i] = (kc != 0ull && i2 < static_cast<uint32_t>(T)) ? static_cast<int32_t>(i2) : 0;
+    unset |= (kr == 0ull || kc == 0ull) ? 1 : 0;
   }
   ssum = block_reduce(ssum, [](double x, double y) { return x + y; }, s_f64);
+  unset = block_reduce(unset, [](int x, int y) { return x | y; }, s_i32);
   const float mean_sim = static_cast<float>(ssum / T);
   const bool same = mean_sim > a.same_thresh;          // vitvs_v2.py:84
   __syncthreads();   // nn1/nn2 of every token visible
@@ -99,9 +106,48 @@ __global__ void __launch_bounds__(256) select_kernel(const SelectArgs a) {
   int32_t* uvs = a.uv_star + static_cast<size_t>(pair) * K * 2;
   int32_t* uvc = a.uv + static_cast<size_t>(pair) * K * 2;
   const int avail = same ? T : ncand;
-  const int nsel = avail < K ? avail : K;
+  int nsel = avail < K ? avail : K;
+  if (a.sel_order) {
+    // reference-faithful selection (vitvs_v2.py:139-141 / :90-91): the caller supplies a priority list of goal tokens
+    // (a host torch.randperm(T)); the first nsel of them that are candidates are taken, in list order - a uniform
+    // random subset of the mutual-NN set in uniform random order, exactly the distribution of perm[:num_to_select]
+    // applied to filtered_points; in the same-image branch it IS perm[:num_points].
+    const int32_t* order = a.sel_order + static_cast<size_t>(pair) * T;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int base = 0;
+    for (int i0 = 0; i0 < T && base < nsel; i0 += blockDim.x) {
+      const int i = i0 + threadIdx.x;
+      int tok = -1;
+      bool f = false;
+      if (i < T) {
+        tok = order[i];
+        f = tok >= 0 && tok < T && (same || cand[tok]);
+      }
+      const unsigned b = __ballot_sync(0xffffffffu, f);
+      __syncthreads();
+      if (lane == 0) s_i32[wid] = __popc(b);
+      __syncthreads();
+      int off = 0, tot = 0;
+      for (int w2 = 0; w2 < (blockDim.x >> 5); ++w2) {
+        if (w2 < wid) off += s_i32[w2];
+        tot += s_i32[w2];
+      }
+      const int rank = base + off + __popc(b & ((1u << lane) - 1u));
+      if (f && rank < nsel) {
+        sel_tok[rank] = tok;
+        sel_sim[rank] = same ? 1.0f : sim1[tok];
+      }
+      base += tot;
+    }
+    __syncthreads();
+    nsel = base < nsel ? base : nsel;          // a list that is not a permutation may run short
+    for (int k = nsel + threadIdx.x; k < K; k += blockDim.x) {
+      sel_tok[k] = -1;
+      sel_sim[k] = 0.f;
+    }
+  }
   unsigned long long prev = ~0ull;
-  for (int k = 0; k < K; ++k) {
+  for (int k = 0; k < K && !a.sel_order; ++k) {
     unsigned long long best = 0ull;
     if (k < nsel) {
       for (int i = threadIdx.x; i < T; i += blockDim.x) {
@@ -157,8 +203,37 @@ __global__ void __launch_bounds__(256) select_kernel(const SelectArgs a) {
     a.mean_sim1[pair] = mean_sim;
     a.n_candidates[pair] = ncand;
     a.n_selected[pair] = nsel;
-    a.flags[pair] = same ? 1 : 0;
+    a.flags[pair] = (same ? 1 : 0) | (unset ? 2 : 0);
   }
+}
+
+// Per-point terms of the control law with the reference's own argument lists (no depth frame involved):
+//   transform_to_real_world(s_uv, s_uv_star)  (vitvs_v2.py:634-648)   uv / uv_star int32 -> xy / xy_star fp64
+//   calculate_interaction_matrix(s_xy, Z)     (vitvs_v2.py:650-659)   xy, z fp64 -> L rows
+// One thread per point.
+__global__ void points_kernel(const int32_t* __restrict__ uv, const int32_t* __restrict__ uv_star, int n, Camera cam,
+                              double* __restrict__ xy, double* __restrict__ xy_star) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (uv && xy) {
+    xy[2 * i] = (uv[2 * i] - cam.cx) / cam.fx;
+    xy[2 * i + 1] = (uv[2 * i + 1] - cam.cy) / cam.fy;
+  }
+  if (uv_star && xy_star) {
+    xy_star[2 * i] = (uv_star[2 * i] - cam.cx) / cam.fx;
+    xy_star[2 * i + 1] = (uv_star[2 * i + 1] - cam.cy) / cam.fy;
+  }
+}
+
+__global__ void interaction_kernel(const double* __restrict__ xy, const double* __restrict__ z, int n,
+                                   double* __restrict__ L) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double x = xy[2 * i], y = xy[2 * i + 1], zz = z[i];
+  double* r = L + static_cast<size_t>(i) * 12;
+  // explicit round-to-nearest products: no FMA contraction, so every entry is the IEEE value numpy computes
+  r[0] = -1.0 / zz; r[1] = 0.0; r[2] = x / zz; r[3] = __dmul_rn(x, y); r[4] = -__dadd_rn(1.0, __dmul_rn(x, x)); r[5] = y;
+  r[6] = 0.0; r[7] = -1.0 / zz; r[8] = y / zz; r[9] = __dadd_rn(1.0, __dmul_rn(y, y)); r[10] = -__dmul_rn(x, y); r[11] = -x;
 }
 
 __device__ __forceinline__ double warp_sum_f64(double v) {
@@ -335,6 +410,19 @@ int launch_select(const SelectArgs& a, cudaStream_t s, std::string* err) {
     return VVS_ERR_INVALID;
   }
   select_kernel<<<a.n_pairs, 256, 0, s>>>(a);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_points(const int32_t* uv, const int32_t* uv_star, int n, const Camera& cam, double* xy, double* xy_star,
+                  cudaStream_t s, std::string* err) {
+  points_kernel<<<(n + 127) / 128, 128, 0, s>>>(uv, uv_star, n, cam, xy, xy_star);
+  VVS_CUDA_OK(cudaGetLastError(), err);
+  return VVS_OK;
+}
+
+int launch_interaction(const double* xy, const double* z, int n, double* L, cudaStream_t s, std::string* err) {
+  interaction_kernel<<<(n + 127) / 128, 128, 0, s>>>(xy, z, n, L);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }

@@ -183,11 +183,12 @@ int launch_resize_h(const uint8_t* in, uint8_t* out, int n_rows, const ResizeAxi
     set_error(err, "resize: input rows wider than the shared-memory staging allows");
     return VVS_ERR_INVALID;
   }
-  static bool attr_set = false;
-  if (!attr_set && smem > 48 * 1024) {
-    VVS_CUDA_OK(cudaFuncSetAttribute(resize_h_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024), err);
-    attr_set = true;
-  }
+  static PerDeviceOnce once;
+  if (smem > 48 * 1024)
+    VVS_CUDA_OK(once.run([] {
+                  return cudaFuncSetAttribute(resize_h_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+                }),
+                err);
   const int grid = (n_rows + kRowsPerBlock - 1) / kRowsPerBlock;
   resize_h_kernel<<<grid, kHThreads, smem, s>>>(in, out, n_rows, ax.in_size, ax.out_size, ax.bounds, ax.kk, ax.ksize,
                                                row_pitch);

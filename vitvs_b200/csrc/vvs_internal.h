@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <mutex>
 #include <string>
 
 namespace vvs {
@@ -29,6 +30,27 @@ void set_error(std::string* slot, const std::string& msg);
       return vvs::VVS_ERR_CUDA;                                                                         \
     }                                                                                                   \
   } while (0)
+
+// ---- per-device one-time setup ---------------------------------------------------------------------
+// cudaFuncSetAttribute / occupancy queries are per DEVICE, not per process: a call site keeps one of these and runs
+// its setup the first time it executes on each device (handles on several GPUs in one process, include/vitvs_b200.h:13).
+// The lock is held across the setup so that a second host thread cannot launch before the attribute is in place.
+struct PerDeviceOnce {
+  std::mutex mu;
+  unsigned long long done = 0;   // bit d: setup has run on device d
+  template <typename F>
+  cudaError_t run(F&& setup) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const unsigned long long bit = 1ull << (dev & 63);
+    std::lock_guard<std::mutex> lock(mu);
+    if (done & bit) return cudaSuccess;
+    e = setup();
+    if (e == cudaSuccess) done |= bit;
+    return e;
+  }
+};
 
 // ---- launches ------------------------------------------------------------------------------------
 // <<< >>> with an optional programmatic-dependent-launch attribute (ptx.cuh: pdl_wait / pdl_launch_dependents)
@@ -96,11 +118,9 @@ int gemm_block_n(int N);   // the N tile the launcher picks for this N (128 or 2
 
 // ---- attention ---------------------------------------------------------------------------------
 // qkv: [n_img * n_tok, 3*D] bf16 (q pre-scaled by hd^-0.5), out: [n_img * n_tok, D] bf16
+// attention_ts.cu: P stays in TMEM (TS MMA), one 128-row query tile per CTA and four CTAs per SM
 int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
                      std::string* err, bool pdl = false);
-// generations 7-9 (attention_ts.cu): P stays in TMEM (TS MMA), one tile per CTA and four CTAs per SM; launch_attention dispatches to it
-int launch_attention_ts(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
-                        std::string* err, bool pdl = false);
 
 // ---- camera frame -> ViT input: Pillow-exact 8-bit bicubic resize (resize.cu) ---------------------
 struct ResizeAxis {          // one separable pass: per output index the first tap, the tap count and the 22-bit taps
@@ -184,6 +204,7 @@ struct SelectArgs {
   float* sel_sim;         // [n_pairs, K]
   int32_t* uv_star;       // [n_pairs, K, 2]
   int32_t* uv;            // [n_pairs, K, 2]
+  const int32_t* sel_order;   // [n_pairs, T] optional priority list of goal tokens (reference-faithful selection)
 };
 int launch_select(const SelectArgs& a, cudaStream_t s, std::string* err);
 
@@ -206,5 +227,9 @@ struct IbvsArgs {
   double* L_out;            // [n_pairs, 2K, 6]
 };
 int launch_ibvs(const IbvsArgs& a, cudaStream_t s, std::string* err);
+// transform_to_real_world / calculate_interaction_matrix with the reference's own argument lists (n points)
+int launch_points(const int32_t* uv, const int32_t* uv_star, int n, const Camera& cam, double* xy, double* xy_star,
+                  cudaStream_t s, std::string* err);
+int launch_interaction(const double* xy, const double* z, int n, double* L, cudaStream_t s, std::string* err);
 
 }  // namespace vvs

@@ -194,7 +194,7 @@ class Engine:
                                                        _stream(self.device)), "vvs_descriptors_hierarchy")
         return out
 
-    def _match_buffers(self, n_pairs: int, T: int, K: int):
+    def _match_buffers(self, n_pairs: int, T: int, K: int, sel_order: torch.Tensor | None = None):
         dev = self.device
         bufs = dict(
             nn1=torch.empty(n_pairs, T, dtype=torch.int32, device=dev),
@@ -211,18 +211,28 @@ class Engine:
             uv=torch.empty(n_pairs, K, 2, dtype=torch.int32, device=dev),
         )
         mo = _lib.MatchOut(**{k: v.data_ptr() for k, v in bufs.items()})
+        if sel_order is not None:
+            # reference-faithful selection (vitvs_v2.py:139-141): a priority list of goal tokens per pair, e.g. randperm(T)
+            order = sel_order.to(dev, torch.int32).contiguous()
+            if order.dim() == 1:
+                order = order[None].expand(n_pairs, -1).contiguous()
+            assert order.shape == (n_pairs, T), order.shape
+            bufs["_sel_order"] = order                # keeps the buffer alive until the caller drops the dict
+            mo.sel_order = order.data_ptr()
         return bufs, mo
 
     def match(self, desc1: torch.Tensor, desc2: torch.Tensor, grid_w: int | None = None,
-              num_pairs: int | None = None) -> dict:
-        """desc1/desc2: fp32 [n_pairs, T, d] (goal / current).  Returns the dict of vvs_match_out tensors."""
+              num_pairs: int | None = None, sel_order: torch.Tensor | None = None) -> dict:
+        """desc1/desc2: fp32 [n_pairs, T, d] (goal / current).  Returns the dict of vvs_match_out tensors.
+        sel_order (optional, int [T] or [n_pairs, T]): priority list of goal tokens - the first num_pairs candidates
+        in that order are selected instead of the num_pairs most similar ones."""
         assert desc1.shape == desc2.shape and desc1.dim() == 3
         n_pairs, T, d = desc1.shape
         K = self.cfg.num_pairs if num_pairs is None else num_pairs
         grid_w = int(math.sqrt(T)) if grid_w is None else grid_w          # vitvs_v2.py:75
         d1 = desc1.to(self.device, torch.float32).contiguous()
         d2 = desc2.to(self.device, torch.float32).contiguous()
-        bufs, mo = self._match_buffers(n_pairs, T, K)
+        bufs, mo = self._match_buffers(n_pairs, T, K, sel_order)
         self._check(self.lib.vvs_match(self._h, _ptr(d1), _ptr(d2), n_pairs, T, d, grid_w, K, C.byref(mo),
                                        _stream(self.device)), "vvs_match")
         return bufs
@@ -265,8 +275,9 @@ class Engine:
         return out
 
     def frame_pairs_to_twist(self, goal: torch.Tensor, current: torch.Tensor, depth: torch.Tensor,
-                             want_match: bool = False) -> dict:
-        """Device-resident batched Controller.ibvs(): goal/current uint8 [B,S,S,3], depth uint16 [B,H,W]."""
+                             want_match: bool = False, sel_order: torch.Tensor | None = None) -> dict:
+        """Device-resident batched Controller.ibvs(): goal/current uint8 [B,S,S,3], depth uint16 [B,H,W].
+        sel_order: see match() - e.g. torch.randperm(T) for the reference's random choice of key-points."""
         B = goal.shape[0]
         K = self.cfg.num_pairs
         goal, current, depth = goal.contiguous(), current.contiguous(), depth.contiguous()
@@ -275,8 +286,8 @@ class Engine:
                    mean_sim_sel=torch.empty(B, dtype=torch.float32, device=self.device))
         po = _lib.PairOut(twist=out["twist"].data_ptr(), n_selected=out["n_selected"].data_ptr(),
                           mean_sim_sel=out["mean_sim_sel"].data_ptr())
-        if want_match:
-            bufs, mo = self._match_buffers(B, self.tokens, K)
+        if want_match or sel_order is not None:
+            bufs, mo = self._match_buffers(B, self.tokens, K, sel_order)
             po.match = mo
             out.update(bufs)
         self._check(self.lib.vvs_frame_pairs_to_twist(self._h, _ptr(goal), _ptr(current), _ptr(depth), B,
@@ -284,6 +295,33 @@ class Engine:
                     "vvs_frame_pairs_to_twist")
         self._n_img = 2 * B
         return out
+
+    def transform_to_real_world(self, uv: torch.Tensor, uv_star: torch.Tensor):
+        """Controller.transform_to_real_world (vitvs_v2.py:634-648): int [..., 2] pixel key-points -> fp64 normalised
+        image coordinates (s_xy, s_star_xy), same leading shape.  No depth frame involved."""
+        uv = uv.to(self.device, torch.int32).contiguous()
+        uv_star = uv_star.to(self.device, torch.int32).contiguous()
+        assert uv.shape == uv_star.shape and uv.shape[-1] == 2
+        xy = torch.empty(uv.shape, dtype=torch.float64, device=self.device)
+        xys = torch.empty(uv.shape, dtype=torch.float64, device=self.device)
+        self._check(self.lib.vvs_transform_to_real_world(self._h, _ptr(uv), _ptr(uv_star), uv.numel() // 2, _ptr(xy),
+                                                         _ptr(xys), _stream(self.device)), "vvs_transform_to_real_world")
+        return xy, xys
+
+    def interaction_matrix(self, s_xy: torch.Tensor, Z: torch.Tensor) -> torch.Tensor:
+        """Controller.calculate_interaction_matrix(s_xy, Z) (vitvs_v2.py:650-659): s_xy fp64 [K, 2], Z fp64 [K] or
+        [K, 1] -> L fp64 [2K, 6]."""
+        xy = s_xy.to(self.device, torch.float64).contiguous()
+        z = Z.to(self.device, torch.float64).reshape(-1).contiguous()
+        assert xy.dim() == 2 and xy.shape[1] == 2 and z.numel() == xy.shape[0]
+        L = torch.empty(2 * xy.shape[0], 6, dtype=torch.float64, device=self.device)
+        self._check(self.lib.vvs_interaction_matrix(self._h, _ptr(xy), _ptr(z), xy.shape[0], _ptr(L),
+                                                    _stream(self.device)), "vvs_interaction_matrix")
+        return L
+
+    @property
+    def build_id(self) -> str:
+        return self.lib.vvs_build_id().decode()
 
     def frame_pairs_to_twist_host(self, goal: torch.Tensor, current: torch.Tensor, depth: torch.Tensor,
                                   twist_out: torch.Tensor, n_selected_out: torch.Tensor | None = None,
@@ -309,7 +347,7 @@ class Engine:
         return out
 
     def frames_to_twist(self, goal_frames: torch.Tensor, current_frames: torch.Tensor, depth: torch.Tensor,
-                        want_match: bool = False) -> dict:
+                        want_match: bool = False, sel_order: torch.Tensor | None = None) -> dict:
         """frame_pairs_to_twist on raw camera frames: uint8 [B, v_max, u_max, 3] x2 + depth uint16 [B, v_max, u_max]."""
         B = goal_frames.shape[0]
         K = self.cfg.num_pairs
@@ -320,8 +358,8 @@ class Engine:
                    mean_sim_sel=torch.empty(B, dtype=torch.float32, device=self.device))
         po = _lib.PairOut(twist=out["twist"].data_ptr(), n_selected=out["n_selected"].data_ptr(),
                           mean_sim_sel=out["mean_sim_sel"].data_ptr())
-        if want_match:
-            bufs, mo = self._match_buffers(B, self.tokens, K)
+        if want_match or sel_order is not None:
+            bufs, mo = self._match_buffers(B, self.tokens, K, sel_order)
             po.match = mo
             out.update(bufs)
         self._check(self.lib.vvs_frames_to_twist(self._h, _ptr(goal_frames), _ptr(current_frames), _ptr(depth), B,

@@ -186,12 +186,16 @@ class Episode:
     pose: np.ndarray
     start_pose: np.ndarray
     ema: list = field(default_factory=lambda: [None] * 6)         # Controller.initialize_ema (vitvs_v2.py:325-327)
+    v_c: np.ndarray | None = None                                  # Controller.v_c: last EMA twist (None until one exists, :223)
     iteration_count: int = 0
     failures: int = 0                                              # feature_failure_count (:500-508)
     done: bool = False
     converged: bool = False
     aborted: str = ""
-    velocity_vector_history: list = field(default_factory=list)
+    velocity_vector_history: list = field(default_factory=list)    # unclipped EMA twists, last 200 (:626-628): the stopping rule's window
+    average_velocities: list = field(default_factory=list)         # mean |v_c| per iteration (:762-764)
+    velocity_mean_100: list = field(default_factory=list)          # running means of the above (:767-775)
+    velocity_mean_10: list = field(default_factory=list)
     position_history: list = field(default_factory=list)
     orientation_history: list = field(default_factory=list)
     applied: list = field(default_factory=list)                    # clipped, re-mapped twist published on /camera_vel
@@ -205,9 +209,15 @@ class EpisodeBatch:
     """B closed-loop servo episodes against one goal view, advanced together on one Engine."""
 
     def __init__(self, engine, texture_u8, goal_pose: np.ndarray, start_poses, dt: float = 1.0,
-                 min_iterations: int = 300, max_iterations: int = 2000, cfg: ServoConfig | None = None):
+                 min_iterations: int = 300, max_iterations: int = 2000, cfg: ServoConfig | None = None,
+                 random_selection: bool = False, selection_seed: int = 121):
         self.engine = engine
         self.cfg = cfg or engine.cfg
+        # random_selection: the reference's choice of key-points - num_pairs mutual nearest neighbours drawn with
+        # torch.randperm (vitvs_v2.py:139-141; main() seeds torch with 121, :1397) - handed to the fused call as a
+        # per-episode priority list.  False: the num_pairs most similar ones (deterministic).
+        self.random_selection = random_selection
+        self._sel_gen = torch.Generator().manual_seed(selection_seed)
         self.dt, self.min_iterations, self.max_iterations = dt, min_iterations, max_iterations
         dev = engine.device
         self.texture = torch.as_tensor(np.ascontiguousarray(texture_u8)).to(dev)
@@ -258,25 +268,45 @@ class EpisodeBatch:
         poses = torch.from_numpy(np.stack([e.pose for e in live]))
         frames, depth = self.engine.render_plane(self.texture, poses)
         goal = self.goal_frame.expand(n, -1, -1, -1).contiguous()
-        out = self.engine.frames_to_twist(goal, frames, depth)
+        if self.random_selection:
+            T = self.engine.tokens
+            order = torch.stack([torch.randperm(T, generator=self._sel_gen) for _ in range(n)]).to(torch.int32)
+            out = self.engine.frames_to_twist(goal, frames, depth, sel_order=order)
+        else:
+            out = self.engine.frames_to_twist(goal, frames, depth)
         twist = out["twist"].cpu().numpy()
         n_sel = out["n_selected"].cpu().numpy()
         mv = self.cfg.max_velocity
+        hist_cap = getattr(self.cfg, "max_velocity_vector_history", 200)
         for k, e in enumerate(live):
-            e.iteration_count += 1
+            # --- Controller.ibvs() (vitvs_v2.py:588-628)
             if n_sel[k] == 0:                                     # detect_features failure (:500-508)
                 e.failures += 1
-                if e.failures >= 10:
+                if e.failures >= 10:                               # RuntimeError -> run() aborts the sample (:746-756)
                     e.done, e.aborted = True, "Persistent feature detection failure"
+                    continue
+                # ibvs() returned early: self.v_c keeps the previous EMA twist and run() goes on with it (:758-795) -
+                # the camera keeps moving, so the next frame differs and detection gets another chance
+            else:
+                e.failures = 0
+                # 1 <= n < 4 pairs: calculate_uv hands back num_pairs all-zero rows (:539-541), len >= 4 passes :603,
+                # e = 0 => v = 0, and that zero twist goes through the EMA like any other (the kernel returns it)
+                e.v_c = np.array([self._update_ema(e, i, float(v)) for i, v in enumerate(twist[k])])
+                e.velocity_vector_history.append(e.v_c.copy())     # the UNCLIPPED EMA twist (:623-626)
+                if len(e.velocity_vector_history) > hist_cap:
+                    e.velocity_vector_history.pop(0)
+            if e.v_c is None:
+                # no twist yet and none computed: run() trips over np.abs(None) and returns its error tuple (:762, :819-821)
+                e.done, e.aborted = True, "Error in run loop: no velocity before the first successful detection"
                 continue
-            e.failures = 0
-            if n_sel[k] < 4:                                       # ibvs() returns early (:602-605)
-                continue
-            v_c = np.array([self._update_ema(e, i, float(v)) for i, v in enumerate(twist[k])])
-            v_c = np.clip(v_c, -mv, mv)                            # publish_twist clips every component (:668-676)
-            e.applied.append([v_c[2], -v_c[0], -v_c[1], v_c[5], -v_c[3], -v_c[4]])
-            e.velocity_vector_history.append(v_c.copy())
-            e.pose = integrate_twist(e.pose, v_c, self.dt)
+            # --- the rest of one run() iteration (:758-795)
+            e.iteration_count += 1
+            e.average_velocities.append(float(np.mean(np.abs(e.v_c))))
+            e.velocity_mean_100.append(float(np.mean(e.average_velocities[-100:])))
+            e.velocity_mean_10.append(float(np.mean(e.average_velocities[-10:])))
+            v_pub = np.clip(e.v_c, -mv, mv)                        # publish_twist clips every component (:668-676)
+            e.applied.append([v_pub[2], -v_pub[0], -v_pub[1], v_pub[5], -v_pub[3], -v_pub[4]])
+            e.pose = integrate_twist(e.pose, v_pub, self.dt)
             err_t, err_r = end_error(e.pose, self.goal_pose)
             e.position_history.append(e.pose[9:].copy())
             e.orientation_history.append(quaternion_xyzw(e.pose))
@@ -315,10 +345,6 @@ class EpisodeBatch:
             return a
         res = self.results()
         applied = [np.asarray(e.applied).reshape(-1, 6) for e in E]
-        vel = [np.asarray(e.velocity_vector_history).reshape(-1, 6) for e in E]
-
-        def window_mean(v, w):
-            return np.array([v[max(0, i - w + 1): i + 1].mean(axis=0) for i in range(len(v))]).reshape(-1, 6)
         np.savez(path,
                  initial_positions=np.array([e.start_pose[9:] for e in E]),
                  initial_orientations=np.array([quaternion_xyzw(e.start_pose) for e in E]),
@@ -333,9 +359,9 @@ class EpisodeBatch:
                  all_iteration_histories=np.array([e.iteration_count for e in E]),
                  lowest_position_errors=np.array([e.lowest_position_error for e in E]),
                  lowest_orientation_errors=np.array([e.lowest_orientation_error for e in E]),
-                 all_average_velocities=obj([v.mean(axis=0) if len(v) else np.zeros(6) for v in vel]),
-                 all_velocity_mean_100=obj([window_mean(v, 100) for v in vel]),
-                 all_velocity_mean_10=obj([window_mean(v, 10) for v in vel]),
+                 all_average_velocities=obj([e.average_velocities for e in E]),
+                 all_velocity_mean_100=obj([e.velocity_mean_100 for e in E]),
+                 all_velocity_mean_10=obj([e.velocity_mean_10 for e in E]),
                  all_applied_velocity_x=obj([a[:, 0] for a in applied]),
                  all_applied_velocity_y=obj([a[:, 1] for a in applied]),
                  all_applied_velocity_z=obj([a[:, 2] for a in applied]),

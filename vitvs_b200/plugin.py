@@ -157,8 +157,11 @@ class DinoServoMixin:
         dev = self.engine.device
         goal = torch.from_numpy(self._camera_frame_u8(self.goal_image))[None].to(dev)
         cur = torch.from_numpy(self._camera_frame_u8(self.latest_pil_image))[None].to(dev)
-        depth = torch.from_numpy(np.array(self.latest_image_depth, copy=True))[None].to(dev)
-        out = self.engine.frames_to_twist(goal, cur, depth, want_match=True)
+        # selection: the reference draws num_pairs of the mutual nearest neighbours at random (vitvs_v2.py:139-141);
+        # ``random_selection = True`` on the controller reproduces that with a host randperm handed to the fused call,
+        # the default takes the num_pairs most similar ones (deterministic)
+        order = torch.randperm(self.engine.tokens) if getattr(self, "random_selection", False) else None
+        out = self.engine.frames_to_twist(goal, cur, self._depth_on_device(), want_match=True, sel_order=order)
         self._last_fused = out
         n = int(out["n_selected"][0].item())
         if n == 0:
@@ -187,32 +190,34 @@ class DinoServoMixin:
             s_uv[i] = (round(c[i, 0] * sx), round(c[i, 1] * sy))
         return s_uv_star, s_uv
 
-    def _terms(self, s_uv, s_uv_star=None):
-        dev = self.engine.device
-        uv = torch.from_numpy(np.asarray(s_uv, dtype=np.int32))[None].to(dev)
-        uvs = uv if s_uv_star is None else torch.from_numpy(np.asarray(s_uv_star, dtype=np.int32))[None].to(dev)
-        depth = torch.from_numpy(np.array(self.latest_image_depth, copy=True))[None].to(dev)
-        return self.engine.ibvs_terms(uv, uvs, depth)
+    def _depth_on_device(self) -> torch.Tensor:
+        """The current depth frame on the GPU, uploaded once per frame object (the camera callback REPLACES
+        ``latest_image_depth`` with a new array per message, vitvs_v2.py:460-462, so identity tells frames apart)."""
+        src = self.latest_image_depth
+        cached = getattr(self, "_depth_cache", None)
+        if cached is None or cached[0] is not src:
+            dev = torch.from_numpy(np.ascontiguousarray(src))[None].to(self.engine.device)
+            self._depth_cache = cached = (src, dev)
+        return cached[1]
 
     def get_depth(self, current_points):
         """vitvs_v2.py:566-586 -> Z [K,1] metres (0 / out of bounds -> 100), evaluated by the IBVS kernel."""
         if self.latest_image_depth is None:
             return None
-        return self._terms(current_points)["Z"][0].cpu().numpy().reshape(-1, 1)
+        uv = torch.from_numpy(np.asarray(current_points, dtype=np.int32))[None].to(self.engine.device)
+        return self.engine.ibvs_terms(uv, uv, self._depth_on_device())["Z"][0].cpu().numpy().reshape(-1, 1)
 
     def transform_to_real_world(self, s_uv, s_uv_star):
-        """vitvs_v2.py:634-648 -> (s_xy, s_star_xy) normalised image coordinates."""
-        t = self._terms(s_uv, s_uv_star)
-        return t["s_xy"][0].cpu().numpy(), t["s_star_xy"][0].cpu().numpy()
+        """vitvs_v2.py:634-648 -> (s_xy, s_star_xy) normalised image coordinates (no depth frame involved)."""
+        xy, xys = self.engine.transform_to_real_world(torch.from_numpy(np.asarray(s_uv, dtype=np.int32)),
+                                                      torch.from_numpy(np.asarray(s_uv_star, dtype=np.int32)))
+        return xy.cpu().numpy(), xys.cpu().numpy()
 
-    def calculate_interaction_matrix(self, s_xy, Z, s_uv=None):
-        """vitvs_v2.py:650-659 -> L [2K,6].  The kernel derives (x, y, Z) from pixel keypoints + depth, so
-        the keypoints must be supplied (``s_uv``) - the (s_xy, Z) arguments are accepted for signature
-        compatibility and cross-checked."""
-        if s_uv is None:
-            raise ValueError("pass s_uv= : the GPU kernel builds L from pixel keypoints and the depth frame")
-        t = self._terms(s_uv)
-        return t["L"][0].cpu().numpy()
+    def calculate_interaction_matrix(self, s_xy, Z):
+        """vitvs_v2.py:650-659 -> L [2K,6] from normalised coordinates and depths, the reference's two arguments."""
+        L = self.engine.interaction_matrix(torch.from_numpy(np.asarray(s_xy, dtype=np.float64)),
+                                           torch.from_numpy(np.asarray(Z, dtype=np.float64)))
+        return L.cpu().numpy()
 
     def ibvs(self):
         """vitvs_v2.py:588-623: sets ``self.v_c`` (EMA-smoothed twist) or returns early on failure."""
@@ -226,6 +231,13 @@ class DinoServoMixin:
             return
         v_c = self._last_fused["twist"][0].cpu().numpy()          # -lambda * pinv(L) @ e from the fused call
         self.v_c = np.array([self.update_ema(i, v) for i, v in enumerate(v_c.flatten())])
+        # velocity history read by is_visual_servoing_done (vitvs_v2.py:373-374, :626-628)
+        if not hasattr(self, "velocity_vector_history"):
+            self.velocity_vector_history = []
+        self.velocity_vector_history.append(self.v_c)
+        if len(self.velocity_vector_history) > getattr(self, "max_velocity_vector_history",
+                                                        self.cfg.max_velocity_vector_history):
+            self.velocity_vector_history.pop(0)
 
 
 class DinoServo(DinoServoMixin):
@@ -239,4 +251,6 @@ class DinoServo(DinoServoMixin):
         self.latest_pil_image = None
         self.latest_image_depth = None
         self.v_c = None
+        self.velocity_vector_history = []
+        self.max_velocity_vector_history = 200
         self.initialize_ema()
