@@ -228,8 +228,15 @@ def calculate_uv(points1_rc, points2_rc, T: int, cfg=DEFAULT_CFG):
     S = cfg["dino_input_size"]
     K = cfg["num_pairs"]
     scale = S / int(np.sqrt(T))
-    g = np.flip(np.asarray(points1_rc, dtype=np.float64) * scale + scale / 2, 1)
-    c = np.flip(np.asarray(points2_rc, dtype=np.float64) * scale + scale / 2, 1)
+    # vitvs_v2.py:511-513 `points1 * scale + scale / 2`: an int64 tensor times a Python float is evaluated by torch in
+    # the default dtype, fp32 - the scalar is rounded to fp32, product and sum round to fp32 separately - and
+    # `.tolist()` then widens those fp32 values to Python floats for calculate_uv.  For S / grid not exactly
+    # representable (stride 7: 112 / 15, 308 / 43) the fp64 form would round some key-points the other way.
+    def centres(p):
+        p = np.asarray(p, dtype=np.int64).reshape(-1, 2).astype(np.float32)
+        return (p * np.float32(scale) + np.float32(scale / 2)).astype(np.float64)
+    g = np.flip(centres(points1_rc), 1)
+    c = np.flip(centres(points2_rc), 1)
     s_uv = np.zeros([K, 2], dtype=int)
     s_uv_star = np.zeros([K, 2], dtype=int)
     n = len(g)

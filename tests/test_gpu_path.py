@@ -11,6 +11,8 @@ pytestmark = pytest.mark.gpu
 from oracle import dinov2, servo  # noqa: E402  (the checker)
 from vitvs_b200 import synth  # noqa: E402
 
+from _parity import check_keypoints  # noqa: E402
+
 TIE_EPS = 2e-3     # similarity margin below which an arg-max disagreement counts as a near-tie (bf16 operands)
 
 
@@ -115,9 +117,8 @@ def test_match_against_reference_fixtures(eng, golden, case):
         assert int(r["n_candidates"][0]) == len(g[f"{case}/sel_tok1"])
         if case == "all_mutual":
             assert len(cand) == 0 and int(r["n_selected"][0]) == 0          # reference returns (None,)*3
-    # whatever the arg-max, the rule itself is exact given the GPU's nn1/nn2
-    mine = servo.match(S_ref)
-    mine.nn1, mine.nn2 = nn1.astype(np.int64), nn2.astype(np.int64)
+    # a11, whatever the arg-max: key-points are exactly calculate_uv of the GPU's own selection
+    check_keypoints(r, 0, int(np.sqrt(T)))
 
 
 def test_candidate_rule_is_bit_exact_given_argmax(eng):
@@ -140,6 +141,7 @@ def test_candidate_rule_is_bit_exact_given_argmax(eng):
     n = int(r["n_selected"][0])
     assert n == len(chosen)
     assert np.array_equal(r["sel_tok"][0, :n].cpu().numpy(), chosen)
+    check_keypoints(r, 0, 10)
 
 
 def test_similarity_matrix_vs_oracle(eng):
@@ -156,6 +158,7 @@ def test_match_large_token_count(eng):
     r = eng.match(a[None], b[None], num_pairs=24)
     S_ref = servo.cosine_similarity_matrix(a[None, None], b[None, None])[0, 0]
     _check_match(r, S_ref)
+    check_keypoints(r, 0, 32)                       # scale 308 / 32 = 9.625
 
 
 def test_match_batched_pairs_are_independent(eng):
@@ -232,6 +235,7 @@ def test_frame_pairs_to_twist_vs_reference_fixture(eng, golden):
         tw_ref = servo.ibvs_twist(uv.astype(int), uvs.astype(int), pairs[i][2])
         tw = out["twist"][i].cpu().numpy()
         assert np.abs(tw - tw_ref).max() <= 1e-9 * np.abs(tw_ref).max()
+        check_keypoints(out, i, 22)                 # a11, unconditional: calculate_uv of the GPU's own selection
         # and against the reference's own twist when the selection coincides
         if np.array_equal(out["sel_tok"][i].cpu().numpy(), g[pre + "chosen"]) and not bad1.any():
             assert np.array_equal(uv, g[pre + "s_uv"]) and np.array_equal(uvs, g[pre + "s_uv_star"])
@@ -394,6 +398,7 @@ def test_overlapping_patches_stride7(vits):
         agree = (out["nn1"][i].cpu().numpy() == m.nn1).mean()
         print(f"[stride 7] pair {i} nn1 agreement {agree:.4f}")
         assert agree >= 0.98
+        check_keypoints(out, i, grid, dict(servo.DEFAULT_CFG, dino_input_size=S))    # scale 112 / 15: not exact in binary
     assert torch.isfinite(out["twist"]).all()
     e.close()
     with pytest.raises(ValueError):
@@ -406,6 +411,7 @@ def test_overlapping_patches_stride7(vits):
                                  torch.from_numpy(dpt[None]).cuda(), want_match=True)
     assert e.tokens == 1849 and out["nn1"].shape == (1, 1849) and torch.isfinite(out["twist"]).all()
     assert int(out["n_selected"][0]) == 24
+    check_keypoints(out, 0, 43)                     # scale 308 / 43
     e.close()
 
 

@@ -75,6 +75,26 @@ def test_full_candidate_set_is_mutual_nn_set():
         assert np.array_equal(m.candidates, np.nonzero(m.mutual)[0])
 
 
+@pytest.mark.parametrize("S,grid", [(308, 22), (112, 15), (308, 43), (518, 37), (308, 128), (308, 64), (322, 45)])
+def test_keypoint_recovery_equals_reference_lines(S, grid):
+    """a11 on grids whose scale S / grid is not a power-of-two fraction: the reference's own three lines
+    (vitvs_v2.py:511-513, evaluated literally: int64 tensor * Python float in torch => fp32) followed by the
+    reference's own Controller.calculate_uv (:525-553, Python round = half-to-even), for EVERY patch of the grid."""
+    cfg = dict(servo.DEFAULT_CFG, dino_input_size=S, num_pairs=grid * grid)
+    ctrl = ref_loader.make_controller(cfg)
+    ctrl.dino_input_size, ctrl.num_pairs = S, grid * grid
+    idx = torch.arange(grid * grid)
+    points1 = torch.stack([idx // grid, idx % grid], dim=-1)                     # _to_cartesian (:58-70)
+    points2 = points1.flip(0).contiguous()
+    scale = S / int(np.sqrt(grid * grid))                                        # :511
+    points1_scaled = points1 * scale + scale / 2                                 # :512
+    points2_scaled = points2 * scale + scale / 2                                 # :513
+    assert points1_scaled.dtype == torch.float32
+    ref_star, ref_uv = ctrl.calculate_uv(points1_scaled.tolist(), points2_scaled.tolist())
+    mine_star, mine_uv = servo.calculate_uv(points1.numpy(), points2.numpy(), grid * grid, cfg)
+    assert np.array_equal(ref_star, mine_star) and np.array_equal(ref_uv, mine_uv)
+
+
 def test_cyclic_distance_bit_equal_to_pairwise_distance():
     """Exhaustive over every (drow, dcol) offset of a 46x46 grid (covers 22x22 and 34x45)."""
     r = torch.arange(-45, 46)
