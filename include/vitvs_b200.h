@@ -251,6 +251,13 @@ enum vvs_kernel_class {
   VVS_K_SIM_GEMM = 10, VVS_K_SELECT = 11, VVS_K_IBVS = 12, VVS_K_RESIZE = 13, VVS_K_STENCIL = 14, VVS_K_COUNT = 15
 };
 VVS_API int vvs_profile_enable(vvs_handle h, int32_t on);
+/* Step accounting.  Re-captures the two CUDA graphs of vvs_frame_pairs_to_twist for n_pairs with a trace slot in every
+ * kernel (first / last warp stamp %globaltimer), replays them `replays` times back to back on the inputs the previous
+ * call left in the workspace, and returns for the LAST replay, per kernel in launch order: its vvs_kernel_class and its
+ * device begin / end time in ns.  end[i] - begin[i] is the kernel, begin[i+1] - end[i] the gap behind it (launch latency
+ * of the next graph node, plus the two memset nodes ahead of the similarity GEMM).  Synchronises. */
+VVS_API int vvs_trace_step(vvs_handle h, int32_t n_pairs, int32_t replays, int32_t* classes, uint64_t* begin_ns,
+                   uint64_t* end_ns, int32_t max_nodes, int32_t* n_nodes, vvs_stream stream);
 /* sums (ms) and launch counts per vvs_kernel_class since the last read; synchronises on the events. */
 VVS_API int vvs_profile_read(vvs_handle h, double* total_ms, int32_t* launches, int32_t n_classes);
 

@@ -73,6 +73,8 @@ SYMBOLS = {
     "vvs_uses_gram_stencil": (c_i32, [c_vp]),
     "vvs_set_num_pairs": (c_i32, [c_vp, c_i32]),
     "vvs_profile_enable": (c_i32, [c_vp, c_i32]),
+    "vvs_trace_step": (c_i32, [c_vp, c_i32, c_i32, C.POINTER(c_i32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), c_i32,
+                               C.POINTER(c_i32), c_vp]),
     "vvs_profile_read": (c_i32, [c_vp, C.POINTER(c_f64), C.POINTER(c_i32), c_i32]),
     "vvs_dbg_gemm": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32,
                              c_f32, c_vp, c_i32, c_vp]),

@@ -13,6 +13,7 @@
 namespace vvs {
 
 static std::string g_create_error;
+thread_local unsigned long long* tl_trace_slot = nullptr;
 
 void set_error(std::string* slot, const std::string& msg) {
   if (slot) *slot = msg;
@@ -64,6 +65,14 @@ __global__ void convert_vector_kernel(const SrcT* __restrict__ src, float* __res
     s = wi < half ? t * half + wi : hidden + t * half + (wi - half);
   }
   dst[i] = static_cast<float>(src[s]);
+}
+
+__global__ void trace_reset_kernel(unsigned long long* buf, int n_slots) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_slots) {
+    buf[2 * i] = ~0ull;
+    buf[2 * i + 1] = 0ull;
+  }
 }
 
 __global__ void mean_selected_kernel(const float* __restrict__ sel_sim, const int32_t* __restrict__ n_sel, int K,
@@ -153,6 +162,11 @@ struct vvs_ctx {
   cudaEvent_t ws_done = nullptr;
   cudaStream_t ws_stream = nullptr;
   bool ws_used = false;
+  // vvs_trace_step: %globaltimer [begin, end] of every kernel of one traced graph replay
+  static constexpr int kTraceSlots = 1024;
+  unsigned long long* trace_buf = nullptr;
+  bool trace_on = false;
+  std::vector<int> trace_cls;      // class of slot i
 };
 
 namespace {
@@ -205,6 +219,10 @@ struct ProfScope {
   cudaStream_t s;
   cudaEvent_t stop = nullptr;
   ProfScope(vvs_ctx* c_, int cls, cudaStream_t s_) : c(c_), s(s_) {
+    if (c->trace_on && c->trace_buf && static_cast<int>(c->trace_cls.size()) < vvs_ctx::kTraceSlots) {
+      tl_trace_slot = c->trace_buf + 2 * c->trace_cls.size();
+      c->trace_cls.push_back(cls);
+    }
     if (!c->prof_on) return;
     if (c->prof_used + 2 > c->prof_events.size()) {
       for (int i = 0; i < 64; ++i) {
@@ -220,6 +238,7 @@ struct ProfScope {
     cudaEventRecord(start, s);
   }
   ~ProfScope() {
+    tl_trace_slot = nullptr;
     if (stop) cudaEventRecord(stop, s);
   }
 };
@@ -437,10 +456,13 @@ int normalise_caller_descriptors(vvs_ctx* c, const float* d1, const float* d2, i
   const int dpad = (d + 7) / 8 * 8;
   if (2ull * n_pairs * T * dpad > c->desc_elems)
     return fail(c, VVS_ERR_STATE, "descriptor workspace too small (raise max_match_tokens / max_match_dim)");
-  int rc = launch_normalize_rows_bf16(d1, c->desc, n_pairs * T, d, dpad, s, &c->err);
+  int rc;
+  { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
+    rc = launch_normalize_rows_bf16(d1, c->desc, n_pairs * T, d, dpad, s, &c->err); }
   if (rc) return rc;
-  rc = launch_normalize_rows_bf16(d2, c->desc + static_cast<size_t>(n_pairs) * T * dpad, n_pairs * T, d, dpad, s,
-                                  &c->err);
+  { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
+    rc = launch_normalize_rows_bf16(d2, c->desc + static_cast<size_t>(n_pairs) * T * dpad, n_pairs * T, d, dpad, s,
+                                    &c->err); }
   c->launch_count += 2;
   *dpad_out = dpad;
   return rc;
@@ -513,6 +535,7 @@ int pairs_control(vvs_ctx* c, const uint16_t* depth, int n_pairs, bool want_mean
   int rc = run_ibvs(c, c->uv, c->uv_star, depth, n_pairs, f.num_pairs, c->twist, nullptr, nullptr, nullptr, s);
   if (rc) return rc;
   if (want_mean) {
+    ProfScope ps(c, VVS_K_OTHER, s);
     mean_selected_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(c->sel_sim, c->n_sel, f.num_pairs, c->mean_sel, n_pairs);
     VVS_CUDA_OK(cudaGetLastError(), &c->err);
     ++c->launch_count;
@@ -870,6 +893,7 @@ int vvs_destroy(vvs_handle c) {
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->depth_ready) cudaEventDestroy(c->depth_ready);
   if (c->ws_done) cudaEventDestroy(c->ws_done);
+  if (c->trace_buf) cudaFree(c->trace_buf);
   for (cudaEvent_t e : c->chunk_events) cudaEventDestroy(e);
   free_resize_axis(&c->rz_w);
   free_resize_axis(&c->rz_h);
@@ -1247,6 +1271,67 @@ int vvs_render_plane(vvs_handle c, const uint8_t* texture, int32_t tex_h, int32_
   ++c->launch_count;
   return launch_render_plane(texture, tex_h, tex_w, plane_w, plane_h, cam_to_world, n, cam, rgb_out, depth_out,
                              static_cast<cudaStream_t>(stream), &c->err);
+}
+
+int vvs_trace_step(vvs_handle c, int32_t n_pairs, int32_t replays, int32_t* classes, uint64_t* begin_ns, uint64_t* end_ns,
+                   int32_t max_nodes, int32_t* n_nodes, vvs_stream stream) {
+  if (!c || !classes || !begin_ns || !end_ns || !n_nodes || max_nodes < 1)
+    return fail(c, VVS_ERR_INVALID, "vvs_trace_step: null argument");
+  if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
+  if (c->prof_on) return fail(c, VVS_ERR_STATE, "vvs_trace_step: switch the event profiler off first");
+  DeviceGuard dg(c);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (s == nullptr || s == cudaStreamLegacy) s = c->own_stream;
+  WorkspaceOrder wo(c, s);
+  if (!c->trace_buf) {
+    int rc = dev_alloc(c, &c->trace_buf, 2 * static_cast<size_t>(vvs_ctx::kTraceSlots));
+    if (rc) return rc;
+  }
+  // the same two graphs the frame-pair entry replays (inputs: whatever the last call left in the staging buffers),
+  // captured once more with a trace slot baked into every kernel
+  cudaGraphExec_t exec[2] = {nullptr, nullptr};
+  c->trace_cls.clear();
+  c->trace_on = true;
+  int rc = VVS_OK;
+  for (int part = 0; part < 2 && rc == VVS_OK; ++part) {
+    cudaGraph_t graph = nullptr;
+    if (cudaStreamBeginCapture(c->own_stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+      rc = fail(c, VVS_ERR_CUDA, "vvs_trace_step: stream capture failed");
+      break;
+    }
+    const int r = part == 0 ? pairs_forward_match(c, c->stage_img, n_pairs, nullptr, c->own_stream)
+                            : pairs_control(c, c->stage_depth, n_pairs, true, c->own_stream);
+    const cudaError_t e = cudaStreamEndCapture(c->own_stream, &graph);
+    if (r != VVS_OK || e != cudaSuccess || !graph || cudaGraphInstantiate(&exec[part], graph, 0) != cudaSuccess)
+      rc = fail(c, VVS_ERR_CUDA, "vvs_trace_step: graph capture / instantiation failed");
+    if (graph) cudaGraphDestroy(graph);
+  }
+  c->trace_on = false;
+  tl_trace_slot = nullptr;
+  const int n = static_cast<int>(c->trace_cls.size());
+  if (rc == VVS_OK) {
+    for (int i = 0; i < std::max(replays, 1) && rc == VVS_OK; ++i) {   // earlier replays bring clocks / caches to steady state
+      trace_reset_kernel<<<(n + 255) / 256, 256, 0, s>>>(c->trace_buf, n);
+      if (cudaGraphLaunch(exec[0], s) != cudaSuccess || cudaGraphLaunch(exec[1], s) != cudaSuccess)
+        rc = fail(c, VVS_ERR_CUDA, "vvs_trace_step: graph launch failed");
+    }
+  }
+  std::vector<unsigned long long> host(2 * static_cast<size_t>(std::max(n, 1)));
+  if (rc == VVS_OK &&
+      (cudaStreamSynchronize(s) != cudaSuccess ||
+       cudaMemcpy(host.data(), c->trace_buf, 2 * static_cast<size_t>(n) * sizeof(unsigned long long), cudaMemcpyDeviceToHost) !=
+           cudaSuccess))
+    rc = fail(c, VVS_ERR_CUDA, "vvs_trace_step: reading the trace failed");
+  for (auto& e : exec)
+    if (e) cudaGraphExecDestroy(e);
+  if (rc) return rc;
+  *n_nodes = std::min(n, max_nodes);
+  for (int i = 0; i < *n_nodes; ++i) {
+    classes[i] = c->trace_cls[i];
+    begin_ns[i] = host[2 * i];
+    end_ns[i] = host[2 * i + 1];
+  }
+  return VVS_OK;
 }
 
 int vvs_profile_enable(vvs_handle c, int32_t on) {

@@ -146,7 +146,9 @@ __device__ long long g_att_trace[4 * 3 * 16 * 8];
 
 __global__ void __launch_bounds__(kThreads, 4 / kQT)
 attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
-                    const __grid_constant__ CUtensorMap tmO, bf16* __restrict__ out, int n_tok, int D) {
+                    const __grid_constant__ CUtensorMap tmO, bf16* __restrict__ out, int n_tok, int D,
+                    unsigned long long* trace) {
+  trace_begin(trace);
 #ifdef VVS_ATT_TRACE
   const long long tr_entry = clock64();
 #endif
@@ -493,6 +495,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #ifdef VVS_ATT_TRACE
   const long long tr_loop_end = clock64();
 #endif
+  trace_end(trace);
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc<kTmemCols>(tmem_base);
@@ -542,7 +545,8 @@ int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads
               err);
   const int q_tiles = (n_tok + kBQ - 1) / kBQ;
   dim3 grid((q_tiles + kQT - 1) / kQT, heads, n_img);
-  VVS_CUDA_OK(launch_kernel(attention_ts_kernel, grid, kThreads, kSmem, stream, pdl, tmq, tmkv, tmo, out, n_tok, D), err);
+  VVS_CUDA_OK(launch_kernel(attention_ts_kernel, grid, kThreads, kSmem, stream, pdl, tmq, tmkv, tmo, out, n_tok, D,
+                            tl_trace_slot), err);
   return VVS_OK;
 }
 

@@ -35,7 +35,8 @@ __device__ __forceinline__ float normalize_px(uint8_t v, int c) {
 // One thread = 8 consecutive k of one patch row -> one 16-byte store.
 template <bool kU8>
 __global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ out, int n_img, int S, int kpad, int gp,
-                              int stride) {
+                              int stride, unsigned long long* trace) {
+  trace_begin(trace);
   // u8 input: the 3 x 256 possible outputs of ToTensor + Normalize, evaluated once per block with the exact
   // arithmetic above (two IEEE divisions each) - the per-element work is then a table lookup
   __shared__ float lut[3][256];
@@ -91,6 +92,7 @@ __global__ void im2col_kernel(const void* __restrict__ img_, bf16* __restrict__ 
     const long long img = idx / k8_per_row;
     *reinterpret_cast<uint4*>(out + img * (T + 1) * kpad + (idx - img * k8_per_row) * 8) = make_uint4(0u, 0u, 0u, 0u);
   }
+  trace_end(trace);
 }
 
 // pos'[0] = cls + pos[0] - patch_bias (the CLS row of the patch-embed GEMM has a zero accumulator: acc + bias + pos'[0]
@@ -114,10 +116,11 @@ __global__ void cls_rows_kernel(float* __restrict__ x, const float* __restrict__
 template <int NV>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
-                 bf16* __restrict__ out, int rows, float eps, int pin_row0) {
+                 bf16* __restrict__ out, int rows, float eps, int pin_row0, unsigned long long* trace) {
   constexpr int D = NV * 128;
   pdl_launch_dependents();
   pdl_wait();   // x is the previous kernel's output
+  trace_begin(trace);
   const int lane = threadIdx.x & 31;
   // The producer (a persistent GEMM) wrote x in ascending row order and x is larger than L2: walk the rows from
   // the end so that the reads start on the lines that are still resident; the consumer GEMM starts at row 0,
@@ -154,6 +157,7 @@ layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const
     const float y3 = (v[i].w - mean) * rstd * g.w + h.w;
     orow[i * 32 + lane] = make_uint2(pack2(y0, y1), pack2(y2, y3));
   }
+  trace_end(trace);
 }
 
 __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
@@ -262,7 +266,9 @@ __global__ void facet_descriptors_f32_kernel(const bf16* __restrict__ qkv, float
 }
 
 // squared L2 norm of every patch token (CLS skipped): one warp per token.
-__global__ void token_sqnorm_kernel(const float* __restrict__ x, float* __restrict__ n2, int n_img, int T, int D) {
+__global__ void token_sqnorm_kernel(const float* __restrict__ x, float* __restrict__ n2, int n_img, int T, int D,
+                                    unsigned long long* trace) {
+  trace_begin(trace);
   const int lane = threadIdx.x & 31;
   const long long tok = blockIdx.x * static_cast<long long>(blockDim.x >> 5) + (threadIdx.x >> 5);
   if (tok >= static_cast<long long>(n_img) * T) return;
@@ -275,6 +281,7 @@ __global__ void token_sqnorm_kernel(const float* __restrict__ x, float* __restri
   }
   s = warp_sum(s);
   if (lane == 0) n2[tok] = s;
+  trace_end(trace);
 }
 
 // unit-norm bf16 descriptors for the similarity GEMM: ||F_p||^2 = sum over the 9 clamped neighbours of
@@ -282,7 +289,8 @@ __global__ void token_sqnorm_kernel(const float* __restrict__ x, float* __restri
 // One block (128 threads) per (image, token).
 __global__ void __launch_bounds__(128)
 descriptors_unit_bf16_kernel(const float* __restrict__ x, const float* __restrict__ n2, bf16* __restrict__ out, int hp,
-                             int wp, int D, int parts) {
+                             int wp, int D, int parts, unsigned long long* trace) {
+  trace_begin(trace);
   const int T = hp * wp;
   const int t = blockIdx.x % T;
   const int img = blockIdx.x / T;
@@ -313,6 +321,7 @@ descriptors_unit_bf16_kernel(const float* __restrict__ x, const float* __restric
                                pack2(b.z * inv, b.w * inv));
     *reinterpret_cast<uint4*>(orow + p * D + c8 * 8) = w;
   }
+  trace_end(trace);
 }
 
 // arbitrary fp32 rows -> unit-norm bf16 rows (zero padded to dpad): one block per row.
@@ -343,7 +352,7 @@ int grid_for(long long work_items, int block) {
 int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpad, int grid, int stride, cudaStream_t s,
                      std::string* err) {
   const long long items = static_cast<long long>(n_img) * grid * grid * (kpad / 8);
-  im2col_kernel<true><<<grid_for(items, 256), 256, 0, s>>>(img, out, n_img, size, kpad, grid, stride);
+  im2col_kernel<true><<<grid_for(items, 256), 256, 0, s>>>(img, out, n_img, size, kpad, grid, stride, tl_trace_slot);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }
@@ -351,7 +360,7 @@ int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpa
 int launch_im2col_f32(const float* img, bf16* out, int n_img, int size, int kpad, int grid, int stride, cudaStream_t s,
                       std::string* err) {
   const long long items = static_cast<long long>(n_img) * grid * grid * (kpad / 8);
-  im2col_kernel<false><<<grid_for(items, 256), 256, 0, s>>>(img, out, n_img, size, kpad, grid, stride);
+  im2col_kernel<false><<<grid_for(items, 256), 256, 0, s>>>(img, out, n_img, size, kpad, grid, stride, tl_trace_slot);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }
@@ -375,10 +384,10 @@ int launch_layernorm(const float* x, const float* w, const float* b, bf16* out, 
   const int grid = (rows + 7) / 8;
   cudaError_t e;
   switch (D) {
-    case 384: e = launch_kernel(layernorm_kernel<3>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0); break;
-    case 768: e = launch_kernel(layernorm_kernel<6>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0); break;
-    case 1024: e = launch_kernel(layernorm_kernel<8>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0); break;
-    case 1536: e = launch_kernel(layernorm_kernel<12>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0); break;
+    case 384: e = launch_kernel(layernorm_kernel<3>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0, tl_trace_slot); break;
+    case 768: e = launch_kernel(layernorm_kernel<6>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0, tl_trace_slot); break;
+    case 1024: e = launch_kernel(layernorm_kernel<8>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0, tl_trace_slot); break;
+    case 1536: e = launch_kernel(layernorm_kernel<12>, grid, 256, 0, s, pdl, x, w, b, out, rows, eps, pin_row0, tl_trace_slot); break;
     default: set_error(err, "layernorm: unsupported width (384/768/1024/1536)"); return VVS_ERR_INVALID;
   }
   VVS_CUDA_OK(e, err);
@@ -416,9 +425,10 @@ int launch_descriptors_unit_bf16(const float* x, bf16* out, float* sqnorm_scratc
                                  int bin, cudaStream_t s, std::string* err) {
   const int T = hp * wp;
   const long long toks = static_cast<long long>(n_img) * T;
-  token_sqnorm_kernel<<<static_cast<int>((toks + 7) / 8), 256, 0, s>>>(x, sqnorm_scratch, n_img, T, D);
+  token_sqnorm_kernel<<<static_cast<int>((toks + 7) / 8), 256, 0, s>>>(x, sqnorm_scratch, n_img, T, D, tl_trace_slot);
   VVS_CUDA_OK(cudaGetLastError(), err);
-  descriptors_unit_bf16_kernel<<<static_cast<int>(toks), 128, 0, s>>>(x, sqnorm_scratch, out, hp, wp, D, bin ? 9 : 1);
+  descriptors_unit_bf16_kernel<<<static_cast<int>(toks), 128, 0, s>>>(x, sqnorm_scratch, out, hp, wp, D, bin ? 9 : 1,
+                                                                      tl_trace_slot);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }

@@ -48,6 +48,7 @@ struct GemmDev {
   unsigned long long* col_best;
   int best_pitch;
   int pin_row0;   // EPI_RESID_F32 / EPI_PATCH_F32: rows >= pin_row0 of x carry the L2 evict-last hint
+  unsigned long long* trace;   // vvs_trace_step slot (null otherwise)
 };
 
 // NCTA = 2: a CTA pair (cluster of 2 on one TPC) computes a 256 x BN tile with cta_group::2 MMAs; each CTA
@@ -158,6 +159,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   // everything above (barriers, TMEM, descriptor prefetch) may overlap the previous kernel's tail
   pdl_launch_dependents();
   pdl_wait();
+  trace_begin(p.trace);
 
   // p.m_tiles counts (128 * NCTA)-row tiles; this CTA owns 128-row block m_tile * NCTA + cta_rank of each
   const int tiles_per_batch = p.m_tiles * p.n_tiles;
@@ -500,6 +502,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) bulk_wait0();   // every bulk store / reduce of this warp has landed before the CTA retires
   }
 
+  trace_end(p.trace);
   tc_fence_before();
   if constexpr (NCTA >= 2) {
     cluster_sync_all();   // the peer may still be reading operands / signalling barriers of this CTA
@@ -671,6 +674,7 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   d.q_cols = a.q_cols; d.q_scale = a.q_scale; d.pos = a.pos; d.T = a.T;
   d.row_best = a.row_best; d.col_best = a.col_best; d.best_pitch = a.best_pitch;
   d.pin_row0 = a.pin_row0 > 0 ? a.pin_row0 : 0x7fffffff;
+  d.trace = tl_trace_slot;
   const long long tiles = static_cast<long long>(d.batch) * d.m_tiles * d.n_tiles;
   if (ncta == 4) {
     // co-resident 4-CTA clusters (a GPC with an odd number of TPCs leaves one TPC out)

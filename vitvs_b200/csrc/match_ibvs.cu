@@ -6,6 +6,7 @@
 //                   fp64, v = -lambda * L^+ e, optional EMA (vitvs_v2.py:566-586, :610-623, :634-659)
 #include <string>
 
+#include "ptx.cuh"
 #include "vvs_internal.h"
 
 namespace vvs {
@@ -40,7 +41,8 @@ __device__ __forceinline__ float cyclic_distance(int dr, int dc) {
   return __fsqrt_rn(__fmaf_rn(b, b, __fmul_rn(a, a)));
 }
 
-__global__ void __launch_bounds__(256) select_kernel(const SelectArgs a) {
+__global__ void __launch_bounds__(256) select_kernel(const SelectArgs a, unsigned long long* trace) {
+  trace_begin(trace);
   __shared__ unsigned long long s_u64[32];
   __shared__ float s_f32[32];
   __shared__ double s_f64[32];
@@ -205,6 +207,7 @@ __global__ void __launch_bounds__(256) select_kernel(const SelectArgs a) {
     a.n_selected[pair] = nsel;
     a.flags[pair] = (same ? 1 : 0) | (unset ? 2 : 0);
   }
+  trace_end(trace);
 }
 
 // Per-point terms of the control law with the reference's own argument lists (no depth frame involved):
@@ -289,7 +292,8 @@ __device__ void pinv_solve6(double A[6][6], const double g[6], double x[6]) {
 }
 
 // one warp per frame pair
-__global__ void __launch_bounds__(128) ibvs_kernel(const IbvsArgs a) {
+__global__ void __launch_bounds__(128) ibvs_kernel(const IbvsArgs a, unsigned long long* trace) {
+  trace_begin(trace);
   const int lane = threadIdx.x & 31;
   const int pair = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (pair >= a.n_pairs) return;
@@ -400,6 +404,7 @@ __global__ void __launch_bounds__(128) ibvs_kernel(const IbvsArgs a) {
     tw[i] = v;
   }
   if (a.ema_state) a.ema_init[pair] = 1;
+  trace_end(trace);
 }
 
 }  // namespace
@@ -409,7 +414,7 @@ int launch_select(const SelectArgs& a, cudaStream_t s, std::string* err) {
     set_error(err, "select: num_pairs must be in [1, 256]");
     return VVS_ERR_INVALID;
   }
-  select_kernel<<<a.n_pairs, 256, 0, s>>>(a);
+  select_kernel<<<a.n_pairs, 256, 0, s>>>(a, tl_trace_slot);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }
@@ -428,7 +433,7 @@ int launch_interaction(const double* xy, const double* z, int n, double* L, cuda
 }
 
 int launch_ibvs(const IbvsArgs& a, cudaStream_t s, std::string* err) {
-  ibvs_kernel<<<(a.n_pairs + 3) / 4, 128, 0, s>>>(a);
+  ibvs_kernel<<<(a.n_pairs + 3) / 4, 128, 0, s>>>(a, tl_trace_slot);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }

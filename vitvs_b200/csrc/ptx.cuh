@@ -73,6 +73,23 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// ----------------------------------------------------------------------------- step tracing (vvs_trace_step)
+// Every kernel of the path takes an optional slot pointer (null in normal operation: one predicated branch).  When
+// set, lane 0 of every warp stamps %globaltimer into slot[0] (atomicMin: first warp to start) on entry and into
+// slot[1] (atomicMax: last warp to finish) on exit, so one traced replay of the captured graphs gives the device
+// time of every node AND of every gap between nodes - which events around launches cannot see inside a graph.
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void trace_begin(unsigned long long* slot) {
+  if (slot != nullptr && (threadIdx.x & 31) == 0) atomicMin(slot, globaltimer_ns());
+}
+__device__ __forceinline__ void trace_end(unsigned long long* slot) {
+  if (slot != nullptr && (threadIdx.x & 31) == 0) atomicMax(slot + 1, globaltimer_ns());
+}
+
 // ----------------------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");

@@ -52,6 +52,11 @@ struct PerDeviceOnce {
   }
 };
 
+// ---- step tracing ------------------------------------------------------------------------------------
+// Slot ([begin, end] device words) the NEXT kernel launched by this host thread stamps its %globaltimer span into
+// (ptx.cuh trace_begin / trace_end); null outside vvs_trace_step.  Set by api.cu around every launch.
+extern thread_local unsigned long long* tl_trace_slot;
+
 // ---- launches ------------------------------------------------------------------------------------
 // <<< >>> with an optional programmatic-dependent-launch attribute (ptx.cuh: pdl_wait / pdl_launch_dependents)
 bool pdl_enabled();   // VITVS_PDL=1 turns it on (off by default, see api.cu)

@@ -406,6 +406,18 @@ class Engine:
         self._check(self.lib.vvs_profile_read(self._h, ms, cnt, n), "vvs_profile_read")
         return {k: (ms[i], cnt[i]) for i, k in enumerate(_lib.KERNEL_CLASSES) if cnt[i]}
 
+    def trace_step(self, n_pairs: int, replays: int = 3) -> list[tuple[str, int, int]]:
+        """[(kernel class, begin_ns, end_ns)] of every kernel of one traced graph replay of the frame-pair path (the
+        last of `replays` back-to-back ones), on the inputs of the previous frame_pairs_to_twist call."""
+        cap = 1024
+        cls = (C.c_int32 * cap)()
+        b = (C.c_uint64 * cap)()
+        e = (C.c_uint64 * cap)()
+        n = C.c_int32(0)
+        self._check(self.lib.vvs_trace_step(self._h, n_pairs, replays, cls, b, e, cap, C.byref(n), _stream(self.device)),
+                    "vvs_trace_step")
+        return [(_lib.KERNEL_CLASSES[cls[i]], int(b[i]), int(e[i])) for i in range(n.value)]
+
     @property
     def gram_stencil(self) -> bool:
         """True when the fused path matches binned descriptors through the token Gram matrix (never materialised)."""
