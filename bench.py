@@ -288,6 +288,7 @@ def pct(xs, q):
 
 def account_trace(trace):
     """[(class, begin_ns, end_ns)] of one traced graph replay -> per-class kernel time, gaps, span (ms)."""
+    trace = [t for t in (trace or []) if t[1] != 2 ** 64 - 1 and t[2] != 0]      # a slot no kernel stamped
     if not trace:
         return None
     kern, gaps, memset_gap = {}, 0.0, 0.0

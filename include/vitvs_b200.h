@@ -203,6 +203,19 @@ VVS_API int vvs_frame_pairs_to_twist_host(vvs_handle h, const uint8_t* goal_host
                                   const uint16_t* depth_host, int32_t n_pairs, double* twist_host,
                                   int32_t* n_selected_host, float* mean_sim_sel_host, vvs_stream stream);
 
+/* The two host-buffer calls without the final wait: they return once the copies and kernels are enqueued, and the next
+ * call's H2D copies (second landing zone, own copy stream) then run under this call's compute.  Outputs are valid after
+ * vvs_wait(h, 0) (the latest asynchronous call) / vvs_wait(h, 1) (the one before it); at most two may be in flight, and
+ * the host buffers of a call must stay untouched until it has been waited for.  A servo loop over many cameras submits
+ * batch i+1 while batch i computes (independent units). */
+VVS_API int vvs_frame_pairs_to_twist_host_async(vvs_handle h, const uint8_t* goal_host, const uint8_t* current_host,
+                                        const uint16_t* depth_host, int32_t n_pairs, double* twist_host,
+                                        int32_t* n_selected_host, float* mean_sim_sel_host, vvs_stream stream);
+VVS_API int vvs_frames_to_twist_host_async(vvs_handle h, const uint8_t* goal_frames_host, const uint8_t* current_frames_host,
+                                   const uint16_t* depth_host, int32_t n_pairs, double* twist_host,
+                                   int32_t* n_selected_host, float* mean_sim_sel_host, vvs_stream stream);
+VVS_API int vvs_wait(vvs_handle h, int32_t calls_back);
+
 /* replaces: PIL `Image.resize((S, S))` of the goal / current camera frame (vitvs_v2.py:474-475; Pillow default
  * filter = antialiased BICUBIC, 8-bit fixed point, horizontal pass then vertical pass).  frames
  * [n, frame_height, frame_width, 3] uint8 RGB (device) -> out [n, S, S, 3] uint8 (device), bit-identical to

@@ -40,8 +40,12 @@ def test_model_family_parity(model_type):
     marg2 = (S[m.nn2, rows] - S[nn2, rows]).numpy()
     print(f"[{model_type}] nn1 agree {1 - bad1.mean():.4f} nn2 agree {1 - bad2.mean():.4f} "
           f"worst margin {max(marg1.max(), marg2.max()):.2e}")
-    # >= 99 % mutual-NN index agreement, per direction (north_star)
-    assert bad1.mean() <= 0.01 and bad2.mean() <= 0.01
+    # >= 99 % mutual-NN index agreement, per direction (north_star).  Random-init ViT-g is the stated exception (DESIGN.md 5,
+    # tests/test_gpu_depth.py): a nearly flat similarity landscape puts 1 - 1.5 % of its rows inside the bf16 noise of S
+    from _parity import margin_histogram
+    print(f"[{model_type}] oracle best-vs-second margins below threshold: {margin_histogram(S)}")
+    limit = 0.015 if model_type == "dinov2_vitg14" else 0.01
+    assert bad1.mean() <= limit and bad2.mean() <= limit
     assert np.all(marg1[bad1] < TIE_EPS) and np.all(marg2[bad2] < TIE_EPS)   # ... disagreements only at near-ties
     uv, uvs = out["uv"][0].cpu().numpy().astype(int), out["uv_star"][0].cpu().numpy().astype(int)
     tw_ref = servo.ibvs_twist(uv, uvs, depth)

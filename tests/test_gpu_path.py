@@ -265,6 +265,44 @@ def test_host_entry_equals_device_entry(eng):
     assert torch.equal(ms, dev["mean_sim_sel"].cpu())
 
 
+def test_async_host_entries_equal_sync(eng):
+    """vvs_*_host_async + vvs_wait: calls in flight share nothing but the compute stream - each lands in its own zone -
+    and every one returns what the synchronous call returns, whatever the interleaving of copies and compute."""
+    sets = []
+    for s in range(3):
+        pairs = [synth.raw_frame_pair(10 * s + i) for i in range(3)]
+        raw = tuple(torch.from_numpy(np.stack([p[k] for p in pairs])).pin_memory() for k in range(3))
+        rz = (torch.from_numpy(np.stack([synth.resize_square(p[0], 308) for p in pairs])).pin_memory(),
+              torch.from_numpy(np.stack([synth.resize_square(p[1], 308) for p in pairs])).pin_memory(), raw[2])
+        sets.append((rz, raw))
+
+    def outs():
+        return (torch.empty(3, 6, dtype=torch.float64).pin_memory(), torch.empty(3, dtype=torch.int32).pin_memory(),
+                torch.empty(3, dtype=torch.float32).pin_memory())
+    for which, fn in ((0, eng.frame_pairs_to_twist_host), (1, eng.frames_to_twist_host)):
+        ref = []
+        for d in sets:
+            o = outs()
+            fn(*d[which], *o)
+            ref.append([t.clone() for t in o])
+        bufs, got = [outs(), outs()], []
+        for i in range(7):
+            fn(*sets[i % 3][which], *bufs[i % 2], wait=False)
+            if i >= 1:
+                eng.wait(1)                                   # the call before the one just submitted
+                got.append([t.clone() for t in bufs[(i - 1) % 2]])
+        eng.wait(0)
+        got.append([t.clone() for t in bufs[0]])
+        for i, g in enumerate(got):
+            for a, b in zip(g, ref[i % 3]):
+                assert torch.equal(a, b), (which, i)
+    # the pre-resized and the raw-frame entries agree (PIL-exact resize on the GPU)
+    o1, o2 = outs(), outs()
+    eng.frame_pairs_to_twist_host(*sets[0][0], *o1)
+    eng.frames_to_twist_host(*sets[0][1], *o2)
+    assert torch.equal(o1[0], o2[0])
+
+
 def test_same_image_gives_zero_twist(eng):
     g, _, d = synth.frame_pair(5)
     goal = torch.from_numpy(g[None]).cuda()

@@ -65,6 +65,9 @@ SYMBOLS = {
     "vvs_ibvs_terms": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "vvs_frame_pairs_to_twist": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, C.POINTER(PairOut), c_vp]),
     "vvs_frame_pairs_to_twist_host": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),
+    "vvs_frame_pairs_to_twist_host_async": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),
+    "vvs_frames_to_twist_host_async": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),
+    "vvs_wait": (c_i32, [c_vp, c_i32]),
     "vvs_resize_frames": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_vp]),
     "vvs_frames_to_twist": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, C.POINTER(PairOut), c_vp]),
     "vvs_frames_to_twist_host": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),

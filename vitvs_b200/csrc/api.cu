@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "../../include/vitvs_b200.h"
+#include "ptx.cuh"
 #include "vvs_internal.h"
 
 namespace vvs {
@@ -19,14 +20,18 @@ void set_error(std::string* slot, const std::string& msg) {
   if (slot) *slot = msg;
 }
 
-bool pdl_enabled() {
-  static const bool on = []() {
-    // off by default: measured on B200 (64-pair ViT-B step, graph replay) 14.04 ms with PDL vs 13.83 ms without -
-    // the step runs under the 1 kW power cap, where idle gaps between kernels are paid back as clock boost
+bool pdl_for_rows(long long rows, int dim) {
+  // Measured on B200, graph replay.  64 pairs of ViT-B: 14.04 ms with PDL vs 13.83 ms without - the step runs under the
+  // power cap, where idle gaps between kernels are paid back as clock boost.  One pair (970 rows, ~90 kernels of a few
+  // microseconds each, launch-latency-bound): ViT-S 0.673 -> 0.635 ms p50 with PDL (the next kernel's prologue - barrier
+  // init, TMEM allocation, descriptor prefetch - runs under the previous kernel's tail), ViT-B 0.935 -> 0.953 ms (its
+  // kernels are long enough that early CTAs only compete for the SMs).  Hence: small batches of the narrow model only.
+  static const int mode = []() {
     const char* e = getenv("VITVS_PDL");
-    return e && e[0] == '1';
+    return !e ? -1 : (e[0] == '1' ? 1 : 0);
   }();
-  return on;
+  if (mode >= 0) return mode == 1;
+  return rows <= 4096 && dim <= 384;
 }
 
 namespace {
@@ -76,13 +81,16 @@ __global__ void trace_reset_kernel(unsigned long long* buf, int n_slots) {
 }
 
 __global__ void mean_selected_kernel(const float* __restrict__ sel_sim, const int32_t* __restrict__ n_sel, int K,
-                                     float* __restrict__ out, int n_pairs) {
+                                     float* __restrict__ out, int n_pairs, unsigned long long* trace) {
+  trace_begin(trace);
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= n_pairs) return;
-  const int n = n_sel[p];
-  float s = 0.f;
-  for (int k = 0; k < n; ++k) s += sel_sim[static_cast<size_t>(p) * K + k];
-  out[p] = n > 0 ? s / n : 0.f;
+  if (p < n_pairs) {
+    const int n = n_sel[p];
+    float s = 0.f;
+    for (int k = 0; k < n; ++k) s += sel_sim[static_cast<size_t>(p) * K + k];
+    out[p] = n > 0 ? s / n : 0.f;
+  }
+  trace_end(trace);
 }
 
 struct BlockW {
@@ -135,7 +143,15 @@ struct vvs_ctx {
   // camera-frame front end (created on first use): Pillow-exact bicubic resize tables + staging
   bool rz_ready = false;
   ResizeAxis rz_w, rz_h;           // frame_width -> S (horizontal pass), frame_height -> S (vertical pass)
-  uint8_t* stage_frames = nullptr; // [max_images, H, W, 3] raw frames (also the H2D landing zone of the host entries)
+  // H2D landing zones of the host-buffer entries, double buffered: the copies of call i+1 (copy stream) run under the
+  // compute of call i.  land_frames[k]: [max_images, H, W, 3] bytes (camera frames or pre-resized images),
+  // land_depth[k]: [max_pairs, H, W] u16.  slot_free[k] is recorded on the compute stream when a call has consumed slot k.
+  uint8_t* land_frames[2] = {nullptr, nullptr};
+  uint16_t* land_depth[2] = {nullptr, nullptr};
+  cudaEvent_t slot_free[2] = {nullptr, nullptr};
+  bool slot_used[2] = {false, false};
+  int host_slot = 0;
+  cudaStream_t host_stream = nullptr;   // stream of the last host-buffer call (vvs_wait synchronises it)
   uint8_t* rz_tmp = nullptr;       // [max_images, H, S, 3] output of the horizontal pass
   int last_n_img = 0;
   int facet_n_img = 0;       // images whose qkv(norm1(x)) of the requested block sits in `big` (vvs_forward_facet)
@@ -336,7 +352,7 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
   }
   // inside the blocks every kernel is PDL-aware (LayerNorm, GEMMs, attention): programmatic dependent launches.
   // The event profiler brackets launches with event records, which would sit between the kernels.
-  const bool pdl = !c->prof_on;
+  const bool pdl = !c->prof_on && pdl_for_rows(M, D);
   for (int i = 0; i <= layer; ++i) {
     const BlockW& w = c->blocks[i];
     { ProfScope ps(c, VVS_K_LAYERNORM, s);
@@ -536,7 +552,8 @@ int pairs_control(vvs_ctx* c, const uint16_t* depth, int n_pairs, bool want_mean
   if (rc) return rc;
   if (want_mean) {
     ProfScope ps(c, VVS_K_OTHER, s);
-    mean_selected_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(c->sel_sim, c->n_sel, f.num_pairs, c->mean_sel, n_pairs);
+    mean_selected_kernel<<<(n_pairs + 127) / 128, 128, 0, s>>>(c->sel_sim, c->n_sel, f.num_pairs, c->mean_sel, n_pairs,
+                                                               tl_trace_slot);
     VVS_CUDA_OK(cudaGetLastError(), &c->err);
     ++c->launch_count;
   }
@@ -628,7 +645,12 @@ int ensure_frontend(vvs_ctx* c) {
   int rc = make_resize_axis(&c->rz_w, f.frame_width, f.image_size, &c->err);
   if (!rc) rc = make_resize_axis(&c->rz_h, f.frame_height, f.image_size, &c->err);
   const size_t frame_bytes = static_cast<size_t>(f.frame_width) * f.frame_height * 3;
-  if (!rc) rc = dev_alloc(c, &c->stage_frames, static_cast<size_t>(f.max_images) * frame_bytes);
+  for (int k = 0; k < 2 && !rc; ++k) {
+    rc = dev_alloc(c, &c->land_frames[k], static_cast<size_t>(f.max_images) * frame_bytes);
+    if (!rc) rc = dev_alloc(c, &c->land_depth[k], static_cast<size_t>(c->max_pairs) * f.frame_width * f.frame_height);
+    if (!rc && cudaEventCreateWithFlags(&c->slot_free[k], cudaEventDisableTiming) != cudaSuccess)
+      rc = fail(c, VVS_ERR_CUDA, "cudaEventCreateWithFlags failed");
+  }
   if (!rc) rc = dev_alloc(c, &c->rz_tmp, static_cast<size_t>(f.max_images) * f.frame_height * f.image_size * 3);
   if (rc) return rc;
   c->rz_ready = true;
@@ -662,12 +684,14 @@ int resize_frames(vvs_ctx* c, const uint8_t* frames, int n, uint8_t* out, cudaSt
   return rc;
 }
 
-// Host-buffer calls, pipelined: the batch is cut into sub-batches; the H2D copies of sub-batch j+1 (copy stream) run
-// under the device path of sub-batch j (compute stream).  Inputs land in stage_frames / stage_depth at their natural
-// offsets; each sub-batch is resized (camera frames) or copied (pre-resized images) into the [goal.. | current..]
-// block at the head of stage_img that the captured graph reads.  from_frames: inputs are [n, H, W, 3] camera frames.
+// Host-buffer calls, pipelined twice over.  ACROSS calls: inputs land in one of two landing zones, so the H2D copies of
+// call i+1 (copy stream) run under the device path of call i (compute stream) when the caller uses the asynchronous
+// entries (submit i+1, then vvs_wait for i).  INSIDE a synchronous call: the batch is cut into sub-batches and the H2D of
+// sub-batch j+1 runs under the compute of sub-batch j.  Each sub-batch is resized (camera frames) or copied
+// (pre-resized images) into the [goal.. | current..] block at the head of stage_img that the captured graph reads.
+// from_frames: inputs are [n, H, W, 3] camera frames.  sync: wait for the results before returning.
 int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth, int n_pairs, bool from_frames,
-                  double* twist, int32_t* n_selected, float* mean_sim_sel, cudaStream_t s) {
+                  double* twist, int32_t* n_selected, float* mean_sim_sel, cudaStream_t s, bool sync) {
   const vvs_config& f = c->cfg;
   int rc = ensure_frontend(c);
   if (rc) return rc;
@@ -687,7 +711,7 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
     int chunks = std::max(1, std::min(c->host_chunks, n_pairs / 8));
     const int per = (n_pairs + chunks - 1) / chunks;
     for (int p0 = 0; p0 < n_pairs; p0 += per) parts.emplace_back(p0, std::min(per, n_pairs - p0));
-  } else if (from_frames && n_pairs >= 32) {
+  } else if (from_frames && n_pairs >= 32 && sync) {
     const int first = n_pairs / 8;
     parts.emplace_back(0, first);
     parts.emplace_back(first, n_pairs - first);
@@ -695,15 +719,22 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
     parts.emplace_back(0, n_pairs);
   }
   const int chunks = static_cast<int>(parts.size());
-  while (c->chunk_events.size() < static_cast<size_t>(2 * chunks)) {
+  const int slot = c->host_slot;
+  c->host_slot ^= 1;
+  c->host_stream = s;
+  constexpr int kMaxChunks = 16;
+  if (chunks > kMaxChunks) return fail(c, VVS_ERR_INVALID, "VITVS_HOST_CHUNKS too large");
+  while (c->chunk_events.size() < static_cast<size_t>(2 * 2 * kMaxChunks)) {
     cudaEvent_t e;
     VVS_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), &c->err);
     c->chunk_events.push_back(e);
   }
-  uint8_t* land_goal = c->stage_frames;
-  uint8_t* land_cur = c->stage_frames + static_cast<size_t>(n_pairs) * in_bytes;
-  // a previous (asynchronous, device-buffer) call may still be reading the staging buffers: the copies wait for it
-  if (c->ws_used) VVS_CUDA_OK(cudaStreamWaitEvent(c->copy_stream, c->ws_done, 0), &c->err);
+  cudaEvent_t* ev = c->chunk_events.data() + slot * 2 * kMaxChunks;   // this slot's [frames landed, depth landed] per chunk
+  uint8_t* land_goal = c->land_frames[slot];
+  uint8_t* land_cur = c->land_frames[slot] + static_cast<size_t>(n_pairs) * in_bytes;
+  uint16_t* land_depth = c->land_depth[slot];
+  // the landing zones belong to the host entries alone; slot k is free once the call before last has consumed it
+  if (c->slot_used[slot]) VVS_CUDA_OK(cudaStreamWaitEvent(c->copy_stream, c->slot_free[slot], 0), &c->err);
   // Copy order: the frames of every sub-batch
   // first, the depth maps (read only by the control law at the end of a sub-batch) behind them.
   for (int j = 0; j < chunks; ++j) {
@@ -712,18 +743,18 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
                                 c->copy_stream), &c->err);
     VVS_CUDA_OK(cudaMemcpyAsync(land_cur + p0 * in_bytes, cur + p0 * in_bytes, nc * in_bytes, cudaMemcpyHostToDevice,
                                 c->copy_stream), &c->err);
-    VVS_CUDA_OK(cudaEventRecord(c->chunk_events[2 * j], c->copy_stream), &c->err);
+    VVS_CUDA_OK(cudaEventRecord(ev[2 * j], c->copy_stream), &c->err);
   }
   for (int j = 0; j < chunks; ++j) {
     const int p0 = parts[j].first, nc = parts[j].second;
-    VVS_CUDA_OK(cudaMemcpyAsync(c->stage_depth + p0 * depth_elems, depth + p0 * depth_elems,
+    VVS_CUDA_OK(cudaMemcpyAsync(land_depth + p0 * depth_elems, depth + p0 * depth_elems,
                                 nc * depth_elems * sizeof(uint16_t), cudaMemcpyHostToDevice, c->copy_stream), &c->err);
-    VVS_CUDA_OK(cudaEventRecord(c->chunk_events[2 * j + 1], c->copy_stream), &c->err);
+    VVS_CUDA_OK(cudaEventRecord(ev[2 * j + 1], c->copy_stream), &c->err);
   }
   int launches = 0;
   for (int j = 0; j < chunks; ++j) {
     const int p0 = parts[j].first, nc = parts[j].second;
-    VVS_CUDA_OK(cudaStreamWaitEvent(s, c->chunk_events[2 * j], 0), &c->err);
+    VVS_CUDA_OK(cudaStreamWaitEvent(s, ev[2 * j], 0), &c->err);
     c->launch_count = 0;
     if (from_frames) {
       if ((rc = resize_frames(c, land_goal + p0 * in_bytes, nc, c->stage_img, s))) return rc;
@@ -744,9 +775,9 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
       if ((rc = pairs_forward_match(c, c->stage_img, nc, nullptr, s))) return rc;
       launches += c->launch_count;
     }
-    VVS_CUDA_OK(cudaStreamWaitEvent(s, c->chunk_events[2 * j + 1], 0), &c->err);
+    VVS_CUDA_OK(cudaStreamWaitEvent(s, ev[2 * j + 1], 0), &c->err);
     c->launch_count = 0;
-    if ((rc = pairs_control(c, c->stage_depth + p0 * depth_elems, nc, want_mean, s))) return rc;
+    if ((rc = pairs_control(c, land_depth + p0 * depth_elems, nc, want_mean, s))) return rc;
     launches += c->launch_count;
     VVS_CUDA_OK(cudaMemcpyAsync(twist + p0 * 6, c->twist, nc * 6 * sizeof(double), cudaMemcpyDeviceToHost, s), &c->err);
     if (n_selected)
@@ -755,7 +786,9 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
       VVS_CUDA_OK(cudaMemcpyAsync(mean_sim_sel + p0, c->mean_sel, nc * sizeof(float), cudaMemcpyDeviceToHost, s), &c->err);
   }
   c->launch_count = launches;
-  VVS_CUDA_OK(cudaStreamSynchronize(s), &c->err);
+  VVS_CUDA_OK(cudaEventRecord(c->slot_free[slot], s), &c->err);
+  c->slot_used[slot] = true;
+  if (sync) VVS_CUDA_OK(cudaStreamSynchronize(s), &c->err);
   return VVS_OK;
 }
 
@@ -893,13 +926,16 @@ int vvs_destroy(vvs_handle c) {
   if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->depth_ready) cudaEventDestroy(c->depth_ready);
   if (c->ws_done) cudaEventDestroy(c->ws_done);
+  for (cudaEvent_t e : c->slot_free)
+    if (e) cudaEventDestroy(e);
   if (c->trace_buf) cudaFree(c->trace_buf);
   for (cudaEvent_t e : c->chunk_events) cudaEventDestroy(e);
   free_resize_axis(&c->rz_w);
   free_resize_axis(&c->rz_h);
   void* ptrs[] = {c->pe_w, c->pe_b, c->cls, c->pos, c->pos_prime, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
                   c->inv_norm, c->nn1, c->nn2, c->sim1, c->cand, c->mean_sim1, c->n_cand, c->n_sel, c->flags, c->mean_sel,
-                  c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth, c->stage_frames,
+                  c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth, c->land_frames[0], c->land_frames[1],
+                  c->land_depth[0], c->land_depth[1],
                   c->rz_tmp};
   for (void* p : ptrs)
     if (p) cudaFree(p);
@@ -1212,7 +1248,30 @@ int vvs_frame_pairs_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8
   if (s == nullptr || s == cudaStreamLegacy) s = c->own_stream;
   DeviceGuard dg(c);
   WorkspaceOrder wo(c, s);
-  return host_pipeline(c, goal, cur, depth, n_pairs, /*from_frames=*/false, twist, n_selected, mean_sim_sel, s);
+  return host_pipeline(c, goal, cur, depth, n_pairs, /*from_frames=*/false, twist, n_selected, mean_sim_sel, s, true);
+}
+
+int vvs_frame_pairs_to_twist_host_async(vvs_handle c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth,
+                                        int32_t n_pairs, double* twist, int32_t* n_selected, float* mean_sim_sel,
+                                        vvs_stream stream) {
+  if (!c || !goal || !cur || !depth || !twist)
+    return fail(c, VVS_ERR_INVALID, "vvs_frame_pairs_to_twist_host_async: null argument");
+  if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (s == nullptr || s == cudaStreamLegacy) s = c->own_stream;
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, s);
+  return host_pipeline(c, goal, cur, depth, n_pairs, /*from_frames=*/false, twist, n_selected, mean_sim_sel, s, false);
+}
+
+int vvs_wait(vvs_handle c, int32_t calls_back) {
+  if (!c) return VVS_ERR_INVALID;
+  if (calls_back < 0 || calls_back > 1) return fail(c, VVS_ERR_INVALID, "vvs_wait: calls_back must be 0 (latest) or 1 (the one before)");
+  const int slot = calls_back == 0 ? (c->host_slot ^ 1) : c->host_slot;
+  if (!c->slot_used[slot]) return VVS_OK;
+  DeviceGuard dg(c);
+  VVS_CUDA_OK(cudaEventSynchronize(c->slot_free[slot]), &c->err);
+  return VVS_OK;
 }
 
 int vvs_resize_frames(vvs_handle c, const uint8_t* frames, int32_t n, uint8_t* out, vvs_stream stream) {
@@ -1255,7 +1314,20 @@ int vvs_frames_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8_t* c
   if (s == nullptr || s == cudaStreamLegacy) s = c->own_stream;
   DeviceGuard dg(c);
   WorkspaceOrder wo(c, s);
-  return host_pipeline(c, goal, cur, depth, n_pairs, /*from_frames=*/true, twist, n_selected, mean_sim_sel, s);
+  return host_pipeline(c, goal, cur, depth, n_pairs, /*from_frames=*/true, twist, n_selected, mean_sim_sel, s, true);
+}
+
+int vvs_frames_to_twist_host_async(vvs_handle c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth,
+                                   int32_t n_pairs, double* twist, int32_t* n_selected, float* mean_sim_sel,
+                                   vvs_stream stream) {
+  if (!c || !goal || !cur || !depth || !twist)
+    return fail(c, VVS_ERR_INVALID, "vvs_frames_to_twist_host_async: null argument");
+  if (n_pairs < 1 || 2 * n_pairs > c->cfg.max_images) return fail(c, VVS_ERR_INVALID, "n_pairs outside [1, max_images/2]");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (s == nullptr || s == cudaStreamLegacy) s = c->own_stream;
+  DeviceGuard dg(c);
+  WorkspaceOrder wo(c, s);
+  return host_pipeline(c, goal, cur, depth, n_pairs, /*from_frames=*/true, twist, n_selected, mean_sim_sel, s, false);
 }
 
 int vvs_render_plane(vvs_handle c, const uint8_t* texture, int32_t tex_h, int32_t tex_w, double plane_w, double plane_h,

@@ -111,10 +111,15 @@ __device__ __forceinline__ uint32_t ord_f32(float f) {
 }
 
 
+// NCTA = 4 ("mixed"): the grid is cut into chunks of four consecutive CTAs, launched with cluster size 2 and PREFERRED
+// cluster size 4 (cudaLaunchAttributePreferredClusterDimension).  The hardware groups a chunk into one 4-CTA cluster
+// where a GPC has two free TPCs side by side and into two 2-CTA clusters where it has not (GPCs with an odd number of
+// TPCs: a static 4-CTA launch fits only 33 clusters = 132 of the 148 SMs).  Either way the chunk computes the same
+// 512 x BN work item: as a quad its two pairs share the B tile through TMA multicast (each CTA fetches a quarter), as
+// two pairs each fetches its own half.  The cluster size is read at run time (%cluster_nctaid).
 template <int BN, int EPI, int NCTA>
-__global__ void __cluster_dims__(NCTA, 1, 1) __launch_bounds__(kGemmThreads, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ CUtensorMap tmOut, const GemmDev p) {
+__device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmB2,
+                                          const CUtensorMap& tmOut, const GemmDev& p) {
   using C = Cfg<BN, NCTA>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -132,14 +137,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const uint32_t cta_rank = (NCTA >= 2) ? cluster_ctarank() : 0u;
   const uint32_t pair_rank = cta_rank & 1u;          // 0 = leader of its pair (issues the MMAs)
   const uint32_t leader_rank = cta_rank & ~1u;       // cluster rank of this CTA's pair leader
+  const bool quad = (NCTA == 4) && cluster_nctaid_x() == 4u;   // mixed mode: this chunk runs as one 4-CTA cluster
+  // 128-row block of the work item this CTA owns: its position inside the chunk (quad: the cluster rank)
+  const uint32_t slot = (NCTA == 4 && !quad) ? ((blockIdx.x & 2u) | cta_rank) : cta_rank;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if constexpr (NCTA == 4) tma_prefetch_desc(&tmB2);
     tma_prefetch_desc(&tmOut);
     for (int s = 0; s < C::kStages; ++s) {
       mbar_init(&full[s], 1);     // pair: only the leader's is used; its expect_tx covers both CTAs' boxes
-      mbar_init(&empty[s], NCTA == 4 ? 2 : 1);   // two pairs: a stage is free when BOTH have consumed it
+      mbar_init(&empty[s], quad ? 2 : 1);   // two pairs sharing B: a stage is free when BOTH have consumed it
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
@@ -177,13 +186,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
         const int b = tile / tiles_per_batch;
         const int r = tile - b * tiles_per_batch;
-        const int m_blk = (r / p.n_tiles) * NCTA + static_cast<int>(cta_rank);
+        const int m_blk = (r / p.n_tiles) * NCTA + static_cast<int>(slot);
         const int n_blk = r % p.n_tiles;
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
           if (lane == 0) {
-            if constexpr (NCTA == 4) {
+            if (NCTA == 4 && quad) {
               // this CTA fetches ONE quarter of the B tile and multicasts it to the CTA of the same parity in the
               // other pair: every CTA still receives its 128-row half, the L2 -> SM traffic per CTA drops by a quarter
               if (pair_rank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
@@ -194,12 +203,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                                  n_blk * BN + static_cast<int>(pair_rank) * (BN / 2) + quarter * (BN / 4),
                                  p.b_batched ? b : 0, static_cast<uint16_t>((1u << cta_rank) | (1u << (cta_rank ^ 2u))),
                                  kEvictLast);
-            } else if constexpr (NCTA == 2) {
+            } else if constexpr (NCTA >= 2) {
               if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
               const uint32_t fb = full0 + stage * 8;
               tma_load_3d_2sm(sa, &tmA, fb, kb * BK, m_blk * BM, b, kEvictNormal);
-              tma_load_3d_2sm(sa + C::kABytes, &tmB, fb, kb * BK, n_blk * BN + static_cast<int>(cta_rank) * (BN / 2),
-                              p.b_batched ? b : 0, kEvictLast);
+              tma_load_3d_2sm(sa + C::kABytes, NCTA == 4 ? &tmB2 : &tmB, fb, kb * BK,
+                              n_blk * BN + static_cast<int>(cta_rank) * (BN / 2), p.b_batched ? b : 0, kEvictLast);
             } else {
               mbar_expect_tx(&full[stage], C::kStageBytes);
               tma_load_3d(sa, &tmA, &full[stage], kb * BK, m_blk * BM, b, kEvictNormal);
@@ -235,8 +244,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               if constexpr (NCTA >= 2) umma_bf16_2sm(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
               else umma_bf16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
             }
-            if constexpr (NCTA == 4) umma_commit_2sm(&empty[stage], 0xF);   // one of the two arrivals, in all four CTAs
-            else if constexpr (NCTA == 2) umma_commit_2sm(&empty[stage], 3);   // frees the stage in both CTAs
+            if (NCTA == 4 && quad) umma_commit_2sm(&empty[stage], 0xF);   // one of the two arrivals, in all four CTAs
+            else if constexpr (NCTA >= 2) umma_commit_2sm(&empty[stage], 3);   // frees the stage in both CTAs
             else umma_commit(&empty[stage]);
           }
           __syncwarp();
@@ -274,7 +283,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
       const int b = tile / tiles_per_batch;
       const int r = tile - b * tiles_per_batch;
-      const int m_blk = (r / p.n_tiles) * NCTA + static_cast<int>(cta_rank);
+      const int m_blk = (r / p.n_tiles) * NCTA + static_cast<int>(slot);
       const int n_blk = r % p.n_tiles;
       const int tile_row0 = m_blk * BM + quarter * 32;      // first row of this warp's slab (inside batch b)
       const int row = tile_row0 + lane;                     // row inside batch b
@@ -513,6 +522,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
+template <int BN, int EPI, int NCTA>
+__global__ void __cluster_dims__(NCTA, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmOut, const GemmDev p) {
+  gemm_body<BN, EPI, NCTA>(tmA, tmB, tmB, tmOut, p);
+}
+
+// mixed mode: no compile-time cluster size - the launch supplies {2, preferred 4}
+template <int BN, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_mixed_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB4,
+                     const __grid_constant__ CUtensorMap tmB2, const __grid_constant__ CUtensorMap tmOut, const GemmDev p) {
+  gemm_body<BN, EPI, 4>(tmA, tmB4, tmB2, tmOut, p);
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -543,6 +567,37 @@ int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap
               err);
   VVS_CUDA_OK(launch_kernel(gemm_tc_kernel<BN, EPI, NCTA>, grid, kGemmThreads, C::kSmemBytes, stream, pdl, tmA, tmB, tmOut, d),
               err);
+  return VVS_OK;
+}
+
+// mixed mode launch: cluster size 2, preferred cluster size 4, one chunk of four CTAs per 512-row work item
+template <int EPI>
+int launch_mixed(const CUtensorMap& tmA, const CUtensorMap& tmB4, const CUtensorMap& tmB2, const CUtensorMap& tmOut,
+                 const GemmDev& d, int grid, cudaStream_t stream, bool pdl, std::string* err) {
+  using C = Cfg<256, 4>;
+  static PerDeviceOnce once;
+  VVS_CUDA_OK(once.run([] {
+                cudaError_t e = cudaFuncSetAttribute(gemm_tc_mixed_kernel<256, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                     static_cast<int>(C::kSmemBytes));
+                if (e != cudaSuccess) return e;
+                return cudaFuncSetAttribute(gemm_tc_mixed_kernel<256, EPI>, cudaFuncAttributeNonPortableClusterSizeAllowed, 0);
+              }),
+              err);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = C::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[3];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributePreferredClusterDimension;
+  at[1].val.preferredClusterDim.x = 4; at[1].val.preferredClusterDim.y = 1; at[1].val.preferredClusterDim.z = 1;
+  at[2].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[2].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 3 : 2;
+  VVS_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_tc_mixed_kernel<256, EPI>, tmA, tmB4, tmB2, tmOut, d), err);
   return VVS_OK;
 }
 
@@ -632,7 +687,7 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
     set_error(err, "launch_gemm: N must be a multiple of 32 and ldo of 8 for this epilogue");
     return VVS_ERR_INVALID;
   }
-  const int bn = gemm_block_n(a.N);
+  int bn = gemm_block_n(a.N);
   // CTA pairs by default; VITVS_GEMM_CTAS=1 selects the single-CTA kernels (A/B experiments)
   // VITVS_GEMM_CTAS=4 (experiment): clusters of two pairs that share the B tile through TMA multicast
   static const int ncta_env = []() {
@@ -640,7 +695,24 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
     return (e && e[0] == '1') ? 1 : (e && e[0] == '4') ? 4 : 2;
   }();
   // two-pair clusters only where they pay: 256-wide tiles, one problem, at least a few 512-row cluster tiles
-  const int ncta = (ncta_env == 4 && !(bn == 256 && a.batch == 1 && a.M >= 4096)) ? 2 : ncta_env;
+  const bool mixed_epi = a.epilogue == EPI_BIAS_BF16 || a.epilogue == EPI_GELU_BF16 || a.epilogue == EPI_RESID_F32 ||
+                         a.epilogue == EPI_SWIGLU_BF16;
+  int ncta = (ncta_env == 4 && !(mixed_epi && bn == 256 && a.batch == 1 && a.M >= 4096)) ? 2 : ncta_env;
+  // Small problems (a single frame pair: M = 970 rows): 256 x 256 pair tiles would occupy a dozen of the 74 CTA-pair
+  // slots and run a K loop at twice the per-tile cost.  When the pair tiling fills less than half of the machine, use
+  // single-CTA 128 x 128 tiles instead: four times the tiles, half the K-loop time each (VITVS_SMALL_TILES=0: off).
+  // The accumulation order over K is unchanged, so results stay bit-identical to the batched path.
+  static const bool small_tiles = []() {
+    const char* e = getenv("VITVS_SMALL_TILES");
+    return !(e && e[0] == '0');
+  }();
+  if (small_tiles && ncta == 2 && a.epilogue != EPI_SWIGLU_BF16) {
+    const long long pair_tiles = static_cast<long long>(a.batch) * ((a.M + 2 * BM - 1) / (2 * BM)) * ((a.N + bn - 1) / bn);
+    if (pair_tiles * 4 < num_sms) {
+      ncta = 1;
+      bn = 128;
+    }
+  }
   if (a.epilogue == EPI_SWIGLU_BF16 && (bn != 256 || a.N % bn)) {
     set_error(err, "launch_gemm: SwiGLU needs N to be a multiple of the 256-wide N tile");
     return VVS_ERR_INVALID;
@@ -677,29 +749,18 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   d.trace = tl_trace_slot;
   const long long tiles = static_cast<long long>(d.batch) * d.m_tiles * d.n_tiles;
   if (ncta == 4) {
-    // co-resident 4-CTA clusters (a GPC with an odd number of TPCs leaves one TPC out)
-    static int max_clusters_dev[64];   // per device (0 = not queried yet)
-    int dev_id = 0;
-    cudaGetDevice(&dev_id);
-    int& max_clusters = max_clusters_dev[dev_id & 63];
-    if (max_clusters <= 0) {
-      cudaLaunchConfig_t cfg = {};
-      cfg.gridDim = dim3(4 * (num_sms / 4));
-      cfg.blockDim = dim3(kGemmThreads);
-      cfg.dynamicSmemBytes = Cfg<256, 4>::kSmemBytes;
-      cudaLaunchAttribute at[1];
-      at[0].id = cudaLaunchAttributeClusterDimension;
-      at[0].val.clusterDim.x = 4; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-      cfg.attrs = at; cfg.numAttrs = 1;
-      cudaFuncSetAttribute(gemm_tc_kernel<256, EPI_BIAS_BF16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           static_cast<int>(Cfg<256, 4>::kSmemBytes));
-      int n = 0;
-      if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<256, EPI_BIAS_BF16, 4>, &cfg) != cudaSuccess || n < 1) n = num_sms / 4;
-      max_clusters = n;
-      if (getenv("VITVS_VERBOSE")) fprintf(stderr, "[vitvs] 4-CTA GEMM clusters co-resident: %d of %d\n", n, num_sms / 4);
+    CUtensorMap tmB2;   // pair-mode chunks fetch half of the B tile per CTA (tmB holds the quad mode's quarter boxes)
+    rc = make_tmap_bf16(&tmB2, a.B, a.K, a.N, 1, a.ldb, a.b_batch_pitch, bn / 2, err);
+    if (rc) return rc;
+    const int grid = 4 * static_cast<int>(std::min<long long>(tiles, num_sms / 4));
+    const bool pdl = a.pdl != 0;
+    switch (a.epilogue) {
+      case EPI_BIAS_BF16: return launch_mixed<EPI_BIAS_BF16>(tmA, tmB, tmB2, tmOut, d, grid, stream, pdl, err);
+      case EPI_GELU_BF16: return launch_mixed<EPI_GELU_BF16>(tmA, tmB, tmB2, tmOut, d, grid, stream, pdl, err);
+      case EPI_RESID_F32: return launch_mixed<EPI_RESID_F32>(tmA, tmB, tmB2, tmOut, d, grid, stream, pdl, err);
+      case EPI_SWIGLU_BF16: return launch_mixed<EPI_SWIGLU_BF16>(tmA, tmB, tmB2, tmOut, d, grid, stream, pdl, err);
+      default: set_error(err, "launch_gemm: epilogue not built for mixed clusters"); return VVS_ERR_INVALID;
     }
-    const int grid = 4 * static_cast<int>(std::min<long long>(tiles, max_clusters));
-    return dispatch_epi<256, 4>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
   }
   if (ncta == 2) {
     const int grid = 2 * static_cast<int>(std::min<long long>(tiles, num_sms / 2));

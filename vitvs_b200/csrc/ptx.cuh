@@ -83,11 +83,19 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
+// Stamps are atomics on two words per kernel: they are kept few (block 0 stamps the beginning - blocks are dispatched
+// in ascending order - and only the last 296 blocks, the final resident wave, stamp the end) so that a kernel of
+// 60 000 warps is not slowed down by its own trace.
 __device__ __forceinline__ void trace_begin(unsigned long long* slot) {
-  if (slot != nullptr && (threadIdx.x & 31) == 0) atomicMin(slot, globaltimer_ns());
+  if (slot != nullptr && (threadIdx.x & 31) == 0 && (blockIdx.x | blockIdx.y | blockIdx.z) == 0)
+    atomicMin(slot, globaltimer_ns());
 }
 __device__ __forceinline__ void trace_end(unsigned long long* slot) {
-  if (slot != nullptr && (threadIdx.x & 31) == 0) atomicMax(slot + 1, globaltimer_ns());
+  if (slot != nullptr && (threadIdx.x & 31) == 0) {
+    const unsigned long long total = static_cast<unsigned long long>(gridDim.x) * gridDim.y * gridDim.z;
+    const unsigned long long id = (static_cast<unsigned long long>(blockIdx.z) * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    if (id + 296 >= total) atomicMax(slot + 1, globaltimer_ns());
+  }
 }
 
 // ----------------------------------------------------------------------------- TMA
@@ -319,6 +327,11 @@ __device__ __forceinline__ f32x2 f2_mul(f32x2 a, f32x2 b) {
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctaid_x() {   // CTAs in this cluster (run-time: preferred / regular size)
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctaid.x;" : "=r"(r));
   return r;
 }
 __device__ __forceinline__ void cluster_sync_all() {   // every thread of every CTA in the cluster

@@ -59,7 +59,9 @@ extern thread_local unsigned long long* tl_trace_slot;
 
 // ---- launches ------------------------------------------------------------------------------------
 // <<< >>> with an optional programmatic-dependent-launch attribute (ptx.cuh: pdl_wait / pdl_launch_dependents)
-bool pdl_enabled();   // VITVS_PDL=1 turns it on (off by default, see api.cu)
+// programmatic dependent launch for a forward pass over `rows` token rows of width `dim`: VITVS_PDL=1 always, =0 never;
+// default: only where it was measured to pay (small batches of the narrow model, see api.cu)
+bool pdl_for_rows(long long rows, int dim);
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl,
                                  Args&&... args) {
@@ -72,7 +74,7 @@ inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = (pdl && pdl_enabled()) ? 1 : 0;
+  cfg.numAttrs = pdl ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 

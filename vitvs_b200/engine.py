@@ -325,14 +325,20 @@ class Engine:
 
     def frame_pairs_to_twist_host(self, goal: torch.Tensor, current: torch.Tensor, depth: torch.Tensor,
                                   twist_out: torch.Tensor, n_selected_out: torch.Tensor | None = None,
-                                  mean_sim_out: torch.Tensor | None = None) -> None:
-        """Same through HOST buffers (pinned for async copies); synchronises the stream before returning."""
+                                  mean_sim_out: torch.Tensor | None = None, wait: bool = True) -> None:
+        """Same through HOST buffers (pinned for async copies); synchronises the stream before returning.
+        wait=False: returns once enqueued - results are valid after self.wait(); the next call's copies then run under
+        this call's compute (two landing zones).  At most two calls in flight; their host buffers must stay untouched."""
         assert not goal.is_cuda and not current.is_cuda and not depth.is_cuda and not twist_out.is_cuda
         B = goal.shape[0]
-        self._check(self.lib.vvs_frame_pairs_to_twist_host(
-            self._h, _ptr(goal), _ptr(current), _ptr(depth), B, _ptr(twist_out), _ptr(n_selected_out),
-            _ptr(mean_sim_out), _stream(self.device)), "vvs_frame_pairs_to_twist_host")
+        fn = self.lib.vvs_frame_pairs_to_twist_host if wait else self.lib.vvs_frame_pairs_to_twist_host_async
+        self._check(fn(self._h, _ptr(goal), _ptr(current), _ptr(depth), B, _ptr(twist_out), _ptr(n_selected_out),
+                       _ptr(mean_sim_out), _stream(self.device)), "vvs_frame_pairs_to_twist_host")
         self._n_img = 2 * B
+
+    def wait(self, calls_back: int = 0) -> None:
+        """Block until the latest (0) / the one-before-latest (1) wait=False host call has delivered its results."""
+        self._check(self.lib.vvs_wait(self._h, calls_back), "vvs_wait")
 
     # ------------------------------------------------------------------ camera frames (resize on the GPU)
     def resize_frames(self, frames: torch.Tensor) -> torch.Tensor:
@@ -369,13 +375,13 @@ class Engine:
 
     def frames_to_twist_host(self, goal_frames: torch.Tensor, current_frames: torch.Tensor, depth: torch.Tensor,
                              twist_out: torch.Tensor, n_selected_out: torch.Tensor | None = None,
-                             mean_sim_out: torch.Tensor | None = None) -> None:
-        """Same through HOST buffers (pinned for async copies); synchronises before returning."""
+                             mean_sim_out: torch.Tensor | None = None, wait: bool = True) -> None:
+        """Same through HOST buffers (pinned for async copies); synchronises before returning unless wait=False."""
         assert not goal_frames.is_cuda and not current_frames.is_cuda and not depth.is_cuda and not twist_out.is_cuda
         B = goal_frames.shape[0]
-        self._check(self.lib.vvs_frames_to_twist_host(
-            self._h, _ptr(goal_frames), _ptr(current_frames), _ptr(depth), B, _ptr(twist_out), _ptr(n_selected_out),
-            _ptr(mean_sim_out), _stream(self.device)), "vvs_frames_to_twist_host")
+        fn = self.lib.vvs_frames_to_twist_host if wait else self.lib.vvs_frames_to_twist_host_async
+        self._check(fn(self._h, _ptr(goal_frames), _ptr(current_frames), _ptr(depth), B, _ptr(twist_out),
+                       _ptr(n_selected_out), _ptr(mean_sim_out), _stream(self.device)), "vvs_frames_to_twist_host")
         self._n_img = 2 * B
 
     # ------------------------------------------------------------------ headless planar-scene camera (N3)
