@@ -324,22 +324,57 @@ descriptors_unit_bf16_kernel(const float* __restrict__ x, const float* __restric
   trace_end(trace);
 }
 
-// arbitrary fp32 rows -> unit-norm bf16 rows (zero padded to dpad): one block per row.
+// arbitrary fp32 rows -> unit-norm bf16 rows (zero padded to dpad).  One WARP per row, 128-bit loads, the row kept in
+// registers between the norm pass and the write pass when it fits (d <= 2048; longer rows are read a second time, from
+// L2), 64-bit packed bf16 stores.  Bandwidth-bound: 4 d bytes in, 2 dpad bytes out per row.
+constexpr int kNormKeep = 16;   // float4 per lane kept in registers (16 * 32 lanes * 4 = 2048 elements)
 __global__ void __launch_bounds__(256)
-normalize_rows_kernel(const float* __restrict__ in, bf16* __restrict__ out, int d, int dpad) {
-  __shared__ float red[8];
-  const float* r = in + static_cast<size_t>(blockIdx.x) * d;
+normalize_rows_kernel(const float* __restrict__ in, bf16* __restrict__ out, long long rows, int d, int dpad,
+                      unsigned long long* trace) {
+  trace_begin(trace);
+  const int lane = threadIdx.x & 31;
+  const long long row = blockIdx.x * static_cast<long long>(blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const float* r = in + row * d;
+  bf16* o = out + row * dpad;
+  const bool vec = (d & 3) == 0 && (reinterpret_cast<uintptr_t>(in) & 15) == 0;
   float s = 0.f;
-  for (int i = threadIdx.x; i < d; i += blockDim.x) s += r[i] * r[i];
-  s = warp_sum(s);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
-  __syncthreads();
-  float tot = 0.f;
+  float4 keep[kNormKeep];
+  const int n4 = d >> 2;
+  if (vec) {
+    const float4* r4 = reinterpret_cast<const float4*>(r);
 #pragma unroll
-  for (int i = 0; i < 8; ++i) tot += red[i];
-  const float inv = 1.0f / fmaxf(sqrtf(tot), 1e-8f);
-  bf16* o = out + static_cast<size_t>(blockIdx.x) * dpad;
-  for (int i = threadIdx.x; i < dpad; i += blockDim.x) o[i] = __float2bfloat16_rn(i < d ? r[i] * inv : 0.f);
+    for (int i = 0; i < kNormKeep; ++i) {
+      const int idx = i * 32 + lane;
+      keep[i] = idx < n4 ? __ldg(r4 + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+      s += (keep[i].x * keep[i].x + keep[i].y * keep[i].y) + (keep[i].z * keep[i].z + keep[i].w * keep[i].w);
+    }
+    for (int idx = kNormKeep * 32 + lane; idx < n4; idx += 32) {
+      const float4 v = __ldg(r4 + idx);
+      s += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+    }
+  } else {
+    for (int i = lane; i < d; i += 32) s += r[i] * r[i];
+  }
+  s = warp_sum(s);
+  const float inv = 1.0f / fmaxf(sqrtf(s), 1e-8f);   // CosineSimilarity eps (vitvs_v2.py:55)
+  if (vec) {
+    uint2* o2 = reinterpret_cast<uint2*>(o);          // dpad is a multiple of 8 and the workspace 256-byte aligned
+    const float4* r4 = reinterpret_cast<const float4*>(r);
+#pragma unroll
+    for (int i = 0; i < kNormKeep; ++i) {
+      const int idx = i * 32 + lane;
+      if (idx < n4) o2[idx] = make_uint2(pack2(keep[i].x * inv, keep[i].y * inv), pack2(keep[i].z * inv, keep[i].w * inv));
+    }
+    for (int idx = kNormKeep * 32 + lane; idx < n4; idx += 32) {
+      const float4 v = __ldg(r4 + idx);
+      o2[idx] = make_uint2(pack2(v.x * inv, v.y * inv), pack2(v.z * inv, v.w * inv));
+    }
+    for (int i = d + lane; i < dpad; i += 32) o[i] = __float2bfloat16_rn(0.f);
+  } else {
+    for (int i = lane; i < dpad; i += 32) o[i] = __float2bfloat16_rn(i < d ? r[i] * inv : 0.f);
+  }
+  trace_end(trace);
 }
 
 int grid_for(long long work_items, int block) {
@@ -435,7 +470,7 @@ int launch_descriptors_unit_bf16(const float* x, bf16* out, float* sqnorm_scratc
 
 int launch_normalize_rows_bf16(const float* in, bf16* out, int rows, int d, int dpad, cudaStream_t s,
                                std::string* err) {
-  normalize_rows_kernel<<<rows, 256, 0, s>>>(in, out, d, dpad);
+  normalize_rows_kernel<<<(rows + 7) / 8, 256, 0, s>>>(in, out, rows, d, dpad, tl_trace_slot);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }

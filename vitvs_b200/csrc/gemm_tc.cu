@@ -336,8 +336,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         const int c_begin = half * NCH;
         // EPI_SIM state: running row best over this warp's columns; ties -> lowest column
         float best_v = -INFINITY;
-        int best_j = 0x7fffffff;
-        const uint32_t row_tag = 0xFFFFFFFFu - static_cast<uint32_t>(row);
+        int best_j = -1;                        // index inside this warp's NCH * 32 columns
         // EPI_PATCH_F32: the positional row of this GEMM row (row r of image i is token r of the residual stream)
         const float* pos_row = nullptr;
         if constexpr (EPI == EPI_PATCH_F32) pos_row = p.pos + static_cast<size_t>(row_ok ? row % (p.T + 1) : 0) * p.ldo;
@@ -368,31 +367,59 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           if (!live) continue;
 
           if constexpr (EPI == EPI_SIM) {
-            unsigned long long key[32];
+            // Row best: a thread owns one accumulator row, so it scans its 32 columns in increasing order (strict >:
+            // ties keep the lowest column).  Column best: the warp's 32 x 32 chunk is transposed through its private
+            // swizzled smem slab (8 conflict-free 16-byte stores per lane, 32 conflict-free word loads), then lane L
+            // scans column col0 + L over the 32 rows in increasing order (ties keep the lowest row) and raises ONE
+            // packed key.  All 32-bit work: ~8 instructions per accumulator element less than a 64-bit shuffle butterfly.
+            const bool chunk_full = (tile_row0 + 32 <= p.M) && (col0 + 32 <= p.N);   // warp-uniform
+            if (chunk_full) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float v = __uint_as_float(rw[j]);
-              const bool col_ok = (col0 + j) < p.N;
-              if (col_ok && v > best_v) {
-                best_v = v;
-                best_j = col0 + j;
+              for (int j = 0; j < 32; ++j) {
+                const float v = __uint_as_float(rw[j]);
+                if (v > best_v) {
+                  best_v = v;
+                  best_j = i * 32 + j;           // chunk-local: a compile-time immediate
+                }
               }
-              key[j] = (row_ok && col_ok) ? ((static_cast<unsigned long long>(ord_f32(v)) << 32) | row_tag) : 0ull;
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                st_shared_v4(my_row_s + ((static_cast<uint32_t>(q) ^ sw) << 4), rw[q * 4 + 0], rw[q * 4 + 1], rw[q * 4 + 2],
+                             rw[q * 4 + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                const float v = __uint_as_float(rw[j]);
+                if ((col0 + j) < p.N && v > best_v) {
+                  best_v = v;
+                  best_j = i * 32 + j;
+                }
+              }
+              // rows past M hold zero accumulators (TMA zero fill): they must never win a column
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                st_shared_v4(my_row_s + ((static_cast<uint32_t>(q) ^ sw) << 4), row_ok ? rw[q * 4 + 0] : 0xff800000u,
+                             row_ok ? rw[q * 4 + 1] : 0xff800000u, row_ok ? rw[q * 4 + 2] : 0xff800000u,
+                             row_ok ? rw[q * 4 + 3] : 0xff800000u);
             }
-            // transposed butterfly: afterwards lane L holds max over the warp's 32 rows of column col0+L
+            __syncwarp();
+            float cb = -INFINITY;
+            int cr = 0;
+            const uint32_t col_s = stg_s + ((static_cast<uint32_t>(lane) & 3u) << 2);
+            const uint32_t unit = static_cast<uint32_t>(lane) >> 2;
 #pragma unroll
-            for (int w = 16; w >= 1; w >>= 1) {
-              const bool upper = (lane & w) != 0;
-#pragma unroll
-              for (int k = 0; k < w; ++k) {
-                const unsigned long long send = upper ? key[k] : key[k + w];
-                const unsigned long long keep = upper ? key[k + w] : key[k];
-                const unsigned long long recv = __shfl_xor_sync(0xffffffffu, send, w);
-                key[k] = keep > recv ? keep : recv;
+            for (int rr = 0; rr < 32; ++rr) {
+              const float v = __uint_as_float(ld_shared_u32(col_s + rr * 128 + ((unit ^ static_cast<uint32_t>(rr & 7)) << 4)));
+              if (v > cb) {
+                cb = v;
+                cr = rr;
               }
             }
-            if (col0 + lane < p.N && key[0] != 0ull)
-              atomicMax(&p.col_best[static_cast<size_t>(b) * p.best_pitch + col0 + lane], key[0]);
+            __syncwarp();                         // the slab is rewritten by the next chunk
+            if (col0 + lane < p.N && cb > -INFINITY)
+              atomicMax(&p.col_best[static_cast<size_t>(b) * p.best_pitch + col0 + lane],
+                        (static_cast<unsigned long long>(ord_f32(cb)) << 32) |
+                            (0xFFFFFFFFu - static_cast<uint32_t>(tile_row0 + cr)));
           } else if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_GELU_BF16) {
             // two 32-column chunks (64 bf16 = 128 bytes per row) form one slab
             if ((i & 1) == 0) {
@@ -492,9 +519,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           }
         }
         if constexpr (EPI == EPI_SIM) {
-          if (row_ok && best_j != 0x7fffffff) {
+          if (row_ok && best_j >= 0) {
             const unsigned long long k = (static_cast<unsigned long long>(ord_f32(best_v)) << 32) |
-                                         (0xFFFFFFFFu - static_cast<uint32_t>(best_j));
+                                         (0xFFFFFFFFu - static_cast<uint32_t>(n_blk * BN + c_begin * 32 + best_j));
             atomicMax(&p.row_best[static_cast<size_t>(b) * p.best_pitch + row], k);
           }
         }
