@@ -708,9 +708,12 @@ def run_match_sweep(args, world, rank, local, dev):
                                      "N(0, 0.5^2), 16 unrelated tokens; caller-supplied fp32 descriptors resident in HBM"},
                 "gpu_launches": 5 * args.steps, "clocks": clocks,
                 "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel<EPI_SIM> (sim_gemm)", "achieved": head["sim_tflops"],
-                             "peak": pk["tf_sustained"], "unit": "TFLOP/s",
-                             "frac": round(head["sim_tflops"] / pk["tf_sustained"], 3), "traffic": None,
-                             "flops_per_launch": algo, "peak_source": pk["source"] + ", sustained figure"},
+                             "peak": pk["tf_burst"], "unit": "TFLOP/s",
+                             "frac": round(head["sim_tflops"] / pk["tf_burst"], 3), "traffic": None,
+                             "flops_per_launch": algo,
+                             "frac_of_sustained_peak": round(head["sim_tflops"] / pk["tf_sustained"], 3),
+                             "peak_source": pk["source"] + ", burst figure: the step is under 2 ms of which the GEMM is "
+                                            "the one long kernel, the clocks stay near their maximum (see `clocks`)"},
                 "e2e": None, "sweep": points}
         print(json.dumps(line), flush=True)
     return 0

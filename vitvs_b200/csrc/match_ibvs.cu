@@ -33,6 +33,15 @@ __device__ __forceinline__ T block_reduce(T v, Op op, T* scratch /* >= 32 */) {
   return r;
 }
 
+// max of a 64-bit key over the warp with two pairs of redux.sync: high words first, then the low words of the lanes
+// that hold the winning high word
+__device__ __forceinline__ unsigned long long warp_max_u64(unsigned long long v) {
+  const uint32_t hi = static_cast<uint32_t>(v >> 32), lo = static_cast<uint32_t>(v);
+  const uint32_t mh = __reduce_max_sync(0xffffffffu, hi);
+  const uint32_t ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+  return (static_cast<unsigned long long>(mh) << 32) | ml;
+}
+
 // vitvs_v2.py:117-120 as evaluated by torch on CPU: fp32, acc = a*a; acc = fma(b,b,acc); sqrt
 // (bit-exactness against PairwiseDistance is pinned by tests/test_oracle_vs_reference.py).
 __device__ __forceinline__ float cyclic_distance(int dr, int dc) {
@@ -41,7 +50,7 @@ __device__ __forceinline__ float cyclic_distance(int dr, int dc) {
   return __fsqrt_rn(__fmaf_rn(b, b, __fmul_rn(a, a)));
 }
 
-__global__ void __launch_bounds__(256) select_kernel(const SelectArgs a, unsigned long long* trace) {
+__global__ void __launch_bounds__(1024) select_kernel(const SelectArgs a, unsigned long long* trace) {
   trace_begin(trace);
   __shared__ unsigned long long s_u64[32];
   __shared__ float s_f32[32];
@@ -148,29 +157,53 @@ __global__ void __launch_bounds__(256) select_kernel(const SelectArgs a, unsigne
       sel_sim[k] = 0.f;
     }
   }
-  unsigned long long prev = ~0ull;
-  for (int k = 0; k < K && !a.sel_order; ++k) {
-    unsigned long long best = 0ull;
-    if (k < nsel) {
+  if (!a.sel_order) {
+    // K rounds of "largest key below the previous winner".  Keys (ordered sim1 << 32 | ~token: unique, ties -> lower
+    // token) sit in shared memory when T * 8 bytes fit; every thread keeps the best key of its own strided tokens in a
+    // register and only the round's winner rescans its tokens, so a round costs two redux pairs and ONE barrier
+    // whatever T is (the alternating scratch rows make the second barrier unnecessary).
+    extern __shared__ unsigned long long s_keys[];
+    const bool in_smem = a.keys_in_smem != 0;
+    auto key_at = [&](int i) -> unsigned long long {
+      if (in_smem) return s_keys[i];
+      return (same || cand[i])
+                 ? (static_cast<unsigned long long>(ord_f32(sim1[i])) << 32) | (0xFFFFFFFFu - static_cast<uint32_t>(i))
+                 : 0ull;
+    };
+    auto my_best_below = [&](unsigned long long prev) {
+      unsigned long long best = 0ull;
       for (int i = threadIdx.x; i < T; i += blockDim.x) {
-        if (same || cand[i]) {
-          const unsigned long long key =
-              (static_cast<unsigned long long>(ord_f32(sim1[i])) << 32) | (0xFFFFFFFFu - static_cast<uint32_t>(i));
-          if (key < prev && key > best) best = key;
-        }
+        const unsigned long long key = key_at(i);
+        if (key < prev && key > best) best = key;
       }
-      best = block_reduce(best, [](unsigned long long x, unsigned long long y) { return x > y ? x : y; }, s_u64);
-      prev = best;
+      return best;
+    };
+    if (in_smem) {
+      for (int i = threadIdx.x; i < T; i += blockDim.x)
+        s_keys[i] = (same || cand[i])
+                        ? (static_cast<unsigned long long>(ord_f32(sim1[i])) << 32) | (0xFFFFFFFFu - static_cast<uint32_t>(i))
+                        : 0ull;
     }
-    if (threadIdx.x == 0) {
-      if (k < nsel) {
+    __shared__ unsigned long long s_best[2][32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    unsigned long long cur = my_best_below(~0ull);     // a thread only reads the keys it wrote itself: no barrier needed
+    for (int k = 0; k < nsel; ++k) {
+      const unsigned long long wb = warp_max_u64(cur);
+      if (lane == 0) s_best[k & 1][wid] = wb;
+      __syncthreads();
+      const unsigned long long best = warp_max_u64(lane < nwarps ? s_best[k & 1][lane] : 0ull);
+      if (best == 0ull) {                              // cannot happen while k < nsel <= number of keys
+        if (threadIdx.x == 0) { sel_tok[k] = -1; sel_sim[k] = 0.f; }
+      } else if (cur == best) {                        // keys are unique: exactly one thread owns the winner
         const int tok = static_cast<int>(0xFFFFFFFFu - static_cast<uint32_t>(best));
         sel_tok[k] = tok;
         sel_sim[k] = same ? 1.0f : sim1[tok];
-      } else {
-        sel_tok[k] = -1;
-        sel_sim[k] = 0.f;
+        cur = my_best_below(best);
       }
+    }
+    for (int k = nsel + threadIdx.x; k < K; k += blockDim.x) {
+      sel_tok[k] = -1;
+      sel_sim[k] = 0.f;
     }
   }
   __syncthreads();
@@ -414,7 +447,16 @@ int launch_select(const SelectArgs& a, cudaStream_t s, std::string* err) {
     set_error(err, "select: num_pairs must be in [1, 256]");
     return VVS_ERR_INVALID;
   }
-  select_kernel<<<a.n_pairs, 256, 0, s>>>(a, tl_trace_slot);
+  // 1024 threads per pair; the selection keys live in dynamic shared memory when they fit (T <= 25 600)
+  constexpr size_t kMaxKeySmem = 200 * 1024;
+  static PerDeviceOnce once;
+  VVS_CUDA_OK(once.run([&] {
+    return cudaFuncSetAttribute(select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kMaxKeySmem));
+  }), err);
+  SelectArgs b = a;
+  const size_t key_bytes = static_cast<size_t>(a.T) * sizeof(unsigned long long);
+  b.keys_in_smem = (!a.sel_order && key_bytes <= kMaxKeySmem) ? 1 : 0;
+  select_kernel<<<a.n_pairs, 1024, b.keys_in_smem ? key_bytes : 0, s>>>(b, tl_trace_slot);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }

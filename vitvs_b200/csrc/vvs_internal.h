@@ -212,6 +212,7 @@ struct SelectArgs {
   int32_t* uv_star;       // [n_pairs, K, 2]
   int32_t* uv;            // [n_pairs, K, 2]
   const int32_t* sel_order;   // [n_pairs, T] optional priority list of goal tokens (reference-faithful selection)
+  int keys_in_smem;           // set by launch_select: the T selection keys fit the kernel's dynamic shared memory
 };
 int launch_select(const SelectArgs& a, cudaStream_t s, std::string* err);
 
