@@ -32,6 +32,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 METRIC = "frame_pairs_to_twist_per_sec"
+LN_FUSED = os.environ.get("VITVS_LN_FUSED", "1")[:1] != "0"   # mirrors csrc/api.cu (default: LayerNorm folded into the GEMMs)
 UNIT = "frame-pairs/s"
 NICE = {"dinov2_vits14": "ViT-S/14", "dinov2_vitb14": "ViT-B/14", "dinov2_vitl14": "ViT-L/14", "dinov2_vitg14": "ViT-g/14"}
 # --config -> (model, pairs per step, strong scaling?, perturbed current frames?)
@@ -526,7 +527,8 @@ def run_ours(args):
                 ent["frac_of_sustained_peak"] = round(ent["tflops"] / pk["tf_sustained"], 3)
             # HBM-bound classes: ALGORITHMIC bytes per launch (SURVEY 8d / DESIGN.md 3) against the measured copy bandwidth
             by = {"layernorm": M * dim * (4 + 2) + 2 * dim * 4,
-                  "proj_gemm": M * dim * (2 + 4 + 4),                                   # h read, x read-modify-write
+                  # h read, x read-modify-write; with the folded LayerNorm also the bf16 copy of x and the row statistics
+                  "proj_gemm": M * dim * (2 + 4 + 4) + (M * dim * 2 + M * (dim // 64) * 8 if LN_FUSED else 0),
                   "im2col": 2 * B * (S_ * S_ * 3 + (T + 1) * 640 * 2),
                   "descriptors": 2 * B * T * (dim * 4 + parts * dim * 2 + 4),           # tokens read once, binned rows written
                   }.get(k)
@@ -564,6 +566,8 @@ def run_ours(args):
                        "baseline_config": args.config, "pairs_per_gpu_per_step": B, "pairs_per_step": total_pairs_step,
                        "image_size": S, "layer": cfg.layer, "binning": bool(cfg.use_feature_binning),
                        "num_pairs": cfg.num_pairs, "weights": "random-init (seed 0)",
+                       "layernorm": ("folded into the GEMMs on either side (residual epilogues emit bf16(x) + row statistics, "
+                                     "QKV / fc1 normalise in their epilogue)" if LN_FUSED else "separate kernel (VITVS_LN_FUSED=0)"),
                        "l2": f"{NSETS} rotated input sets; per-step activation traffic (~GBs) exceeds the 126 MB L2",
                        "mean_selected_pairs": n_sel,
                        "matching": ("Gram-stencil: 9-point stencil over the [T,D]x[D,T] token Gram matrix (executed "

@@ -24,8 +24,8 @@ def test_bench_line_contract():
               "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches", "clocks", "roofline"):
         assert k in d, k
     assert d["steps"] == steps and d["n_gpus"] == 1 and d["value"] > 0
-    # 12 blocks x (2 LayerNorm + 4 GEMM + attention) + front end + matching + control, every step
-    assert d["gpu_launches"] >= 80 * steps, d["gpu_launches"]
+    # 12 blocks x (4 GEMM + attention; LayerNorm is folded into the GEMMs) + front end + matching + control, every step
+    assert d["gpu_launches"] >= 60 * steps, d["gpu_launches"]
     assert d["e2e"]["value"] > 0 and d["e2e"]["h2d_bytes_per_step"] > 0 and d["e2e"]["d2h_bytes_per_step"] > 0
     assert d["e2e"]["value"] != d["value"]
     rf = d["roofline"]
@@ -35,7 +35,7 @@ def test_bench_line_contract():
     assert d["step_ms_p50"] > 0 and d["step_ms_p95"] >= d["step_ms_p50"]
     assert d["parity_check"]["pairs_checked"] >= 8 and d["parity_check"]["max_twist_rel_err_vs_unbatched"] == 0.0
     acct = d["step_accounting"]
-    assert acct["nodes"] >= 80 and acct["kernels_ms"] > 0 and 0.9 < acct["sum_over_step"] < 1.1, acct
+    assert acct["nodes"] >= 60 and acct["kernels_ms"] > 0 and 0.9 < acct["sum_over_step"] < 1.1, acct
     assert d["latency"]["p50_ms"] > 0
 
 

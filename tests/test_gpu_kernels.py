@@ -168,6 +168,108 @@ def test_gemm_swiglu(eng):
     assert rel < 1e-2
 
 
+# ---- LayerNorm folded into the GEMMs on either side of it (dino_patch/block.py:90-95: x + ls(attn(norm1(x))), ...) ----
+def _group_stats(x):
+    """(sum, sum of squares) of every 64-column group of the fp32 rows: what a producer epilogue emits."""
+    g = x.float().reshape(x.shape[0], -1, 64)
+    return torch.stack([g.sum(-1), (g * g).sum(-1)], dim=-1).contiguous()
+
+
+# small tiles (1 CTA, 128-wide), CTA pairs (256-wide), mixed clusters (M >= 4096), K = 1 and many k-blocks, ragged M
+@pytest.mark.parametrize("M,N,K", [(300, 768, 256), (970, 384, 1536), (3400, 768, 768), (4400 + 37, 768, 768)])
+def test_gemm_residual_ln_producer(eng, M, N, K):
+    """EPI_RESID_LN_F32: the new residual rows must equal the reduce-add epilogue's bit for bit, xb must be their
+    bf16 rounding, and the per-group statistics must be those of the stored rows."""
+    A = _rand((M, K), 60, dtype=torch.bfloat16)
+    B = _rand((N, K), 61, 0.05, dtype=torch.bfloat16)
+    bias, gamma = _rand((N,), 62, 0.1), _rand((N,), 63)
+    x0 = _rand((M, N), 64) + 0.3
+    x_ref = x0.clone()
+    eng.dbg_gemm(A, B, _lib.EPI_RESID_F32, bias=bias, gamma=gamma, x_f32=x_ref, ldo=N)
+    x = x0.clone()
+    xb = torch.full((M + 2, N), 5.0, dtype=torch.bfloat16, device="cuda")       # 2 guard rows
+    part = torch.full((M + 2, N // 64, 2), -1.0, device="cuda")
+    eng.dbg_gemm_ln(A, B, _lib.EPI_RESID_LN_F32, bias=bias, gamma=gamma, x_f32=x, ldo=N, xb_out=xb, ln_part_out=part)
+    torch.cuda.synchronize()
+    assert torch.equal(x, x_ref)
+    assert torch.equal(xb[:M], x.to(torch.bfloat16))
+    assert torch.all(xb[M:] == 5.0) and torch.all(part[M:] == -1.0)             # rows past M untouched
+    ref = _group_stats(x)
+    assert torch.allclose(part[:M], ref, rtol=2e-5, atol=1e-4), (part[:M] - ref).abs().max().item()
+
+
+def test_gemm_patch_ln_producer(eng):
+    n_img, T, D, K = 3, 49, 384, 640
+    A = _rand((n_img, T + 1, K), 16, dtype=torch.bfloat16)
+    A[:, 0] = 0
+    A = A.reshape(n_img * (T + 1), K).contiguous()
+    B = _rand((D, K), 17, 0.05, dtype=torch.bfloat16)
+    bias, pos = _rand((D,), 18, 0.1), _rand((T + 1, D), 19)
+    M = n_img * (T + 1)
+    x_ref = torch.zeros(M, D, device="cuda")
+    eng.dbg_gemm(A, B, _lib.EPI_PATCH_F32, bias=bias, x_f32=x_ref, ldo=D, pos=pos, T=T)
+    x = torch.zeros(M, D, device="cuda")
+    xb = torch.zeros(M, D, dtype=torch.bfloat16, device="cuda")
+    part = torch.zeros(M, D // 64, 2, device="cuda")
+    eng.dbg_gemm_ln(A, B, _lib.EPI_PATCH_LN_F32, bias=bias, x_f32=x, ldo=D, pos=pos, T=T, xb_out=xb, ln_part_out=part)
+    torch.cuda.synchronize()
+    assert torch.equal(x, x_ref) and torch.equal(xb, x.to(torch.bfloat16))
+    assert torch.allclose(part, _group_stats(x), rtol=2e-5, atol=1e-4)
+
+
+def _ln_consumer_case(M, N, K, seed, mean_shift=0.5):
+    """x rows with a non-zero mean, LayerNorm(gamma, beta), Linear(W, b): the fp32 reference of Linear(LN(x)) and the
+    operands of the folded form (what api.cu's fold_layernorm_kernel and a producer epilogue hand to the consumer)."""
+    x = _rand((M, K), seed) * 1.7 + mean_shift
+    g, be = 1.0 + _rand((K,), seed + 1, 0.1), _rand((K,), seed + 2, 0.05)
+    W, b = _rand((N, K), seed + 3, 0.03), _rand((N,), seed + 4, 0.1)
+    ref = torch.nn.functional.layer_norm(x, (K,), g, be, 1e-6) @ W.T + b
+    Wf = (W * g).to(torch.bfloat16)
+    return dict(xb=x.to(torch.bfloat16), part=_group_stats(x), Wf=Wf, cs=Wf.float().sum(1).contiguous(),
+                bf=(b + W @ be).contiguous(), ref=ref)
+
+
+@pytest.mark.parametrize("M,N,K", [(970, 1152, 384), (300, 2304, 768), (4400 + 37, 2304, 768), (3400, 768, 1024)])
+def test_gemm_bias_ln_consumer(eng, M, N, K):
+    c = _ln_consumer_case(M, N, K, 70)
+    out = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+    D = N // 3
+    eng.dbg_gemm_ln(c["xb"], c["Wf"], _lib.EPI_BIAS_LN_BF16, bias=c["bf"], out_bf16=out, ldo=N, q_cols=D, q_scale=0.125,
+                    ln_part_in=c["part"], colsum=c["cs"])
+    torch.cuda.synchronize()
+    ref = c["ref"].clone()
+    ref[:, :D] *= 0.125
+    _, rel = _report(f"gemm bias+LN {M}x{N}x{K}", out, ref)
+    assert rel < 1e-2
+
+
+def test_gemm_gelu_ln_consumer(eng):
+    M, N, K = 970, 1536, 384
+    c = _ln_consumer_case(M, N, K, 80)
+    out = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+    eng.dbg_gemm_ln(c["xb"], c["Wf"], _lib.EPI_GELU_LN_BF16, bias=c["bf"], out_bf16=out, ldo=N, ln_part_in=c["part"],
+                    colsum=c["cs"])
+    torch.cuda.synchronize()
+    _, rel = _report("gemm gelu+LN", out, torch.nn.functional.gelu(c["ref"]))
+    assert rel < 1e-2
+
+
+def test_gemm_swiglu_ln_consumer(eng):
+    M, D, H = 300, 1536, 4096
+    c = _ln_consumer_case(M, 2 * H, D, 90)
+    bn, half = 256, 128
+    r = torch.arange(2 * H)
+    n, wi = r // bn, r % bn
+    src = torch.where(wi < half, n * half + wi, H + n * half + (wi - half)).cuda()
+    out = torch.zeros(M, H, dtype=torch.bfloat16, device="cuda")
+    eng.dbg_gemm_ln(c["xb"], c["Wf"][src].contiguous(), _lib.EPI_SWIGLU_LN_BF16, bias=c["bf"][src].contiguous(),
+                    out_bf16=out, ldo=H, ln_part_in=c["part"], colsum=c["cs"][src].contiguous())
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.silu(c["ref"][:, :H]) * c["ref"][:, H:]
+    _, rel = _report("gemm swiglu+LN", out, ref)
+    assert rel < 1e-2
+
+
 @pytest.mark.parametrize("n_img,n_tok,heads", [(1, 128, 1), (2, 485, 6), (3, 50, 2), (1, 1370, 12), (2, 257, 3)])
 def test_attention(eng, n_img, n_tok, heads):
     D = heads * 64

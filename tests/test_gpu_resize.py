@@ -88,7 +88,7 @@ def test_host_entries_pipelined_equal_device_entry(eng, n):
         ms = torch.zeros(n, dtype=torch.float32).pin_memory()
         eng.frames_to_twist_host(gh, ch, dh, tw, ns, ms)
         assert torch.equal(tw, tw_ref) and torch.equal(ns, ns_ref) and torch.equal(ms, ms_ref), rep
-        assert eng.last_launch_count() > 90
+        assert eng.last_launch_count() > 65
     # pre-resized host entry through the same pipeline
     g = torch.from_numpy(np.stack([synth.resize_square(f, 308) for f in graw])).pin_memory()
     c = torch.from_numpy(np.stack([synth.resize_square(f, 308) for f in craw])).pin_memory()

@@ -13,6 +13,8 @@ c_i32, c_i64, c_f32, c_f64, c_vp = C.c_int32, C.c_int64, C.c_float, C.c_double, 
 F32, BF16 = 0, 1
 IMAGE_U8_HWC, IMAGE_F32_NCHW = 0, 1
 EPI_BIAS_BF16, EPI_GELU_BF16, EPI_RESID_F32, EPI_PATCH_F32, EPI_SWIGLU_BF16, EPI_SIM, EPI_STORE_F32 = range(7)
+# folded-LayerNorm variants (csrc/vvs_internal.h)
+EPI_RESID_LN_F32, EPI_PATCH_LN_F32, EPI_BIAS_LN_BF16, EPI_GELU_LN_BF16, EPI_SWIGLU_LN_BF16 = range(7, 12)
 
 
 class VvsError(RuntimeError):
@@ -81,6 +83,8 @@ SYMBOLS = {
     "vvs_profile_read": (c_i32, [c_vp, C.POINTER(c_f64), C.POINTER(c_i32), c_i32]),
     "vvs_dbg_gemm": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32,
                              c_f32, c_vp, c_i32, c_vp]),
+    "vvs_dbg_gemm_ln": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32,
+                                c_f32, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp, c_f32, c_vp]),
     "vvs_dbg_attention": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp]),
     "vvs_dbg_layernorm": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_vp]),
 }

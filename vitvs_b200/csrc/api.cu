@@ -72,6 +72,53 @@ __global__ void convert_vector_kernel(const SrcT* __restrict__ src, float* __res
   dst[i] = static_cast<float>(src[s]);
 }
 
+// fp32 / bf16 [rows, cols] -> fp32 copy with the same optional row interleave (the unrounded source of the LayerNorm fold)
+template <typename SrcT>
+__global__ void convert_matrix_f32_kernel(const SrcT* __restrict__ src, float* __restrict__ dst, int rows, int cols,
+                                          int interleave_bn, int hidden) {
+  const long long total = static_cast<long long>(rows) * cols;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(i / cols), c = static_cast<int>(i % cols);
+    int sr = r;
+    if (interleave_bn) {
+      const int half = interleave_bn / 2, n = r / interleave_bn, wi = r % interleave_bn;
+      sr = wi < half ? n * half + wi : hidden + n * half + (wi - half);
+    }
+    dst[i] = static_cast<float>(src[static_cast<size_t>(sr) * cols + c]);
+  }
+}
+
+// LayerNorm folded into the Linear that consumes it (block.py:90-95: y = Linear(LN(x))):
+//   Linear(LN(x)) = rstd * (x W'^T - mean * colsum(W')) + b',   W' = W diag(gamma),  b' = b + W beta
+// W' is rounded to bf16 ONCE from the fp32 product; colsum is taken over the rounded values (the ones the tensor core
+// multiplies), so that the mean term cancels exactly what the GEMM accumulated.  One warp per output row.
+__global__ void fold_layernorm_kernel(const float* __restrict__ w32, const float* __restrict__ gamma,
+                                      const float* __restrict__ beta, const float* __restrict__ bias,
+                                      bf16* __restrict__ wf, float* __restrict__ colsum, float* __restrict__ bias_f, int rows,
+                                      int D) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  float cs = 0.f, wb = 0.f;
+  for (int k = lane; k < D; k += 32) {
+    const float w = w32[static_cast<size_t>(row) * D + k];
+    const bf16 r = __float2bfloat16_rn(w * gamma[k]);
+    wf[static_cast<size_t>(row) * D + k] = r;
+    cs += __bfloat162float(r);
+    wb = fmaf(w, beta[k], wb);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    cs += __shfl_xor_sync(0xffffffffu, cs, o);
+    wb += __shfl_xor_sync(0xffffffffu, wb, o);
+  }
+  if (lane == 0) {
+    colsum[row] = cs;
+    bias_f[row] = bias[row] + wb;
+  }
+}
+
 __global__ void trace_reset_kernel(unsigned long long* buf, int n_slots) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n_slots) {
@@ -98,6 +145,12 @@ struct BlockW {
   float* qkv_b = nullptr; float* proj_b = nullptr; float* ffn1_b = nullptr; float* ffn2_b = nullptr;
   float* n1w = nullptr; float* n1b = nullptr; float* n2w = nullptr; float* n2b = nullptr;
   float* ls1 = nullptr; float* ls2 = nullptr;
+  // folded LayerNorm (fold_layernorm_kernel): fp32 copies of the two consuming matrices, W' = W diag(gamma_ln) in bf16,
+  // colsum(W') and b' = b + W beta_ln
+  float* qkv_w32 = nullptr; float* ffn1_w32 = nullptr;
+  bf16* qkv_wf = nullptr; bf16* ffn1_wf = nullptr;
+  float* qkv_cs = nullptr; float* ffn1_cs = nullptr;
+  float* qkv_bf = nullptr; float* ffn1_bf = nullptr;
   unsigned set_mask = 0;   // 14 bits
 };
 
@@ -120,6 +173,12 @@ struct vvs_ctx {
   // workspace
   float* x = nullptr;        // residual stream [max_images * N, D] fp32
   bf16* h = nullptr;         // LN out / attention out [max_images * N, D]
+  // LayerNorm folded into the GEMMs around it (default; VITVS_LN_FUSED=0 runs the LayerNorm kernel): the residual GEMMs
+  // and the patch embedding also write xb = bf16(x) and per-row (sum, sum of squares) partials, QKV / fc1 / w12 multiply
+  // xb by gamma-folded weights and normalise in their epilogue
+  bool ln_fused = true;
+  bf16* xb = nullptr;        // [max_images * N, D]
+  float2* ln_part = nullptr; // [max_images * N, D / 64]
   bf16* big = nullptr;       // im2col / qkv / ffn hidden
   size_t big_elems = 0;
   int x_pin_mb = 40;          // MB of the residual stream (its last rows) that every kernel asks L2 to keep; 0 = no hints
@@ -330,6 +389,7 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
   const long long pin_rows = static_cast<long long>(c->x_pin_mb) * 1000000ll / (static_cast<long long>(D) * 4);
   const int pin_row0 = (c->x_pin_mb > 0 && static_cast<long long>(M) * D * 4 > 100000000ll)
                            ? static_cast<int>(std::max<long long>(1, M - pin_rows)) : 0x7fffffff;
+  const bool fused = c->ln_fused;
   int rc;
   if (kind == VVS_IMAGE_U8_HWC)
   { ProfScope ps(c, VVS_K_IM2COL, s);
@@ -345,8 +405,9 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
   ++c->launch_count;
   {
     // A has one zero row per CLS slot, so GEMM row r is residual-stream row r: x = acc + bias + pos'[r % N]
-    GemmArgs g = plain_gemm(c->big, c->pe_w, M, D, kPatchKPad, EPI_PATCH_F32);
+    GemmArgs g = plain_gemm(c->big, c->pe_w, M, D, kPatchKPad, fused ? EPI_PATCH_LN_F32 : EPI_PATCH_F32);
     g.bias = c->pe_b; g.x_f32 = c->x; g.ldo = D; g.pos = c->pos_prime; g.T = T; g.pin_row0 = pin_row0;
+    g.xb_out = c->xb; g.ln_part_out = c->ln_part;
     g.pdl = 0;   // predecessor (im2col) is not PDL-aware
     if ((rc = gemm(c, g, s, VVS_K_PATCH_GEMM))) return rc;
   }
@@ -355,12 +416,16 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
   const bool pdl = !c->prof_on && pdl_for_rows(M, D);
   for (int i = 0; i <= layer; ++i) {
     const BlockW& w = c->blocks[i];
-    { ProfScope ps(c, VVS_K_LAYERNORM, s);
-      rc = launch_layernorm(c->x, w.n1w, w.n1b, c->h, M, D, 1e-6f, pin_row0, s, &c->err, pdl); }
-    if (rc) return rc;
+    if (!fused) {
+      ProfScope ps(c, VVS_K_LAYERNORM, s);
+      if ((rc = launch_layernorm(c->x, w.n1w, w.n1b, c->h, M, D, 1e-6f, pin_row0, s, &c->err, pdl))) return rc;
+    }
     {
-      GemmArgs g = plain_gemm(c->h, w.qkv_w, M, 3 * D, D, EPI_BIAS_BF16);
-      g.bias = w.qkv_b; g.out_bf16 = c->big; g.ldo = 3 * D; g.q_cols = D; g.q_scale = 0.125f;   // hd^-0.5, hd = 64
+      // fused: raw bf16 rows of x times W diag(gamma), normalised by the epilogue from the producer's row statistics
+      GemmArgs g = plain_gemm(fused ? c->xb : c->h, fused ? w.qkv_wf : w.qkv_w, M, 3 * D, D,
+                              fused ? EPI_BIAS_LN_BF16 : EPI_BIAS_BF16);
+      g.bias = fused ? w.qkv_bf : w.qkv_b; g.out_bf16 = c->big; g.ldo = 3 * D; g.q_cols = D; g.q_scale = 0.125f;   // hd^-0.5, hd = 64
+      g.ln_part_in = c->ln_part; g.colsum = w.qkv_cs; g.ln_eps = 1e-6f;
       g.pdl = pdl;
       const bool facet_stop = stop_after_qkv && i == layer;   // key / query / value facet: the hook sees raw qkv(norm1(x))
       if (facet_stop) g.q_scale = 1.0f;
@@ -376,24 +441,31 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
       rc = launch_attention(c->big, c->h, n_img, N, f.heads, s, &c->err, pdl); }
     if (rc) return rc;
     {
-      GemmArgs g = plain_gemm(c->h, w.proj_w, M, D, D, EPI_RESID_F32);
+      GemmArgs g = plain_gemm(c->h, w.proj_w, M, D, D, fused ? EPI_RESID_LN_F32 : EPI_RESID_F32);
       g.bias = w.proj_b; g.gamma = w.ls1; g.x_f32 = c->x; g.ldo = D; g.pdl = pdl; g.pin_row0 = pin_row0;
+      g.xb_out = c->xb; g.ln_part_out = c->ln_part;
       if ((rc = gemm(c, g, s, VVS_K_PROJ_GEMM))) return rc;
     }
-    { ProfScope ps(c, VVS_K_LAYERNORM, s);
-      rc = launch_layernorm(c->x, w.n2w, w.n2b, c->h, M, D, 1e-6f, pin_row0, s, &c->err, pdl); }
-    if (rc) return rc;
+    if (!fused) {
+      ProfScope ps(c, VVS_K_LAYERNORM, s);
+      if ((rc = launch_layernorm(c->x, w.n2w, w.n2b, c->h, M, D, 1e-6f, pin_row0, s, &c->err, pdl))) return rc;
+    }
     {
-      GemmArgs g = plain_gemm(c->h, w.ffn1_w, M, f.swiglu ? 2 * H : H, D, f.swiglu ? EPI_SWIGLU_BF16 : EPI_GELU_BF16);
-      g.bias = w.ffn1_b; g.out_bf16 = c->big; g.ldo = H; g.pdl = pdl;
+      const int epi = f.swiglu ? (fused ? EPI_SWIGLU_LN_BF16 : EPI_SWIGLU_BF16) : (fused ? EPI_GELU_LN_BF16 : EPI_GELU_BF16);
+      GemmArgs g = plain_gemm(fused ? c->xb : c->h, fused ? w.ffn1_wf : w.ffn1_w, M, f.swiglu ? 2 * H : H, D, epi);
+      g.bias = fused ? w.ffn1_bf : w.ffn1_b; g.out_bf16 = c->big; g.ldo = H; g.pdl = pdl;
+      g.ln_part_in = c->ln_part; g.colsum = w.ffn1_cs; g.ln_eps = 1e-6f;
       if ((rc = gemm(c, g, s, VVS_K_FFN1_GEMM))) return rc;
     }
     {
-      GemmArgs g = plain_gemm(c->big, w.ffn2_w, M, D, H, EPI_RESID_F32);
+      // the last block's output is read by the descriptor kernels only: no bf16 copy, no statistics
+      const bool feeds_ln = fused && i < layer;
+      GemmArgs g = plain_gemm(c->big, w.ffn2_w, M, D, H, feeds_ln ? EPI_RESID_LN_F32 : EPI_RESID_F32);
       g.bias = w.ffn2_b; g.gamma = w.ls2; g.x_f32 = c->x; g.ldo = D; g.pdl = pdl; g.pin_row0 = pin_row0;
+      g.xb_out = c->xb; g.ln_part_out = c->ln_part;
       if ((rc = gemm(c, g, s, VVS_K_FFN2_GEMM))) return rc;
     }
-    c->launch_count += 3;   // 2 LayerNorms + attention
+    c->launch_count += fused ? 1 : 3;   // attention (+ 2 LayerNorms)
   }
   c->last_n_img = n_img;
   c->facet_n_img = 0;
@@ -795,6 +867,47 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
 }  // namespace
 
 namespace {
+// fp32 copy (row-interleaved like the bf16 one) of a matrix whose input LayerNorm is folded into it
+int upload_matrix_f32(vvs_ctx* c, float** dst, const void* src, int dtype, int rows, int cols, int interleave_bn, int hidden,
+                      cudaStream_t s) {
+  if (!*dst) {
+    int rc = dev_alloc(c, dst, static_cast<size_t>(rows) * cols);
+    if (rc) return rc;
+  }
+  const long long total = static_cast<long long>(rows) * cols;
+  const int grid = static_cast<int>(std::min<long long>((total + 255) / 256, 148 * 16));
+  if (dtype == VVS_F32)
+    convert_matrix_f32_kernel<float><<<grid, 256, 0, s>>>(static_cast<const float*>(src), *dst, rows, cols, interleave_bn, hidden);
+  else
+    convert_matrix_f32_kernel<bf16><<<grid, 256, 0, s>>>(static_cast<const bf16*>(src), *dst, rows, cols, interleave_bn, hidden);
+  VVS_CUDA_OK(cudaGetLastError(), &c->err);
+  return VVS_OK;
+}
+
+// (re)folds norm1 into attn.qkv and norm2 into mlp.fc1 / w12 of one block once the four tensors of a group are set
+// (set_mask bits: norm1.weight 0, norm1.bias 1, qkv.bias 6, qkv.weight 10; norm2.weight 2, norm2.bias 3, fc1.bias 8,
+// fc1.weight 12); called after every upload into the block, so re-setting any member refreshes the fold
+int refold_block(vvs_ctx* c, BlockW& w, cudaStream_t s) {
+  if (!c->ln_fused) return VVS_OK;
+  const int D = c->cfg.dim, H = c->cfg.ffn_hidden;
+  struct Group { unsigned mask; int rows; const float* w32; const float* g; const float* b; const float* bias; bf16** wf; float** cs; float** bf; };
+  const Group groups[2] = {
+      {(1u << 0) | (1u << 1) | (1u << 6) | (1u << 10), 3 * D, w.qkv_w32, w.n1w, w.n1b, w.qkv_b, &w.qkv_wf, &w.qkv_cs, &w.qkv_bf},
+      {(1u << 2) | (1u << 3) | (1u << 8) | (1u << 12), c->cfg.swiglu ? 2 * H : H, w.ffn1_w32, w.n2w, w.n2b, w.ffn1_b, &w.ffn1_wf,
+       &w.ffn1_cs, &w.ffn1_bf}};
+  for (const Group& g : groups) {
+    if ((w.set_mask & g.mask) != g.mask) continue;
+    int rc = VVS_OK;
+    if (!*g.wf) rc = dev_alloc(c, g.wf, static_cast<size_t>(g.rows) * D);
+    if (!rc && !*g.cs) rc = dev_alloc(c, g.cs, static_cast<size_t>(g.rows));
+    if (!rc && !*g.bf) rc = dev_alloc(c, g.bf, static_cast<size_t>(g.rows));
+    if (rc) return rc;
+    fold_layernorm_kernel<<<(g.rows + 7) / 8, 256, 0, s>>>(g.w32, g.g, g.b, g.bias, *g.wf, *g.cs, *g.bf, g.rows, D);
+    VVS_CUDA_OK(cudaGetLastError(), &c->err);
+  }
+  return VVS_OK;
+}
+
 // pos' depends on patch_embed.proj.bias, cls_token and pos_embed_interp: refreshed whenever one of them is (re)set
 int refresh_pos_prime(vvs_ctx* c, cudaStream_t s) {
   if ((c->emb_mask & 0xE) != 0xE) return VVS_OK;
@@ -859,6 +972,11 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
   int rc = 0;
   rc |= dev_alloc(c, &c->x, rows * D);
   rc |= dev_alloc(c, &c->h, rows * D);
+  if (const char* e = getenv("VITVS_LN_FUSED")) c->ln_fused = e[0] != '0';
+  if (c->ln_fused) {
+    rc |= dev_alloc(c, &c->xb, rows * D);
+    rc |= dev_alloc(c, &c->ln_part, rows * (D / 64));
+  }
   rc |= dev_alloc(c, &c->big, c->big_elems);
   rc |= dev_alloc(c, &c->desc, c->desc_elems);
   rc |= dev_alloc(c, &c->sqn, static_cast<size_t>(cfg->max_images) * c->T);
@@ -932,7 +1050,7 @@ int vvs_destroy(vvs_handle c) {
   for (cudaEvent_t e : c->chunk_events) cudaEventDestroy(e);
   free_resize_axis(&c->rz_w);
   free_resize_axis(&c->rz_h);
-  void* ptrs[] = {c->pe_w, c->pe_b, c->cls, c->pos, c->pos_prime, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
+  void* ptrs[] = {c->xb, c->ln_part, c->pe_w, c->pe_b, c->cls, c->pos, c->pos_prime, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
                   c->inv_norm, c->nn1, c->nn2, c->sim1, c->cand, c->mean_sim1, c->n_cand, c->n_sel, c->flags, c->mean_sel,
                   c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth, c->land_frames[0], c->land_frames[1],
                   c->land_depth[0], c->land_depth[1],
@@ -942,7 +1060,8 @@ int vvs_destroy(vvs_handle c) {
   for (cudaEvent_t e : c->prof_events) cudaEventDestroy(e);
   for (BlockW& w : c->blocks) {
     void* bp[] = {w.qkv_w, w.proj_w, w.ffn1_w, w.ffn2_w, w.qkv_b, w.proj_b, w.ffn1_b, w.ffn2_b,
-                  w.n1w, w.n1b, w.n2w, w.n2b, w.ls1, w.ls2};
+                  w.n1w, w.n1b, w.n2w, w.n2b, w.ls1, w.ls2, w.qkv_w32, w.ffn1_w32, w.qkv_wf, w.ffn1_wf, w.qkv_cs, w.ffn1_cs,
+                  w.qkv_bf, w.ffn1_bf};
     for (void* p : bp)
       if (p) cudaFree(p);
   }
@@ -1032,7 +1151,8 @@ int vvs_set_weight(vvs_handle c, const char* name_c, const void* p, int32_t dtyp
       if (leaf == v.leaf) {
         if (n != v.n) return bad_shape();
         w.set_mask |= 1u << v.bit;
-        return upload_vector(c, v.dst, p, dtype, v.n, v.il, H, s);
+        int rc = upload_vector(c, v.dst, p, dtype, v.n, v.il, H, s);
+        return rc ? rc : refold_block(c, w, s);
       }
     struct Mat { const char* leaf; bf16** dst; int rows, cols; int bit; int il; };
     const Mat mats[] = {
@@ -1043,7 +1163,10 @@ int vvs_set_weight(vvs_handle c, const char* name_c, const void* p, int32_t dtyp
       if (leaf == m.leaf) {
         if (n != static_cast<long long>(m.rows) * m.cols) return bad_shape();
         w.set_mask |= 1u << m.bit;
-        return upload_matrix(c, m.dst, p, dtype, m.rows, m.cols, m.cols, m.il, H, s);
+        int rc = upload_matrix(c, m.dst, p, dtype, m.rows, m.cols, m.cols, m.il, H, s);
+        if (!rc && c->ln_fused && (m.bit == 10 || m.bit == 12))   // consumers of a LayerNorm: keep the unrounded source
+          rc = upload_matrix_f32(c, m.bit == 10 ? &w.qkv_w32 : &w.ffn1_w32, p, dtype, m.rows, m.cols, m.il, H, s);
+        return rc ? rc : refold_block(c, w, s);
       }
   }
   return fail(c, VVS_ERR_INVALID, "vvs_set_weight: unknown parameter name " + name);
@@ -1441,6 +1564,20 @@ int vvs_dbg_gemm(vvs_handle c, const void* A, const void* B, int32_t M, int32_t 
   GemmArgs g = plain_gemm(static_cast<const bf16*>(A), static_cast<const bf16*>(B), M, N, K, epilogue);
   g.bias = bias; g.gamma = gamma; g.x_f32 = x_f32; g.out_bf16 = static_cast<bf16*>(out_bf16); g.ldo = ldo;
   g.q_cols = q_cols; g.q_scale = q_scale; g.pos = pos; g.T = T;
+  return gemm(c, g, static_cast<cudaStream_t>(stream));
+}
+
+int vvs_dbg_gemm_ln(vvs_handle c, const void* A, const void* B, int32_t M, int32_t N, int32_t K, int32_t epilogue,
+                    const float* bias, const float* gamma, float* x_f32, void* out_bf16, int32_t ldo, int32_t q_cols,
+                    float q_scale, const float* pos, int32_t T, float* ln_part_out, void* xb_out, const float* ln_part_in,
+                    const float* colsum, float ln_eps, vvs_stream stream) {
+  if (!c || !A || !B) return fail(c, VVS_ERR_INVALID, "vvs_dbg_gemm_ln: null argument");
+  DeviceGuard dg(c);
+  GemmArgs g = plain_gemm(static_cast<const bf16*>(A), static_cast<const bf16*>(B), M, N, K, epilogue);
+  g.bias = bias; g.gamma = gamma; g.x_f32 = x_f32; g.out_bf16 = static_cast<bf16*>(out_bf16); g.ldo = ldo;
+  g.q_cols = q_cols; g.q_scale = q_scale; g.pos = pos; g.T = T;
+  g.ln_part_out = reinterpret_cast<float2*>(ln_part_out); g.xb_out = static_cast<bf16*>(xb_out);
+  g.ln_part_in = reinterpret_cast<const float2*>(ln_part_in); g.colsum = colsum; g.ln_eps = ln_eps;
   return gemm(c, g, static_cast<cudaStream_t>(stream));
 }
 

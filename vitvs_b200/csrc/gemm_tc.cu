@@ -49,22 +49,46 @@ struct GemmDev {
   int best_pitch;
   int pin_row0;   // EPI_RESID_F32 / EPI_PATCH_F32: rows >= pin_row0 of x carry the L2 evict-last hint
   unsigned long long* trace;   // vvs_trace_step slot (null otherwise)
+  // folded LayerNorm (EPI_*_LN_*)
+  float2* ln_part_out;         // producers: [M, N / 64]
+  bf16* xb_out;                // producers: bf16 copy of the new residual rows (pitch ldo)
+  const float2* ln_part_in;    // consumers: [M, K / 64]
+  const float* colsum;         // consumers: [N]
+  float ln_inv_d, ln_eps;
 };
+
+// LayerNorm-folded epilogues share the code of the epilogue they extend
+__host__ __device__ constexpr int epi_base(int e) {
+  return e == EPI_RESID_LN_F32 ? EPI_RESID_F32
+       : e == EPI_PATCH_LN_F32 ? EPI_PATCH_F32
+       : e == EPI_BIAS_LN_BF16 ? EPI_BIAS_BF16
+       : e == EPI_GELU_LN_BF16 ? EPI_GELU_BF16
+       : e == EPI_SWIGLU_LN_BF16 ? EPI_SWIGLU_BF16 : e;
+}
 
 // NCTA = 2: a CTA pair (cluster of 2 on one TPC) computes a 256 x BN tile with cta_group::2 MMAs; each CTA
 // stages its own 128 rows of A and HALF of the B tile, so the L2 -> SM operand traffic per flop drops by a
 // third against the 1-CTA 128 x 256 tile (measured: the 1-CTA kernel saturates the L2 -> SM fabric at
 // ~13-15 TB/s while the tensor pipe idles).
-template <int BN, int NCTA>
+template <int BN, int NCTA, int EPI = EPI_STORE_F32>
 struct Cfg {
   static constexpr int kPair = NCTA >= 2 ? 2 : 1;   // CTAs per MMA (cta_group); NCTA = 4: two pairs sharing the B tile
-  static constexpr int kStages = (NCTA >= 2) ? 6 : ((BN == 256) ? 4 : 6);
   static constexpr uint32_t kABytes = BM * BK * 2;
   static constexpr uint32_t kBBytes = (BN / kPair) * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr uint32_t kTmemCols = 2 * BN;
-  static constexpr uint32_t kStagingBytes = 8 * 4096;   // one 32-row x 128-byte transpose buffer per epilogue warp
-  static constexpr uint32_t kSmemBytes = kStages * kStageBytes + kStagingBytes + 256 /*barriers*/ + 1024 /*align slack*/;
+  // one 32-row x 128-byte slab per epilogue warp (transpose buffer of the TMA stores); EPI_RESID_LN_F32 has two: the
+  // old residual values of chunk i + 1 land in one (TMA load) while chunk i is updated in place in the other
+  static constexpr uint32_t kSlabsPerWarp = (EPI == EPI_RESID_LN_F32) ? 2 : 1;
+  static constexpr uint32_t kStagingBytes = 8 * 4096 * kSlabsPerWarp;
+  static constexpr uint32_t kBarrierBytes = 512;
+  static constexpr uint32_t kRingBudget = 192 * 1024 - (kStagingBytes - 8 * 4096);   // what the extra slabs leave to the ring
+  static constexpr int kStages = (kRingBudget / kStageBytes) < 6 ? static_cast<int>(kRingBudget / kStageBytes) : 6;
+  // per-tile column operands (bias / gamma / colsum of the tile's BN columns): read from shared memory by the chunk
+  // loops, so that no global-load latency sits between an accumulator chunk and its arithmetic
+  static constexpr uint32_t kColopBytes = 2 * BN * 4;
+  // the dynamic shared-memory window is declared 1024-byte aligned (SWIZZLE_128B atoms) and the kernel traps if it is not
+  static constexpr uint32_t kSmemBytes = kStages * kStageBytes + kStagingBytes + kBarrierBytes + kColopBytes;
 };
 
 // exact (erf) GELU = x * Phi(x) with Phi(x) = 1 - q (x >= 0) or q (x < 0), q = 0.5 erfc(|x| / sqrt 2).
@@ -120,15 +144,21 @@ __device__ __forceinline__ uint32_t ord_f32(float f) {
 template <int BN, int EPI, int NCTA>
 __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmB2,
                                           const CUtensorMap& tmOut, const GemmDev& p) {
-  using C = Cfg<BN, NCTA>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  using C = Cfg<BN, NCTA, EPI>;
+  constexpr int EB = epi_base(EPI);     // the epilogue whose arithmetic this one extends
+  constexpr bool kLnOut = (EPI == EPI_RESID_LN_F32 || EPI == EPI_PATCH_LN_F32);   // emits xb + row statistics
+  constexpr bool kLnIn = (EPI == EPI_BIAS_LN_BF16 || EPI == EPI_GELU_LN_BF16 || EPI == EPI_SWIGLU_LN_BF16);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();   // the layout below has no alignment slack
   uint8_t* staging = smem + C::kStages * C::kStageBytes;
   uint64_t* full = reinterpret_cast<uint64_t*>(staging + C::kStagingBytes);
   uint64_t* empty = full + C::kStages;
   uint64_t* tfull = empty + C::kStages;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* xfull = tempty + 2;         // EPI_RESID_LN_F32: [epilogue warp][slab] the old residual values have landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xfull + 16);
+  float* colop = reinterpret_cast<float*>(staging + C::kStagingBytes + C::kBarrierBytes);   // [2][BN]
 
   // shuffle broadcast: warp-uniform for the compiler too, so descriptors / barrier addresses stay on the uniform
   // datapath (a plain threadIdx.x >> 5 wraps every tcgen05.mma / TMA issue in an ELECT + R2UR waterfall loop)
@@ -154,6 +184,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       mbar_init(&tfull[a], 1);
       mbar_init(&tempty[a], 8 * C::kPair);   // pair: the peer's epilogue warps arrive on the leader's barrier
     }
+    if constexpr (EPI == EPI_RESID_LN_F32)
+      for (int a = 0; a < 16; ++a) mbar_init(&xfull[a], 1);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -275,27 +307,134 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     const int half = (warp - 2) >> 2;         // which half of the chunks
     const uint32_t lane_field = static_cast<uint32_t>(quarter * 32) << 16;
     constexpr int NC = BN / 32;               // chunks per tile
-    const uint32_t stg_s = smem_u32(staging + (warp - 2) * 4096);   // 1024-byte aligned: swizzle phase = row & 7
+    const uint32_t stg_s = smem_u32(staging + (warp - 2) * 4096 * C::kSlabsPerWarp);   // 1024-byte aligned: swizzle phase = row & 7
     const uint32_t my_row_s = stg_s + lane * 128;
+    uint64_t* const xbar = xfull + (warp - 2) * 2;   // EPI_RESID_LN_F32
+    uint32_t xphase = 0;                             // bit s: parity the next wait on xbar[s] expects
     const uint32_t sw = static_cast<uint32_t>(lane & 7);
     uint32_t acc = 0, acc_phase = 0;
     const uint32_t tempty0 = (NCTA >= 2) ? mapa_shared(smem_u32(&tempty[0]), leader_rank) : 0u;   // leader's tempty[]
+    // folded LayerNorm, consumer side: (rstd, -rstd * mean) of this thread's row of tile t from the producer's
+    // per-64-column partials, summed in a fixed order (bit-identical whatever the tiling of producer and consumer)
+    float ln_a_next = 1.0f, ln_c_next = 0.0f;
+    auto ln_stats = [&](int t) {
+      if constexpr (kLnIn) {
+        ln_a_next = 1.0f;
+        ln_c_next = 0.0f;
+        if (t >= total_tiles) return;
+        const int tb = t / tiles_per_batch, tr = t - tb * tiles_per_batch;
+        const int trow = ((tr / p.n_tiles) * NCTA + static_cast<int>(slot)) * BM + quarter * 32 + lane;
+#ifdef VVS_LNEXP_NOSTATS   // timing experiment only (wrong values): no statistics fetch
+        ln_a_next = 1.0f + p.ln_eps;
+        ln_c_next = p.ln_eps;
+        if (false) {
+#else
+        if (trow < p.M) {
+#endif
+          const float4* pp = reinterpret_cast<const float4*>(p.ln_part_in + (static_cast<size_t>(tb) * p.M + trow) * p.num_kb);
+          float s1 = 0.f, s2 = 0.f;
+#pragma unroll 4
+          for (int g = 0; g < (p.num_kb >> 1); ++g) {   // K / 64 partials, two per 16-byte load
+            const float4 t4 = __ldg(pp + g);
+            s1 += t4.x; s2 += t4.y;
+            s1 += t4.z; s2 += t4.w;
+          }
+          const float mean = s1 * p.ln_inv_d;
+          const float var = fmaxf(fmaf(-mean, mean, s2 * p.ln_inv_d), 0.f);
+          ln_a_next = rsqrtf(var + p.ln_eps);
+          ln_c_next = -ln_a_next * mean;
+        }
+      }
+    };
+    ln_stats(first_tile);
+    // Column operands of a tile: thread t of the 256 epilogue threads owns tile column t.  Array 0 = bias (b' for the
+    // folded LayerNorm), array 1 = gamma (residual epilogues) or colsum (folded LayerNorm).  The values of tile i + 1 are
+    // requested while tile i is processed (two registers), and written to shared memory between two named barriers
+    // at the top of tile i + 1: nobody still reads tile i's, everybody sees tile i + 1's.
+    constexpr bool kColop = (EB == EPI_BIAS_BF16 || EB == EPI_GELU_BF16 || EB == EPI_RESID_F32 || EB == EPI_PATCH_F32 ||
+                             EB == EPI_SWIGLU_BF16);
+    constexpr bool kColop1 = (EB == EPI_RESID_F32 || kLnIn);
+    const uint32_t colop_s = smem_u32(colop);
+    const int ct = (warp - 2) * 32 + lane;      // tile column this thread stages
+    float co0 = 0.f, co1 = 0.f;
+    auto colop_fetch = [&](int t) {
+      if constexpr (kColop) {
+        if (t < total_tiles && ct < BN) {
+          const int col = ((t % tiles_per_batch) % p.n_tiles) * BN + ct;
+          if (col < p.N) {
+            co0 = __ldg(p.bias + col);
+            if constexpr (kColop1) co1 = __ldg((kLnIn ? p.colsum : p.gamma) + col);
+          }
+        }
+      }
+    };
+    colop_fetch(first_tile);
     for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
       const int b = tile / tiles_per_batch;
       const int r = tile - b * tiles_per_batch;
       const int m_blk = (r / p.n_tiles) * NCTA + static_cast<int>(slot);
       const int n_blk = r % p.n_tiles;
+      if constexpr (kColop) {
+        named_bar_sync<1>(256);
+        if (ct < BN) {
+          colop[ct] = co0;
+          if constexpr (kColop1) colop[BN + ct] = co1;
+        }
+        named_bar_sync<2>(256);
+        colop_fetch(tile + tile_step);
+      }
       const int tile_row0 = m_blk * BM + quarter * 32;      // first row of this warp's slab (inside batch b)
       const int row = tile_row0 + lane;                     // row inside batch b
       const bool row_ok = row < p.M;
       const size_t grow = static_cast<size_t>(b) * p.M + row;
+      // folded LayerNorm, consumer side:  y = rstd * (acc - mean * colsum) + b' = ln_a * acc + (ln_c * colsum + b').
+      // The statistics of THIS tile's rows were computed at the end of the previous tile (ln_stats below), off the
+      // accumulator's critical path; here only the next tile's partials are pulled into L1.
+      float ln_a = 1.0f, ln_c = 0.0f;
+      if constexpr (kLnIn) {
+        ln_a = ln_a_next;
+        ln_c = ln_c_next;
+        const int tn = tile + tile_step;
+        if (tn < total_tiles) {
+          const int bnx = tn / tiles_per_batch, rn = tn - bnx * tiles_per_batch;
+          const int rown = ((rn / p.n_tiles) * NCTA + static_cast<int>(slot)) * BM + quarter * 32 + lane;
+          if (rown < p.M && (rn / p.n_tiles) != (r / p.n_tiles)) {   // same rows as this tile: already there
+            const char* q = reinterpret_cast<const char*>(p.ln_part_in + (static_cast<size_t>(bnx) * p.M + rown) * p.num_kb);
+            prefetch_l1(q);
+            prefetch_l1(q + p.num_kb * 8 - 1);
+          }
+        }
+      }
+      // EPI_RESID_LN_F32 adds to x in the SM: the old values of a chunk arrive by TMA in one of this warp's two slabs
+      // (the very boxes the store writes back), requested one chunk ahead; chunk 0 here, ahead of the accumulator wait
+      if constexpr (EPI == EPI_RESID_LN_F32) {
+        constexpr int NCHP = BN / 64;
+        const int col_first = n_blk * BN + ((warp - 2) >> 2) * NCHP * 32;
+        if (lane == 0 && col_first < p.N) {
+          bulk_wait_read1();                 // slab 0 was last read by the store of the previous tile's chunk NCHP - 2
+          mbar_expect_tx(&xbar[0], 4096);
+          tma_load_2d_s(stg_s, &tmOut, &xbar[0], col_first, tile_row0, kEvictNormal);
+        }
+      }
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_acc = tmem_base + acc * BN + lane_field;
+      // The accumulator goes back to the MMA warp as soon as this warp's LAST chunk of it sits in registers - a chunk's
+      // arithmetic and stores earlier than the end of the tile.  tcgen05.wait::ld is warp-collective, so every lane's
+      // reads are complete; the arrive carries no memory fence (the tcgen05 fences order the TMEM accesses, and a
+      // release at cluster scope would wait for every global store of the epilogue).
+      auto release_acc = [&]() {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (NCTA >= 2) mbar_arrive_cluster_nofence(tempty0 + acc * 8);
+          else mbar_arrive(&tempty[acc]);
+        }
+      };
 
-      if constexpr (EPI == EPI_SWIGLU_BF16 && BN != 256) {
+      if constexpr (EB == EPI_SWIGLU_BF16 && BN != 256) {
         __trap();   // never launched: the launcher only pairs the SwiGLU epilogue with 256-wide tiles
-      } else if constexpr (EPI == EPI_SWIGLU_BF16) {
+      } else if constexpr (EB == EPI_SWIGLU_BF16) {
         // tile columns [0,BN/2) = x1 slice, [BN/2,BN) = matching x2 slice (rows of w12 interleaved on load);
         // N % BN == 0 is enforced by the launcher, so every tile is complete.
         constexpr int NP = NC / 4;              // (x1, x2) chunk pairs per warp: 2 -> one 64-column slab
@@ -309,15 +448,22 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           tmem_ld32(t_acc + c * 32, r1);
           tmem_ld32(t_acc + BN / 2 + c * 32, r2);
           tmem_ld_wait();
+          if (i == NP - 1) release_acc();
           float v[32];
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
-            const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + tcol) + q);
-            const float4 b2 = __ldg(reinterpret_cast<const float4*>(p.bias + tcol + BN / 2) + q);
-            v[q * 4 + 0] = silu(__uint_as_float(r1[q * 4 + 0]) + b1.x) * (__uint_as_float(r2[q * 4 + 0]) + b2.x);
-            v[q * 4 + 1] = silu(__uint_as_float(r1[q * 4 + 1]) + b1.y) * (__uint_as_float(r2[q * 4 + 1]) + b2.y);
-            v[q * 4 + 2] = silu(__uint_as_float(r1[q * 4 + 2]) + b1.z) * (__uint_as_float(r2[q * 4 + 2]) + b2.z);
-            v[q * 4 + 3] = silu(__uint_as_float(r1[q * 4 + 3]) + b1.w) * (__uint_as_float(r2[q * 4 + 3]) + b2.w);
+            float4 b1 = ld_shared_v4f(colop_s + (c * 32 + q * 4) * 4);
+            float4 b2 = ld_shared_v4f(colop_s + (BN / 2 + c * 32 + q * 4) * 4);
+            if constexpr (kLnIn) {
+              const float4 c1 = ld_shared_v4f(colop_s + (BN + c * 32 + q * 4) * 4);
+              const float4 c2 = ld_shared_v4f(colop_s + (BN + BN / 2 + c * 32 + q * 4) * 4);
+              b1 = make_float4(fmaf(ln_c, c1.x, b1.x), fmaf(ln_c, c1.y, b1.y), fmaf(ln_c, c1.z, b1.z), fmaf(ln_c, c1.w, b1.w));
+              b2 = make_float4(fmaf(ln_c, c2.x, b2.x), fmaf(ln_c, c2.y, b2.y), fmaf(ln_c, c2.z, b2.z), fmaf(ln_c, c2.w, b2.w));
+            }
+            v[q * 4 + 0] = silu(fmaf(ln_a, __uint_as_float(r1[q * 4 + 0]), b1.x)) * fmaf(ln_a, __uint_as_float(r2[q * 4 + 0]), b2.x);
+            v[q * 4 + 1] = silu(fmaf(ln_a, __uint_as_float(r1[q * 4 + 1]), b1.y)) * fmaf(ln_a, __uint_as_float(r2[q * 4 + 1]), b2.y);
+            v[q * 4 + 2] = silu(fmaf(ln_a, __uint_as_float(r1[q * 4 + 2]), b1.z)) * fmaf(ln_a, __uint_as_float(r2[q * 4 + 2]), b2.z);
+            v[q * 4 + 3] = silu(fmaf(ln_a, __uint_as_float(r1[q * 4 + 3]), b1.w)) * fmaf(ln_a, __uint_as_float(r2[q * 4 + 3]), b2.w);
           }
 #pragma unroll
           for (int q = 0; q < 4; ++q)
@@ -339,34 +485,94 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         int best_j = -1;                        // index inside this warp's NCH * 32 columns
         // EPI_PATCH_F32: the positional row of this GEMM row (row r of image i is token r of the residual stream)
         const float* pos_row = nullptr;
-        if constexpr (EPI == EPI_PATCH_F32) pos_row = p.pos + static_cast<size_t>(row_ok ? row % (p.T + 1) : 0) * p.ldo;
+        if constexpr (EB == EPI_PATCH_F32) pos_row = p.pos + static_cast<size_t>(row_ok ? row % (p.T + 1) : 0) * p.ldo;
+        // kLnOut: running (sum, sum of squares) of this thread's row over the current 64-column group, two packed lanes
+        f32x2 st1a = 0ull, st1b = 0ull, st2a = 0ull, st2b = 0ull;
         uint32_t raw[2][32];
         tmem_ld32(t_acc + c_begin * 32, raw[0]);
+        // folded LayerNorm, consumer side, 256-wide tiles: the NEXT tile's row statistics are gathered while this tile is
+        // processed - chunk i requests a third of the partials, chunk i + 1 adds them up (same order as ln_stats), so
+        // that no load latency is left at either end of the tile
+        constexpr bool kStreamStats = kLnIn && NCH >= 4;
+        const float4* spp = nullptr;
+        float4 sp[4];
+        float sx1 = 0.f, sx2 = 0.f;
+        const int sG = p.num_kb >> 1, sper = (sG + NCH - 2) / (NCH - 1);
+        if constexpr (kStreamStats) {
+          const int tn = tile + tile_step;
+          if (tn < total_tiles) {
+            const int tb = tn / tiles_per_batch, tr = tn - tb * tiles_per_batch;
+            const int trow = ((tr / p.n_tiles) * NCTA + static_cast<int>(slot)) * BM + quarter * 32 + lane;
+            if (trow < p.M)
+              spp = reinterpret_cast<const float4*>(p.ln_part_in + (static_cast<size_t>(tb) * p.M + trow) * p.num_kb);
+          }
+        }
 #pragma unroll
         for (int i = 0; i < NCH; ++i) {
           const int c = c_begin + i;
           const int col0 = n_blk * BN + c * 32;
           const bool live = col0 < p.N;         // warp-uniform (ragged last N tile)
-          // per-column operands, requested before the TMEM wait so their latency overlaps it
-          float4 bq[8], gq[8];
-          if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_GELU_BF16 || EPI == EPI_RESID_F32 || EPI == EPI_PATCH_F32) {
-            if (live) {
+          if constexpr (kStreamStats) {
+            if (spp != nullptr) {
+              if (i >= 1) {
 #pragma unroll
-              for (int q = 0; q < 8; ++q) bq[q] = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + q);
+                for (int k = 0; k < 4; ++k)
+                  if (k < sper && (i - 1) * sper + k < sG) {
+                    sx1 += sp[k].x; sx2 += sp[k].y;
+                    sx1 += sp[k].z; sx2 += sp[k].w;
+                  }
+              }
+              if (i < NCH - 1) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                  if (k < sper && i * sper + k < sG) sp[k] = __ldg(spp + i * sper + k);
+              }
             }
           }
-          if constexpr (EPI == EPI_RESID_F32) {
+          // per-column operands, requested before the TMEM wait so their latency overlaps it
+          float4 bq[8], gq[8];
+          if constexpr (EB == EPI_BIAS_BF16 || EB == EPI_GELU_BF16 || EB == EPI_RESID_F32 || EB == EPI_PATCH_F32) {
             if (live) {
 #pragma unroll
-              for (int q = 0; q < 8; ++q) gq[q] = __ldg(reinterpret_cast<const float4*>(p.gamma + col0) + q);
+              for (int q = 0; q < 8; ++q) bq[q] = ld_shared_v4f(colop_s + (c * 32 + q * 4) * 4);
+            }
+          }
+          if constexpr (EB == EPI_RESID_F32) {
+            if (live) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) gq[q] = ld_shared_v4f(colop_s + (BN + c * 32 + q * 4) * 4);
+            }
+          }
+          if constexpr (kLnIn) {
+            // the column term of the folded LayerNorm, ln_c * colsum(W') + b', replaces the bias before the accumulator
+            // arrives: one live operand array and one FMA per element, as in the plain epilogue
+            if (live) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+#ifdef VVS_LNEXP_NOCS       // timing experiment only (wrong values): no colsum term
+                const float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
+#else
+                const float4 cs = ld_shared_v4f(colop_s + (BN + c * 32 + q * 4) * 4);
+#endif
+                bq[q] = make_float4(fmaf(ln_c, cs.x, bq[q].x), fmaf(ln_c, cs.y, bq[q].y), fmaf(ln_c, cs.z, bq[q].z),
+                                    fmaf(ln_c, cs.w, bq[q].w));
+              }
+            }
+          }
+          if constexpr (EPI == EPI_RESID_LN_F32) {
+            if (lane == 0 && i + 1 < NCH && col0 + 32 < p.N) {   // the next chunk's old values -> the other slab
+              bulk_wait_read0();             // ... which the previous chunk's store has finished reading
+              mbar_expect_tx(&xbar[(i + 1) & 1], 4096);
+              tma_load_2d_s(stg_s + ((i + 1) & 1) * 4096, &tmOut, &xbar[(i + 1) & 1], col0 + 32, tile_row0, kEvictNormal);
             }
           }
           tmem_ld_wait();
           if (i + 1 < NCH) tmem_ld32(t_acc + (c + 1) * 32, raw[(i + 1) & 1]);
+          else release_acc();
           const uint32_t(&rw)[32] = raw[i & 1];
           if (!live) continue;
 
-          if constexpr (EPI == EPI_SIM) {
+          if constexpr (EB == EPI_SIM) {
             // Row best: a thread owns one accumulator row, so it scans its 32 columns in increasing order (strict >:
             // ties keep the lowest column).  Column best: the warp's 32 x 32 chunk is transposed through its private
             // swizzled smem slab (8 conflict-free 16-byte stores per lane, 32 conflict-free word loads), then lane L
@@ -420,23 +626,28 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
               atomicMax(&p.col_best[static_cast<size_t>(b) * p.best_pitch + col0 + lane],
                         (static_cast<unsigned long long>(ord_f32(cb)) << 32) |
                             (0xFFFFFFFFu - static_cast<uint32_t>(tile_row0 + cr)));
-          } else if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_GELU_BF16) {
+          } else if constexpr (EB == EPI_BIAS_BF16 || EB == EPI_GELU_BF16) {
             // two 32-column chunks (64 bf16 = 128 bytes per row) form one slab
             if ((i & 1) == 0) {
               if (lane == 0) bulk_wait_read0();   // the previous slab's store has finished reading the buffer
               __syncwarp();
             }
             uint32_t pk[16];
-            if constexpr (EPI == EPI_BIAS_BF16) {
+            // pre-activation of a column pair: acc + b, or with the folded LayerNorm ln_a * acc + (ln_c * colsum + b')
+            const f32x2 la2 = f2_pack(ln_a, ln_a);
+            auto pre = [&](uint32_t r0, uint32_t r1, float b0, float b1) -> f32x2 {
+              const f32x2 a = f2_pack(__uint_as_float(r0), __uint_as_float(r1));
+              if constexpr (kLnIn) return f2_fma(la2, a, f2_pack(b0, b1));
+              else return f2_add(a, f2_pack(b0, b1));
+            };
+            if constexpr (EB == EPI_BIAS_BF16) {
               const float s = (col0 < p.q_cols) ? p.q_scale : 1.0f;
               const f32x2 s2 = f2_pack(s, s);
 #pragma unroll
               for (int q = 0; q < 8; ++q) {
                 float a0, a1, a2, a3;
-                f2_unpack(f2_mul(f2_add(f2_pack(__uint_as_float(rw[q * 4 + 0]), __uint_as_float(rw[q * 4 + 1])),
-                                        f2_pack(bq[q].x, bq[q].y)), s2), a0, a1);
-                f2_unpack(f2_mul(f2_add(f2_pack(__uint_as_float(rw[q * 4 + 2]), __uint_as_float(rw[q * 4 + 3])),
-                                        f2_pack(bq[q].z, bq[q].w)), s2), a2, a3);
+                f2_unpack(f2_mul(pre(rw[q * 4 + 0], rw[q * 4 + 1], bq[q].x, bq[q].y), s2), a0, a1);
+                f2_unpack(f2_mul(pre(rw[q * 4 + 2], rw[q * 4 + 3], bq[q].z, bq[q].w), s2), a2, a3);
                 pk[q * 2 + 0] = pack_bf16x2(a0, a1);
                 pk[q * 2 + 1] = pack_bf16x2(a2, a3);
               }
@@ -444,10 +655,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 #pragma unroll
               for (int q = 0; q < 8; ++q) {
                 float a0, a1, a2, a3;
-                gelu_erf2(f2_add(f2_pack(__uint_as_float(rw[q * 4 + 0]), __uint_as_float(rw[q * 4 + 1])),
-                                 f2_pack(bq[q].x, bq[q].y)), a0, a1);
-                gelu_erf2(f2_add(f2_pack(__uint_as_float(rw[q * 4 + 2]), __uint_as_float(rw[q * 4 + 3])),
-                                 f2_pack(bq[q].z, bq[q].w)), a2, a3);
+                gelu_erf2(pre(rw[q * 4 + 0], rw[q * 4 + 1], bq[q].x, bq[q].y), a0, a1);
+                gelu_erf2(pre(rw[q * 4 + 2], rw[q * 4 + 3], bq[q].z, bq[q].w), a2, a3);
                 pk[q * 2 + 0] = pack_bf16x2(a0, a1);
                 pk[q * 2 + 1] = pack_bf16x2(a2, a3);
               }
@@ -463,6 +672,69 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
               if (lane == 0 && tile_row0 < p.M) {
                 tma_store_2d(&tmOut, stg_s, col0 - (i & 1) * 32, tile_row0);   // columns >= N are clipped
                 bulk_commit();
+              }
+            }
+          } else if constexpr (kLnOut) {
+            // The new residual values in registers: x + gamma * (acc + bias) with the old x loaded above (the very
+            // arithmetic of the reduce-add path: one rounding per operation), or acc + bias + pos' (patch embed).
+            // They leave three ways: the fp32 slab by TMA store, the bf16 copy the next GEMM multiplies by two 256-bit
+            // stores of this thread's row, and the (sum, sum of squares) of every 64-column group for the consumer.
+            const uint32_t slab_s = (EPI == EPI_RESID_LN_F32) ? stg_s + (i & 1) * 4096 : stg_s;
+            const uint32_t slab_row_s = slab_s + lane * 128;
+            if constexpr (EPI == EPI_RESID_LN_F32) {
+              mbar_wait(&xbar[i & 1], (xphase >> (i & 1)) & 1u);   // the old values of this chunk have landed
+              xphase ^= 1u << (i & 1);
+            } else {
+              if (lane == 0) bulk_wait_read0();
+              __syncwarp();
+            }
+            if ((col0 & 63) == 0) st1a = st1b = st2a = st2b = 0ull;   // a new 64-column group starts
+            uint32_t pk[8];
+            // four columns at a time: a thread reads and rewrites only its own row of the slab (no cross-lane hazard)
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              float v0, v1, v2, v3;
+              const uint32_t cell = slab_row_s + ((static_cast<uint32_t>(q) ^ sw) << 4);
+              if constexpr (EPI == EPI_RESID_LN_F32) {
+                const float4 xo = ld_shared_v4f(cell);
+                v0 = __fadd_rn(xo.x, __fmul_rn(gq[q].x, __fadd_rn(__uint_as_float(rw[q * 4 + 0]), bq[q].x)));
+                v1 = __fadd_rn(xo.y, __fmul_rn(gq[q].y, __fadd_rn(__uint_as_float(rw[q * 4 + 1]), bq[q].y)));
+                v2 = __fadd_rn(xo.z, __fmul_rn(gq[q].z, __fadd_rn(__uint_as_float(rw[q * 4 + 2]), bq[q].z)));
+                v3 = __fadd_rn(xo.w, __fmul_rn(gq[q].w, __fadd_rn(__uint_as_float(rw[q * 4 + 3]), bq[q].w)));
+              } else {
+                const float4 ps = __ldg(reinterpret_cast<const float4*>(pos_row + col0) + q);
+                v0 = __uint_as_float(rw[q * 4 + 0]) + bq[q].x + ps.x;
+                v1 = __uint_as_float(rw[q * 4 + 1]) + bq[q].y + ps.y;
+                v2 = __uint_as_float(rw[q * 4 + 2]) + bq[q].z + ps.z;
+                v3 = __uint_as_float(rw[q * 4 + 3]) + bq[q].w + ps.w;
+              }
+              st_shared_v4f(cell, v0, v1, v2, v3);
+              const f32x2 va = f2_pack(v0, v1), vb = f2_pack(v2, v3);
+              st1a = f2_add(st1a, va);
+              st1b = f2_add(st1b, vb);
+              st2a = f2_fma(va, va, st2a);
+              st2b = f2_fma(vb, vb, st2b);
+              pk[(2 * q) & 7] = pack_bf16x2(v0, v1);
+              pk[(2 * q + 1) & 7] = pack_bf16x2(v2, v3);
+              if ((q & 3) == 3 && row_ok)   // 16 columns of the bf16 copy: one 32-byte sector of this thread's row
+                st_global_v8(p.xb_out + grow * p.ldo + col0 + (q >> 2) * 16, pk[0], pk[1], pk[2], pk[3], pk[4], pk[5], pk[6], pk[7]);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && tile_row0 < p.M) {
+              if (tile_row0 >= p.pin_row0) tma_store_2d_hint(&tmOut, slab_s, col0, tile_row0, kEvictLast);
+              else tma_store_2d(&tmOut, slab_s, col0, tile_row0);
+              bulk_commit();
+            }
+            if (row_ok) {
+              if ((col0 & 63) == 32) {
+                float a0, a1, b0, b1, c0, c1, d0, d1;
+                f2_unpack(st1a, a0, a1);
+                f2_unpack(st1b, b0, b1);
+                f2_unpack(st2a, c0, c1);
+                f2_unpack(st2b, d0, d1);
+                p.ln_part_out[grow * static_cast<size_t>(p.N >> 6) + (col0 >> 6)] =
+                    make_float2((a0 + a1) + (b0 + b1), (c0 + c1) + (d0 + d1));
               }
             }
           } else if constexpr (EPI == EPI_RESID_F32) {
@@ -518,7 +790,17 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             }
           }
         }
-        if constexpr (EPI == EPI_SIM) {
+        if constexpr (kStreamStats) {
+          ln_a_next = 1.0f;
+          ln_c_next = 0.0f;
+          if (spp != nullptr) {
+            const float mean = sx1 * p.ln_inv_d;
+            const float var = fmaxf(fmaf(-mean, mean, sx2 * p.ln_inv_d), 0.f);
+            ln_a_next = rsqrtf(var + p.ln_eps);
+            ln_c_next = -ln_a_next * mean;
+          }
+        }
+        if constexpr (EB == EPI_SIM) {
           if (row_ok && best_j >= 0) {
             const unsigned long long k = (static_cast<unsigned long long>(ord_f32(best_v)) << 32) |
                                          (0xFFFFFFFFu - static_cast<uint32_t>(n_blk * BN + c_begin * 32 + best_j));
@@ -526,11 +808,12 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           }
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if constexpr (NCTA >= 2) mbar_arrive_cluster(tempty0 + acc * 8);
-        else mbar_arrive(&tempty[acc]);
+      if constexpr (kLnIn) {
+        if constexpr (EB != EPI_SWIGLU_BF16 && BN / 64 >= 4) {
+          // gathered by the chunk loop above
+        } else {
+          ln_stats(tile + tile_step);   // the accumulator is long released: this latency is nobody's critical path
+        }
       }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
@@ -585,7 +868,7 @@ EncodeTiledFn get_encode_fn(std::string* err) {
 template <int BN, int EPI, int NCTA>
 int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const GemmDev& d, int grid,
                cudaStream_t stream, bool pdl, std::string* err) {
-  using C = Cfg<BN, NCTA>;
+  using C = Cfg<BN, NCTA, EPI>;
   static PerDeviceOnce once;
   VVS_CUDA_OK(once.run([] {
                 return cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -601,7 +884,7 @@ int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap
 template <int EPI>
 int launch_mixed(const CUtensorMap& tmA, const CUtensorMap& tmB4, const CUtensorMap& tmB2, const CUtensorMap& tmOut,
                  const GemmDev& d, int grid, cudaStream_t stream, bool pdl, std::string* err) {
-  using C = Cfg<256, 4>;
+  using C = Cfg<256, 4, EPI>;
   static PerDeviceOnce once;
   VVS_CUDA_OK(once.run([] {
                 cudaError_t e = cudaFuncSetAttribute(gemm_tc_mixed_kernel<256, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -639,6 +922,11 @@ int dispatch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const 
     case EPI_SWIGLU_BF16: return launch_one<BN, EPI_SWIGLU_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
     case EPI_SIM: return launch_one<BN, EPI_SIM, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
     case EPI_STORE_F32: return launch_one<BN, EPI_STORE_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_RESID_LN_F32: return launch_one<BN, EPI_RESID_LN_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_PATCH_LN_F32: return launch_one<BN, EPI_PATCH_LN_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_BIAS_LN_BF16: return launch_one<BN, EPI_BIAS_LN_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_GELU_LN_BF16: return launch_one<BN, EPI_GELU_LN_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_SWIGLU_LN_BF16: return launch_one<BN, EPI_SWIGLU_LN_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
     default: set_error(err, "launch_gemm: unknown epilogue"); return VVS_ERR_INVALID;
   }
 }
@@ -709,6 +997,17 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
     set_error(err, "launch_gemm: K, lda, ldb must be multiples of 8 (16-byte TMA rows)");
     return VVS_ERR_INVALID;
   }
+  const int eb = epi_base(a.epilogue);
+  const bool ln_out = a.epilogue == EPI_RESID_LN_F32 || a.epilogue == EPI_PATCH_LN_F32;
+  const bool ln_in = a.epilogue == EPI_BIAS_LN_BF16 || a.epilogue == EPI_GELU_LN_BF16 || a.epilogue == EPI_SWIGLU_LN_BF16;
+  if (ln_out && (!a.ln_part_out || !a.xb_out || a.N % 64 || a.ldo % 16)) {
+    set_error(err, "launch_gemm: folded-LayerNorm producer needs ln_part_out, xb_out, N % 64 == 0 and ldo % 16 == 0");
+    return VVS_ERR_INVALID;
+  }
+  if (ln_in && (!a.ln_part_in || !a.colsum || a.K % 128)) {
+    set_error(err, "launch_gemm: folded-LayerNorm consumer needs ln_part_in, colsum and K % 128 == 0");
+    return VVS_ERR_INVALID;
+  }
   const bool masked_n = (a.epilogue == EPI_SIM || a.epilogue == EPI_STORE_F32);
   if (!masked_n && (a.N % 32 || a.ldo % 8)) {
     set_error(err, "launch_gemm: N must be a multiple of 32 and ldo of 8 for this epilogue");
@@ -724,8 +1023,7 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
     return (e && e[0] == '1') ? 1 : (e && e[0] == '2') ? 2 : 4;
   }();
   // two-pair clusters only where they pay: 256-wide tiles, one problem, at least a few 512-row cluster tiles
-  const bool mixed_epi = a.epilogue == EPI_BIAS_BF16 || a.epilogue == EPI_GELU_BF16 || a.epilogue == EPI_RESID_F32 ||
-                         a.epilogue == EPI_SWIGLU_BF16;
+  const bool mixed_epi = eb == EPI_BIAS_BF16 || eb == EPI_GELU_BF16 || eb == EPI_RESID_F32 || eb == EPI_SWIGLU_BF16;
   int ncta = (ncta_env == 4 && !(mixed_epi && bn == 256 && a.batch == 1 && a.M >= 4096)) ? 2 : ncta_env;
   // Small problems (a single frame pair: M = 970 rows): 256 x 256 pair tiles would occupy a dozen of the 74 CTA-pair
   // slots and run a K loop at twice the per-tile cost.  When the pair tiling fills less than half of the machine, use
@@ -735,19 +1033,19 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
     const char* e = getenv("VITVS_SMALL_TILES");
     return !(e && e[0] == '0');
   }();
-  if (small_tiles && ncta == 2 && a.epilogue != EPI_SWIGLU_BF16) {
+  if (small_tiles && ncta == 2 && eb != EPI_SWIGLU_BF16) {
     const long long pair_tiles = static_cast<long long>(a.batch) * ((a.M + 2 * BM - 1) / (2 * BM)) * ((a.N + bn - 1) / bn);
     if (pair_tiles * 4 < num_sms) {
       ncta = 1;
       bn = 128;
     }
   }
-  if (a.epilogue == EPI_SWIGLU_BF16 && (bn != 256 || a.N % bn)) {
+  if (eb == EPI_SWIGLU_BF16 && (bn != 256 || a.N % bn)) {
     set_error(err, "launch_gemm: SwiGLU needs N to be a multiple of the 256-wide N tile");
     return VVS_ERR_INVALID;
   }
-  const bool tma_out = a.epilogue == EPI_BIAS_BF16 || a.epilogue == EPI_GELU_BF16 || a.epilogue == EPI_SWIGLU_BF16 ||
-                       a.epilogue == EPI_RESID_F32 || a.epilogue == EPI_PATCH_F32;
+  const bool tma_out = eb == EPI_BIAS_BF16 || eb == EPI_GELU_BF16 || eb == EPI_SWIGLU_BF16 || eb == EPI_RESID_F32 ||
+                       eb == EPI_PATCH_F32;
   if (tma_out && a.batch != 1) {
     set_error(err, "launch_gemm: this epilogue stores through a 2-D tensor map (batch must be 1)");
     return VVS_ERR_INVALID;
@@ -759,9 +1057,9 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   rc = make_tmap_bf16(&tmB, a.B, a.K, a.N, b_batched ? a.batch : 1, a.ldb, a.b_batch_pitch, bn / ncta, err);   // pair: half, two pairs: quarter
   if (rc) return rc;
   CUtensorMap tmOut = tmA;   // unused by the epilogues that write with plain stores
-  if (a.epilogue == EPI_RESID_F32 || a.epilogue == EPI_PATCH_F32)
+  if (eb == EPI_RESID_F32 || eb == EPI_PATCH_F32)
     rc = make_tmap_out(&tmOut, a.x_f32, 4, a.N, a.M, a.ldo, 32, 32, err);
-  else if (a.epilogue == EPI_SWIGLU_BF16)
+  else if (eb == EPI_SWIGLU_BF16)
     rc = make_tmap_out(&tmOut, a.out_bf16, 2, a.N / 2, a.M, a.ldo, 64, 32, err);
   else if (tma_out)
     rc = make_tmap_out(&tmOut, a.out_bf16, 2, a.N, a.M, a.ldo, 64, 32, err);
@@ -776,6 +1074,8 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   d.row_best = a.row_best; d.col_best = a.col_best; d.best_pitch = a.best_pitch;
   d.pin_row0 = a.pin_row0 > 0 ? a.pin_row0 : 0x7fffffff;
   d.trace = tl_trace_slot;
+  d.ln_part_out = a.ln_part_out; d.xb_out = a.xb_out; d.ln_part_in = a.ln_part_in; d.colsum = a.colsum;
+  d.ln_inv_d = 1.0f / static_cast<float>(a.K); d.ln_eps = a.ln_eps;
   const long long tiles = static_cast<long long>(d.batch) * d.m_tiles * d.n_tiles;
   if (ncta == 4) {
     CUtensorMap tmB2;   // pair-mode chunks fetch half of the B tile per CTA (tmB holds the quad mode's quarter boxes)
@@ -788,6 +1088,10 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
       case EPI_GELU_BF16: return launch_mixed<EPI_GELU_BF16>(tmA, tmB, tmB2, tmOut, d, grid, stream, pdl, err);
       case EPI_RESID_F32: return launch_mixed<EPI_RESID_F32>(tmA, tmB, tmB2, tmOut, d, grid, stream, pdl, err);
       case EPI_SWIGLU_BF16: return launch_mixed<EPI_SWIGLU_BF16>(tmA, tmB, tmB2, tmOut, d, grid, stream, pdl, err);
+      case EPI_RESID_LN_F32: return launch_mixed<EPI_RESID_LN_F32>(tmA, tmB, tmB2, tmOut, d, grid, stream, pdl, err);
+      case EPI_BIAS_LN_BF16: return launch_mixed<EPI_BIAS_LN_BF16>(tmA, tmB, tmB2, tmOut, d, grid, stream, pdl, err);
+      case EPI_GELU_LN_BF16: return launch_mixed<EPI_GELU_LN_BF16>(tmA, tmB, tmB2, tmOut, d, grid, stream, pdl, err);
+      case EPI_SWIGLU_LN_BF16: return launch_mixed<EPI_SWIGLU_LN_BF16>(tmA, tmB, tmB2, tmOut, d, grid, stream, pdl, err);
       default: set_error(err, "launch_gemm: epilogue not built for mixed clusters"); return VVS_ERR_INVALID;
     }
   }

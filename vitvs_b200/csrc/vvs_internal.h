@@ -92,7 +92,16 @@ enum Epilogue : int {
   EPI_PATCH_F32 = 3,   // x_f32[r] = acc + bias + pos'[r % (T+1)], A has a zero row per CLS slot        (patch embed)
   EPI_SWIGLU_BF16 = 4, // out_bf16 = silu(acc1 + b1) * (acc2 + b2), weight rows tile-interleaved (mlp.w12)
   EPI_SIM = 5,         // packed row / column arg-max of the similarity tile, S never stored    (matching)
-  EPI_STORE_F32 = 6    // out_f32 = acc  (plain fp32 store; unit tests / similarity dump)
+  EPI_STORE_F32 = 6,   // out_f32 = acc  (plain fp32 store; unit tests / similarity dump)
+  // LayerNorm folded into the GEMMs on either side of it (no LayerNorm pass over the residual stream):
+  // PRODUCERS of the residual stream also emit its bf16 copy and per-row (sum, sum of squares) partials, one per
+  // 64-column group; CONSUMERS multiply the RAW bf16 rows by gamma-folded weights and normalise in the epilogue:
+  //   LN(x) W^T + b = rstd * (x W'^T - mean * colsum(W')) + b',  W' = W diag(gamma_ln),  b' = b + W beta_ln
+  EPI_RESID_LN_F32 = 7,    // EPI_RESID_F32 computed in registers (x loaded, stored) + xb_out + ln_part_out
+  EPI_PATCH_LN_F32 = 8,    // EPI_PATCH_F32 + xb_out + ln_part_out
+  EPI_BIAS_LN_BF16 = 9,    // EPI_BIAS_BF16 on rstd * (acc - mean * colsum) instead of acc
+  EPI_GELU_LN_BF16 = 10,   // EPI_GELU_BF16 likewise
+  EPI_SWIGLU_LN_BF16 = 11  // EPI_SWIGLU_BF16 likewise
 };
 
 struct GemmArgs {
@@ -119,6 +128,12 @@ struct GemmArgs {
   int best_pitch;
   int pin_row0;          // EPI_RESID_F32: rows >= pin_row0 of x are reduce-added with the L2 evict-last hint (<= 0: no hint)
   int pdl;               // launch with the programmatic-dependent-launch attribute (predecessor is a PDL-aware kernel)
+  // folded LayerNorm (EPI_*_LN_*): partials are float2 (sum, sum of squares) per row and 64-column group
+  float2* ln_part_out;        // producers: [M, N / 64] statistics of the NEW residual rows
+  bf16* xb_out;               // producers: bf16 copy of the new residual rows, pitch ldo
+  const float2* ln_part_in;   // consumers: [M, K / 64] statistics of A's rows
+  const float* colsum;        // consumers: [N] sum over k of B[n, k] (of the bf16 values the tensor core multiplies)
+  float ln_eps;
 };
 int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string* err);
 int gemm_block_n(int N);   // the N tile the launcher picks for this N (128 or 256)

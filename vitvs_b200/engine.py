@@ -446,6 +446,16 @@ class Engine:
                                           _ptr(x_f32), _ptr(out_bf16), ldo, q_cols, q_scale, _ptr(pos), T,
                                           _stream(self.device)), "vvs_dbg_gemm")
 
+    def dbg_gemm_ln(self, A, B, epilogue, bias=None, gamma=None, x_f32=None, out_bf16=None, ldo=0, q_cols=0,
+                    q_scale=1.0, pos=None, T=0, ln_part_out=None, xb_out=None, ln_part_in=None, colsum=None, ln_eps=1e-6):
+        """GEMM with a folded-LayerNorm epilogue (csrc/vvs_internal.h EPI_*_LN_*)."""
+        M, K = A.shape
+        N = B.shape[0]
+        self._check(self.lib.vvs_dbg_gemm_ln(self._h, _ptr(A), _ptr(B), M, N, K, epilogue, _ptr(bias), _ptr(gamma),
+                                             _ptr(x_f32), _ptr(out_bf16), ldo, q_cols, q_scale, _ptr(pos), T,
+                                             _ptr(ln_part_out), _ptr(xb_out), _ptr(ln_part_in), _ptr(colsum), ln_eps,
+                                             _stream(self.device)), "vvs_dbg_gemm_ln")
+
     def dbg_attention(self, qkv, n_img, n_tok, heads):
         out = torch.empty(n_img * n_tok, heads * 64, dtype=torch.bfloat16, device=self.device)
         self._check(self.lib.vvs_dbg_attention(self._h, _ptr(qkv), _ptr(out), n_img, n_tok, heads,
