@@ -307,6 +307,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     const int half = (warp - 2) >> 2;         // which half of the chunks
     const uint32_t lane_field = static_cast<uint32_t>(quarter * 32) << 16;
     constexpr int NC = BN / 32;               // chunks per tile
+    // 64-wide tiles (launch-bound small problems): both chunks belong to the warps of half 0, so that a warp still owns
+    // whole 64-column groups (bf16 slabs, LayerNorm partials); the warps of half 1 only keep the protocol going
+    constexpr int NCH = (BN == 64) ? 2 : NC / 2;   // chunks per working warp
+    const bool idle_warp = (BN == 64) && half == 1;
+    const int c_begin = (BN == 64) ? 0 : half * NCH;
     const uint32_t stg_s = smem_u32(staging + (warp - 2) * 4096 * C::kSlabsPerWarp);   // 1024-byte aligned: swizzle phase = row & 7
     const uint32_t my_row_s = stg_s + lane * 128;
     uint64_t* const xbar = xfull + (warp - 2) * 2;   // EPI_RESID_LN_F32
@@ -408,10 +413,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       // EPI_RESID_LN_F32 adds to x in the SM: the old values of a chunk arrive by TMA in one of this warp's two slabs
       // (the very boxes the store writes back), requested one chunk ahead; chunk 0 here, ahead of the accumulator wait
       if constexpr (EPI == EPI_RESID_LN_F32) {
-        constexpr int NCHP = BN / 64;
-        const int col_first = n_blk * BN + ((warp - 2) >> 2) * NCHP * 32;
-        if (lane == 0 && col_first < p.N) {
-          bulk_wait_read1();                 // slab 0 was last read by the store of the previous tile's chunk NCHP - 2
+        const int col_first = n_blk * BN + c_begin * 32;
+        if (lane == 0 && col_first < p.N && !idle_warp) {
+          bulk_wait_read1();                 // slab 0 was last read by the store of the previous tile's chunk NCH - 2
           mbar_expect_tx(&xbar[0], 4096);
           tma_load_2d_s(stg_s, &tmOut, &xbar[0], col_first, tile_row0, kEvictNormal);
         }
@@ -434,6 +438,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 
       if constexpr (EB == EPI_SWIGLU_BF16 && BN != 256) {
         __trap();   // never launched: the launcher only pairs the SwiGLU epilogue with 256-wide tiles
+      } else if (idle_warp) {
+        release_acc();
       } else if constexpr (EB == EPI_SWIGLU_BF16) {
         // tile columns [0,BN/2) = x1 slice, [BN/2,BN) = matching x2 slice (rows of w12 interleaved on load);
         // N % BN == 0 is enforced by the launcher, so every tile is complete.
@@ -478,8 +484,6 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           bulk_commit();
         }
       } else {
-        constexpr int NCH = NC / 2;             // chunks per warp
-        const int c_begin = half * NCH;
         // EPI_SIM state: running row best over this warp's columns; ties -> lowest column
         float best_v = -INFINITY;
         int best_j = -1;                        // index inside this warp's NCH * 32 columns
@@ -1038,6 +1042,18 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
     if (pair_tiles * 4 < num_sms) {
       ncta = 1;
       bn = 128;
+      // ... and when even those leave half of the SMs without a tile, 128 x 64 ones: such a kernel is one K loop per CTA,
+      // bound by what one SM can pull from L2 (24 KB instead of 32 KB per k-block), and twice as many SMs pull
+      // (VITVS_SMALL_TILES=1: 128-wide only)
+      static const bool tiles64 = []() {
+        const char* e = getenv("VITVS_SMALL_TILES");
+        return !(e && e[0] == '1');
+      }();
+      const long long tiles128 = static_cast<long long>(a.batch) * ((a.M + BM - 1) / BM) * ((a.N + 127) / 128);
+      // Not under programmatic dependent launch (ViT-S, single pair): there the SMs a kernel leaves free are where
+      // its successor's prologue runs, and filling them costs more than the shorter K loop gives (measured on B200,
+      // single pair: ViT-B 0.843 -> 0.808 ms p50, ViT-S with PDL 0.597 -> 0.634).
+      if (tiles64 && !a.pdl && tiles128 * 2 <= num_sms && eb != EPI_SWIGLU_BF16) bn = 64;   // still one tile per CTA
     }
   }
   if (eb == EPI_SWIGLU_BF16 && (bn != 256 || a.N % bn)) {
@@ -1102,6 +1118,7 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   }
   const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
   if (bn == 256) return dispatch_epi<256, 1>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
+  if (bn == 64) return dispatch_epi<64, 1>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
   return dispatch_epi<128, 1>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
 }
 
