@@ -4,6 +4,7 @@
 //                   camera pixels (vitvs_v2.py:80-151, :511-513, :525-553)
 //   ibvs_kernel   : depth lookup, normalised coordinates, interaction rows, 6x6 normal equations in
 //                   fp64, v = -lambda * L^+ e, optional EMA (vitvs_v2.py:566-586, :610-623, :634-659)
+#include <algorithm>
 #include <string>
 
 #include "ptx.cuh"
@@ -186,8 +187,25 @@ __global__ void __launch_bounds__(1024) select_kernel(const SelectArgs a, unsign
     }
     __shared__ unsigned long long s_best[2][32];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    unsigned long long cur = my_best_below(~0ull);     // a thread only reads the keys it wrote itself: no barrier needed
-    for (int k = 0; k < nsel; ++k) {
+    // Few tokens (the servo grid: 484): every key counts the keys above it - its rank IS its slot (keys are unique) -
+    // with broadcast reads of the shared array: one barrier instead of K rounds of reduce + barrier.
+    const bool by_rank = in_smem && T <= 2048;
+    if (by_rank) {
+      __syncthreads();
+      for (int i = threadIdx.x; i < T; i += blockDim.x) {
+        const unsigned long long key = s_keys[i];
+        if (key == 0ull) continue;
+        int rank = 0;
+        for (int j = 0; j < T; ++j) rank += s_keys[j] > key ? 1 : 0;
+        if (rank < nsel) {
+          const int tok = static_cast<int>(0xFFFFFFFFu - static_cast<uint32_t>(key));
+          sel_tok[rank] = tok;
+          sel_sim[rank] = same ? 1.0f : sim1[tok];
+        }
+      }
+    }
+    unsigned long long cur = by_rank ? 0ull : my_best_below(~0ull);   // a thread only reads the keys it wrote itself: no barrier needed
+    for (int k = 0; k < (by_rank ? 0 : nsel); ++k) {
       const unsigned long long wb = warp_max_u64(cur);
       if (lane == 0) s_best[k & 1][wid] = wb;
       __syncthreads();
@@ -447,7 +465,7 @@ int launch_select(const SelectArgs& a, cudaStream_t s, std::string* err) {
     set_error(err, "select: num_pairs must be in [1, 256]");
     return VVS_ERR_INVALID;
   }
-  // 1024 threads per pair; the selection keys live in dynamic shared memory when they fit (T <= 25 600)
+  // up to 1024 threads per pair; the selection keys live in dynamic shared memory when they fit (T <= 25 600)
   constexpr size_t kMaxKeySmem = 200 * 1024;
   static PerDeviceOnce once;
   VVS_CUDA_OK(once.run([&] {
@@ -456,7 +474,8 @@ int launch_select(const SelectArgs& a, cudaStream_t s, std::string* err) {
   SelectArgs b = a;
   const size_t key_bytes = static_cast<size_t>(a.T) * sizeof(unsigned long long);
   b.keys_in_smem = (!a.sel_order && key_bytes <= kMaxKeySmem) ? 1 : 0;
-  select_kernel<<<a.n_pairs, 1024, b.keys_in_smem ? key_bytes : 0, s>>>(b, tl_trace_slot);
+  const int threads = std::min(1024, std::max(128, (a.T + 127) / 128 * 128));   // a function of T alone (reduction orders)
+  select_kernel<<<a.n_pairs, threads, b.keys_in_smem ? key_bytes : 0, s>>>(b, tl_trace_slot);
   VVS_CUDA_OK(cudaGetLastError(), err);
   return VVS_OK;
 }
