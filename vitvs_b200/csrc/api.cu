@@ -22,16 +22,19 @@ void set_error(std::string* slot, const std::string& msg) {
 
 bool pdl_for_rows(long long rows, int dim) {
   // Measured on B200, graph replay.  64 pairs of ViT-B: 14.04 ms with PDL vs 13.83 ms without - the step runs under the
-  // power cap, where idle gaps between kernels are paid back as clock boost.  One pair (970 rows, ~90 kernels of a few
-  // microseconds each, launch-latency-bound): ViT-S 0.673 -> 0.635 ms p50 with PDL (the next kernel's prologue - barrier
-  // init, TMEM allocation, descriptor prefetch - runs under the previous kernel's tail), ViT-B 0.935 -> 0.953 ms (its
-  // kernels are long enough that early CTAs only compete for the SMs).  Hence: small batches of the narrow model only.
+  // power cap, where idle gaps between kernels are paid back as clock boost.  A single pair (970 rows, ~70 kernels of a
+  // few microseconds each) is launch-latency-bound: the next kernel's prologue (barrier init, TMEM allocation, descriptor
+  // prefetch) runs under the previous kernel's tail and the gaps between kernels halve (2.1 -> 1.0 us).  Round 1 found
+  // PDL slower for ViT-B; the cause was the attention kernel, whose early-resident CTAs packed four to an SM
+  // (attention_ts.cu: a small grid now asks to be alone on its SM).  p50 of one pair with / without: ViT-S 0.538 / -,
+  // ViT-B 0.734 / 0.798, ViT-L 0.858 / 0.930, ViT-g 1.162 / 1.163 ms.  Hence: small batches, every width.
+  (void)dim;
   static const int mode = []() {
     const char* e = getenv("VITVS_PDL");
     return !e ? -1 : (e[0] == '1' ? 1 : 0);
   }();
   if (mode >= 0) return mode == 1;
-  return rows <= 4096 && dim <= 384;
+  return rows <= 4096;
 }
 
 namespace {
@@ -425,6 +428,7 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
       GemmArgs g = plain_gemm(fused ? c->xb : c->h, fused ? w.qkv_wf : w.qkv_w, M, 3 * D, D,
                               fused ? EPI_BIAS_LN_BF16 : EPI_BIAS_BF16);
       g.bias = fused ? w.qkv_bf : w.qkv_b; g.out_bf16 = c->big; g.ldo = 3 * D; g.q_cols = D; g.q_scale = 0.125f;   // hd^-0.5, hd = 64
+      g.b_static = 1;
       g.ln_part_in = c->ln_part; g.colsum = w.qkv_cs; g.ln_eps = 1e-6f;
       g.pdl = pdl;
       const bool facet_stop = stop_after_qkv && i == layer;   // key / query / value facet: the hook sees raw qkv(norm1(x))
@@ -438,11 +442,12 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
       }
     }
     { ProfScope ps(c, VVS_K_ATTENTION, s);
-      rc = launch_attention(c->big, c->h, n_img, N, f.heads, s, &c->err, pdl); }
+      rc = launch_attention(c->big, c->h, n_img, N, f.heads, s, &c->err, pdl, c->num_sms); }
     if (rc) return rc;
     {
       GemmArgs g = plain_gemm(c->h, w.proj_w, M, D, D, fused ? EPI_RESID_LN_F32 : EPI_RESID_F32);
       g.bias = w.proj_b; g.gamma = w.ls1; g.x_f32 = c->x; g.ldo = D; g.pdl = pdl; g.pin_row0 = pin_row0;
+      g.b_static = 1;
       g.xb_out = c->xb; g.ln_part_out = c->ln_part;
       if ((rc = gemm(c, g, s, VVS_K_PROJ_GEMM))) return rc;
     }
@@ -454,6 +459,7 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
       const int epi = f.swiglu ? (fused ? EPI_SWIGLU_LN_BF16 : EPI_SWIGLU_BF16) : (fused ? EPI_GELU_LN_BF16 : EPI_GELU_BF16);
       GemmArgs g = plain_gemm(fused ? c->xb : c->h, fused ? w.ffn1_wf : w.ffn1_w, M, f.swiglu ? 2 * H : H, D, epi);
       g.bias = fused ? w.ffn1_bf : w.ffn1_b; g.out_bf16 = c->big; g.ldo = H; g.pdl = pdl;
+      g.b_static = 1;
       g.ln_part_in = c->ln_part; g.colsum = w.ffn1_cs; g.ln_eps = 1e-6f;
       if ((rc = gemm(c, g, s, VVS_K_FFN1_GEMM))) return rc;
     }
@@ -462,6 +468,7 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
       const bool feeds_ln = fused && i < layer;
       GemmArgs g = plain_gemm(c->big, w.ffn2_w, M, D, H, feeds_ln ? EPI_RESID_LN_F32 : EPI_RESID_F32);
       g.bias = w.ffn2_b; g.gamma = w.ls2; g.x_f32 = c->x; g.ldo = D; g.pdl = pdl; g.pin_row0 = pin_row0;
+      g.b_static = 1;
       g.xb_out = c->xb; g.ln_part_out = c->ln_part;
       if ((rc = gemm(c, g, s, VVS_K_FFN2_GEMM))) return rc;
     }

@@ -522,7 +522,7 @@ extern "C" __attribute__((visibility("default"))) int vvs_dbg_att_trace(long lon
 #endif
 
 int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
-                        std::string* err, bool pdl) {
+                        std::string* err, bool pdl, int num_sms) {
   const int D = heads * kHD;
   CUtensorMap tmq, tmkv;
   const uint64_t rows = static_cast<uint64_t>(n_img) * n_tok;
@@ -534,10 +534,15 @@ int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads
   rc = make_tmap_bf16(&tmo, out, static_cast<uint64_t>(D), static_cast<uint64_t>(n_tok), static_cast<uint64_t>(n_img),
                       static_cast<uint64_t>(D), static_cast<uint64_t>(n_tok) * D, kBQ, err);
   if (rc) return rc;
+  // Under programmatic dependent launch the CTAs of this kernel become resident while the QKV GEMM still owns most SMs:
+  // four of them pack onto every SM that frees up first, and a grid of a hundred CTAs (a single frame pair) then runs on
+  // a few dozen SMs at a quarter of an SM each (measured: 8.8 -> 21 us per launch).  A small grid therefore asks for
+  // enough shared memory to be alone on its SM - the CTAs spread as the GEMM's CTAs retire.
+  constexpr uint32_t kSmemAlone = 116 * 1024;
   static PerDeviceOnce once;
   VVS_CUDA_OK(once.run([] {
                 cudaError_t e = cudaFuncSetAttribute(attention_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                     static_cast<int>(kSmem));
+                                                     static_cast<int>(kSmemAlone));
                 if (e != cudaSuccess) return e;
                 return cudaFuncSetAttribute(attention_ts_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
                                             cudaSharedmemCarveoutMaxShared);
@@ -545,8 +550,9 @@ int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads
               err);
   const int q_tiles = (n_tok + kBQ - 1) / kBQ;
   dim3 grid((q_tiles + kQT - 1) / kQT, heads, n_img);
-  VVS_CUDA_OK(launch_kernel(attention_ts_kernel, grid, kThreads, kSmem, stream, pdl, tmq, tmkv, tmo, out, n_tok, D,
-                            tl_trace_slot), err);
+  const bool alone = pdl && static_cast<long long>(grid.x) * grid.y * grid.z <= num_sms;
+  VVS_CUDA_OK(launch_kernel(attention_ts_kernel, grid, kThreads, alone ? kSmemAlone : kSmem, stream, pdl, tmq, tmkv, tmo, out,
+                            n_tok, D, tl_trace_slot), err);
   return VVS_OK;
 }
 

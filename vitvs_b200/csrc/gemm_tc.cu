@@ -47,6 +47,7 @@ struct GemmDev {
   unsigned long long* row_best;
   unsigned long long* col_best;
   int best_pitch;
+  int b_static;   // B does not depend on the previous kernel (weights): its first boxes may be requested ahead of griddepcontrol.wait
   int pin_row0;   // EPI_RESID_F32 / EPI_PATCH_F32: rows >= pin_row0 of x carry the L2 evict-last hint
   unsigned long long* trace;   // vvs_trace_step slot (null otherwise)
   // folded LayerNorm (EPI_*_LN_*)
@@ -199,8 +200,6 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   // everything above (barriers, TMEM, descriptor prefetch) may overlap the previous kernel's tail
   pdl_launch_dependents();
-  pdl_wait();
-  trace_begin(p.trace);
 
   // p.m_tiles counts (128 * NCTA)-row tiles; this CTA owns 128-row block m_tile * NCTA + cta_rank of each
   const int tiles_per_batch = p.m_tiles * p.n_tiles;
@@ -208,13 +207,57 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   const int first_tile = blockIdx.x / NCTA;
   const int tile_step = gridDim.x / NCTA;
 
+  // One stage of operands (lane 0 of the producer warp).  `arm`: post the stage's byte count on its barrier (once per
+  // use of the stage); want_a / want_b: which of the two boxes to request now.
+  const uint32_t full0 = (NCTA >= 2) ? mapa_shared(smem_u32(&full[0]), leader_rank) : 0u;   // leader's full[] in cluster space
+  auto issue_stage = [&](uint32_t stage, int b, int m_blk, int n_blk, int kb, bool arm, bool want_a, bool want_b) {
+    uint8_t* sa = smem + stage * C::kStageBytes;
+    if (NCTA == 4 && quad) {
+      // this CTA fetches ONE quarter of the B tile and multicasts it to the CTA of the same parity in the
+      // other pair: every CTA still receives its 128-row half, the L2 -> SM traffic per CTA drops by a quarter
+      if (arm && pair_rank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
+      const uint32_t fb = full0 + stage * 8;
+      const int quarter = static_cast<int>(cta_rank >> 1);
+      if (want_a) tma_load_3d_2sm(sa, &tmA, fb, kb * BK, m_blk * BM, b, kEvictNormal);
+      if (want_b)
+        tma_load_3d_2sm_mc(sa + C::kABytes + quarter * (BN / 4) * BK * 2, &tmB, fb, kb * BK,
+                           n_blk * BN + static_cast<int>(pair_rank) * (BN / 2) + quarter * (BN / 4), p.b_batched ? b : 0,
+                           static_cast<uint16_t>((1u << cta_rank) | (1u << (cta_rank ^ 2u))), kEvictLast);
+    } else if constexpr (NCTA >= 2) {
+      if (arm && cta_rank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
+      const uint32_t fb = full0 + stage * 8;
+      if (want_a) tma_load_3d_2sm(sa, &tmA, fb, kb * BK, m_blk * BM, b, kEvictNormal);
+      if (want_b)
+        tma_load_3d_2sm(sa + C::kABytes, NCTA == 4 ? &tmB2 : &tmB, fb, kb * BK,
+                        n_blk * BN + static_cast<int>(cta_rank) * (BN / 2), p.b_batched ? b : 0, kEvictLast);
+    } else {
+      if (arm) mbar_expect_tx(&full[stage], C::kStageBytes);
+      if (want_a) tma_load_3d(sa, &tmA, &full[stage], kb * BK, m_blk * BM, b, kEvictNormal);
+      if (want_b) tma_load_3d(sa + C::kABytes, &tmB, &full[stage], kb * BK, n_blk * BN, p.b_batched ? b : 0, kEvictLast);
+    }
+  };
+  // Programmatic dependent launch: B is a WEIGHT matrix (b_static), not the predecessor's output, so the B boxes of the
+  // first stages are requested before the grid dependency resolves - their latency runs under the predecessor's tail
+  // and only the A boxes wait.  (Every stage is free at this point: no empty-barrier wait.)
+  int pre = 0;
+  if (warp == 0 && p.b_static && first_tile < total_tiles) {
+    pre = p.num_kb < C::kStages ? p.num_kb : C::kStages;
+    const int b0 = first_tile / tiles_per_batch, r0 = first_tile - b0 * tiles_per_batch;
+    if (lane == 0)
+      for (int kb = 0; kb < pre; ++kb)
+        issue_stage(static_cast<uint32_t>(kb), b0, (r0 / p.n_tiles) * NCTA + static_cast<int>(slot), r0 % p.n_tiles, kb, true,
+                    false, true);
+    __syncwarp();
+  }
+  pdl_wait();
+  trace_begin(p.trace);
+
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     // The whole warp walks the loop (stage / phase / tile stay warp-uniform values on the uniform datapath);
     // only the issue instructions themselves are predicated on lane 0.
     {
       uint32_t stage = 0, phase = 0;
-      const uint32_t full0 = (NCTA >= 2) ? mapa_shared(smem_u32(&full[0]), leader_rank) : 0u;   // leader's full[] in cluster space
       for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
         const int b = tile / tiles_per_batch;
         const int r = tile - b * tiles_per_batch;
@@ -222,31 +265,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         const int n_blk = r % p.n_tiles;
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * C::kStageBytes;
-          if (lane == 0) {
-            if (NCTA == 4 && quad) {
-              // this CTA fetches ONE quarter of the B tile and multicasts it to the CTA of the same parity in the
-              // other pair: every CTA still receives its 128-row half, the L2 -> SM traffic per CTA drops by a quarter
-              if (pair_rank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
-              const uint32_t fb = full0 + stage * 8;
-              const int quarter = static_cast<int>(cta_rank >> 1);
-              tma_load_3d_2sm(sa, &tmA, fb, kb * BK, m_blk * BM, b, kEvictNormal);
-              tma_load_3d_2sm_mc(sa + C::kABytes + quarter * (BN / 4) * BK * 2, &tmB, fb, kb * BK,
-                                 n_blk * BN + static_cast<int>(pair_rank) * (BN / 2) + quarter * (BN / 4),
-                                 p.b_batched ? b : 0, static_cast<uint16_t>((1u << cta_rank) | (1u << (cta_rank ^ 2u))),
-                                 kEvictLast);
-            } else if constexpr (NCTA >= 2) {
-              if (cta_rank == 0) mbar_expect_tx(&full[stage], 2 * C::kStageBytes);
-              const uint32_t fb = full0 + stage * 8;
-              tma_load_3d_2sm(sa, &tmA, fb, kb * BK, m_blk * BM, b, kEvictNormal);
-              tma_load_3d_2sm(sa + C::kABytes, NCTA == 4 ? &tmB2 : &tmB, fb, kb * BK,
-                              n_blk * BN + static_cast<int>(cta_rank) * (BN / 2), p.b_batched ? b : 0, kEvictLast);
-            } else {
-              mbar_expect_tx(&full[stage], C::kStageBytes);
-              tma_load_3d(sa, &tmA, &full[stage], kb * BK, m_blk * BM, b, kEvictNormal);
-              tma_load_3d(sa + C::kABytes, &tmB, &full[stage], kb * BK, n_blk * BN, p.b_batched ? b : 0, kEvictLast);
-            }
-          }
+          const bool early_b = tile == first_tile && kb < pre;   // armed, B on its way
+          if (lane == 0) issue_stage(stage, b, m_blk, n_blk, kb, !early_b, true, !early_b);
           __syncwarp();
           if (++stage == C::kStages) {
             stage = 0;
@@ -1050,10 +1070,9 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
         return !(e && e[0] == '1');
       }();
       const long long tiles128 = static_cast<long long>(a.batch) * ((a.M + BM - 1) / BM) * ((a.N + 127) / 128);
-      // Not under programmatic dependent launch (ViT-S, single pair): there the SMs a kernel leaves free are where
-      // its successor's prologue runs, and filling them costs more than the shorter K loop gives (measured on B200,
-      // single pair: ViT-B 0.843 -> 0.808 ms p50, ViT-S with PDL 0.597 -> 0.634).
-      if (tiles64 && !a.pdl && tiles128 * 2 <= num_sms && eb != EPI_SWIGLU_BF16) bn = 64;   // still one tile per CTA
+      // (measured on B200, single pair, p50: ViT-B 0.843 -> 0.808 ms; under programmatic dependent launch - once the
+      // attention CTAs spread instead of packing, attention_ts.cu - ViT-B 0.769 -> 0.734, ViT-S 0.583 -> 0.538)
+      if (tiles64 && tiles128 * 2 <= num_sms && eb != EPI_SWIGLU_BF16) bn = 64;   // still one tile per CTA
     }
   }
   if (eb == EPI_SWIGLU_BF16 && (bn != 256 || a.N % bn)) {
@@ -1082,6 +1101,7 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   if (rc) return rc;
   GemmDev d;
   d.M = a.M; d.N = a.N; d.K = a.K; d.batch = a.batch; d.b_batched = b_batched ? 1 : 0;
+  d.b_static = (a.b_static && a.pdl) ? 1 : 0;
   d.m_tiles = (a.M + BM * ncta - 1) / (BM * ncta);
   d.n_tiles = (a.N + bn - 1) / bn;
   d.num_kb = (a.K + BK - 1) / BK;

@@ -128,6 +128,8 @@ struct GemmArgs {
   int best_pitch;
   int pin_row0;          // EPI_RESID_F32: rows >= pin_row0 of x are reduce-added with the L2 evict-last hint (<= 0: no hint)
   int pdl;               // launch with the programmatic-dependent-launch attribute (predecessor is a PDL-aware kernel)
+  int b_static;          // B is a weight matrix (never written by the preceding kernel): under PDL its first boxes are
+                         // requested before the grid dependency resolves
   // folded LayerNorm (EPI_*_LN_*): partials are float2 (sum, sum of squares) per row and 64-column group
   float2* ln_part_out;        // producers: [M, N / 64] statistics of the NEW residual rows
   bf16* xb_out;               // producers: bf16 copy of the new residual rows, pitch ldo
@@ -142,7 +144,7 @@ int gemm_block_n(int N);   // the N tile the launcher picks for this N (128 or 2
 // qkv: [n_img * n_tok, 3*D] bf16 (q pre-scaled by hd^-0.5), out: [n_img * n_tok, D] bf16
 // attention_ts.cu: P stays in TMEM (TS MMA), one 128-row query tile per CTA and four CTAs per SM
 int launch_attention(const bf16* qkv, bf16* out, int n_img, int n_tok, int heads, cudaStream_t stream,
-                     std::string* err, bool pdl = false);
+                     std::string* err, bool pdl = false, int num_sms = 148);
 
 // ---- camera frame -> ViT input: Pillow-exact 8-bit bicubic resize (resize.cu) ---------------------
 struct ResizeAxis {          // one separable pass: per output index the first tap, the tap count and the 22-bit taps
