@@ -216,6 +216,19 @@ VVS_API int vvs_frames_to_twist_host_async(vvs_handle h, const uint8_t* goal_fra
                                    int32_t* n_selected_host, float* mean_sim_sel_host, vvs_stream stream);
 VVS_API int vvs_wait(vvs_handle h, int32_t calls_back);
 
+/* Cached-goal mode - an EXTRA, never the benchmarked path.  The reference recomputes the goal view's descriptors on
+ * every servo iteration (vitvs_v2.py:482-487) although the goal image is loaded once per episode (:255) and never
+ * changes; vvs_set_goal runs n goal views through the backbone once and keeps their unit descriptors in the handle,
+ * vvs_current_to_twist then forwards only the current views and matches view i against goal i (i < n_pairs <= n).
+ * Results are bit-identical to vvs_frame_pairs_to_twist / vvs_frames_to_twist on the same (goal, current) pairs.
+ * from_frames = 0: [n, S, S, 3] uint8 images as in vvs_frame_pairs_to_twist; 1: [n, frame_height, frame_width, 3]
+ * camera frames as in vvs_frames_to_twist.  Device pointers, stream-ordered; `out` as in vvs_frame_pairs_to_twist.
+ * Setting weights or calling any other forward entry leaves the cached goal descriptors untouched; re-set the goal
+ * after changing weights. */
+VVS_API int vvs_set_goal(vvs_handle h, const uint8_t* goal, int32_t n, int32_t from_frames, vvs_stream stream);
+VVS_API int vvs_current_to_twist(vvs_handle h, const uint8_t* current, const uint16_t* depth_mm, int32_t n_pairs,
+                         int32_t from_frames, const vvs_pair_out* out, vvs_stream stream);
+
 /* replaces: PIL `Image.resize((S, S))` of the goal / current camera frame (vitvs_v2.py:474-475; Pillow default
  * filter = antialiased BICUBIC, 8-bit fixed point, horizontal pass then vertical pass).  frames
  * [n, frame_height, frame_width, 3] uint8 RGB (device) -> out [n, S, S, 3] uint8 (device), bit-identical to

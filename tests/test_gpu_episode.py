@@ -120,3 +120,42 @@ def test_best_pose_search_and_num_pairs(eng):
     from vitvs_b200 import VvsError
     with pytest.raises(VvsError):
         eng.set_num_pairs(1000)
+
+
+def test_cached_goal_matches_pair_call(eng):
+    """vvs_set_goal + vvs_current_to_twist (an extra: the goal view's descriptors computed once) return, bit for bit, what
+    the pair entries return for the same (goal, current) views - images and raw camera frames, per-token outputs,
+    fewer current views than cached goals."""
+    from vitvs_b200 import synth
+    fr = [synth.frame_pair(i) for i in range(4)]
+    g, c, d = (torch.from_numpy(np.stack([f[k] for f in fr])).cuda() for k in range(3))
+    ref = eng.frame_pairs_to_twist(g, c, d, want_match=True)
+    eng.set_goal(g)
+    out = eng.current_to_twist(c, d, want_match=True)
+    torch.cuda.synchronize()
+    for k in ("twist", "n_selected", "mean_sim_sel", "nn1", "nn2", "sim1", "sel_tok", "uv", "uv_star"):
+        assert torch.equal(out[k], ref[k]), k
+    out2 = eng.current_to_twist(c[:2], d[:2])       # a prefix of the cached goals
+    assert torch.equal(out2["twist"], ref["twist"][:2])
+    graw, craw, depth = synth.raw_frame_batch(3, distinct=3)
+    graw, craw, depth = (torch.from_numpy(x).cuda() for x in (graw, craw, depth))
+    ref = eng.frames_to_twist(graw, craw, depth)
+    eng.set_goal(graw)
+    out = eng.current_to_twist(craw, depth)
+    assert torch.equal(out["twist"], ref["twist"]) and torch.equal(out["n_selected"], ref["n_selected"])
+    with pytest.raises(Exception):
+        eng.current_to_twist(torch.cat([craw, craw]), torch.cat([depth, depth]))   # more views than cached goals
+
+
+def test_episode_batch_with_cached_goal(eng):
+    """EpisodeBatch(cache_goal=True) walks the same trajectory as the default driver."""
+    tex = _texture()
+    goal = episode.make_pose((0.0, 0.0, -0.61))
+    starts = [episode.make_pose((0.03, -0.02, -0.66), (0.0, 0.0, 0.06)), episode.make_pose((-0.04, 0.03, -0.58), (0.02, -0.03, -0.05))]
+    runs = []
+    for cache in (False, True):
+        eb = episode.EpisodeBatch(eng, tex, goal, starts, min_iterations=5, max_iterations=6, cache_goal=cache)
+        for _ in range(4):
+            eb.step()
+        runs.append(np.stack([e.pose for e in eb.episodes]))
+    assert np.array_equal(runs[0], runs[1])

@@ -73,6 +73,8 @@ SYMBOLS = {
     "vvs_resize_frames": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_vp]),
     "vvs_frames_to_twist": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, C.POINTER(PairOut), c_vp]),
     "vvs_frames_to_twist_host": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),
+    "vvs_set_goal": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp]),
+    "vvs_current_to_twist": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, C.POINTER(PairOut), c_vp]),
     "vvs_render_plane": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_f64, c_f64, c_vp, c_i32, c_vp, c_vp, c_vp]),
     "vvs_last_launch_count": (c_i32, [c_vp]),
     "vvs_uses_gram_stencil": (c_i32, [c_vp]),

@@ -186,6 +186,8 @@ struct vvs_ctx {
   size_t big_elems = 0;
   int x_pin_mb = 40;          // MB of the residual stream (its last rows) that every kernel asks L2 to keep; 0 = no hints
   bf16* desc = nullptr;      // unit-norm descriptors
+  bf16* goal_desc = nullptr; // cached-goal mode (vvs_set_goal): unit descriptors of the goal views, [goal_n, T, parts * D]
+  int goal_n = 0;
   size_t desc_elems = 0;
   float* sqn = nullptr;      // [max_images * T]
   float* inv_norm = nullptr; // [max_images * T] inverse norms of the binned descriptors (Gram-stencil matching)
@@ -525,7 +527,7 @@ int match_tail(vvs_ctx* c, int n_pairs, int T, int grid_w, int K, const vvs_matc
 // similarity arg-max + selection on unit-norm bf16 descriptors already in c->desc:
 // goal sets at desc[0 .. n_pairs), current sets at desc[n_pairs .. 2 n_pairs), each [T, dpad].
 int match_on_desc(vvs_ctx* c, int n_pairs, int T, int dpad, int grid_w, int K, const vvs_match_out* out,
-                  cudaStream_t s) {
+                  cudaStream_t s, const bf16* descA = nullptr, const bf16* descB = nullptr) {
   if (static_cast<size_t>(n_pairs) * T > c->match_cap)
     return fail(c, VVS_ERR_STATE, "match workspace too small (raise max_images / max_match_tokens)");
   if (K > c->k_cap || n_pairs > c->max_pairs)
@@ -535,8 +537,8 @@ int match_on_desc(vvs_ctx* c, int n_pairs, int T, int dpad, int grid_w, int K, c
   VVS_CUDA_OK(cudaMemsetAsync(c->col_best, 0, keys * sizeof(unsigned long long), s), &c->err);
   GemmArgs g;
   memset(&g, 0, sizeof(g));
-  g.A = c->desc;
-  g.B = c->desc + static_cast<size_t>(n_pairs) * T * dpad;
+  g.A = descA ? descA : c->desc;                                               // goal sets ...
+  g.B = descB ? descB : c->desc + static_cast<size_t>(n_pairs) * T * dpad;     // ... then current sets
   g.M = T; g.N = T; g.K = dpad; g.lda = dpad; g.ldb = dpad; g.batch = n_pairs;
   g.a_batch_pitch = static_cast<long long>(T) * dpad;
   g.b_batch_pitch = static_cast<long long>(T) * dpad;
@@ -622,6 +624,40 @@ int pairs_forward_match(vvs_ctx* c, const uint8_t* images, int n_pairs, const vv
   if (rc) return rc;
   c->launch_count += 2;
   return match_on_desc(c, n_pairs, c->T, parts * f.dim, c->grid, f.num_pairs, match, s);
+}
+
+// cached-goal mode, goal side: goal views -> tokens -> unit descriptors kept in the handle
+int goal_forward(vvs_ctx* c, const uint8_t* images, int n, cudaStream_t s) {
+  const vvs_config& f = c->cfg;
+  if (c->gram_stencil) return fail(c, VVS_ERR_STATE, "cached-goal mode needs the materialised descriptors (unset VITVS_GRAM)");
+  const int parts = f.use_feature_binning ? 9 : 1;
+  if (!c->goal_desc) {
+    int rc = dev_alloc(c, &c->goal_desc, static_cast<size_t>(c->max_pairs) * c->T * parts * f.dim);
+    if (rc) return rc;
+  }
+  c->goal_n = 0;
+  int rc = forward_tokens(c, images, VVS_IMAGE_U8_HWC, n, f.layer, s);
+  if (rc) return rc;
+  { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
+    rc = launch_descriptors_unit_bf16(c->x, c->goal_desc, c->sqn, n, c->grid, c->grid, f.dim, f.use_feature_binning, s, &c->err); }
+  if (rc) return rc;
+  c->launch_count += 2;
+  c->goal_n = n;
+  return VVS_OK;
+}
+
+// cached-goal mode, current side: current views -> tokens -> unit descriptors -> matches against the cached goal sets
+int current_forward_match(vvs_ctx* c, const uint8_t* images, int n_pairs, const vvs_match_out* match, cudaStream_t s) {
+  const vvs_config& f = c->cfg;
+  int rc = forward_tokens(c, images, VVS_IMAGE_U8_HWC, n_pairs, f.layer, s);
+  if (rc) return rc;
+  { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
+    rc = launch_descriptors_unit_bf16(c->x, c->desc, c->sqn, n_pairs, c->grid, c->grid, f.dim, f.use_feature_binning, s,
+                                      &c->err); }
+  if (rc) return rc;
+  c->launch_count += 2;
+  const int parts = f.use_feature_binning ? 9 : 1;
+  return match_on_desc(c, n_pairs, c->T, parts * f.dim, c->grid, f.num_pairs, match, s, c->goal_desc, c->desc);
 }
 
 // part B: keypoints (workspace) + depth -> twist (+ mean similarity of the selected pairs), workspace outputs
@@ -1057,7 +1093,7 @@ int vvs_destroy(vvs_handle c) {
   for (cudaEvent_t e : c->chunk_events) cudaEventDestroy(e);
   free_resize_axis(&c->rz_w);
   free_resize_axis(&c->rz_h);
-  void* ptrs[] = {c->xb, c->ln_part, c->pe_w, c->pe_b, c->cls, c->pos, c->pos_prime, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
+  void* ptrs[] = {c->goal_desc, c->xb, c->ln_part, c->pe_w, c->pe_b, c->cls, c->pos, c->pos_prime, c->x, c->h, c->big, c->desc, c->sqn, c->row_best, c->col_best,
                   c->inv_norm, c->nn1, c->nn2, c->sim1, c->cand, c->mean_sim1, c->n_cand, c->n_sel, c->flags, c->mean_sel,
                   c->sel_tok, c->sel_sim, c->uv_star, c->uv, c->twist, c->stage_img, c->stage_depth, c->land_frames[0], c->land_frames[1],
                   c->land_depth[0], c->land_depth[1],
@@ -1433,6 +1469,46 @@ int vvs_frames_to_twist(vvs_handle c, const uint8_t* goal, const uint8_t* cur, c
   rc = vvs_frame_pairs_to_twist(c, c->stage_img, c->stage_img + n_pairs * img_bytes, depth, n_pairs, out, stream);
   c->launch_count += resize_launches;
   return rc;
+}
+
+int vvs_set_goal(vvs_handle c, const uint8_t* goal, int32_t n, int32_t from_frames, vvs_stream stream) {
+  if (!c || !goal) return fail(c, VVS_ERR_INVALID, "vvs_set_goal: null argument");
+  if (n < 1 || n > c->max_pairs) return fail(c, VVS_ERR_INVALID, "vvs_set_goal: n outside [1, max_images/2]");
+  DeviceGuard dg(c);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  WorkspaceOrder wo(c, s);
+  c->launch_count = 0;
+  const uint8_t* images = goal;
+  if (from_frames) {
+    int rc = ensure_frontend(c);
+    if (rc) return rc;
+    if ((rc = resize_frames(c, goal, n, c->stage_img, s))) return rc;
+    images = c->stage_img;
+  }
+  return goal_forward(c, images, n, s);
+}
+
+int vvs_current_to_twist(vvs_handle c, const uint8_t* cur, const uint16_t* depth, int32_t n_pairs, int32_t from_frames,
+                         const vvs_pair_out* out, vvs_stream stream) {
+  if (!c || !cur || !depth) return fail(c, VVS_ERR_INVALID, "vvs_current_to_twist: null argument");
+  if (!out || !out->twist) return fail(c, VVS_ERR_INVALID, "out->twist is required");
+  if (n_pairs < 1 || n_pairs > c->goal_n)
+    return fail(c, VVS_ERR_STATE, "vvs_current_to_twist: n_pairs exceeds the goal views set by vvs_set_goal");
+  DeviceGuard dg(c);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  WorkspaceOrder wo(c, s);
+  c->launch_count = 0;
+  const uint8_t* images = cur;
+  if (from_frames) {
+    int rc = ensure_frontend(c);
+    if (rc) return rc;
+    if ((rc = resize_frames(c, cur, n_pairs, c->stage_img, s))) return rc;
+    images = c->stage_img;
+  }
+  int rc = current_forward_match(c, images, n_pairs, &out->match, s);
+  if (rc) return rc;
+  if ((rc = pairs_control(c, depth, n_pairs, out->mean_sim_sel != nullptr, s))) return rc;
+  return copy_pair_results(c, n_pairs, out, s);
 }
 
 int vvs_frames_to_twist_host(vvs_handle c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth,

@@ -373,6 +373,44 @@ class Engine:
         self._n_img = 2 * B
         return out
 
+    # ------------------------------------------------------------------ cached-goal mode (an extra, SURVEY 7 design note)
+    def _is_frames(self, t: torch.Tensor) -> bool:
+        S = self.cfg.dino_input_size
+        if tuple(t.shape[1:]) == (self.cfg.v_max, self.cfg.u_max, 3):
+            return True
+        assert tuple(t.shape[1:]) == (S, S, 3), "expected [n, S, S, 3] images or [n, v_max, u_max, 3] camera frames"
+        return False
+
+    def set_goal(self, goal: torch.Tensor) -> None:
+        """Run the goal views (uint8 [n, S, S, 3] images or [n, v_max, u_max, 3] camera frames, on this device) through
+        the backbone once and keep their descriptors: the reference recomputes them on every iteration
+        (vitvs_v2.py:482-487) although the goal never changes inside an episode."""
+        goal = goal.contiguous()
+        self._check(self.lib.vvs_set_goal(self._h, _ptr(goal), goal.shape[0], int(self._is_frames(goal)),
+                                          _stream(self.device)), "vvs_set_goal")
+        self._n_img = 0
+
+    def current_to_twist(self, current: torch.Tensor, depth: torch.Tensor, want_match: bool = False,
+                         sel_order: torch.Tensor | None = None) -> dict:
+        """frame_pairs_to_twist / frames_to_twist against the goal views of set_goal (current view i with goal i):
+        only the current views are forwarded; the results are bit-identical to the pair call."""
+        B = current.shape[0]
+        K = self.cfg.num_pairs
+        current, depth = current.contiguous(), depth.contiguous()
+        out = dict(twist=torch.empty(B, 6, dtype=torch.float64, device=self.device),
+                   n_selected=torch.empty(B, dtype=torch.int32, device=self.device),
+                   mean_sim_sel=torch.empty(B, dtype=torch.float32, device=self.device))
+        po = _lib.PairOut(twist=out["twist"].data_ptr(), n_selected=out["n_selected"].data_ptr(),
+                          mean_sim_sel=out["mean_sim_sel"].data_ptr())
+        if want_match or sel_order is not None:
+            bufs, mo = self._match_buffers(B, self.tokens, K, sel_order)
+            po.match = mo
+            out.update(bufs)
+        self._check(self.lib.vvs_current_to_twist(self._h, _ptr(current), _ptr(depth), B, int(self._is_frames(current)),
+                                                  C.byref(po), _stream(self.device)), "vvs_current_to_twist")
+        self._n_img = B
+        return out
+
     def frames_to_twist_host(self, goal_frames: torch.Tensor, current_frames: torch.Tensor, depth: torch.Tensor,
                              twist_out: torch.Tensor, n_selected_out: torch.Tensor | None = None,
                              mean_sim_out: torch.Tensor | None = None, wait: bool = True) -> None:

@@ -210,8 +210,12 @@ class EpisodeBatch:
 
     def __init__(self, engine, texture_u8, goal_pose: np.ndarray, start_poses, dt: float = 1.0,
                  min_iterations: int = 300, max_iterations: int = 2000, cfg: ServoConfig | None = None,
-                 random_selection: bool = False, selection_seed: int = 121):
+                 random_selection: bool = False, selection_seed: int = 121, cache_goal: bool = False):
         self.engine = engine
+        # cache_goal: the goal view's descriptors are computed once (Engine.set_goal) and every iteration forwards only
+        # the current frames - same twists bit for bit, about half the work.  The reference recomputes them each time
+        # (vitvs_v2.py:482-487); False keeps its work per iteration.
+        self.cache_goal = cache_goal
         self.cfg = cfg or engine.cfg
         # random_selection: the reference's choice of key-points - num_pairs mutual nearest neighbours drawn with
         # torch.randperm (vitvs_v2.py:139-141; main() seeds torch with 121, :1397) - handed to the fused call as a
@@ -230,6 +234,8 @@ class EpisodeBatch:
             e.initial_error_translation, e.initial_error_rotation = end_error(e.pose, self.goal_pose)
         # the goal view never changes: rendered once (the reference loads goalrgb.jpg once, vitvs_v2.py:255)
         self.goal_frame, _ = engine.render_plane(self.texture, torch.from_numpy(self.goal_pose[None]))
+        if cache_goal:
+            engine.set_goal(self.goal_frame.expand(len(self.episodes), -1, -1, -1).contiguous())
 
     # -- vitvs_v2.py:329-343
     def _update_ema(self, e: Episode, i: int, v: float) -> float:
@@ -267,13 +273,15 @@ class EpisodeBatch:
         n = len(live)
         poses = torch.from_numpy(np.stack([e.pose for e in live]))
         frames, depth = self.engine.render_plane(self.texture, poses)
-        goal = self.goal_frame.expand(n, -1, -1, -1).contiguous()
+        order = None
         if self.random_selection:
             T = self.engine.tokens
             order = torch.stack([torch.randperm(T, generator=self._sel_gen) for _ in range(n)]).to(torch.int32)
-            out = self.engine.frames_to_twist(goal, frames, depth, sel_order=order)
+        if self.cache_goal:      # every cached goal set is the same view: the first n of them serve any n live episodes
+            out = self.engine.current_to_twist(frames, depth, sel_order=order)
         else:
-            out = self.engine.frames_to_twist(goal, frames, depth)
+            goal = self.goal_frame.expand(n, -1, -1, -1).contiguous()
+            out = self.engine.frames_to_twist(goal, frames, depth, sel_order=order)
         twist = out["twist"].cpu().numpy()
         n_sel = out["n_selected"].cpu().numpy()
         mv = self.cfg.max_velocity
