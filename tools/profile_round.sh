@@ -5,5 +5,5 @@ CMD="python bench.py --steps 2 --warmup 3 --fast"
 timeout 600 $CMD > gpurun_out/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
 timeout 600 $CMD > gpurun_out/plain2.log 2>&1 &&
-timeout 1500 ncu --set full --clock-control none --import-source on -k regex:"gemm_tc|attention|layernorm|descriptors_unit|im2col" -s 130 -c 12 -f -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
+timeout 1500 ncu --set full --clock-control none --import-source on -k regex:"gemm_tc|attention_ts|descriptors_unit|im2col_kernel" -s 119 -c 14 -f -o gpurun_out/prof $CMD > gpurun_out/ncu_full.log 2>&1
 tail -2 gpurun_out/ncu_launches.log; tail -2 gpurun_out/ncu_full.log; ls -la gpurun_out/prof.ncu-rep gpurun_out/launches.csv
