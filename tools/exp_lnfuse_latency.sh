@@ -1,4 +1,4 @@
-# gpurun -- 'bash tools/exp_lnfuse4.sh': folded LayerNorm A/B on latency (single pair, ViT-B and ViT-S) and on the other configs
+# gpurun -- 'bash tools/exp_lnfuse_latency.sh': folded LayerNorm A/B on latency (single pair, ViT-B and ViT-S) and on the other configs
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests/test_gpu_kernels.py tests/test_gpu_bench_config.py -q -x -p no:cacheprovider 2>&1 | tail -2
 for f in 0 1 0 1; do

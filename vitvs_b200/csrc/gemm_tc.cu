@@ -349,13 +349,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         if (t >= total_tiles) return;
         const int tb = t / tiles_per_batch, tr = t - tb * tiles_per_batch;
         const int trow = ((tr / p.n_tiles) * NCTA + static_cast<int>(slot)) * BM + quarter * 32 + lane;
-#ifdef VVS_LNEXP_NOSTATS   // timing experiment only (wrong values): no statistics fetch
-        ln_a_next = 1.0f + p.ln_eps;
-        ln_c_next = p.ln_eps;
-        if (false) {
-#else
         if (trow < p.M) {
-#endif
           const float4* pp = reinterpret_cast<const float4*>(p.ln_part_in + (static_cast<size_t>(tb) * p.M + trow) * p.num_kb);
           float s1 = 0.f, s2 = 0.f;
 #pragma unroll 4
@@ -573,11 +567,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             if (live) {
 #pragma unroll
               for (int q = 0; q < 8; ++q) {
-#ifdef VVS_LNEXP_NOCS       // timing experiment only (wrong values): no colsum term
-                const float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
-#else
                 const float4 cs = ld_shared_v4f(colop_s + (BN + c * 32 + q * 4) * 4);
-#endif
                 bq[q] = make_float4(fmaf(ln_c, cs.x, bq[q].x), fmaf(ln_c, cs.y, bq[q].y), fmaf(ln_c, cs.z, bq[q].z),
                                     fmaf(ln_c, cs.w, bq[q].w));
               }
