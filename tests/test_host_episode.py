@@ -171,6 +171,43 @@ def test_random_selection_hands_a_seeded_permutation_to_the_fused_call():
     assert not torch.equal(orders[0][0], orders[0][1])
 
 
+def test_cache_goal_sets_the_goal_once_and_forwards_only_current_frames():
+    """EpisodeBatch(cache_goal=True): one Engine.set_goal call with one goal view per episode at construction, then
+    Engine.current_to_twist per iteration (never frames_to_twist), the random-selection list still handed over, and the
+    same trajectory as the default driver."""
+    class _CachingEngine(_IdealEngine):
+        def __init__(self, *a, **k):
+            super().__init__(*a, **k)
+            self.goal_sets, self.current_calls, self.pair_calls = [], 0, 0
+
+        def set_goal(self, goal):
+            self.goal_sets.append(tuple(goal.shape))
+
+        def current_to_twist(self, cur, depth, want_match=False, sel_order=None):
+            self.current_calls += 1
+            return _IdealEngine.frames_to_twist(self, None, cur, depth, want_match, sel_order)
+
+        def frames_to_twist(self, *a, **k):
+            self.pair_calls += 1
+            return super().frames_to_twist(*a, **k)
+
+    goal = episode.make_pose((0, 0, -0.61))
+    starts = [episode.make_pose((0.05, 0.0, -0.7)), episode.make_pose((0.0, 0.03, -0.6)), episode.make_pose((0.02, 0.01, -0.65))]
+    poses = []
+    for cache in (False, True):
+        eng = _CachingEngine(goal)
+        b = episode.EpisodeBatch(eng, np.zeros((4, 4, 3), np.uint8), goal, starts, cache_goal=cache, random_selection=True)
+        for _ in range(5):
+            b.step()
+        poses.append(np.stack([e.pose for e in b.episodes]))
+        if cache:
+            assert eng.goal_sets == [(3, 4, 4, 3)] and eng.current_calls == 5 and eng.pair_calls == 0
+            assert eng.last_order.shape == (3, 484)
+        else:
+            assert eng.goal_sets == [] and eng.current_calls == 0 and eng.pair_calls == 5
+    assert np.array_equal(poses[0], poses[1])
+
+
 def test_velocity_clip():
     goal = episode.make_pose((0, 0, -0.61))
     eng = _IdealEngine(goal, gain=50.0)
