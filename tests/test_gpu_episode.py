@@ -135,14 +135,19 @@ def test_cached_goal_matches_pair_call(eng):
     torch.cuda.synchronize()
     for k in ("twist", "n_selected", "mean_sim_sel", "nn1", "nn2", "sim1", "sel_tok", "uv", "uv_star"):
         assert torch.equal(out[k], ref[k]), k
+    for rep in range(4):                            # eager, graph capture, graph replays
+        o = eng.current_to_twist(c, d)
+        assert torch.equal(o["twist"], ref["twist"]) and torch.equal(o["n_selected"], ref["n_selected"]), rep
+        assert torch.equal(o["mean_sim_sel"], ref["mean_sim_sel"]), rep
     out2 = eng.current_to_twist(c[:2], d[:2])       # a prefix of the cached goals
     assert torch.equal(out2["twist"], ref["twist"][:2])
     graw, craw, depth = synth.raw_frame_batch(3, distinct=3)
     graw, craw, depth = (torch.from_numpy(x).cuda() for x in (graw, craw, depth))
     ref = eng.frames_to_twist(graw, craw, depth)
     eng.set_goal(graw)
-    out = eng.current_to_twist(craw, depth)
-    assert torch.equal(out["twist"], ref["twist"]) and torch.equal(out["n_selected"], ref["n_selected"])
+    for rep in range(3):
+        out = eng.current_to_twist(craw, depth)
+        assert torch.equal(out["twist"], ref["twist"]) and torch.equal(out["n_selected"], ref["n_selected"]), rep
     with pytest.raises(Exception):
         eng.current_to_twist(torch.cat([craw, craw]), torch.cat([depth, depth]))   # more views than cached goals
 

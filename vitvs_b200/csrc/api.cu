@@ -231,7 +231,8 @@ struct vvs_ctx {
   cudaStream_t copy_stream = nullptr;   // depth H2D overlaps the forward pass (depth is only read by the IBVS stage)
   cudaEvent_t depth_ready = nullptr;
   // execA: images (workspace) -> tokens -> descriptors -> matches;  execB: depth (workspace) -> twist
-  struct GraphEntry { int n_pairs; int want_mean; cudaGraphExec_t execA; cudaGraphExec_t execB; int launchesA; int launches; };
+  // mode 0: goal + current views (pairs_forward_match); mode 1: current views against the cached goal descriptors
+  struct GraphEntry { int n_pairs; int want_mean; cudaGraphExec_t execA; cudaGraphExec_t execB; int launchesA; int launches; int mode; };
   std::vector<cudaEvent_t> chunk_events;   // host pipeline: [2 * chunk] frames landed / depth landed
   int host_chunks = 0;                     // sub-batches of a host-buffer call (H2D of chunk j+1 under the compute of chunk j);
                                            // 0 = default: see host_pipeline
@@ -713,13 +714,14 @@ int pairs_to_twist(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const ui
 // (launch gaps are ~10 % of a 64-pair step when launched eagerly).  The first call per batch size runs eagerly
 // (lazy function attributes), the second is captured - on the handle's own stream, which executes nothing, so
 // the caller's stream may be the legacy default one.  Returns null when graphs are off / unavailable.
-const vvs_ctx::GraphEntry* graphs_for(vvs_ctx* c, int n_pairs, bool want_mean) {
+const vvs_ctx::GraphEntry* graphs_for(vvs_ctx* c, int n_pairs, bool want_mean, int mode = 0) {
   if (!c->graphs_enabled || c->prof_on) return nullptr;
   for (auto& g : c->graphs)
-    if (g.n_pairs == n_pairs && g.want_mean == (want_mean ? 1 : 0)) return &g;
-  const bool warmed = std::find(c->eager_calls.begin(), c->eager_calls.end(), n_pairs) != c->eager_calls.end();
+    if (g.n_pairs == n_pairs && g.want_mean == (want_mean ? 1 : 0) && g.mode == mode) return &g;
+  const int warm_key = n_pairs | (mode << 20);
+  const bool warmed = std::find(c->eager_calls.begin(), c->eager_calls.end(), warm_key) != c->eager_calls.end();
   if (!warmed) {
-    c->eager_calls.push_back(n_pairs);
+    c->eager_calls.push_back(warm_key);
     return nullptr;
   }
   if (c->graphs.size() >= 16) return nullptr;
@@ -734,8 +736,9 @@ const vvs_ctx::GraphEntry* graphs_for(vvs_ctx* c, int n_pairs, bool want_mean) {
       break;
     }
     if (part == 0) c->launch_count = 0;
-    const int rc = part == 0 ? pairs_forward_match(c, c->stage_img, n_pairs, nullptr, cs)
-                             : pairs_control(c, c->stage_depth, n_pairs, want_mean, cs);
+    const int rc = part == 1   ? pairs_control(c, c->stage_depth, n_pairs, want_mean, cs)
+                   : mode == 0 ? pairs_forward_match(c, c->stage_img, n_pairs, nullptr, cs)
+                               : current_forward_match(c, c->stage_img, n_pairs, nullptr, cs);
     if (part == 0) launches_a = c->launch_count;
     const cudaError_t e = cudaStreamEndCapture(cs, &graph);
     ok = rc == VVS_OK && e == cudaSuccess && graph && cudaGraphInstantiate(&exec[part], graph, 0) == cudaSuccess;
@@ -748,7 +751,7 @@ const vvs_ctx::GraphEntry* graphs_for(vvs_ctx* c, int n_pairs, bool want_mean) {
     cudaGetLastError();
     return nullptr;
   }
-  c->graphs.push_back({n_pairs, want_mean ? 1 : 0, exec[0], exec[1], launches_a, c->launch_count});
+  c->graphs.push_back({n_pairs, want_mean ? 1 : 0, exec[0], exec[1], launches_a, c->launch_count, mode});
   return &c->graphs.back();
 }
 
@@ -1499,15 +1502,35 @@ int vvs_current_to_twist(vvs_handle c, const uint8_t* cur, const uint16_t* depth
   WorkspaceOrder wo(c, s);
   c->launch_count = 0;
   const uint8_t* images = cur;
+  int rc;
   if (from_frames) {
-    int rc = ensure_frontend(c);
-    if (rc) return rc;
+    if ((rc = ensure_frontend(c))) return rc;
     if ((rc = resize_frames(c, cur, n_pairs, c->stage_img, s))) return rc;
     images = c->stage_img;
   }
-  int rc = current_forward_match(c, images, n_pairs, &out->match, s);
-  if (rc) return rc;
-  if ((rc = pairs_control(c, depth, n_pairs, out->mean_sim_sel != nullptr, s))) return rc;
+  const int front_launches = c->launch_count;
+  // as in vvs_frame_pairs_to_twist: the per-token match outputs launch eagerly, everything else replays two graphs
+  const vvs_match_out& m = out->match;
+  const bool wants_match = m.nn1 || m.nn2 || m.sim1 || m.candidate || m.mean_sim1 || m.n_candidates || m.n_selected ||
+                           m.flags || m.sel_tok || m.sel_sim || m.uv_star || m.uv || m.sel_order;
+  const bool want_mean = out->mean_sim_sel != nullptr;
+  const vvs_ctx::GraphEntry* g = wants_match ? nullptr : graphs_for(c, n_pairs, want_mean, 1);
+  if (g) {
+    const size_t img_bytes = static_cast<size_t>(c->cfg.image_size) * c->cfg.image_size * 3;
+    const size_t depth_bytes = static_cast<size_t>(c->cfg.frame_width) * c->cfg.frame_height * sizeof(uint16_t);
+    if (images != c->stage_img)
+      VVS_CUDA_OK(cudaMemcpyAsync(c->stage_img, images, n_pairs * img_bytes, cudaMemcpyDeviceToDevice, s), &c->err);
+    if (depth != c->stage_depth)
+      VVS_CUDA_OK(cudaMemcpyAsync(c->stage_depth, depth, n_pairs * depth_bytes, cudaMemcpyDeviceToDevice, s), &c->err);
+    VVS_CUDA_OK(cudaGraphLaunch(g->execA, s), &c->err);
+    VVS_CUDA_OK(cudaGraphLaunch(g->execB, s), &c->err);
+    c->launch_count = front_launches + g->launches;
+    return copy_pair_results(c, n_pairs, out, s);
+  }
+  c->launch_count = 0;
+  if ((rc = current_forward_match(c, images, n_pairs, &out->match, s))) return rc;
+  if ((rc = pairs_control(c, depth, n_pairs, want_mean, s))) return rc;
+  c->launch_count += front_launches;
   return copy_pair_results(c, n_pairs, out, s);
 }
 
