@@ -81,10 +81,18 @@ struct Cfg {
   // one 32-row x 128-byte slab per epilogue warp (transpose buffer of the TMA stores); EPI_RESID_LN_F32 has two: the
   // old residual values of chunk i + 1 land in one (TMA load) while chunk i is updated in place in the other
   static constexpr uint32_t kSlabsPerWarp = (EPI == EPI_RESID_LN_F32) ? 2 : 1;
-  static constexpr uint32_t kStagingBytes = 8 * 4096 * kSlabsPerWarp;
+  static constexpr uint32_t kSlabWarps = (BN == 64) ? 4 : 8;   // 64-wide tiles: only the warps of half 0 write slabs
+  static constexpr uint32_t kStagingBytes = kSlabWarps * 4096 * kSlabsPerWarp;
   static constexpr uint32_t kBarrierBytes = 512;
-  static constexpr uint32_t kRingBudget = 192 * 1024 - (kStagingBytes - 8 * 4096);   // what the extra slabs leave to the ring
-  static constexpr int kStages = (kRingBudget / kStageBytes) < 6 ? static_cast<int>(kRingBudget / kStageBytes) : 6;
+  static constexpr uint32_t kRingBudget = 224 * 1024 - kStagingBytes;   // what the slabs leave to the operand ring
+  // 64-wide tiles serve single-pair problems: one K loop per CTA whose pace is the round trip of a stage (TMA issue ->
+  // operands landed -> MMA -> commit -> producer) divided by the stages in flight; the big tiles are tensor-bound with six
+#ifndef VVS_STAGES64
+#define VVS_STAGES64 8
+#endif
+  static constexpr int kMaxStages = (BN == 64) ? VVS_STAGES64 : 6;
+  static constexpr int kStages =
+      (kRingBudget / kStageBytes) < kMaxStages ? static_cast<int>(kRingBudget / kStageBytes) : kMaxStages;
   // per-tile column operands (bias / gamma / colsum of the tile's BN columns): read from shared memory by the chunk
   // loops, so that no global-load latency sits between an accumulator chunk and its arithmetic
   static constexpr uint32_t kColopBytes = 2 * BN * 4;
@@ -280,6 +288,13 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     if (pair_rank == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(BM * C::kPair, BN, false);
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
+      // Operand descriptors: only the 14-bit start-address field of the low word changes from one MMA to the next
+      // (stage and 32-byte k step; the ring ends below 256 KB, so the field never carries).  Built once and advanced by
+      // one 32-bit add per operand - rebuilding them from the address cost eight dependent uniform-datapath instructions
+      // per MMA, which is what paces the K loop of the small tiles (four 128 x 64 x 16 MMAs of 32 clk each per k-block).
+      const uint64_t desc0 = umma_smem_desc(smem_u32(smem), 16, 1024);
+      const uint32_t desc_hi = static_cast<uint32_t>(desc0 >> 32);
+      const uint32_t a_lo0 = static_cast<uint32_t>(desc0), b_lo0 = a_lo0 + (C::kABytes >> 4);
       for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
@@ -287,12 +302,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem + stage * C::kStageBytes);
-          const uint32_t b_addr = a_addr + C::kABytes;
+          const uint32_t a_lo = a_lo0 + stage * (C::kStageBytes >> 4), b_lo = b_lo0 + stage * (C::kStageBytes >> 4);
           if (lane == 0) {
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
-              const uint64_t da = umma_smem_desc(a_addr + k * 32, 16, 1024), db = umma_smem_desc(b_addr + k * 32, 16, 1024);
+              const uint64_t da = pack_u64(a_lo + 2 * k, desc_hi), db = pack_u64(b_lo + 2 * k, desc_hi);
               if constexpr (NCTA >= 2) umma_bf16_2sm(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
               else umma_bf16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
             }

@@ -458,6 +458,11 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t 
   d |= static_cast<uint64_t>(2) << 61;
   return d;
 }
+__device__ __forceinline__ uint64_t pack_u64(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
 // Instruction descriptor (32-bit) for kind::f16: D fp32, A/B bf16, dense, no negate.
 //   [4,6) D format (1 = F32)  [7,10) A format (1 = BF16)  [10,13) B format (1 = BF16)
 //   bit 15 A major (0 = K)    bit 16 B major (0 = K, 1 = MN)  [17,23) N >> 3   [24,29) M >> 4
