@@ -21,20 +21,21 @@ void set_error(std::string* slot, const std::string& msg) {
 }
 
 bool pdl_for_rows(long long rows, int dim) {
-  // Measured on B200, graph replay.  64 pairs of ViT-B: 14.04 ms with PDL vs 13.83 ms without - the step runs under the
-  // power cap, where idle gaps between kernels are paid back as clock boost.  A single pair (970 rows, ~70 kernels of a
-  // few microseconds each) is launch-latency-bound: the next kernel's prologue (barrier init, TMEM allocation, descriptor
-  // prefetch) runs under the previous kernel's tail and the gaps between kernels halve (2.1 -> 1.0 us).  Round 1 found
-  // PDL slower for ViT-B; the cause was the attention kernel, whose early-resident CTAs packed four to an SM
-  // (attention_ts.cu: a small grid now asks to be alone on its SM).  p50 of one pair with / without: ViT-S 0.538 / -,
-  // ViT-B 0.734 / 0.798, ViT-L 0.858 / 0.930, ViT-g 1.162 / 1.163 ms.  Hence: small batches, every width.
+  // Programmatic dependent launch for every forward pass (VITVS_PDL=0: never).  Measured on B200, graph replay.  A single
+  // pair (970 rows, ~70 kernels of a few microseconds) is launch-latency-bound: the next kernel's prologue (barrier init,
+  // TMEM allocation, descriptor prefetch) runs under the previous kernel's tail and the gaps between kernels halve
+  // (2.1 -> 1.0 us): p50 of one pair with / without - ViT-B 0.734 / 0.798 ms, ViT-L 0.858 / 0.930, ViT-g 1.162 / 1.163.
+  // Round 1 had found PDL slower for ViT-B; the cause was the attention kernel, whose early-resident CTAs packed four
+  // to an SM (attention_ts.cu: a small grid now asks to be alone on its SM).  Larger batches gain less and never lose:
+  // ViT-B pairs per call 4 / 8 / 16 / 32 / 64: 1.171 -> 1.143, 1.914 -> 1.810, 3.420 -> 3.368, 6.605 -> 6.543,
+  // 12.55 -> 12.45 ms per step (round 1's 14.04 against 13.83 at 64 pairs predates the attention fix).
+  (void)rows;
   (void)dim;
   static const int mode = []() {
     const char* e = getenv("VITVS_PDL");
     return !e ? -1 : (e[0] == '1' ? 1 : 0);
   }();
-  if (mode >= 0) return mode == 1;
-  return rows <= 4096;
+  return mode != 0;
 }
 
 namespace {
