@@ -15,6 +15,16 @@
 //   TMEM: two accumulators of BN columns (double buffered: epilogue of tile i overlaps MMA of tile i+1)
 // Tiles are ordered N-fastest so the CTAs running at one time share A row-panels and the whole weight
 // matrix through the 126 MB L2.
+//
+// Epilogue protocol (every variant): the tile's column operands (bias, gamma / colsum) are staged in shared memory by
+// the 256 epilogue threads between two named barriers, fetched one tile ahead; a warp hands the accumulator back to the
+// MMA warp as soon as its last chunk sits in registers (fence-free arrive: the tcgen05 fences order the TMEM accesses);
+// outputs leave through per-warp swizzled slabs and TMA stores / reduce-adds.
+// LayerNorm folded into the GEMMs around it (EPI_*_LN_*, dino_patch/block.py:90-95): the producers of the residual
+// stream (patch embedding, attn.proj, mlp.fc2) also write bf16(x) and per-64-column (sum, sum of squares) partials;
+// the consumers (qkv, fc1 / w12) multiply the raw rows by W diag(gamma) and apply rstd (acc - mean colsum) + b'.
+// Tile regimes: mixed clusters / pairs of 256 x BN for the batched step, single CTAs of 128 x 128 and 128 x 64 for the
+// launch-bound problems of a single frame pair (same accumulation order over K: results do not depend on the regime).
 #include <cuda.h>
 
 #include <algorithm>
