@@ -437,7 +437,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 
     mbar_wait(&s_full[t], nblk & 1);      // PV(nblk - 1) has completed
     tc_fence_after();
-    const int q = (qt0 + t) * kBQ + row;
+    [[maybe_unused]] const int q = (qt0 + t) * kBQ + row;
     const float inv = 1.0f / l_run;
 #if VVS_ATT_TMA_STORE
     // The tile's Q buffer is free (every S MMA has completed): the normalised bf16 rows go there in the 128-byte

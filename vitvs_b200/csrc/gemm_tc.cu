@@ -114,7 +114,7 @@ struct Cfg {
 // q = exp2(P(|x|)): P is a degree-6 fit of log2(0.5 erfc(z / sqrt 2)) on z in [0, 9] (q(9) ~ 1e-19, clamp beyond),
 // evaluated in fp32: |gelu - exact| <= 6e-7 over [-12, 12] (checked against scipy erf; the bf16 output ulp at
 // |x| ~ 1 is 4e-3).  1 MUFU (ex2) + 10 FMA/ALU instructions instead of erff()'s ~30.
-__device__ __forceinline__ float gelu_erf(float x) {
+[[maybe_unused]] __device__ __forceinline__ float gelu_erf(float x) {
   const float z = fminf(fabsf(x), 9.0f);
   float p = fmaf(3.314364715e-05f, z, -7.678688386e-04f);
   p = fmaf(p, z, 8.068593625e-03f);
@@ -487,7 +487,6 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 #pragma unroll
         for (int i = 0; i < NP; ++i) {
           const int c = half * NP + i;
-          const int tcol = n_blk * BN + c * 32;                 // column in the interleaved N space
           uint32_t r1[32], r2[32];
           tmem_ld32(t_acc + c * 32, r1);
           tmem_ld32(t_acc + BN / 2 + c * 32, r2);

@@ -53,7 +53,6 @@ __device__ __forceinline__ float cyclic_distance(int dr, int dc) {
 
 __global__ void __launch_bounds__(1024) select_kernel(const SelectArgs a, unsigned long long* trace) {
   trace_begin(trace);
-  __shared__ unsigned long long s_u64[32];
   __shared__ float s_f32[32];
   __shared__ double s_f64[32];
   __shared__ int s_i32[32];
