@@ -298,7 +298,8 @@ def account_trace(trace):
         if i + 1 < len(trace):
             g = (trace[i + 1][1] - e) / 1e6
             if trace[i + 1][0] == "sim_gemm":
-                memset_gap += g          # two memset nodes (arg-max keys) sit in this gap
+                memset_gap += g          # the gap in front of the similarity GEMM (held two memset nodes until the arg-max
+                                         # keys were cleared inside the descriptor launch)
             else:
                 gaps += g
     span = (trace[-1][2] - trace[0][1]) / 1e6
@@ -553,7 +554,7 @@ def run_ours(args):
                 "sm_mhz_timed": clocks.get("sm_mhz"), "sm_mhz_profile": clocks_prof.get("sm_mhz"),
                 "what": "per_class_ms / gaps_ms: one traced replay of the step's two CUDA graphs (%globaltimer stamped by the "
                         "first and last warp of every kernel), taken right after the timed loop; copies_memsets_ms: the gap "
-                        "holding the two memset nodes; outside_graphs_ms: ms_per_step minus the traced span (3 D2D input "
+                        "in front of the similarity GEMM (no memset node left in it); outside_graphs_ms: ms_per_step minus the traced span (3 D2D input "
                         "copies, 3 result copies, graph launch latency).  profiled_*: the event-bracketed eager loop the "
                         "`kernels` table comes from"})
         traffic, traffic_file = ncu_traffic(dom) if (model_type == "dinov2_vitb14" and B == 64) else (None, None)

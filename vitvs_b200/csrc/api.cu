@@ -529,14 +529,16 @@ int match_tail(vvs_ctx* c, int n_pairs, int T, int grid_w, int K, const vvs_matc
 // similarity arg-max + selection on unit-norm bf16 descriptors already in c->desc:
 // goal sets at desc[0 .. n_pairs), current sets at desc[n_pairs .. 2 n_pairs), each [T, dpad].
 int match_on_desc(vvs_ctx* c, int n_pairs, int T, int dpad, int grid_w, int K, const vvs_match_out* out,
-                  cudaStream_t s, const bf16* descA = nullptr, const bf16* descB = nullptr) {
+                  cudaStream_t s, const bf16* descA = nullptr, const bf16* descB = nullptr, bool keys_cleared = false) {
   if (static_cast<size_t>(n_pairs) * T > c->match_cap)
     return fail(c, VVS_ERR_STATE, "match workspace too small (raise max_images / max_match_tokens)");
   if (K > c->k_cap || n_pairs > c->max_pairs)
     return fail(c, VVS_ERR_STATE, "num_pairs / n_pairs beyond the workspace of this handle");
   const size_t keys = static_cast<size_t>(n_pairs) * T;
-  VVS_CUDA_OK(cudaMemsetAsync(c->row_best, 0, keys * sizeof(unsigned long long), s), &c->err);
-  VVS_CUDA_OK(cudaMemsetAsync(c->col_best, 0, keys * sizeof(unsigned long long), s), &c->err);
+  if (!keys_cleared) {   // (the frame-pair paths clear the keys inside their descriptor launch)
+    VVS_CUDA_OK(cudaMemsetAsync(c->row_best, 0, keys * sizeof(unsigned long long), s), &c->err);
+    VVS_CUDA_OK(cudaMemsetAsync(c->col_best, 0, keys * sizeof(unsigned long long), s), &c->err);
+  }
   GemmArgs g;
   memset(&g, 0, sizeof(g));
   g.A = descA ? descA : c->desc;                                               // goal sets ...
@@ -620,12 +622,15 @@ int pairs_forward_match(vvs_ctx* c, const uint8_t* images, int n_pairs, const vv
     ++c->launch_count;
     return match_tail(c, n_pairs, T, c->grid, f.num_pairs, match, s);
   }
+  if (static_cast<size_t>(n_pairs) * c->T > c->match_cap || n_pairs > c->max_pairs)
+    return fail(c, VVS_ERR_STATE, "match workspace too small for this batch");
   { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
     rc = launch_descriptors_unit_bf16(c->x, c->desc, c->sqn, 2 * n_pairs, c->grid, c->grid, f.dim,
-                                      f.use_feature_binning, s, &c->err); }
+                                      f.use_feature_binning, s, &c->err, c->row_best, c->col_best,
+                                      static_cast<long long>(n_pairs) * c->T); }
   if (rc) return rc;
   c->launch_count += 2;
-  return match_on_desc(c, n_pairs, c->T, parts * f.dim, c->grid, f.num_pairs, match, s);
+  return match_on_desc(c, n_pairs, c->T, parts * f.dim, c->grid, f.num_pairs, match, s, nullptr, nullptr, true);
 }
 
 // cached-goal mode, goal side: goal views -> tokens -> unit descriptors kept in the handle
@@ -653,13 +658,15 @@ int current_forward_match(vvs_ctx* c, const uint8_t* images, int n_pairs, const 
   const vvs_config& f = c->cfg;
   int rc = forward_tokens(c, images, VVS_IMAGE_U8_HWC, n_pairs, f.layer, s);
   if (rc) return rc;
+  if (static_cast<size_t>(n_pairs) * c->T > c->match_cap || n_pairs > c->max_pairs)
+    return fail(c, VVS_ERR_STATE, "match workspace too small for this batch");
   { ProfScope ps(c, VVS_K_DESCRIPTORS, s);
     rc = launch_descriptors_unit_bf16(c->x, c->desc, c->sqn, n_pairs, c->grid, c->grid, f.dim, f.use_feature_binning, s,
-                                      &c->err); }
+                                      &c->err, c->row_best, c->col_best, static_cast<long long>(n_pairs) * c->T); }
   if (rc) return rc;
   c->launch_count += 2;
   const int parts = f.use_feature_binning ? 9 : 1;
-  return match_on_desc(c, n_pairs, c->T, parts * f.dim, c->grid, f.num_pairs, match, s, c->goal_desc, c->desc);
+  return match_on_desc(c, n_pairs, c->T, parts * f.dim, c->grid, f.num_pairs, match, s, c->goal_desc, c->desc, true);
 }
 
 // part B: keypoints (workspace) + depth -> twist (+ mean similarity of the selected pairs), workspace outputs

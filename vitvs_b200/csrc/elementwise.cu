@@ -266,8 +266,11 @@ __global__ void facet_descriptors_f32_kernel(const bf16* __restrict__ qkv, float
 }
 
 // squared L2 norm of every patch token (CLS skipped): one warp per token.
+// zero_a / zero_b (optional): the packed arg-max keys of the matching stage, zero_n entries each, cleared here by the
+// first zero_n tokens - the two memset nodes a frame pair's graph would otherwise carry (2-3 us each at one pair).
 __global__ void token_sqnorm_kernel(const float* __restrict__ x, float* __restrict__ n2, int n_img, int T, int D,
-                                    unsigned long long* trace) {
+                                    unsigned long long* __restrict__ zero_a, unsigned long long* __restrict__ zero_b,
+                                    long long zero_n, unsigned long long* trace) {
   trace_begin(trace);
   const int lane = threadIdx.x & 31;
   const long long tok = blockIdx.x * static_cast<long long>(blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -280,7 +283,13 @@ __global__ void token_sqnorm_kernel(const float* __restrict__ x, float* __restri
     s += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
   }
   s = warp_sum(s);
-  if (lane == 0) n2[tok] = s;
+  if (lane == 0) {
+    n2[tok] = s;
+    if (zero_a != nullptr && tok < zero_n) {
+      zero_a[tok] = 0ull;
+      zero_b[tok] = 0ull;
+    }
+  }
   trace_end(trace);
 }
 
@@ -457,10 +466,16 @@ int launch_facet_descriptors_f32(const bf16* qkv, float* out, int n_img, int hp,
 }
 
 int launch_descriptors_unit_bf16(const float* x, bf16* out, float* sqnorm_scratch, int n_img, int hp, int wp, int D,
-                                 int bin, cudaStream_t s, std::string* err) {
+                                 int bin, cudaStream_t s, std::string* err, unsigned long long* zero_a,
+                                 unsigned long long* zero_b, long long zero_n) {
   const int T = hp * wp;
   const long long toks = static_cast<long long>(n_img) * T;
-  token_sqnorm_kernel<<<static_cast<int>((toks + 7) / 8), 256, 0, s>>>(x, sqnorm_scratch, n_img, T, D, tl_trace_slot);
+  if (zero_a != nullptr && (zero_b == nullptr || zero_n > toks)) {
+    set_error(err, "descriptors: key clearing needs both arrays and at most one entry per token");
+    return VVS_ERR_INVALID;
+  }
+  token_sqnorm_kernel<<<static_cast<int>((toks + 7) / 8), 256, 0, s>>>(x, sqnorm_scratch, n_img, T, D, zero_a, zero_b, zero_n,
+                                                                       tl_trace_slot);
   VVS_CUDA_OK(cudaGetLastError(), err);
   descriptors_unit_bf16_kernel<<<static_cast<int>(toks), 128, 0, s>>>(x, sqnorm_scratch, out, hp, wp, D, bin ? 9 : 1,
                                                                       tl_trace_slot);

@@ -182,8 +182,11 @@ int launch_descriptors_hier_f32(const float* x, float* out, int n_img, int hp, i
 // [n_img, T (+1 with CLS), parts * D] in the reference's channel order (d major, head minor)
 int launch_facet_descriptors_f32(const bf16* qkv, float* out, int n_img, int hp, int wp, int D, int heads, int facet,
                                  int bin, int include_cls, cudaStream_t s, std::string* err);
+// zero_a / zero_b: optional arrays of zero_n (<= n_img * hp * wp) 64-bit words cleared by the same launch (the matching
+// stage's packed arg-max keys)
 int launch_descriptors_unit_bf16(const float* x, bf16* out, float* sqnorm_scratch, int n_img, int hp, int wp, int D,
-                                 int bin, cudaStream_t s, std::string* err);
+                                 int bin, cudaStream_t s, std::string* err, unsigned long long* zero_a = nullptr,
+                                 unsigned long long* zero_b = nullptr, long long zero_n = 0);
 // arbitrary fp32 rows [rows, d] -> unit-norm bf16 rows [rows, dpad] (zero padded)
 int launch_normalize_rows_bf16(const float* in, bf16* out, int rows, int d, int dpad, cudaStream_t s,
                                std::string* err);
