@@ -295,7 +295,9 @@ VVS_API int vvs_dbg_gemm(vvs_handle h, const void* A_bf16, const void* B_bf16, i
 /* The same with a folded-LayerNorm epilogue (csrc/vvs_internal.h EPI_*_LN_*; dino_patch/block.py:90-95 norm1 / norm2):
  * producers (EPI_RESID_LN_F32, EPI_PATCH_LN_F32) also write xb_out = bf16(new x) [M, ldo] and ln_part_out [M, N/64, 2]
  * = (sum, sum of squares) of every 64-column group of the new rows; consumers (EPI_BIAS_LN_BF16, EPI_GELU_LN_BF16,
- * EPI_SWIGLU_LN_BF16) read ln_part_in [M, K/64, 2] and colsum [N] and compute rstd * (acc - mean * colsum) + bias. */
+ * EPI_SWIGLU_LN_BF16) read ln_part_in [M, K/64, 2] and colsum [N] and compute rstd * (acc - mean * colsum) + bias.
+ * EPI_PATCH_LN_F32 fetches its positional rows in 32-row boxes: `pos` must hold T + 1 + 31 rows, the last 31 repeating
+ * the first ones. */
 VVS_API int vvs_dbg_gemm_ln(vvs_handle h, const void* A_bf16, const void* B_bf16, int32_t M, int32_t N, int32_t K,
                     int32_t epilogue, const float* bias, const float* gamma, float* x_f32, void* out_bf16, int32_t ldo,
                     int32_t q_cols, float q_scale, const float* pos, int32_t T, float* ln_part_out, void* xb_out_bf16,

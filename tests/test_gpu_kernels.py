@@ -211,7 +211,8 @@ def test_gemm_patch_ln_producer(eng):
     x = torch.zeros(M, D, device="cuda")
     xb = torch.zeros(M, D, dtype=torch.bfloat16, device="cuda")
     part = torch.zeros(M, D // 64, 2, device="cuda")
-    eng.dbg_gemm_ln(A, B, _lib.EPI_PATCH_LN_F32, bias=bias, x_f32=x, ldo=D, pos=pos, T=T, xb_out=xb, ln_part_out=part)
+    pos_ext = torch.cat([pos, pos[:31]]).contiguous()      # the epilogue fetches 32-row boxes: periodic extension
+    eng.dbg_gemm_ln(A, B, _lib.EPI_PATCH_LN_F32, bias=bias, x_f32=x, ldo=D, pos=pos_ext, T=T, xb_out=xb, ln_part_out=part)
     torch.cuda.synchronize()
     assert torch.equal(x, x_ref) and torch.equal(xb, x.to(torch.bfloat16))
     assert torch.allclose(part, _group_stats(x), rtol=2e-5, atol=1e-4)

@@ -413,7 +413,7 @@ int forward_tokens(vvs_ctx* c, const void* images, int kind, int n_img, int laye
   {
     // A has one zero row per CLS slot, so GEMM row r is residual-stream row r: x = acc + bias + pos'[r % N]
     GemmArgs g = plain_gemm(c->big, c->pe_w, M, D, kPatchKPad, fused ? EPI_PATCH_LN_F32 : EPI_PATCH_F32);
-    g.bias = c->pe_b; g.x_f32 = c->x; g.ldo = D; g.pos = c->pos_prime; g.T = T; g.pin_row0 = pin_row0;
+    g.bias = c->pe_b; g.x_f32 = c->x; g.ldo = D; g.pos = c->pos_prime; g.T = T; g.pos_rows = N + 31; g.pin_row0 = pin_row0;
     g.xb_out = c->xb; g.ln_part_out = c->ln_part;
     g.pdl = 0;   // predecessor (im2col) is not PDL-aware
     if ((rc = gemm(c, g, s, VVS_K_PATCH_GEMM))) return rc;
@@ -965,11 +965,22 @@ int refold_block(vvs_ctx* c, BlockW& w, cudaStream_t s) {
 // pos' depends on patch_embed.proj.bias, cls_token and pos_embed_interp: refreshed whenever one of them is (re)set
 int refresh_pos_prime(vvs_ctx* c, cudaStream_t s) {
   if ((c->emb_mask & 0xE) != 0xE) return VVS_OK;
+  // N rows, extended periodically by 31: the patch-embed epilogue fetches 32-row boxes of it by TMA, and a box that runs
+  // over the end of an image continues with the first rows of the next one
+  constexpr int kWrap = 31;
   if (!c->pos_prime) {
-    int rc = dev_alloc(c, &c->pos_prime, static_cast<size_t>(c->N) * c->cfg.dim);
+    int rc = dev_alloc(c, &c->pos_prime, static_cast<size_t>(c->N + kWrap) * c->cfg.dim);
     if (rc) return rc;
   }
-  return launch_pos_prime(c->pos, c->cls, c->pe_b, c->pos_prime, c->N, c->cfg.dim, s, &c->err);
+  int rc = launch_pos_prime(c->pos, c->cls, c->pe_b, c->pos_prime, c->N, c->cfg.dim, s, &c->err);
+  if (rc) return rc;
+  for (int r = 0; r < kWrap; r += c->N) {   // (N < 31 only for toy grids: copy in pieces of at most N rows)
+    const int rows = std::min(kWrap - r, c->N);
+    VVS_CUDA_OK(cudaMemcpyAsync(c->pos_prime + static_cast<size_t>(c->N + r) * c->cfg.dim, c->pos_prime,
+                                static_cast<size_t>(rows) * c->cfg.dim * sizeof(float), cudaMemcpyDeviceToDevice, s),
+                &c->err);
+  }
+  return VVS_OK;
 }
 }  // namespace
 
@@ -1690,6 +1701,7 @@ int vvs_dbg_gemm_ln(vvs_handle c, const void* A, const void* B, int32_t M, int32
   GemmArgs g = plain_gemm(static_cast<const bf16*>(A), static_cast<const bf16*>(B), M, N, K, epilogue);
   g.bias = bias; g.gamma = gamma; g.x_f32 = x_f32; g.out_bf16 = static_cast<bf16*>(out_bf16); g.ldo = ldo;
   g.q_cols = q_cols; g.q_scale = q_scale; g.pos = pos; g.T = T;
+  g.pos_rows = T + 1 + 31;   // EPI_PATCH_LN_F32: the caller's pos holds the T + 1 rows and their first 31 again
   g.ln_part_out = reinterpret_cast<float2*>(ln_part_out); g.xb_out = static_cast<bf16*>(xb_out);
   g.ln_part_in = reinterpret_cast<const float2*>(ln_part_in); g.colsum = colsum; g.ln_eps = ln_eps;
   return gemm(c, g, static_cast<cudaStream_t>(stream));

@@ -88,9 +88,10 @@ struct Cfg {
   static constexpr uint32_t kBBytes = (BN / kPair) * BK * 2;
   static constexpr uint32_t kStageBytes = kABytes + kBBytes;
   static constexpr uint32_t kTmemCols = 2 * BN;
-  // one 32-row x 128-byte slab per epilogue warp (transpose buffer of the TMA stores); EPI_RESID_LN_F32 has two: the
-  // old residual values of chunk i + 1 land in one (TMA load) while chunk i is updated in place in the other
-  static constexpr uint32_t kSlabsPerWarp = (EPI == EPI_RESID_LN_F32) ? 2 : 1;
+  // one 32-row x 128-byte slab per epilogue warp (transpose buffer of the TMA stores); the epilogues that ADD to rows they
+  // load (EPI_RESID_LN_F32: the old residual values; EPI_PATCH_LN_F32: the positional rows) have two: the operand of
+  // chunk i + 1 lands in one (TMA load) while chunk i is updated in place in the other
+  static constexpr uint32_t kSlabsPerWarp = (EPI == EPI_RESID_LN_F32 || EPI == EPI_PATCH_LN_F32) ? 2 : 1;
   static constexpr uint32_t kSlabWarps = (BN == 64) ? 4 : 8;   // 64-wide tiles: only the warps of half 0 write slabs
   static constexpr uint32_t kStagingBytes = kSlabWarps * 4096 * kSlabsPerWarp;
   static constexpr uint32_t kBarrierBytes = 512;
@@ -193,7 +194,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
-    if constexpr (NCTA == 4) tma_prefetch_desc(&tmB2);
+    if constexpr (NCTA == 4 || EPI == EPI_PATCH_LN_F32) tma_prefetch_desc(&tmB2);
     tma_prefetch_desc(&tmOut);
     for (int s = 0; s < C::kStages; ++s) {
       mbar_init(&full[s], 1);     // pair: only the leader's is used; its expect_tx covers both CTAs' boxes
@@ -203,7 +204,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       mbar_init(&tfull[a], 1);
       mbar_init(&tempty[a], 8 * C::kPair);   // pair: the peer's epilogue warps arrive on the leader's barrier
     }
-    if constexpr (EPI == EPI_RESID_LN_F32)
+    if constexpr (kLnOut)
       for (int a = 0; a < 16; ++a) mbar_init(&xfull[a], 1);
     fence_mbar_init();
   }
@@ -450,12 +451,16 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       }
       // EPI_RESID_LN_F32 adds to x in the SM: the old values of a chunk arrive by TMA in one of this warp's two slabs
       // (the very boxes the store writes back), requested one chunk ahead; chunk 0 here, ahead of the accumulator wait
-      if constexpr (EPI == EPI_RESID_LN_F32) {
+      // (EPI_PATCH_LN_F32: the same machinery fetches the positional rows - tmB2 is the map of pos', extended
+      // periodically by 31 rows so that a slab that runs over the end of an image is still one box)
+      [[maybe_unused]] const CUtensorMap* const xmap = (EPI == EPI_PATCH_LN_F32) ? &tmB2 : &tmOut;
+      [[maybe_unused]] const int xrow0 = (EPI == EPI_PATCH_LN_F32) ? tile_row0 % (p.T + 1) : tile_row0;
+      if constexpr (kLnOut) {
         const int col_first = n_blk * BN + c_begin * 32;
         if (lane == 0 && col_first < p.N && !idle_warp) {
           bulk_wait_read1();                 // slab 0 was last read by the store of the previous tile's chunk NCH - 2
           mbar_expect_tx(&xbar[0], 4096);
-          tma_load_2d_s(stg_s, &tmOut, &xbar[0], col_first, tile_row0, kEvictNormal);
+          tma_load_2d_s(stg_s, xmap, &xbar[0], col_first, xrow0, kEvictNormal);
         }
       }
       mbar_wait(&tfull[acc], acc_phase);
@@ -596,11 +601,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
               }
             }
           }
-          if constexpr (EPI == EPI_RESID_LN_F32) {
+          if constexpr (kLnOut) {
             if (lane == 0 && i + 1 < NCH && col0 + 32 < p.N) {   // the next chunk's old values -> the other slab
               bulk_wait_read0();             // ... which the previous chunk's store has finished reading
               mbar_expect_tx(&xbar[(i + 1) & 1], 4096);
-              tma_load_2d_s(stg_s + ((i + 1) & 1) * 4096, &tmOut, &xbar[(i + 1) & 1], col0 + 32, tile_row0, kEvictNormal);
+              tma_load_2d_s(stg_s + ((i + 1) & 1) * 4096, xmap, &xbar[(i + 1) & 1], col0 + 32, xrow0, kEvictNormal);
             }
           }
           tmem_ld_wait();
@@ -716,15 +721,10 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             // arithmetic of the reduce-add path: one rounding per operation), or acc + bias + pos' (patch embed).
             // They leave three ways: the fp32 slab by TMA store, the bf16 copy the next GEMM multiplies by two 256-bit
             // stores of this thread's row, and the (sum, sum of squares) of every 64-column group for the consumer.
-            const uint32_t slab_s = (EPI == EPI_RESID_LN_F32) ? stg_s + (i & 1) * 4096 : stg_s;
+            const uint32_t slab_s = stg_s + (i & 1) * 4096;
             const uint32_t slab_row_s = slab_s + lane * 128;
-            if constexpr (EPI == EPI_RESID_LN_F32) {
-              mbar_wait(&xbar[i & 1], (xphase >> (i & 1)) & 1u);   // the old values of this chunk have landed
-              xphase ^= 1u << (i & 1);
-            } else {
-              if (lane == 0) bulk_wait_read0();
-              __syncwarp();
-            }
+            mbar_wait(&xbar[i & 1], (xphase >> (i & 1)) & 1u);   // the old values / positional rows of this chunk have landed
+            xphase ^= 1u << (i & 1);
             if ((col0 & 63) == 0) st1a = st1b = st2a = st2b = 0ull;   // a new 64-column group starts
             uint32_t pk[8];
             // four columns at a time: a thread reads and rewrites only its own row of the slab (no cross-lane hazard)
@@ -739,7 +739,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
                 v2 = __fadd_rn(xo.z, __fmul_rn(gq[q].z, __fadd_rn(__uint_as_float(rw[q * 4 + 2]), bq[q].z)));
                 v3 = __fadd_rn(xo.w, __fmul_rn(gq[q].w, __fadd_rn(__uint_as_float(rw[q * 4 + 3]), bq[q].w)));
               } else {
-                const float4 ps = __ldg(reinterpret_cast<const float4*>(pos_row + col0) + q);
+                const float4 ps = ld_shared_v4f(cell);
                 v0 = __uint_as_float(rw[q * 4 + 0]) + bq[q].x + ps.x;
                 v1 = __uint_as_float(rw[q * 4 + 1]) + bq[q].y + ps.y;
                 v2 = __uint_as_float(rw[q * 4 + 2]) + bq[q].z + ps.z;
@@ -872,8 +872,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 template <int BN, int EPI, int NCTA>
 __global__ void __cluster_dims__(NCTA, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ CUtensorMap tmOut, const GemmDev p) {
-  gemm_body<BN, EPI, NCTA>(tmA, tmB, tmB, tmOut, p);
+               const __grid_constant__ CUtensorMap tmAux, const __grid_constant__ CUtensorMap tmOut, const GemmDev p) {
+  gemm_body<BN, EPI, NCTA>(tmA, tmB, tmAux, tmOut, p);   // tmAux: the positional rows of EPI_PATCH_LN_F32 (else unused)
 }
 
 // mixed mode: no compile-time cluster size - the launch supplies {2, preferred 4}
@@ -903,8 +903,8 @@ EncodeTiledFn get_encode_fn(std::string* err) {
 }
 
 template <int BN, int EPI, int NCTA>
-int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const GemmDev& d, int grid,
-               cudaStream_t stream, bool pdl, std::string* err) {
+int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmAux, const CUtensorMap& tmOut,
+               const GemmDev& d, int grid, cudaStream_t stream, bool pdl, std::string* err) {
   using C = Cfg<BN, NCTA, EPI>;
   static PerDeviceOnce once;
   VVS_CUDA_OK(once.run([] {
@@ -912,7 +912,8 @@ int launch_one(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap
                                             static_cast<int>(C::kSmemBytes));
               }),
               err);
-  VVS_CUDA_OK(launch_kernel(gemm_tc_kernel<BN, EPI, NCTA>, grid, kGemmThreads, C::kSmemBytes, stream, pdl, tmA, tmB, tmOut, d),
+  VVS_CUDA_OK(launch_kernel(gemm_tc_kernel<BN, EPI, NCTA>, grid, kGemmThreads, C::kSmemBytes, stream, pdl, tmA, tmB, tmAux, tmOut,
+                            d),
               err);
   return VVS_OK;
 }
@@ -949,21 +950,21 @@ int launch_mixed(const CUtensorMap& tmA, const CUtensorMap& tmB4, const CUtensor
 }
 
 template <int BN, int NCTA>
-int dispatch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmOut, const GemmDev& d,
-                 int grid, cudaStream_t stream, bool pdl, std::string* err) {
+int dispatch_epi(int epi, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmAux, const CUtensorMap& tmOut,
+                 const GemmDev& d, int grid, cudaStream_t stream, bool pdl, std::string* err) {
   switch (epi) {
-    case EPI_BIAS_BF16: return launch_one<BN, EPI_BIAS_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
-    case EPI_GELU_BF16: return launch_one<BN, EPI_GELU_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
-    case EPI_RESID_F32: return launch_one<BN, EPI_RESID_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
-    case EPI_PATCH_F32: return launch_one<BN, EPI_PATCH_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
-    case EPI_SWIGLU_BF16: return launch_one<BN, EPI_SWIGLU_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
-    case EPI_SIM: return launch_one<BN, EPI_SIM, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
-    case EPI_STORE_F32: return launch_one<BN, EPI_STORE_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
-    case EPI_RESID_LN_F32: return launch_one<BN, EPI_RESID_LN_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
-    case EPI_PATCH_LN_F32: return launch_one<BN, EPI_PATCH_LN_F32, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
-    case EPI_BIAS_LN_BF16: return launch_one<BN, EPI_BIAS_LN_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
-    case EPI_GELU_LN_BF16: return launch_one<BN, EPI_GELU_LN_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
-    case EPI_SWIGLU_LN_BF16: return launch_one<BN, EPI_SWIGLU_LN_BF16, NCTA>(tmA, tmB, tmOut, d, grid, stream, pdl, err);
+    case EPI_BIAS_BF16: return launch_one<BN, EPI_BIAS_BF16, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
+    case EPI_GELU_BF16: return launch_one<BN, EPI_GELU_BF16, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
+    case EPI_RESID_F32: return launch_one<BN, EPI_RESID_F32, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
+    case EPI_PATCH_F32: return launch_one<BN, EPI_PATCH_F32, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
+    case EPI_SWIGLU_BF16: return launch_one<BN, EPI_SWIGLU_BF16, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
+    case EPI_SIM: return launch_one<BN, EPI_SIM, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
+    case EPI_STORE_F32: return launch_one<BN, EPI_STORE_F32, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
+    case EPI_RESID_LN_F32: return launch_one<BN, EPI_RESID_LN_F32, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
+    case EPI_PATCH_LN_F32: return launch_one<BN, EPI_PATCH_LN_F32, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
+    case EPI_BIAS_LN_BF16: return launch_one<BN, EPI_BIAS_LN_BF16, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
+    case EPI_GELU_LN_BF16: return launch_one<BN, EPI_GELU_LN_BF16, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
+    case EPI_SWIGLU_LN_BF16: return launch_one<BN, EPI_SWIGLU_LN_BF16, NCTA>(tmA, tmB, tmAux, tmOut, d, grid, stream, pdl, err);
     default: set_error(err, "launch_gemm: unknown epilogue"); return VVS_ERR_INVALID;
   }
 }
@@ -1112,6 +1113,15 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   else if (tma_out)
     rc = make_tmap_out(&tmOut, a.out_bf16, 2, a.N, a.M, a.ldo, 64, 32, err);
   if (rc) return rc;
+  CUtensorMap tmAux = tmB;   // unused unless ...
+  if (a.epilogue == EPI_PATCH_LN_F32) {   // ... the epilogue adds positional rows it fetches by TMA
+    if (!a.pos || a.pos_rows < a.T + 1 + 31) {
+      set_error(err, "launch_gemm: EPI_PATCH_LN_F32 needs pos with T + 1 + 31 rows (periodic extension)");
+      return VVS_ERR_INVALID;
+    }
+    rc = make_tmap_out(&tmAux, a.pos, 4, a.N, a.pos_rows, a.ldo, 32, 32, err);
+    if (rc) return rc;
+  }
   GemmDev d;
   d.M = a.M; d.N = a.N; d.K = a.K; d.batch = a.batch; d.b_batched = b_batched ? 1 : 0;
   d.b_static = (a.b_static && a.pdl) ? 1 : 0;
@@ -1146,13 +1156,13 @@ int launch_gemm(const GemmArgs& a, int num_sms, cudaStream_t stream, std::string
   }
   if (ncta == 2) {
     const int grid = 2 * static_cast<int>(std::min<long long>(tiles, num_sms / 2));
-    if (bn == 256) return dispatch_epi<256, 2>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
-    return dispatch_epi<128, 2>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
+    if (bn == 256) return dispatch_epi<256, 2>(a.epilogue, tmA, tmB, tmAux, tmOut, d, grid, stream, a.pdl != 0, err);
+    return dispatch_epi<128, 2>(a.epilogue, tmA, tmB, tmAux, tmOut, d, grid, stream, a.pdl != 0, err);
   }
   const int grid = static_cast<int>(std::min<long long>(tiles, num_sms));
-  if (bn == 256) return dispatch_epi<256, 1>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
-  if (bn == 64) return dispatch_epi<64, 1>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
-  return dispatch_epi<128, 1>(a.epilogue, tmA, tmB, tmOut, d, grid, stream, a.pdl != 0, err);
+  if (bn == 256) return dispatch_epi<256, 1>(a.epilogue, tmA, tmB, tmAux, tmOut, d, grid, stream, a.pdl != 0, err);
+  if (bn == 64) return dispatch_epi<64, 1>(a.epilogue, tmA, tmB, tmAux, tmOut, d, grid, stream, a.pdl != 0, err);
+  return dispatch_epi<128, 1>(a.epilogue, tmA, tmB, tmAux, tmOut, d, grid, stream, a.pdl != 0, err);
 }
 
 }  // namespace vvs

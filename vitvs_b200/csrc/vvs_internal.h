@@ -123,6 +123,7 @@ struct GemmArgs {
   float q_scale;
   const float* pos;      // [T+1, ldo] (EPI_PATCH_F32): pos' with the CLS row folded in (launch_pos_prime)
   int T;                 // patches per image (EPI_PATCH_F32)
+  int pos_rows;          // rows of `pos` (EPI_PATCH_LN_F32 fetches 32-row boxes: T + 1 rows extended periodically by 31)
   unsigned long long* row_best;   // [batch, best_pitch] (EPI_SIM)
   unsigned long long* col_best;   // [batch, best_pitch]
   int best_pitch;
