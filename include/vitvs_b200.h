@@ -81,7 +81,8 @@ typedef struct vvs_config {
  * dinov2_extractor.py:25-55).  Allocates the workspace; weights arrive through vvs_set_weight. */
 VVS_API int vvs_create(const vvs_config* cfg, vvs_handle* out);
 VVS_API int vvs_destroy(vvs_handle h);
-/* message of the last failing call on this handle (h may be NULL: last vvs_create failure). */
+/* message of the last failing call on this handle (h may be NULL: last failure of vvs_create or of a handle-free
+ * call such as vvs_resize_frames_static). */
 VVS_API const char* vvs_last_error(vvs_handle h);
 VVS_API int vvs_num_sms(vvs_handle h);
 /* hash of the CUDA sources this library was compiled from (vitvs_b200/build.py computes it; smoke() compares it with
@@ -234,6 +235,32 @@ VVS_API int vvs_current_to_twist(vvs_handle h, const uint8_t* current, const uin
  * [n, frame_height, frame_width, 3] uint8 RGB (device) -> out [n, S, S, 3] uint8 (device), bit-identical to
  * Pillow 12.2 (integer arithmetic).  n <= max_images. */
 VVS_API int vvs_resize_frames(vvs_handle h, const uint8_t* frames, int32_t n, uint8_t* out, vvs_stream stream);
+/* No counterpart in the reference - an addition of this library for callers that cannot obtain device memory at call
+ * time.  vvs_resize_frames needs a handle, and vvs_create / the first frame call of a handle cudaMalloc tap tables and
+ * an intermediate image.  Two kinds of caller cannot afford that: (1) a servo node that shares its GPU with a framework
+ * which has already claimed the device's memory for its own pool (torch's caching allocator after a large model, an
+ * inference server with a fixed memory budget) - cudaMalloc then fails or succeeds depending on what else ran first;
+ * (2) a camera-callback / control thread with a deadline (vitvs_v2.py:455-462 feed a 30 Hz loop) - cudaMalloc and
+ * cudaFree take a driver lock and can wait for all work on the device, so one allocation stalls every other stream for
+ * an unbounded time.  This entry gives them the same resize with NO allocation of any kind on the device: no handle,
+ * no cudaMalloc / cudaFree, no library allocator.  The tap tables and the intermediate image live in a fixed array
+ * inside the library image (8.25 MiB; every GPU that loads the library holds it until the process exits).
+ *
+ * frames [n, frame_height, frame_width, 3] uint8 RGB (device) -> out [n, image_size, image_size, 3] uint8 (device), on
+ * the caller's CURRENT device, stream-ordered on `stream`; output bit-identical to vvs_resize_frames / Pillow.
+ * Limits (VVS_INVALID_ARGUMENT with a message naming the limit, read it with vvs_last_error(NULL)):
+ * image_size <= 1024; when both sides change, n * frame_height * image_size * 3 <= 8 MiB (18 frames of 640x480 -> 308);
+ * image_size * (2 + taps per output sample) <= 32768 per pass, i.e. down-scaling up to about 25x at image_size 308.
+ * Set-up: the first call on each GPU looks up the array's device address, and the first call with a new
+ * (frame_height, frame_width, image_size) computes the tap tables on the host and copies them into the array on
+ * `stream` (a pageable-memory copy, which may wait for `stream`).  Make that first call once during start-up, before
+ * any stream capture; later calls with the same geometry only launch the two kernels.
+ * The array is shared by every call on that GPU and keeps what the last call left in it; nothing needs to start at
+ * zero (each call writes all it reads).  Calls must therefore not overlap on the GPU: issue them on one stream, or order
+ * them with events - two calls running concurrently on different streams race on the intermediate image and on the
+ * tables.  Host-side the call is thread-safe. */
+VVS_API int vvs_resize_frames_static(const uint8_t* frames, int32_t n, int32_t frame_height, int32_t frame_width,
+                             int32_t image_size, uint8_t* out, vvs_stream stream);
 /* vvs_frame_pairs_to_twist on raw camera frames: goal / current [n_pairs, frame_height, frame_width, 3] uint8
  * (device); the resize of vitvs_v2.py:474-475 runs on the GPU ahead of the patch embedding. */
 VVS_API int vvs_frames_to_twist(vvs_handle h, const uint8_t* goal_frames, const uint8_t* current_frames,

@@ -71,6 +71,7 @@ SYMBOLS = {
     "vvs_frames_to_twist_host_async": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "vvs_wait": (c_i32, [c_vp, c_i32]),
     "vvs_resize_frames": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "vvs_resize_frames_static": (c_i32, [c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp]),
     "vvs_frames_to_twist": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, C.POINTER(PairOut), c_vp]),
     "vvs_frames_to_twist_host": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "vvs_set_goal": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp]),

@@ -1473,6 +1473,16 @@ int vvs_resize_frames(vvs_handle c, const uint8_t* frames, int32_t n, uint8_t* o
   return resize_frames(c, frames, n, out, static_cast<cudaStream_t>(stream));
 }
 
+// Handle-free and allocation-free (include/vitvs_b200.h): everything happens in resize.cu on the caller's current
+// device; a failure's message is read with vvs_last_error(NULL).
+int vvs_resize_frames_static(const uint8_t* frames, int32_t n, int32_t frame_height, int32_t frame_width,
+                             int32_t image_size, uint8_t* out, vvs_stream stream) {
+  std::string err;
+  const int rc = resize_frames_static(frames, n, frame_height, frame_width, image_size, out,
+                                      static_cast<cudaStream_t>(stream), &err);
+  return rc ? fail(nullptr, rc, err) : rc;
+}
+
 int vvs_frames_to_twist(vvs_handle c, const uint8_t* goal, const uint8_t* cur, const uint16_t* depth, int32_t n_pairs,
                         const vvs_pair_out* out, vvs_stream stream) {
   if (!c || !goal || !cur || !depth) return fail(c, VVS_ERR_INVALID, "vvs_frames_to_twist: null argument");

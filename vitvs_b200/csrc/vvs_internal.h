@@ -160,6 +160,10 @@ int launch_resize_h(const uint8_t* in, uint8_t* out, int n_rows, const ResizeAxi
 // in [n_img, ax.in_size, row_bytes] -> out [n_img, ax.out_size, row_bytes]
 int launch_resize_v(const uint8_t* in, uint8_t* out, int n_img, int row_bytes, const ResizeAxis& ax, cudaStream_t s,
                     std::string* err);
+// both passes on the current device with tables and intermediate image in the library's built-in device array: no
+// device allocation, no handle (resize.cu; vvs_resize_frames_static)
+int resize_frames_static(const uint8_t* frames, int n, int in_h, int in_w, int side, uint8_t* out, cudaStream_t s,
+                         std::string* err);
 
 // ---- bandwidth-bound kernels -------------------------------------------------------------------
 int launch_im2col_u8(const uint8_t* img, bf16* out, int n_img, int size, int kpad, int grid, int stride, cudaStream_t s,
