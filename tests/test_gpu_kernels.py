@@ -271,6 +271,43 @@ def test_gemm_swiglu_ln_consumer(eng):
     assert rel < 1e-2
 
 
+def _rms(a, ref):
+    return ((a.double() - ref) ** 2).mean().sqrt().item()
+
+
+@pytest.mark.parametrize("offset,outlier", [(0.3, 300.0), (10.0, 0.0), (30.0, 300.0)])
+def test_ln_fold_rows_with_offset_and_outlier_channel(eng, offset, outlier):
+    """Rows unlike the random-init ones of the model tests: a common offset of `offset` standard deviations and one
+    channel `outlier` standard deviations away (the massive-activation channels of trained ViTs).  The folded form feeds
+    bf16(x) to the tensor cores, the unfused form (LayerNorm kernel, then EPI_BIAS_BF16) feeds bf16(LN(x)).  bf16 rounding
+    is relative, so a large channel costs nothing; an offset does, because x_k carries it and LN(x)_k does not: the
+    operand error of the fold grows like sqrt(1 + (mean/std)^2) of the row.  The test pins exactly that law against the
+    unfused path ON THE SAME INPUT - a fold that loses more than the law allows fails - and keeps the variance
+    E[x^2] - mean^2 honest at 30 sigma."""
+    M, N, K = 970, 1152, 768
+    x = _rand((M, K), 170) + offset
+    x[:, 17] += outlier
+    g, be = 1.0 + _rand((K,), 171, 0.1), _rand((K,), 172, 0.05)
+    W, b = _rand((N, K), 173, 0.03), _rand((N,), 174, 0.1)
+    ref = torch.nn.functional.layer_norm(x.double(), (K,), g.double(), be.double(), 1e-6) @ W.double().T + b.double()
+    # unfused: the LayerNorm kernel rounds LN(x) to bf16, the plain GEMM multiplies it
+    out_u = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+    eng.dbg_gemm(eng.dbg_layernorm(x, g, be), W.to(torch.bfloat16), _lib.EPI_BIAS_BF16, bias=b, out_bf16=out_u, ldo=N)
+    # folded: raw bf16 rows, row statistics, W' = W diag(gamma), colsum(W'), b' = b + W beta
+    Wf = (W * g).to(torch.bfloat16)
+    out_f = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+    eng.dbg_gemm_ln(x.to(torch.bfloat16), Wf, _lib.EPI_BIAS_LN_BF16, bias=(b + W @ be).contiguous(), out_bf16=out_f, ldo=N,
+                    ln_part_in=_group_stats(x), colsum=Wf.float().sum(1).contiguous())
+    torch.cuda.synchronize()
+    err_u, err_f, scale = _rms(out_u, ref), _rms(out_f, ref), ref.pow(2).mean().sqrt().item()
+    ratio = (x.mean(1).abs() / x.std(1)).max().item()
+    print(f"[ln fold offset {offset} outlier {outlier}] row |mean|/std {ratio:.2f}: rms err unfused {err_u:.3e} "
+          f"folded {err_f:.3e} (output rms {scale:.3e}) -> folded / unfused {err_f / err_u:.2f}, "
+          f"law {math.sqrt(1 + ratio * ratio):.2f}")
+    assert err_u < 1e-2 * scale
+    assert err_f <= 1.5 * math.sqrt(1 + ratio * ratio) * err_u
+
+
 @pytest.mark.parametrize("n_img,n_tok,heads", [(1, 128, 1), (2, 485, 6), (3, 50, 2), (1, 1370, 12), (2, 257, 3)])
 def test_attention(eng, n_img, n_tok, heads):
     D = heads * 64

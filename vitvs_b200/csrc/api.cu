@@ -845,8 +845,8 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
     parts.emplace_back(0, n_pairs);
   }
   const int chunks = static_cast<int>(parts.size());
-  const int slot = c->host_slot;
-  c->host_slot ^= 1;
+  const int slot = c->host_slot;   // flipped only once the call is fully enqueued (below): a call that fails part-way
+                                   // leaves vvs_wait(0 / 1) pointing at the last two calls that did succeed
   c->host_stream = s;
   constexpr int kMaxChunks = 16;
   if (chunks > kMaxChunks) return fail(c, VVS_ERR_INVALID, "VITVS_HOST_CHUNKS too large");
@@ -914,6 +914,7 @@ int host_pipeline(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const uin
   c->launch_count = launches;
   VVS_CUDA_OK(cudaEventRecord(c->slot_free[slot], s), &c->err);
   c->slot_used[slot] = true;
+  c->host_slot = slot ^ 1;
   if (sync) VVS_CUDA_OK(cudaStreamSynchronize(s), &c->err);
   return VVS_OK;
 }

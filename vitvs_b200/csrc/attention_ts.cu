@@ -148,7 +148,6 @@ __global__ void __launch_bounds__(kThreads, 4 / kQT)
 attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                     const __grid_constant__ CUtensorMap tmO, bf16* __restrict__ out, int n_tok, int D,
                     unsigned long long* trace) {
-  trace_begin(trace);
 #ifdef VVS_ATT_TRACE
   const long long tr_entry = clock64();
 #endif
@@ -224,6 +223,7 @@ attention_ts_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
   pdl_launch_dependents();   // the prologue above may overlap the previous kernel's tail
   pdl_wait();
+  trace_begin(trace);        // behind the wait, like gemm_tc.cu: the span must not include the QKV GEMM's tail
 
   if (warp >= kSoftmaxWarps) {
     // ---- issuer warps: MMA issuer of tile u; the first one also feeds the K / V ring.  The whole warp walks the

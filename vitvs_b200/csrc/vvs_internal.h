@@ -59,8 +59,9 @@ extern thread_local unsigned long long* tl_trace_slot;
 
 // ---- launches ------------------------------------------------------------------------------------
 // <<< >>> with an optional programmatic-dependent-launch attribute (ptx.cuh: pdl_wait / pdl_launch_dependents)
-// programmatic dependent launch for a forward pass over `rows` token rows of width `dim`: VITVS_PDL=1 always, =0 never;
-// default: only where it was measured to pay (small batches of the narrow model, see api.cu)
+// programmatic dependent launch for a forward pass over `rows` token rows of width `dim`: on for every shape unless
+// VITVS_PDL=0 (measured to help small batches most and never to lose, see api.cu); `rows` / `dim` are kept in the
+// signature for a shape-dependent policy but are not consulted today
 bool pdl_for_rows(long long rows, int dim);
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl,
