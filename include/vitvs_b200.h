@@ -75,6 +75,10 @@ typedef struct vvs_config {
   int32_t patch_stride;        /* ViTExtractor stride (dinov2_extractor.py:25,123-144): 14 = non-overlapping patches
                                   (vitvs_v2.py:250), a divisor of 14 = overlapping patches, 1 + (S-14)/stride tokens
                                   per side; 0 => 14 */
+  double damping_mu;           /* Levenberg-Marquardt damping of the control law: v = -lambda (L^T L + mu I)^-1 L^T e.
+                                  0 (default) = the reference's undamped pinv(L) (vitvs_v2.py:622); > 0 keeps the twist
+                                  bounded when the matched points leave L badly conditioned.  No counterpart in the
+                                  reference; appended last so that the layout of the fields above is unchanged. */
 } vvs_config;
 
 /* replaces: Controller.__init__ -> ViTExtractor(...) model construction (vitvs_v2.py:249-250,
@@ -97,7 +101,11 @@ VVS_API const char* vvs_build_id(void);
  * dinov2_extractor.py:94-120).  dev_ptr is a device pointer, copied/converted (bf16 for GEMM operands). */
 VVS_API int vvs_set_weight(vvs_handle h, const char* name, const void* dev_ptr, int32_t dtype, const int64_t* shape,
                    int32_t rank, vvs_stream stream);
-/* 0 when every parameter of blocks[0..layer] and the embeddings has been set. */
+/* 0 when every parameter of blocks[0..layer] and the embeddings has been set.  On success the fp32 copies of
+ * attn.qkv.weight and mlp.fc1 / w12.weight that were held for folding norm1 / norm2 into them are released.  Re-setting
+ * a tensor that is folded into one of these matrices afterwards (norm1.*, attn.qkv.bias; norm2.*, mlp.fc1 / w12.bias)
+ * therefore needs that block's matrix set again as well: until it is, this function and every forward call report the
+ * block as incomplete.  Re-loading a whole state_dict in any order works as before. */
 VVS_API int vvs_weights_ready(vvs_handle h);
 
 /* replaces: ViTExtractor._extract_features with facet 'token' (dinov2_extractor.py:245-263): runs

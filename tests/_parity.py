@@ -3,7 +3,10 @@ import numpy as np
 
 from oracle import servo
 
-TIE_EPS = 2e-3     # similarity margin below which an arg-max disagreement counts as a near-tie (bf16 operands)
+# Two limits: north_star's acceptance numbers (cosine >= 0.999, near-tie) and, tighter, REGRESSION gates a factor ~2-5 off
+# what the path measures (cosine 0.99998 S/B, 0.99997 L-23, 0.99983 g-39; worst margin at a disagreement 4e-4), so that a
+# defect costing a factor 10 in accuracy (wrong ln_eps, a positional row off, a dropped k-block) cannot stay green.
+TIE_EPS = 1e-3     # similarity margin below which an arg-max disagreement counts as a near-tie (bf16 operands)
 
 
 def check_keypoints(out: dict, p: int, grid_w: int, cfg: dict | None = None) -> int:

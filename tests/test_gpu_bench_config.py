@@ -101,7 +101,7 @@ def test_bench_configuration_equals_single_pair_calls_and_oracle(vitb, batch):
         print(f"[bench config] pair {i}: token cosine min {cos:.6f}  nn1/nn2 agree {a1:.4f}/{a2:.4f} (worst margin "
               f"{marg:.1e})  twist rel err on the GPU's key-points {rel_same_kp:.1e}; vs the oracle's own twist "
               f"{rel:.1e} ({'identical' if same_sel else 'different'} selection)")
-        assert cos >= 0.999
+        assert cos >= 0.9999          # north_star 0.999; regression gate (measured 0.99998)
         assert rel_same_kp <= 1e-9
         if same_sel:
             assert rel <= 1e-3

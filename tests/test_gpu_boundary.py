@@ -162,3 +162,42 @@ def test_handles_on_two_devices_in_one_process(vits):
         assert torch.equal(outs[0][k], outs[1][k]), k
     for e in engines:
         e.close()
+
+
+def test_fold_sources_released_after_weights_ready(vits):
+    """vvs_weights_ready hands the fp32 fold sources back to the device (include/vitvs_b200.h): a second load of the same
+    state_dict gives the same twists bit for bit; changing only norm1.weight afterwards makes the block incomplete (loud,
+    not stale) until its attn.qkv.weight is set again, and the result then equals that of a fresh handle."""
+    import ctypes as C
+    from vitvs_b200 import Engine, ServoConfig, VvsError, _lib
+    g, c, d = synth.frame_batch(2)
+    args = (torch.from_numpy(g).cuda(), torch.from_numpy(c).cuda(), torch.from_numpy(d).cuda())
+    e = Engine(ServoConfig(model_type="dinov2_vits14"), max_images=4)
+    e.load_weights(vits)
+    base = e.frame_pairs_to_twist(*args)["twist"].clone()
+    e.load_weights(vits)                                               # whole state_dict again, sources re-uploaded
+    assert torch.equal(e.frame_pairs_to_twist(*args)["twist"], base)
+
+    state = {k: v.clone() for k, v in vits.state_dict().items()}
+    state["blocks.3.norm1.weight"] = state["blocks.3.norm1.weight"] * 1.25
+
+    def put(name):
+        t = state[name].detach().to("cuda", torch.float32).contiguous()
+        shape = (C.c_int64 * t.dim())(*t.shape)
+        rc = e.lib.vvs_set_weight(e._h, name.encode(), t.data_ptr(), _lib.F32, shape, t.dim(), None)
+        torch.cuda.synchronize()
+        assert rc == 0, e.lib.vvs_last_error(e._h)
+
+    put("blocks.3.norm1.weight")
+    assert e.lib.vvs_weights_ready(e._h) != 0 and b"blocks.3 incomplete" in e.lib.vvs_last_error(e._h)
+    with pytest.raises(VvsError):
+        e.frame_pairs_to_twist(*args)
+    put("blocks.3.attn.qkv.weight")
+    assert e.lib.vvs_weights_ready(e._h) == 0
+    changed = e.frame_pairs_to_twist(*args)["twist"].clone()
+    fresh = Engine(ServoConfig(model_type="dinov2_vits14"), max_images=4)
+    fresh.load_weights(state)
+    assert torch.equal(changed, fresh.frame_pairs_to_twist(*args)["twist"])
+    assert not torch.equal(changed, base)
+    fresh.close()
+    e.close()

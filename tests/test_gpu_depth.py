@@ -17,6 +17,8 @@ from _parity import check_argmax, check_keypoints, margin_histogram  # noqa: E40
 # the rows have a best-vs-second margin under 2e-4 - inside the noise bf16 operands leave on S (token cosine 0.99987 after
 # 40 blocks) - so 1 - 3 % of the arg-max indices flip, every one of them at a margin < 2e-4 (the test still demands that).
 MAX_BAD = {"dinov2_vitl14": 0.01, "dinov2_vitg14": 0.035}
+# token cosine: north_star's limit is 0.999; regression gates next to the measurements (L-23 0.99997, g-39 0.99983)
+MIN_COS = {"dinov2_vitl14": 0.9999, "dinov2_vitg14": 0.9995}
 
 
 @pytest.mark.parametrize("model_type,layers", [("dinov2_vitl14", (11, 17, 23)), ("dinov2_vitg14", (11, 23, 31, 39))])
@@ -39,7 +41,7 @@ def test_full_depth_parity(model_type, layers):
         report.append((layer, cos.min().item(), cos.mean().item()))
     print(f"[{model_type}] token cosine by depth: " + "  ".join(f"L{l}: min {a:.6f} mean {b:.6f}" for l, a, b in report))
     for layer, cmin, _ in report:
-        assert cmin >= 0.999, f"{model_type}: descriptor cosine {cmin:.6f} < 0.999 at layer {layer}"
+        assert cmin >= MIN_COS[model_type], f"{model_type}: descriptor cosine {cmin:.6f} < {MIN_COS[model_type]} at layer {layer}"
     # the whole path at the last layer
     out = eng.frame_pairs_to_twist(imgs[:1], imgs[1:], torch.from_numpy(depth[None].copy()).cuda(), want_match=True)
     torch.cuda.synchronize()

@@ -12,7 +12,7 @@ from vitvs_b200 import synth  # noqa: E402
 
 from _parity import check_keypoints  # noqa: E402
 
-TIE_EPS = 2e-3
+TIE_EPS = 1e-3     # regression gate (tests/_parity.py); worst measured margin at a disagreement: 4e-4
 
 
 @pytest.mark.parametrize("model_type", ["dinov2_vitb14", "dinov2_vitl14", "dinov2_vitg14"])
@@ -30,7 +30,8 @@ def test_model_family_parity(model_type):
     ref_tok = torch.cat([servo.block_tokens(model, servo.preprocess_u8(im), 11) for im in (goal, cur)])
     cos = torch.nn.functional.cosine_similarity(tok, ref_tok, dim=-1)
     print(f"[{model_type}] token cosine min {cos.min():.6f}")
-    assert cos.min() >= 0.999                                                # north_star: descriptor cosine >= 0.999
+    # north_star: descriptor cosine >= 0.999; regression gate: 0.9999 (measured 0.99998), ViT-g 0.9995 (0.99990)
+    assert cos.min() >= (0.9995 if model_type == "dinov2_vitg14" else 0.9999)
     ref = servo.frame_pair_to_twist(model, goal, cur, depth)
     S, m = ref["S"], ref["match"]
     nn1, nn2 = out["nn1"][0].cpu().numpy(), out["nn2"][0].cpu().numpy()
@@ -41,10 +42,10 @@ def test_model_family_parity(model_type):
     print(f"[{model_type}] nn1 agree {1 - bad1.mean():.4f} nn2 agree {1 - bad2.mean():.4f} "
           f"worst margin {max(marg1.max(), marg2.max()):.2e}")
     # >= 99 % mutual-NN index agreement, per direction (north_star).  Random-init ViT-g is the stated exception (DESIGN.md 5,
-    # tests/test_gpu_depth.py): a nearly flat similarity landscape puts 1 - 1.5 % of its rows inside the bf16 noise of S
+    # tests/test_gpu_depth.py) at FULL depth only; at layer 11 it measures 0.6 - 0.8 % and is held to the same 1 %
     from _parity import margin_histogram
     print(f"[{model_type}] oracle best-vs-second margins below threshold: {margin_histogram(S)}")
-    limit = 0.015 if model_type == "dinov2_vitg14" else 0.01
+    limit = 0.01
     assert bad1.mean() <= limit and bad2.mean() <= limit
     assert np.all(marg1[bad1] < TIE_EPS) and np.all(marg2[bad2] < TIE_EPS)   # ... disagreements only at near-ties
     uv, uvs = out["uv"][0].cpu().numpy().astype(int), out["uv_star"][0].cpu().numpy().astype(int)

@@ -13,7 +13,7 @@ from vitvs_b200 import synth  # noqa: E402
 
 from _parity import check_keypoints  # noqa: E402
 
-TIE_EPS = 2e-3     # similarity margin below which an arg-max disagreement counts as a near-tie (bf16 operands)
+TIE_EPS = 1e-3     # similarity margin below which an arg-max disagreement counts as a near-tie (bf16 operands)
 
 
 @pytest.fixture(scope="module")
@@ -39,14 +39,14 @@ def test_tokens_and_descriptors_vs_oracle(eng, vits):
     ref = torch.cat([servo.block_tokens(vits, servo.preprocess_u8(im), 11) for im in imgs])
     cos = torch.nn.functional.cosine_similarity(tok, ref, dim=-1)
     print(f"[tokens] cosine min {cos.min():.6f} mean {cos.mean():.6f}; max abs err {(tok - ref).abs().max():.4f}")
-    assert cos.min() >= 0.999
+    assert cos.min() >= 0.9999       # acceptance limit 0.999 (north_star); regression gate, measured 0.99998
     for bin_ in (False, True):
         d = eng.descriptors(bin_).cpu()
         dref = torch.stack([servo.extract_descriptors(vits, servo.preprocess_u8(im), 11, bin_)[0] for im in imgs])
         assert d.shape == dref.shape
         cos = torch.nn.functional.cosine_similarity(d, dref, dim=-1)
         print(f"[descriptors bin={bin_}] cosine min {cos.min():.6f}")
-        assert cos.min() >= 0.999
+        assert cos.min() >= 0.9999
         # binning is a pure gather of the GPU tokens: bit-exact against the oracle's log_bin of those tokens
         mine = tok[:, 1:]
         expect = servo.log_bin(mine, (22, 22)) if bin_ else mine
@@ -173,6 +173,29 @@ def test_match_batched_pairs_are_independent(eng):
 
 
 # ------------------------------------------------------------------------------ control law
+@pytest.mark.parametrize("mu", [1e-3, 0.5])
+def test_ibvs_damped_normal_equations(golden, mu):
+    """vvs_config.damping_mu (no counterpart in the reference, default 0): v = -lambda (L^T L + mu I)^-1 L^T e against
+    numpy on the L / e the library itself reports for a reference fixture; mu = 0 stays the reference's pinv (the test
+    below).  A rank-deficient L (3 points cannot happen here: K = 24) is not needed - mu > 0 makes the system definite."""
+    from vitvs_b200 import Engine, ServoConfig
+    g = golden("ibvs.npz")
+    uv = torch.from_numpy(g["k24/s_uv"].astype(np.int32))[None]
+    uvs = torch.from_numpy(g["k24/s_uv_star"].astype(np.int32))[None]
+    depth = torch.from_numpy(g["depth"])[None]
+    e = Engine(ServoConfig(model_type="dinov2_vits14", damping_mu=mu), max_images=2)
+    t = e.ibvs_terms(uv, uvs, depth)
+    L = t["L"][0].cpu().numpy()
+    err = (t["s_xy"][0] - t["s_star_xy"][0]).cpu().numpy().reshape(-1, 1)
+    v_ref = (-0.03 * np.linalg.solve(L.T @ L + mu * np.eye(6), L.T @ err)).ravel()
+    v = t["twist"][0].cpu().numpy()
+    assert np.abs(v - v_ref).max() <= 1e-9 * np.abs(v_ref).max()
+    assert np.linalg.norm(v) < np.linalg.norm(g["k24/v"])            # damping shrinks the twist
+    e.close()
+    with pytest.raises(Exception, match="damping_mu"):
+        Engine(ServoConfig(model_type="dinov2_vits14", damping_mu=-1.0), max_images=2)
+
+
 @pytest.mark.parametrize("case", ["k24", "k48", "k7_padded", "k3_too_few", "k24_oob_depth"])
 def test_ibvs_against_reference_fixtures(eng, golden, case):
     g = golden("ibvs.npz")

@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     # struct layouts the ctypes mirror assumes
     import ctypes as C
     # see vvs_config: ... + patch_stride, padded to the 8-byte alignment of the doubles
-    assert C.sizeof(_lib.Config) == (7 * 4 + 2 * 4 + 4 + 6 * 8 + 3 * 4 + 4 + 2 * 4 + 4) + 4
+    assert C.sizeof(_lib.Config) == (7 * 4 + 2 * 4 + 4 + 6 * 8 + 3 * 4 + 4 + 2 * 4 + 4) + 4 + 8
     assert C.sizeof(_lib.MatchOut) == 13 * 8 and C.sizeof(_lib.PairOut) == 16 * 8
 
 

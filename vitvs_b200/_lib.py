@@ -31,6 +31,7 @@ class Config(C.Structure):
         ("num_pairs", c_i32), ("layer", c_i32), ("use_feature_binning", c_i32),
         ("same_image_threshold", c_f32),
         ("max_match_tokens", c_i32), ("max_match_dim", c_i32), ("patch_stride", c_i32),
+        ("damping_mu", c_f64),
     ]
 
 

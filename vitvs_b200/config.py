@@ -34,6 +34,8 @@ class ServoConfig:
     facet: str = "token"                      # vitvs_v2.py:485
     distance_threshold: float = 1.0           # vitvs_v2.py:72
     same_image_threshold: float = 0.99        # vitvs_v2.py:84
+    # not in the reference: damping of the control law, v = -lambda (L^T L + mu I)^-1 L^T e; 0 = the reference's pinv(L)
+    damping_mu: float = 0.0
 
     @property
     def c_x(self) -> float:                   # vitvs_v2.py:282

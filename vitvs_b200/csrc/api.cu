@@ -576,7 +576,7 @@ int run_ibvs(vvs_ctx* c, const int32_t* uv, const int32_t* uv_star, const uint16
   a.uv = uv; a.uv_star = uv_star; a.depth = depth; a.n_pairs = n_pairs; a.K = K;
   a.cam.width = c->cfg.frame_width; a.cam.height = c->cfg.frame_height;
   a.cam.fx = c->cfg.f_x; a.cam.fy = c->cfg.f_y; a.cam.cx = c->cfg.c_x; a.cam.cy = c->cfg.c_y;
-  a.lambda = c->cfg.lambda_; a.ema_alpha = c->cfg.ema_alpha;
+  a.lambda = c->cfg.lambda_; a.mu = c->cfg.damping_mu; a.ema_alpha = c->cfg.ema_alpha;
   a.ema_state = ema_state; a.ema_init = ema_init; a.twist = twist; a.twist_raw = twist_raw;
   ++c->launch_count;
   ProfScope ps(c, VVS_K_IBVS, s);
@@ -724,6 +724,10 @@ int pairs_to_twist(vvs_ctx* c, const uint8_t* goal, const uint8_t* cur, const ui
 // the caller's stream may be the legacy default one.  Returns null when graphs are off / unavailable.
 const vvs_ctx::GraphEntry* graphs_for(vvs_ctx* c, int n_pairs, bool want_mean, int mode = 0) {
   if (!c->graphs_enabled || c->prof_on) return nullptr;
+  // a block whose weights became incomplete after its graph was captured (vvs_set_weight of a folded vector once the
+  // fold sources are released): no replay - the eager path refuses with the block's name
+  for (int i = 0; i <= c->cfg.layer && i < c->cfg.depth; ++i)
+    if (c->blocks[i].set_mask != 0x3FFF) return nullptr;
   for (auto& g : c->graphs)
     if (g.n_pairs == n_pairs && g.want_mean == (want_mean ? 1 : 0) && g.mode == mode) return &g;
   const int warm_key = n_pairs | (mode << 20);
@@ -952,6 +956,8 @@ int refold_block(vvs_ctx* c, BlockW& w, cudaStream_t s) {
        &w.ffn1_cs, &w.ffn1_bf}};
   for (const Group& g : groups) {
     if ((w.set_mask & g.mask) != g.mask) continue;
+    if (!g.w32) continue;   // source released by vvs_weights_ready: the fold on the device is current (vvs_set_weight
+                            // un-sets the matrix bit when a member of a released group changes)
     int rc = VVS_OK;
     if (!*g.wf) rc = dev_alloc(c, g.wf, static_cast<size_t>(g.rows) * D);
     if (!rc && !*g.cs) rc = dev_alloc(c, g.cs, static_cast<size_t>(g.rows));
@@ -1004,6 +1010,7 @@ int vvs_create(const vvs_config* cfg, vvs_handle* out) {
       cfg->num_pairs > 256 || cfg->layer < 0 || cfg->layer >= cfg->depth)
     return fail(nullptr, VVS_ERR_INVALID, "vvs_create: inconsistent vvs_config");
   {
+    if (!(cfg->damping_mu >= 0.0)) return fail(nullptr, VVS_ERR_INVALID, "vvs_create: damping_mu must be >= 0");
     const int st = cfg->patch_stride > 0 ? cfg->patch_stride : kPatch;
     if (kPatch % st != 0 || (cfg->image_size - kPatch) % st != 0)
       return fail(nullptr, VVS_ERR_INVALID,
@@ -1218,6 +1225,13 @@ int vvs_set_weight(vvs_handle c, const char* name_c, const void* p, int32_t dtyp
         if (n != v.n) return bad_shape();
         w.set_mask |= 1u << v.bit;
         int rc = upload_vector(c, v.dst, p, dtype, v.n, v.il, H, s);
+        if (c->ln_fused) {
+          // This vector is folded into a matrix whose fp32 source vvs_weights_ready has released: the fold cannot be
+          // redone until that matrix is set again, and until then the block counts as incomplete (forward calls refuse).
+          constexpr unsigned kIntoQkv = (1u << 0) | (1u << 1) | (1u << 6), kIntoFfn1 = (1u << 2) | (1u << 3) | (1u << 8);
+          if (((kIntoQkv >> v.bit) & 1u) && !w.qkv_w32) w.set_mask &= ~(1u << 10);
+          if (((kIntoFfn1 >> v.bit) & 1u) && !w.ffn1_w32) w.set_mask &= ~(1u << 12);
+        }
         return rc ? rc : refold_block(c, w, s);
       }
     struct Mat { const char* leaf; bf16** dst; int rows, cols; int bit; int il; };
@@ -1229,9 +1243,11 @@ int vvs_set_weight(vvs_handle c, const char* name_c, const void* p, int32_t dtyp
       if (leaf == m.leaf) {
         if (n != static_cast<long long>(m.rows) * m.cols) return bad_shape();
         w.set_mask |= 1u << m.bit;
-        int rc = upload_matrix(c, m.dst, p, dtype, m.rows, m.cols, m.cols, m.il, H, s);
-        if (!rc && c->ln_fused && (m.bit == 10 || m.bit == 12))   // consumers of a LayerNorm: keep the unrounded source
-          rc = upload_matrix_f32(c, m.bit == 10 ? &w.qkv_w32 : &w.ffn1_w32, p, dtype, m.rows, m.cols, m.il, H, s);
+        // Consumers of a LayerNorm are multiplied in their folded form only (refold_block writes it from the unrounded
+        // fp32 source): the plain bf16 copy would never be read, so it is not made.
+        const bool folded = c->ln_fused && (m.bit == 10 || m.bit == 12);
+        int rc = folded ? upload_matrix_f32(c, m.bit == 10 ? &w.qkv_w32 : &w.ffn1_w32, p, dtype, m.rows, m.cols, m.il, H, s)
+                        : upload_matrix(c, m.dst, p, dtype, m.rows, m.cols, m.cols, m.il, H, s);
         return rc ? rc : refold_block(c, w, s);
       }
   }
@@ -1243,6 +1259,18 @@ int vvs_weights_ready(vvs_handle c) {
   if (c->emb_mask != 0xF) return fail(c, VVS_ERR_STATE, "embedding weights not set");
   for (int i = 0; i <= c->cfg.layer; ++i)
     if (c->blocks[i].set_mask != 0x3FFF) return fail(c, VVS_ERR_STATE, "weights of blocks." + std::to_string(i) + " incomplete");
+  if (c->ln_fused) {
+    // The fp32 sources were kept only so that the fold could be (re)done whatever order the tensors arrived in.  Every
+    // block that is complete has its folded matrices now; its sources go back to the device (ViT-g: 3.1 GB).
+    DeviceGuard dg(c);
+    VVS_CUDA_OK(cudaDeviceSynchronize(), &c->err);   // the last fold kernels read them
+    for (BlockW& w : c->blocks) {
+      if (w.set_mask != 0x3FFF) continue;
+      if (w.qkv_w32) cudaFree(w.qkv_w32);
+      if (w.ffn1_w32) cudaFree(w.ffn1_w32);
+      w.qkv_w32 = w.ffn1_w32 = nullptr;
+    }
+  }
   return VVS_OK;
 }
 
@@ -1389,7 +1417,7 @@ int vvs_ibvs_terms(vvs_handle c, const int32_t* uv, const int32_t* uv_star, cons
   a.uv = uv; a.uv_star = uv_star; a.depth = depth; a.n_pairs = n_pairs; a.K = K;
   a.cam.width = c->cfg.frame_width; a.cam.height = c->cfg.frame_height;
   a.cam.fx = c->cfg.f_x; a.cam.fy = c->cfg.f_y; a.cam.cx = c->cfg.c_x; a.cam.cy = c->cfg.c_y;
-  a.lambda = c->cfg.lambda_; a.twist = twist;
+  a.lambda = c->cfg.lambda_; a.mu = c->cfg.damping_mu; a.twist = twist;
   a.z_out = z; a.xy_out = xy; a.xy_star_out = xy_star; a.L_out = L;
   ++c->launch_count;
   return launch_ibvs(a, static_cast<cudaStream_t>(stream), &c->err);

@@ -406,6 +406,8 @@ __global__ void __launch_bounds__(128) ibvs_kernel(const IbvsArgs a, unsigned lo
         ++n;
       }
     for (int i = 0; i < 6; ++i) g[i] = acc[21 + i];
+    if (a.mu > 0.0)   // damped least squares (vvs_config.damping_mu); untouched arithmetic when 0
+      for (int i = 0; i < 6; ++i) A[i][i] += a.mu;
   }
   // Cholesky A = C C^T when safely positive definite (rank 6), else Jacobi pseudo-inverse
   double C[6][6];

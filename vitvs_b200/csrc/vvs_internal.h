@@ -249,6 +249,7 @@ struct IbvsArgs {
   int n_pairs, K;
   Camera cam;
   double lambda;
+  double mu;                // damping added to the diagonal of L^T L (0 = the reference's pinv)
   double ema_alpha;         // used when ema_state != null
   double* ema_state;        // [n_pairs, 6] or null
   int32_t* ema_init;        // [n_pairs] 0 = first call copies

@@ -75,7 +75,8 @@ class Engine:
             num_pairs=self.cfg.num_pairs, layer=min(self.cfg.layer, depth - 1),
             use_feature_binning=int(self.cfg.use_feature_binning),
             same_image_threshold=self.cfg.same_image_threshold,
-            max_match_tokens=max_match_tokens, max_match_dim=max_match_dim, patch_stride=self.cfg.stride)
+            max_match_tokens=max_match_tokens, max_match_dim=max_match_dim, patch_stride=self.cfg.stride,
+            damping_mu=self.cfg.damping_mu)
         self._h = C.c_void_p()
         with torch.cuda.device(self.device):
             rc = self.lib.vvs_create(C.byref(c), C.byref(self._h))
