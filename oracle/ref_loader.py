@@ -69,6 +69,69 @@ def attention():
     return _load()["attention"]
 
 
+def block():
+    """The reference module dino_patch/block.py (Block, NestedTensorBlock), executed where it lies.
+
+    block.py:17-20 imports four siblings; only ``attention.py`` is vendored in the reference.  The other three
+    (``drop_path``, ``layer_scale``, ``mlp``) belong to the un-vendored upstream package (github facebookresearch/dinov2,
+    dinov2/layers/, unpinned) and are supplied here as minimal stand-ins that state the published definitions: DropPath is
+    the identity outside training, LayerScale multiplies by a learned per-channel ``gamma``, Mlp is fc1 -> act -> fc2.
+    What is pinned by importing block.py itself is everything the reference's file decides: which sub-modules a block
+    has, LayerNorm placement, the residual order and the inference branch (block.py:90-95,112-114)."""
+    if "block" in _cache:
+        return _cache["block"]
+    _load()
+    import torch
+    from torch import nn
+    pkg_name = "_ref_dino_patch"
+    pkg_dir = os.path.join(REF_ROOT, "dino_patch")
+    pkg = types.ModuleType(pkg_name)
+    pkg.__path__ = [pkg_dir]                    # `.attention` resolves to the reference's own file
+    sys.modules[pkg_name] = pkg
+
+    class DropPath(nn.Module):
+        def __init__(self, drop_prob=None):
+            super().__init__()
+            self.drop_prob = drop_prob
+
+        def forward(self, x):
+            assert not self.training, "stand-in: inference only"
+            return x
+
+    class LayerScale(nn.Module):
+        def __init__(self, dim, init_values=1e-5, inplace=False):
+            super().__init__()
+            self.gamma = nn.Parameter(init_values * torch.ones(dim))
+
+        def forward(self, x):
+            return x * self.gamma
+
+    class Mlp(nn.Module):
+        def __init__(self, in_features, hidden_features=None, out_features=None, act_layer=nn.GELU, drop=0.0, bias=True):
+            super().__init__()
+            self.fc1 = nn.Linear(in_features, hidden_features or in_features, bias=bias)
+            self.act = act_layer()
+            self.fc2 = nn.Linear(hidden_features or in_features, out_features or in_features, bias=bias)
+
+        def forward(self, x):
+            return self.fc2(self.act(self.fc1(x)))
+
+    for sub, attrs in (("drop_path", {"DropPath": DropPath}), ("layer_scale", {"LayerScale": LayerScale}),
+                       ("mlp", {"Mlp": Mlp})):
+        m = types.ModuleType(f"{pkg_name}.{sub}")
+        m.__dict__.update(attrs)
+        sys.modules[m.__name__] = m
+    spec = importlib.util.spec_from_file_location(f"{pkg_name}.block", os.path.join(pkg_dir, "block.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[spec.name] = mod
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        spec.loader.exec_module(mod)
+    _cache["block"] = mod
+    return mod
+
+
 def make_controller(cfg: dict, depth_u16=None):
     """A reference ``Controller`` without ROS: ``Controller.__new__`` + the attributes
     ``load_parameters`` (vitvs_v2.py:272-323) and ``initialize_ema`` (:325-327) would set."""

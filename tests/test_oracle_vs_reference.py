@@ -1,5 +1,7 @@
 """Live cross-check of the oracle against the reference's own functions, executed from
 /root/reference (build container only; skipped on the GPU box where it does not exist)."""
+import copy
+import sys
 import warnings
 
 import numpy as np
@@ -40,6 +42,30 @@ def test_attention_matches_reference_module(vits):
     x = torch.randn(2, 50, 384, generator=torch.Generator().manual_seed(1))
     with torch.no_grad():
         assert torch.equal(ref(x), blk(x))
+
+
+@pytest.mark.parametrize("cls_name", ["Block", "NestedTensorBlock"])
+def test_block_matches_reference_module(vits, cls_name):
+    """oracle Block == dino_patch/block.py Block / NestedTensorBlock (inference branch, :90-95,112-114) with the reference's
+    own MemEffAttention inside: LayerNorm placement, residual order and LayerScale position are the reference file's.
+    LayerScale / Mlp are stand-ins for the un-vendored upstream siblings (oracle/ref_loader.block)."""
+    from functools import partial
+    B = ref_loader.block()
+    A = sys.modules["_ref_dino_patch.attention"]
+    for idx in (0, 7):
+        blk = vits.blocks[idx]
+        ref = getattr(B, cls_name)(384, num_heads=6, mlp_ratio=4.0, qkv_bias=True, proj_bias=True, ffn_bias=True,
+                                   init_values=1.0, norm_layer=partial(torch.nn.LayerNorm, eps=1e-6),
+                                   attn_class=A.MemEffAttention).eval()
+        sd = {k: v.clone() for k, v in blk.state_dict().items()}
+        sd["ls1.gamma"] = torch.linspace(0.5, 1.5, 384)          # LayerScale must sit on the branch, not on x
+        sd["ls2.gamma"] = torch.linspace(1.5, 0.5, 384)
+        ref.load_state_dict(sd, strict=True)
+        mine = copy.deepcopy(blk)
+        mine.load_state_dict(sd, strict=True)
+        x = torch.randn(2, 50, 384, generator=torch.Generator().manual_seed(idx))
+        with torch.no_grad():
+            assert torch.equal(ref(x), mine(x))
 
 
 def test_preprocess_matches_reference(vits):
