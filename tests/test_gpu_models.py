@@ -157,3 +157,58 @@ def test_perturbed_frame_parity(model_type, pair):
         rel = np.abs(out["twist"][0].cpu().numpy() - ref["twist"]).max() / np.abs(ref["twist"]).max()
         assert rel <= 1e-3
     eng.close()
+
+
+def _flips(nn_a1, nn_a2, S):
+    """arg-max disagreement of index lists (nn_a1 rows, nn_a2 columns) with similarity matrix S, and the worst margin S
+    itself sees at a disagreement"""
+    S = S.numpy() if hasattr(S, "numpy") else S
+    rows = np.arange(S.shape[0])
+    r1, r2 = S.argmax(1), S.argmax(0)
+    b1, b2 = nn_a1 != r1, nn_a2 != r2
+    m1, m2 = S[rows, r1] - S[rows, nn_a1], S[r2, rows] - S[nn_a2, rows]
+    return float(b1.mean()), float(b2.mean()), float(max(m1[b1].max(initial=0), m2[b2].max(initial=0)))
+
+
+@pytest.mark.parametrize("model_type,layer", [("dinov2_vitb14", 11), ("dinov2_vitl14", 23), ("dinov2_vitg14", 11),
+                                              ("dinov2_vitg14", 39)])
+def test_gpu_against_bf16_emulated_oracle(model_type, layer):
+    """Attribution of the fp32-vs-GPU differences (oracle/bf16_emulation.py): the CPU emulation rounds where the GPU
+    path rounds.  (1) GPU vs emulation must be much tighter than GPU vs fp32 - what is left is accumulation order and
+    exp / erf implementations, so a kernel defect shows here even where the fp32 comparison is inside its tolerance.
+    (2) emulation vs fp32 must flip about as many arg-max indices as the GPU does - the ViT-g exception to north_star's
+    99 % (tests/test_gpu_depth.py) is then arithmetic, not a kernel."""
+    from oracle import bf16_emulation as be
+    from vitvs_b200 import Engine, ServoConfig
+    model = dinov2.build(model_type, seed=1, max_depth=layer + 1)
+    eng = Engine(ServoConfig(model_type=model_type, layer=layer), max_images=2)
+    eng.load_weights(model)
+    goal, cur, depth = synth.frame_pair(7)
+    out = eng.frame_pairs_to_twist(torch.from_numpy(goal[None].copy()).cuda(), torch.from_numpy(cur[None].copy()).cuda(),
+                                   torch.from_numpy(depth[None].copy()).cuda(), want_match=True)
+    torch.cuda.synchronize()
+    tok = eng.tokens_out().cpu()
+    nn1, nn2 = out["nn1"][0].cpu().numpy(), out["nn2"][0].cpu().numpy()
+    eng.close()
+    tok_e, S_e = be.similarity_matrices(model, goal, cur, layer)
+    ref = servo.frame_pair_to_twist(model, goal, cur, depth, dict(servo.DEFAULT_CFG, layer=layer))
+    tok_f = torch.cat([servo.block_tokens(model, servo.preprocess_u8(im), layer) for im in (goal, cur)])
+    cosine = torch.nn.functional.cosine_similarity
+    cos_ge, cos_gf, cos_ef = (cosine(a, b, dim=-1).min().item() for a, b in ((tok, tok_e), (tok, tok_f), (tok_e, tok_f)))
+    ge1, ge2, ge_m = _flips(nn1, nn2, S_e)                                        # GPU indices judged by the emulation's S
+    gf1, gf2, gf_m = _flips(nn1, nn2, ref["S"])                                   # ... by the fp32 oracle's S
+    ef1, ef2, ef_m = _flips(S_e.argmax(1).numpy(), S_e.argmax(0).numpy(), ref["S"])   # emulation's indices by fp32's S
+    print(f"[{model_type} L{layer}] token cosine min: GPU~emul {cos_ge:.7f}  GPU~fp32 {cos_gf:.7f}  emul~fp32 {cos_ef:.7f}")
+    print(f"[{model_type} L{layer}] arg-max flips nn1/nn2: GPU~emul {ge1:.4f}/{ge2:.4f} (worst margin {ge_m:.1e})  "
+          f"GPU~fp32 {gf1:.4f}/{gf2:.4f} ({gf_m:.1e})  emul~fp32 {ef1:.4f}/{ef2:.4f} ({ef_m:.1e})")
+    # (1) The GPU is closer to the emulation than to fp32 (measured 1 - cos: 0.42 - 0.66 of the fp32 figure).  Not 10x closer:
+    # the flash-attention kernel rounds P = exp(s - RUNNING max) and rescales later, the emulation rounds exp(s - final max),
+    # so the P rounding noise is independent between the two; x, W, qkv, attention-output and GELU roundings are shared.
+    assert 1 - cos_ge <= 0.8 * (1 - cos_gf)
+    assert ge1 + ge2 <= gf1 + gf2 + 3 / 484 and ge_m < TIE_EPS
+    # (2) rounding alone (no kernel involved) flips as many indices against fp32 as the GPU does
+    assert ef1 + ef2 >= 0.5 * (gf1 + gf2) - 2 / 484
+    if (model_type, layer) == ("dinov2_vitg14", 39):
+        # the stated exception to north_star's 99 %: the CPU emulation misses it too, by the same amount (2.3 % / 2.3 %
+        # against the GPU's 2.9 % / 2.3 %), every flip at a margin the fp32 oracle itself calls a near-tie
+        assert max(ef1, ef2) > 0.01 and ef_m < TIE_EPS
